@@ -1,0 +1,354 @@
+// K1 (weight gradient): dW[n][k] += sum_m dY[m, n] * A[m, k] on tcgen05 (kind::tf32).
+//
+// GEMM view:  D[k, n] = sum over pixels m of  At[k, m] * dYt[n, m]   (UMMA M = 128 filter taps x channels,
+// UMMA N = C_out, reduction over the N*OH*OW output pixels).  Both operands are "pixel-minor" in the GEMM
+// but channel-minor in HBM (NHWC), so the producer warps transpose 4x4 blocks in registers while staging:
+// four LDG.128 (4 channels of 4 consecutive pixels) become four STS.128 (4 pixels of 4 consecutive
+// channels) into the 128B-swizzled K-major layout.  That keeps every descriptor K-major (the one tf32
+// layout that has no special cases) and needs no transposed copy of activations or gradients in HBM.
+// The pixel range is split across CTAs (persistent, one per SM); partial sums are combined with
+// red.global.add.f32 — the gradient buffer is zeroed once per step by the engine.
+//
+// Reference ops replaced: the Conv2DBackpropFilter / MatMul-grad nodes that
+// opt.compute_gradients() adds (e.g. cifarnet/cifar10_cifarnet_bsp.py:85,
+// inception/imagenet_inception_bsp.py:150).
+#include "../include/dtf_b200.h"
+#include "host_common.h"
+#include "umma.cuh"
+
+namespace dtf {
+
+constexpr int WG_BM = 128;
+constexpr int WG_BK = 32;   // pixels per stage
+constexpr int WG_A_STAGE_BYTES = WG_BM * WG_BK * 4;
+constexpr int WG_PRODUCERS = 256;   // warps 4..11
+constexpr int WG_THREADS = 128 + WG_PRODUCERS + 32;
+constexpr int WG_MMA_WARP = (128 + WG_PRODUCERS) / 32;
+
+struct WgradCfg {
+  int BN, stages, m_tiles, n_tiles, splits, kb_total, kb_per_split, tmem_cols, M, Ktot;
+  int vec_dy;
+  FastDiv d_ohow, d_ow, d_c, d_s;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+  const int BN = cfg.BN;
+  const int stages = cfg.stages;
+  const int b_stage_bytes = BN * WG_BK * 4;
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + stages * WG_A_STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + stages * b_stage_bytes);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* tfull_bar = empty_bar + stages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  if (warp == WG_MMA_WARP) {
+    if (lane == 0) {
+      for (int i = 0; i < stages; ++i) {
+        mbar_init(&full_bar[i], WG_PRODUCERS);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull_bar[i], 1);
+        mbar_init(&tempty_bar[i], 128);
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, (uint32_t)cfg.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_units = cfg.m_tiles * cfg.n_tiles * cfg.splits;
+
+  if (warp >= 4 && warp < WG_MMA_WARP) {
+    // =========================== producers =================================================
+    // Thread pt owns pixel chunk pc (4 consecutive output pixels) and 4-row chunk rc0 of the A tile
+    // (one filter tap, 4 consecutive input channels), plus up to two 4-row chunks of the dY tile.
+    const int pt = tid - 128;
+    const int pc = pt & 7;
+    const int rc0 = pt >> 3;      // 0..31
+    const bool has_aff = p.in_scale != nullptr;
+    int stage = 0; uint32_t phase = 0;
+
+    bool a_ok = false; int a_c = 0, a_r = 0, a_s = 0;
+    float4 a_sc = make_float4(1.f, 1.f, 1.f, 1.f), a_sh = make_float4(0.f, 0.f, 0.f, 0.f);
+    int n0 = 0;
+
+    auto issue_loads = [&](int kb, float4 (&xa)[4], uint32_t& okmask, float4 (&yb)[2][4]) {
+      const int mbase = kb * WG_BK + pc * 4;
+      okmask = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int m = mbase + q;
+        const bool mok = m < cfg.M;
+        const int mm = mok ? m : 0;
+        const int img = (int)fdiv((uint32_t)mm, cfg.d_ohow);
+        const int rem = mm - img * p.OH * p.OW;
+        const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
+        const int ow = rem - oh * p.OW;
+        const int ih = oh * p.stride_h - p.pad_h + a_r;
+        const int iw = ow * p.stride_w - p.pad_w + a_s;
+        const bool valid = a_ok && mok && ih >= 0 && iw >= 0 && ih < p.srcH && iw < p.srcW;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) {
+          const size_t off = (size_t)((img * p.srcH + ih) * p.srcW + iw) * (size_t)p.src_ld + a_c;
+          x = __ldg(reinterpret_cast<const float4*>(p.src + off));
+          okmask |= 1u << q;
+        }
+        xa[q] = x;
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int rc = rc0 + 32 * i;
+        const int co = n0 + rc * 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (rc * 4 < BN && (mbase + q) < cfg.M && co < p.Nout) {
+            const float* src = p.dy + (size_t)(mbase + q) * p.dy_ld + co;
+            if (cfg.vec_dy && co + 3 < p.Nout) {
+              t = __ldg(reinterpret_cast<const float4*>(src));
+            } else {
+              t.x = __ldg(src);
+              if (co + 1 < p.Nout) t.y = __ldg(src + 1);
+              if (co + 2 < p.Nout) t.z = __ldg(src + 2);
+              if (co + 3 < p.Nout) t.w = __ldg(src + 3);
+            }
+          }
+          yb[i][q] = t;
+        }
+      }
+    };
+
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      const int split = unit % cfg.splits;
+      const int tile = unit / cfg.splits;
+      const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
+      const int kb0 = split * cfg.kb_per_split;
+      int kb1 = kb0 + cfg.kb_per_split;
+      if (kb1 > cfg.kb_total) kb1 = cfg.kb_total;
+      {
+        const int k = mt * WG_BM + rc0 * 4;
+        a_ok = k < cfg.Ktot;
+        const int tap = a_ok ? (int)fdiv((uint32_t)k, cfg.d_c) : 0;
+        a_c = a_ok ? k - tap * p.srcC : 0;
+        a_r = (int)fdiv((uint32_t)tap, cfg.d_s);
+        a_s = tap - a_r * p.S;
+        a_sc = make_float4(1.f, 1.f, 1.f, 1.f);
+        a_sh = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (has_aff && a_ok) {
+          a_sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + a_c));
+          a_sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + a_c));
+        }
+      }
+      n0 = nt * BN;
+      float4 xa[4], xn[4], yb[2][4], yn[2][4];
+      uint32_t ok_cur = 0, ok_nxt = 0;
+      if (kb0 < kb1) issue_loads(kb0, xa, ok_cur, yb);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (kb + 1 < kb1) issue_loads(kb + 1, xn, ok_nxt, yn);
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        uint8_t* a_stage = sA + stage * WG_A_STAGE_BYTES;
+        uint8_t* b_stage = sB + stage * b_stage_bytes;
+        if (has_aff) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if ((ok_cur >> q) & 1u) {
+              float4 x = xa[q];
+              x.x = fmaf(x.x, a_sc.x, a_sh.x); x.y = fmaf(x.y, a_sc.y, a_sh.y);
+              x.z = fmaf(x.z, a_sc.z, a_sh.z); x.w = fmaf(x.w, a_sc.w, a_sh.w);
+              if (p.in_relu) {
+                x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+              }
+              xa[q] = x;
+            }
+          }
+        }
+        {
+          // 4x4 transpose in registers: row e <- channel e of the 4 pixels
+          const int row0 = rc0 * 4;
+          const float4 t0 = make_float4(xa[0].x, xa[1].x, xa[2].x, xa[3].x);
+          const float4 t1 = make_float4(xa[0].y, xa[1].y, xa[2].y, xa[3].y);
+          const float4 t2 = make_float4(xa[0].z, xa[1].z, xa[2].z, xa[3].z);
+          const float4 t3 = make_float4(xa[0].w, xa[1].w, xa[2].w, xa[3].w);
+          *reinterpret_cast<float4*>(a_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
+          *reinterpret_cast<float4*>(a_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
+          *reinterpret_cast<float4*>(a_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
+          *reinterpret_cast<float4*>(a_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int rc = rc0 + 32 * i;
+          if (rc * 4 < BN) {
+            const int row0 = rc * 4;
+            const float4 t0 = make_float4(yb[i][0].x, yb[i][1].x, yb[i][2].x, yb[i][3].x);
+            const float4 t1 = make_float4(yb[i][0].y, yb[i][1].y, yb[i][2].y, yb[i][3].y);
+            const float4 t2 = make_float4(yb[i][0].z, yb[i][1].z, yb[i][2].z, yb[i][3].z);
+            const float4 t3 = make_float4(yb[i][0].w, yb[i][1].w, yb[i][2].w, yb[i][3].w);
+            *reinterpret_cast<float4*>(b_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
+            *reinterpret_cast<float4*>(b_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
+            *reinterpret_cast<float4*>(b_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
+            *reinterpret_cast<float4*>(b_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[stage]);
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          xa[q] = xn[q];
+          yb[0][q] = yn[0][q];
+          yb[1][q] = yn[1][q];
+        }
+        ok_cur = ok_nxt;
+      }
+    }
+  } else if (warp == WG_MMA_WARP) {
+    // =========================== MMA issuer ================================================
+    const uint32_t idesc = make_idesc_tf32(WG_BM, (uint32_t)BN);
+    int stage = 0; uint32_t phase = 0;
+    int local = 0;
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++local) {
+      const int split = unit % cfg.splits;
+      const int kb0 = split * cfg.kb_per_split;
+      int kb1 = kb0 + cfg.kb_per_split;
+      if (kb1 > cfg.kb_total) kb1 = cfg.kb_total;
+      const int acc = local & 1;
+      const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      uint32_t accumulate = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t adesc = make_desc_k_sw128(smem_u32(sA + stage * WG_A_STAGE_BYTES));
+          const uint64_t bdesc = make_desc_k_sw128(smem_u32(sB + stage * b_stage_bytes));
+#pragma unroll
+          for (int kk = 0; kk < WG_BK / 8; ++kk) {
+            umma_tf32_ss(d_tmem, desc_advance(adesc, kk * 32), desc_advance(bdesc, kk * 32), idesc, accumulate);
+            accumulate = 1;
+          }
+          umma_commit(&empty_bar[stage]);
+        }
+        __syncwarp();
+        accumulate = 1;
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+      }
+      if (lane == 0) umma_commit(&tfull_bar[acc]);
+      __syncwarp();
+    }
+  } else {
+    // =========================== epilogue ==================================================
+    int local = 0;
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++local) {
+      const int split = unit % cfg.splits;
+      const int tile = unit / cfg.splits;
+      const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
+      const int kb0 = split * cfg.kb_per_split;
+      const bool nonempty = kb0 < cfg.kb_total;
+      const int acc = local & 1;
+      const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const int k = mt * WG_BM + tid;
+      const bool kvalid = nonempty && k < cfg.Ktot;
+      const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
+      for (int cc = 0; cc < BN; cc += 16) {
+        const int nb = nt * BN + cc;
+        if (nb >= p.Nout) break;
+        float v[16];
+        tmem_ld16(t_row + (uint32_t)cc, v);
+        if (kvalid) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int n = nb + e;
+            if (n < p.Nout) {
+              float* dst = p.dw + (size_t)n * cfg.Ktot + k;
+              if (cfg.splits == 1) *dst += v[e];
+              else atomicAdd(dst, v[e]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WG_MMA_WARP) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)cfg.tmem_cols);
+  }
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  const dtf_conv_wgrad_params& p = *pp;
+  DTF_REQUIRE(p.srcC % 4 == 0 && p.src_ld % 4 == 0, "source channels / pitch must be multiples of 4");
+  DTF_REQUIRE((reinterpret_cast<uintptr_t>(p.src) & 15) == 0, "source must be 16-byte aligned");
+  WgradCfg cfg;
+  cfg.Ktot = p.R * p.S * p.srcC;
+  cfg.M = p.N * p.OH * p.OW;
+  if (cfg.M == 0) return 0;
+  cfg.BN = p.Nout <= 256 ? round_up(p.Nout, 16) : 256;
+  cfg.n_tiles = ceil_div(p.Nout, cfg.BN);
+  cfg.m_tiles = ceil_div(cfg.Ktot, WG_BM);
+  cfg.kb_total = ceil_div(cfg.M, WG_BK);
+  const int base_units = cfg.m_tiles * cfg.n_tiles;
+  int splits = ceil_div(2 * num_sms(), base_units);
+  const int max_splits = cfg.kb_total / 4 > 0 ? cfg.kb_total / 4 : 1;   // at least 4 k-blocks per split
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  cfg.kb_per_split = ceil_div(cfg.kb_total, splits);
+  cfg.splits = ceil_div(cfg.kb_total, cfg.kb_per_split);
+  int tc = 32;
+  while (tc < 2 * cfg.BN) tc <<= 1;
+  cfg.tmem_cols = tc;
+  const int stage_bytes = WG_A_STAGE_BYTES + cfg.BN * WG_BK * 4;
+  int stages = (196 * 1024) / stage_bytes;
+  if (stages > 6) stages = 6;
+  if (stages < 2) stages = 2;
+  cfg.stages = stages;
+  cfg.d_ohow = make_fastdiv((uint32_t)(p.OH * p.OW));
+  cfg.d_ow = make_fastdiv((uint32_t)p.OW);
+  cfg.d_c = make_fastdiv((uint32_t)p.srcC);
+  cfg.d_s = make_fastdiv((uint32_t)p.S);
+  cfg.vec_dy = (p.dy_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.dy) & 15) == 0);
+
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + (2 * stages + 4) * sizeof(uint64_t) + 16;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    DTF_CHECK(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  const int units = cfg.m_tiles * cfg.n_tiles * cfg.splits;
+  const int grid = units < num_sms() ? units : num_sms();
+  conv_wgrad_kernel<<<grid, WG_THREADS, smem, stream>>>(p, cfg);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,45 @@
+// Host-side helpers shared by the launchers: error plumbing, device properties and the
+// TMA tensor-map cache (cuTensorMapEncodeTiled is resolved through the runtime's driver
+// entry-point API so the library never links libcuda directly and still loads on a CPU box).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+
+namespace dtf {
+
+void set_last_error(const std::string& s);
+
+#define DTF_CHECK(expr)                                                                     \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      ::dtf::set_last_error(std::string(#expr) + ": " + cudaGetErrorString(_e));            \
+      return static_cast<int>(_e);                                                          \
+    }                                                                                       \
+  } while (0)
+
+#define DTF_REQUIRE(cond, msg)                                                              \
+  do {                                                                                      \
+    if (!(cond)) {                                                                          \
+      ::dtf::set_last_error(std::string("requirement failed: ") + #cond + " — " + (msg));   \
+      return -1;                                                                            \
+    }                                                                                       \
+  } while (0)
+
+int num_sms();
+
+// [rows][cols] fp32 row-major matrix, box = {32 cols (128 B), box_rows}, 128-byte swizzle.
+// Returns nullptr (and sets last error) on failure.  Cached per (ptr, rows, cols, box_rows).
+const CUtensorMap* get_tmap_2d_f32_sw128(const float* ptr, int rows, int cols, int box_rows);
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
+
+}  // namespace dtf

@@ -1,0 +1,105 @@
+"""ctypes binding of ``libdtfb200.so`` (the hand-written sm_100a kernels; C ABI in ``include/dtf_b200.h``).
+
+The library is loaded lazily.  On a machine with a GPU a missing or stale library is rebuilt
+with ``nvcc`` when possible and is otherwise a hard error — GPU code paths never fall back
+silently to PyTorch ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libdtfb200.so"
+
+_lib = None
+_lock = threading.Lock()
+
+c_float_p = C.POINTER(C.c_float)
+
+
+class ConvGemmParams(C.Structure):
+    """Mirror of ``dtf_conv_gemm_params``."""
+    _fields_ = [
+        ("src", C.c_void_p), ("srcH", C.c_int), ("srcW", C.c_int), ("srcC", C.c_int), ("src_ld", C.c_int),
+        ("N", C.c_int), ("OH", C.c_int), ("OW", C.c_int),
+        ("R", C.c_int), ("S", C.c_int),
+        ("a_h", C.c_int), ("b_h", C.c_int), ("c_h", C.c_int), ("div_h", C.c_int),
+        ("a_w", C.c_int), ("b_w", C.c_int), ("c_w", C.c_int), ("div_w", C.c_int),
+        ("wt", C.c_void_p),
+        ("Nout", C.c_int),
+        ("out", C.c_void_p), ("out_ld", C.c_int),
+        ("in_scale", C.c_void_p), ("in_shift", C.c_void_p), ("in_relu", C.c_int),
+        ("bias", C.c_void_p), ("residual", C.c_void_p), ("res_ld", C.c_int), ("out_relu", C.c_int),
+        ("stats", C.c_void_p),
+    ]
+
+
+class ConvWgradParams(C.Structure):
+    """Mirror of ``dtf_conv_wgrad_params``."""
+    _fields_ = [
+        ("src", C.c_void_p), ("srcH", C.c_int), ("srcW", C.c_int), ("srcC", C.c_int), ("src_ld", C.c_int),
+        ("N", C.c_int), ("OH", C.c_int), ("OW", C.c_int),
+        ("R", C.c_int), ("S", C.c_int),
+        ("stride_h", C.c_int), ("stride_w", C.c_int), ("pad_h", C.c_int), ("pad_w", C.c_int),
+        ("dy", C.c_void_p), ("dy_ld", C.c_int), ("Nout", C.c_int),
+        ("dw", C.c_void_p),
+        ("in_scale", C.c_void_p), ("in_shift", C.c_void_p), ("in_relu", C.c_int),
+    ]
+
+
+def available() -> bool:
+    """True when the shared object exists (it may still be unusable without a GPU)."""
+    return LIB_PATH.exists()
+
+
+def build(force: bool = False) -> Path:
+    from . import build as _b
+    return _b.build(force=force)
+
+
+def _declare(lib: C.CDLL) -> None:
+    lib.dtf_version.restype = C.c_int
+    lib.dtf_last_error.restype = C.c_char_p
+    for name in dir(lib):
+        pass
+    # every other entry point returns int; argument types are declared where they are wrapped
+
+
+def lib() -> C.CDLL:
+    """Load (building first if necessary) and return the native library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not LIB_PATH.exists() or os.environ.get("DTF_REBUILD") == "1":
+            build(force=os.environ.get("DTF_REBUILD") == "1")
+        l = C.CDLL(str(LIB_PATH))
+        _declare(l)
+        _lib = l
+    return _lib
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().dtf_last_error()
+        raise NativeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")
+
+
+def stream_ptr() -> C.c_void_p:
+    """Current torch CUDA stream as a ``void*`` for the C ABI."""
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t) -> int | None:
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()

@@ -1,0 +1,136 @@
+"""Thin Python launchers for the tcgen05 implicit-GEMM kernels (``csrc/conv_igemm.cu``,
+``csrc/conv_wgrad.cu``).  Tensors are NHWC fp32 (the last-dim stride must be 1; the pixel pitch may
+exceed the channel count so a layer can read or write a channel slice of a wider buffer — this is how
+Inception's concats are eliminated).  Weights are OHWI ``[C_out, R, S, C_in]``.
+
+Autograd wiring lives in ``ops/functional.py``; this module only validates and launches.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from .. import _native as nat
+
+
+def _pitch(t: torch.Tensor) -> int:
+    """Pixel pitch (floats) of an NHWC tensor / view whose pixels are laid out densely."""
+    assert t.dim() == 4 and t.stride(3) == 1, "expected NHWC with unit channel stride"
+    n, h, w, c = t.shape
+    ld = t.stride(2) if w > 1 else (t.stride(1) if h > 1 else (t.stride(0) if n > 1 else c))
+    if w > 1 and h > 1:
+        assert t.stride(1) == ld * w, "rows must be densely packed"
+    if n > 1:
+        assert t.stride(0) == ld * w * h, "images must be densely packed"
+    return ld
+
+
+def out_size(i: int, k: int, stride: int, pad: int) -> int:
+    return (i + 2 * pad - k) // stride + 1
+
+
+def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: Tuple[int, int], *,
+               bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+               relu: bool = False, in_scale: Optional[torch.Tensor] = None,
+               in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
+               stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+               out_hw: Optional[Tuple[int, int]] = None) -> torch.Tensor:
+    """y = epilogue(conv(act(x), w)); see ``dtf_conv_gemm`` in include/dtf_b200.h.
+
+    ``pad`` is the padding *before* (top, left); with TensorFlow 'SAME' the padding after may be one
+    larger, which is expressed by passing the output size explicitly in ``out_hw``."""
+    n, h, wd, c = x.shape
+    co, r, s, ci = w.shape
+    assert ci == c and w.is_contiguous() and x.dtype == torch.float32 and w.dtype == torch.float32
+    if out_hw is None:
+        oh, ow = out_size(h, r, stride[0], pad[0]), out_size(wd, s, stride[1], pad[1])
+    else:
+        oh, ow = out_hw
+    if out is None:
+        out = torch.empty((n, oh, ow, co), device=x.device, dtype=torch.float32)
+    assert out.shape == (n, oh, ow, co)
+    p = nat.ConvGemmParams()
+    p.src, p.srcH, p.srcW, p.srcC, p.src_ld = x.data_ptr(), h, wd, c, _pitch(x)
+    p.N, p.OH, p.OW = n, oh, ow
+    p.R, p.S = r, s
+    p.a_h, p.b_h, p.c_h, p.div_h = stride[0], -pad[0], 1, 1
+    p.a_w, p.b_w, p.c_w, p.div_w = stride[1], -pad[1], 1, 1
+    p.wt, p.Nout = w.data_ptr(), co
+    p.out, p.out_ld = out.data_ptr(), _pitch(out)
+    p.in_scale, p.in_shift, p.in_relu = nat.ptr(in_scale), nat.ptr(in_shift), int(in_relu)
+    p.bias, p.residual = nat.ptr(bias), nat.ptr(residual)
+    p.res_ld = _pitch(residual) if residual is not None else 0
+    p.out_relu = int(relu)
+    p.stats = nat.ptr(stats)
+    nat.check(nat.lib().dtf_conv_gemm(C.byref(p), nat.stream_ptr()), "dtf_conv_gemm(fprop)")
+    return out
+
+
+def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
+               pad: Tuple[int, int], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx = conv_transpose(dy, w).  ``w_t`` is the dgrad operand ``[C_in, R, S, C_out]``
+    (``weight_transpose`` of the OHWI weights)."""
+    n, p_, q_, co = dy.shape
+    ci, r, s, co2 = w_t.shape
+    assert co2 == co and w_t.is_contiguous()
+    if co % 4 != 0:
+        # the gather reads 16-byte channel chunks and TMA needs a 16-byte row pitch: zero-pad the
+        # (tiny: logits layers only) gradient and weight operand to a multiple of 4 channels
+        padc = (-co) % 4
+        dy = torch.nn.functional.pad(dy, (0, padc))
+        w_t = torch.nn.functional.pad(w_t, (0, padc)).contiguous()
+        co += padc
+    h, wd = in_hw
+    if out is None:
+        out = torch.empty((n, h, wd, ci), device=dy.device, dtype=torch.float32)
+    p = nat.ConvGemmParams()
+    p.src, p.srcH, p.srcW, p.srcC, p.src_ld = dy.data_ptr(), p_, q_, co, _pitch(dy)
+    p.N, p.OH, p.OW = n, h, wd
+    p.R, p.S = r, s
+    p.a_h, p.b_h, p.c_h, p.div_h = 1, pad[0], -1, stride[0]
+    p.a_w, p.b_w, p.c_w, p.div_w = 1, pad[1], -1, stride[1]
+    p.wt, p.Nout = w_t.data_ptr(), ci
+    p.out, p.out_ld = out.data_ptr(), _pitch(out)
+    p.in_scale = p.in_shift = None
+    p.in_relu = 0
+    p.bias = p.residual = None
+    p.res_ld = 0
+    p.out_relu = 0
+    p.stats = None
+    nat.check(nat.lib().dtf_conv_gemm(C.byref(p), nat.stream_ptr()), "dtf_conv_gemm(dgrad)")
+    return out
+
+
+def weight_transpose(w: torch.Tensor) -> torch.Tensor:
+    """OHWI ``[C_out,R,S,C_in]`` -> ``[C_in,R,S,C_out]`` (B operand of the dgrad GEMM)."""
+    co, r, s, ci = w.shape
+    wt = torch.empty((ci, r, s, co), device=w.device, dtype=torch.float32)
+    nat.check(nat.lib().dtf_weight_transpose(C.c_void_p(w.data_ptr()), C.c_void_p(wt.data_ptr()),
+                                             co, r * s, ci, nat.stream_ptr()), "dtf_weight_transpose")
+    return wt
+
+
+def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, w_shape: Sequence[int], stride: Tuple[int, int],
+               pad: Tuple[int, int], *, in_scale: Optional[torch.Tensor] = None,
+               in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dW (OHWI).  Accumulates into ``out`` when given (it must already hold zeros / a running sum)."""
+    n, h, wd, c = x.shape
+    co, r, s, ci = w_shape
+    assert ci == c
+    _, oh, ow, co2 = dy.shape
+    assert co2 == co
+    if out is None:
+        out = torch.zeros((co, r, s, ci), device=x.device, dtype=torch.float32)
+    p = nat.ConvWgradParams()
+    p.src, p.srcH, p.srcW, p.srcC, p.src_ld = x.data_ptr(), h, wd, c, _pitch(x)
+    p.N, p.OH, p.OW = n, oh, ow
+    p.R, p.S = r, s
+    p.stride_h, p.stride_w, p.pad_h, p.pad_w = stride[0], stride[1], pad[0], pad[1]
+    p.dy, p.dy_ld, p.Nout = dy.data_ptr(), _pitch(dy), co
+    p.dw = out.data_ptr()
+    p.in_scale, p.in_shift, p.in_relu = nat.ptr(in_scale), nat.ptr(in_shift), int(in_relu)
+    nat.check(nat.lib().dtf_conv_wgrad(C.byref(p), nat.stream_ptr()), "dtf_conv_wgrad")
+    return out
