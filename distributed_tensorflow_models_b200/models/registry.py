@@ -1,0 +1,111 @@
+"""Model registry — the ``nets_factory`` of the framework (reference ``vgg/nets/nets_factory.py:39-145``:
+name -> constructor, matching arg_scope, ``default_image_size``), covering the six networks the reference
+trains plus the ImageNet ResNets and VGG variants it ships.
+
+``get_network_fn(name, num_classes, weight_decay, is_training)`` returns ``fn(images) -> (logits,
+end_points)`` exactly like the reference factory (including its ``is_training=False`` default that makes
+VGG train without dropout).  ``MODEL_SPECS`` additionally records what the trainers need:
+input geometry, class count and default batch size per worker.
+"""
+from __future__ import annotations
+
+import contextlib
+import functools
+from dataclasses import dataclass
+from typing import Callable, Dict, Optional
+
+from . import alexnet, cifarnet, inception_v3, plain_cnn, resnet, vgg
+
+
+@dataclass(frozen=True)
+class ModelSpec:
+    name: str
+    image_size: int          # network input H = W
+    source_size: int         # dataset image size before cropping
+    channels: int
+    num_classes: int
+    batch_size: int          # reference default per-worker batch
+    dataset: str             # 'cifar10' | 'imagenet'
+
+
+MODEL_SPECS: Dict[str, ModelSpec] = {
+    "cnn": ModelSpec("cnn", 24, 32, 3, 10, 512, "cifar10"),
+    "cifarnet": ModelSpec("cifarnet", 32, 32, 3, 10, 512, "cifar10"),
+    "alexnet": ModelSpec("alexnet", 32, 32, 3, 10, 128, "cifar10"),
+    "vgg": ModelSpec("vgg", 32, 32, 3, 10, 72, "cifar10"),
+    "resnet": ModelSpec("resnet", 32, 32, 3, 10, 128, "cifar10"),
+    "inception": ModelSpec("inception", 299, 299, 3, 1001, 32, "imagenet"),
+}
+
+
+@contextlib.contextmanager
+def _null_scope(weight_decay: float = 0.0):
+    yield None
+
+
+def _resnet_cifar(images, num_classes=10, is_training=False, resnet_size=32, **_):
+    net = resnet.cifar10_resnet_v2_generator(resnet_size, num_classes)
+    return net(images, is_training), {}
+
+
+def _resnet_imagenet(size):
+    def fn(images, num_classes=1001, is_training=False, **_):
+        return resnet.resnet_v2(size, num_classes)(images, is_training), {}
+    fn.default_image_size = 224
+    return fn
+
+
+def _plain_cnn(images, num_classes=10, is_training=False, **_):
+    return plain_cnn.inference(images), {}
+
+
+def _cifarnet(images, num_classes=10, is_training=False, **kw):
+    out = cifarnet.cifarnet(images, num_classes, is_training=is_training, **kw)
+    from ..slim import variables as V
+    return out, V.current_store().end_points
+
+
+def _inception(images, num_classes=1001, is_training=False, **_):
+    logits, aux = inception_v3.inference(images, num_classes, for_training=is_training)
+    return (logits, aux), {"aux_logits": aux}
+
+
+networks_map: Dict[str, Callable] = {
+    "cnn": _plain_cnn,
+    "cifarnet": _cifarnet,
+    "alexnet_v2": alexnet.alexnet_v2,
+    "vgg_a": vgg.vgg_a,
+    "vgg_16": vgg.vgg_16,
+    "vgg_19": vgg.vgg_19,
+    "resnet_cifar": _resnet_cifar,
+    "resnet_v2_18": _resnet_imagenet(18),
+    "resnet_v2_34": _resnet_imagenet(34),
+    "resnet_v2_50": _resnet_imagenet(50),
+    "resnet_v2_101": _resnet_imagenet(101),
+    "resnet_v2_152": _resnet_imagenet(152),
+    "resnet_v2_200": _resnet_imagenet(200),
+    "inception_v3": _inception,
+}
+
+arg_scopes_map: Dict[str, Callable] = {
+    "vgg_a": vgg.vgg_arg_scope, "vgg_16": vgg.vgg_arg_scope, "vgg_19": vgg.vgg_arg_scope,
+}
+
+default_image_sizes = {"cnn": 24, "cifarnet": 32, "alexnet_v2": 224, "vgg_a": 224, "vgg_16": 224, "vgg_19": 224,
+                       "resnet_cifar": 32, "inception_v3": 299}
+
+
+def get_network_fn(name: str, num_classes: int, weight_decay: float = 0.0, is_training: bool = False) -> Callable:
+    """-> ``network_fn(images, **kwargs) -> (logits, end_points)`` with ``default_image_size``."""
+    if name not in networks_map:
+        raise ValueError("Name of network unknown %s" % name)
+    func = networks_map[name]
+    scope_fn = arg_scopes_map.get(name, _null_scope)
+
+    @functools.wraps(func)
+    def network_fn(images, **kwargs):
+        with scope_fn(weight_decay=weight_decay):
+            return func(images, num_classes=num_classes, is_training=is_training, **kwargs)
+
+    network_fn.default_image_size = getattr(func, "default_image_size", default_image_sizes.get(name, 224))
+    return network_fn

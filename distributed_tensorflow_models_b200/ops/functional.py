@@ -1,0 +1,285 @@
+"""Functional NHWC ops with TensorFlow semantics (padding rules, LRN formula, pooling divisors).
+
+Two implementations sit behind each function:
+
+* **reference** – plain PyTorch fp32 ops (runs anywhere; it is the numerical oracle of the test-suite and
+  the engine of the CPU plumbing mode);
+* **native** – the hand-written sm_100a kernels of ``libdtfb200.so`` wrapped in ``torch.autograd.Function``
+  (``ops/native_ops.py``), selected automatically for CUDA tensors.
+
+``set_backend('torch')`` forces the reference path on CUDA too — that is the cuDNN/cuBLAS baseline arm
+(BASELINE.md B0/B1), never the product path.
+
+Layouts: activations NHWC, conv weights OHWI ``[C_out, R, S, C_in]``, FC weights ``[out, in]``.
+Reference semantics being reproduced are cited per function (paths relative to the reference repo).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Sequence, Tuple, Union
+
+import torch
+import torch.nn.functional as F
+
+_STATE = {"backend": "auto"}
+
+Padding = Union[str, Tuple[Tuple[int, int], Tuple[int, int]]]
+
+
+def set_backend(name: str) -> None:
+    """'auto' (native kernels on CUDA, reference on CPU), 'torch' (reference everywhere) or 'native'."""
+    assert name in ("auto", "torch", "native")
+    _STATE["backend"] = name
+
+
+def get_backend() -> str:
+    return _STATE["backend"]
+
+
+def use_native(x: torch.Tensor) -> bool:
+    b = _STATE["backend"]
+    if b == "torch":
+        return False
+    if b == "native" and not x.is_cuda:
+        raise RuntimeError("native backend requested for a CPU tensor")
+    return x.is_cuda
+
+
+# ----------------------------------------------------------------------------------------------
+# padding arithmetic (TensorFlow rules)
+# ----------------------------------------------------------------------------------------------
+def same_pad_1d(size: int, k: int, stride: int) -> Tuple[int, int, int]:
+    """TF 'SAME': out = ceil(size/stride); total pad split with the extra pixel *after*."""
+    out = -(-size // stride)
+    total = max((out - 1) * stride + k - size, 0)
+    before = total // 2
+    return out, before, total - before
+
+
+def resolve_padding(h: int, w: int, r: int, s: int, stride: Tuple[int, int], padding: Padding):
+    """-> (out_h, out_w, (pad_top, pad_bottom), (pad_left, pad_right))"""
+    if isinstance(padding, str):
+        p = padding.upper()
+        if p == "SAME":
+            oh, pt, pb = same_pad_1d(h, r, stride[0])
+            ow, pl, pr = same_pad_1d(w, s, stride[1])
+            return oh, ow, (pt, pb), (pl, pr)
+        if p == "VALID":
+            return (h - r) // stride[0] + 1, (w - s) // stride[1] + 1, (0, 0), (0, 0)
+        raise ValueError(f"unknown padding {padding}")
+    (pt, pb), (pl, pr) = padding
+    return (h + pt + pb - r) // stride[0] + 1, (w + pl + pr - s) // stride[1] + 1, (pt, pb), (pl, pr)
+
+
+def _pair(v) -> Tuple[int, int]:
+    return (v, v) if isinstance(v, int) else (int(v[0]), int(v[1]))
+
+
+# ----------------------------------------------------------------------------------------------
+# convolution / FC
+# ----------------------------------------------------------------------------------------------
+def conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, stride=1,
+           padding: Padding = "SAME", relu: bool = False) -> torch.Tensor:
+    """NHWC convolution, OHWI weights (tf.nn.conv2d semantics — cnn/cifar10.py:221,
+    inception/slim/ops.py:232, resnet/resnet_model.py:87)."""
+    stride = _pair(stride)
+    n, h, wd, c = x.shape
+    co, r, s, ci = w.shape
+    oh, ow, ph, pw = resolve_padding(h, wd, r, s, stride, padding)
+    if use_native(x):
+        from . import native_ops
+        return native_ops.conv2d(x, w, bias, stride, (ph[0], pw[0]), (oh, ow), relu)
+    xn = x.permute(0, 3, 1, 2)
+    if ph[0] != ph[1] or pw[0] != pw[1]:
+        xn = F.pad(xn, (pw[0], pw[1], ph[0], ph[1]))
+        pad = (0, 0)
+    else:
+        pad = (ph[0], pw[0])
+    y = F.conv2d(xn, w.permute(0, 3, 1, 2), bias, stride=stride, padding=pad)
+    y = y[:, :, :oh, :ow]
+    if relu:
+        y = F.relu(y)
+    return y.permute(0, 2, 3, 1)
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False) -> torch.Tensor:
+    """x[N, in] @ w[out, in]^T + b (tf.matmul/xw_plus_b — cnn/cifar10.py:262, slim/ops.py:305)."""
+    if use_native(x):
+        from . import native_ops
+        return native_ops.linear(x, w, bias, relu)
+    y = F.linear(x, w, bias)
+    return F.relu(y) if relu else y
+
+
+# ----------------------------------------------------------------------------------------------
+# batch norm
+# ----------------------------------------------------------------------------------------------
+def batch_norm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
+               moving_mean: torch.Tensor, moving_var: torch.Tensor, *, training: bool, decay: float,
+               eps: float, relu: bool = False, update_moving: bool = True,
+               unbiased_moving_var: bool = False) -> torch.Tensor:
+    """Batch normalisation over N,H,W of an NHWC tensor.
+
+    Training: normalise with the batch mean / *biased* variance (tf.nn.moments, slim/ops.py:117-124) and,
+    when ``update_moving``, ``moving = moving*decay + batch*(1-decay)`` in place.  Eval: moving statistics
+    (slim/ops.py:125-128).  ``gamma is None`` reproduces Inception's centre-only BN (ops.py:49 scale=False).
+    """
+    c = x.shape[-1]
+    if use_native(x):
+        from . import native_ops
+        return native_ops.batch_norm(x, gamma, beta, moving_mean, moving_var, training, decay, eps, relu,
+                                     update_moving, unbiased_moving_var)
+    if training:
+        xf = x.reshape(-1, c)
+        mean = xf.mean(0)
+        var = xf.var(0, unbiased=False)
+        if update_moving:
+            with torch.no_grad():
+                m = xf.shape[0]
+                v_upd = var * (m / max(m - 1, 1)) if unbiased_moving_var else var
+                moving_mean.mul_(decay).add_(mean.detach(), alpha=1 - decay)
+                moving_var.mul_(decay).add_(v_upd.detach(), alpha=1 - decay)
+    else:
+        mean, var = moving_mean, moving_var
+    inv = torch.rsqrt(var + eps)
+    scale = inv if gamma is None else inv * gamma
+    shift = -mean * scale
+    if beta is not None:
+        shift = shift + beta
+    y = x * scale + shift
+    return F.relu(y) if relu else y
+
+
+# ----------------------------------------------------------------------------------------------
+# pooling
+# ----------------------------------------------------------------------------------------------
+def _pool_geometry(x, k, stride, padding):
+    k, stride = _pair(k), _pair(stride)
+    n, h, w, c = x.shape
+    oh, ow, ph, pw = resolve_padding(h, w, k[0], k[1], stride, padding)
+    return k, stride, oh, ow, ph, pw
+
+
+def max_pool(x: torch.Tensor, k, stride, padding: Padding = "VALID") -> torch.Tensor:
+    """tf.nn.max_pool (padding contributes -inf) — cnn/cifar10.py:228, slim/ops.py:370."""
+    k, stride, oh, ow, ph, pw = _pool_geometry(x, k, stride, padding)
+    if use_native(x):
+        from . import native_ops
+        return native_ops.max_pool(x, k, stride, (ph[0], pw[0]), (oh, ow))
+    xn = x.permute(0, 3, 1, 2)
+    if any(ph) or any(pw):
+        xn = F.pad(xn, (pw[0], pw[1], ph[0], ph[1]), value=float("-inf"))
+    y = F.max_pool2d(xn, k, stride)[:, :, :oh, :ow]
+    return y.permute(0, 2, 3, 1)
+
+
+def avg_pool(x: torch.Tensor, k, stride, padding: Padding = "VALID") -> torch.Tensor:
+    """tf.nn.avg_pool: padded positions are excluded from the divisor — slim/ops.py:400."""
+    k, stride, oh, ow, ph, pw = _pool_geometry(x, k, stride, padding)
+    if use_native(x):
+        from . import native_ops
+        return native_ops.avg_pool(x, k, stride, (ph[0], pw[0]), (oh, ow))
+    xn = x.permute(0, 3, 1, 2)
+    if any(ph) or any(pw):
+        ones = torch.ones((1, 1, x.shape[1], x.shape[2]), dtype=x.dtype, device=x.device)
+        xs = F.avg_pool2d(F.pad(xn, (pw[0], pw[1], ph[0], ph[1])), k, stride, divisor_override=1)
+        cnt = F.avg_pool2d(F.pad(ones, (pw[0], pw[1], ph[0], ph[1])), k, stride, divisor_override=1)
+        y = (xs / cnt)[:, :, :oh, :ow]
+    else:
+        y = F.avg_pool2d(xn, k, stride)[:, :, :oh, :ow]
+    return y.permute(0, 2, 3, 1)
+
+
+def global_avg_pool(x: torch.Tensor) -> torch.Tensor:
+    """Mean over H,W -> [N, C] (resnet/resnet_model.py:271 with an 8x8 window on an 8x8 map)."""
+    return avg_pool(x, (x.shape[1], x.shape[2]), 1, "VALID").reshape(x.shape[0], x.shape[3])
+
+
+# ----------------------------------------------------------------------------------------------
+# LRN
+# ----------------------------------------------------------------------------------------------
+def lrn(x: torch.Tensor, depth_radius: int = 4, bias: float = 1.0, alpha: float = 0.001 / 9.0,
+        beta: float = 0.75) -> torch.Tensor:
+    """tf.nn.lrn: x / (bias + alpha * sum_{|d'-d|<=r} x[d']^2)^beta — cnn/cifar10.py:231 (note: unlike
+    torch's LocalResponseNorm, alpha is *not* divided by the window size)."""
+    if use_native(x):
+        from . import native_ops
+        return native_ops.lrn(x, depth_radius, bias, alpha, beta)
+    c = x.shape[-1]
+    sq = (x * x).reshape(-1, 1, c)
+    kern = torch.ones((1, 1, 2 * depth_radius + 1), dtype=x.dtype, device=x.device)
+    ssum = F.conv1d(sq, kern, padding=depth_radius).reshape(x.shape)
+    return x * torch.pow(bias + alpha * ssum, -beta)
+
+
+# ----------------------------------------------------------------------------------------------
+# dropout / misc
+# ----------------------------------------------------------------------------------------------
+def dropout(x: torch.Tensor, keep_prob: float, training: bool) -> torch.Tensor:
+    """tf.nn.dropout(keep_prob): scale kept units by 1/keep_prob; identity when not training
+    (slim/ops.py:420-424)."""
+    if not training or keep_prob >= 1.0:
+        return x
+    if use_native(x):
+        from . import native_ops
+        return native_ops.dropout(x, keep_prob)
+    return F.dropout(x, 1.0 - keep_prob, training=True)
+
+
+def relu(x: torch.Tensor) -> torch.Tensor:
+    return F.relu(x)
+
+
+def flatten(x: torch.Tensor) -> torch.Tensor:
+    """[N, ...] -> [N, prod] in NHWC order, the order TF's reshape produces (cnn/cifar10.py:255)."""
+    return x.reshape(x.shape[0], -1)
+
+
+def concat_channels(xs: Sequence[torch.Tensor]) -> torch.Tensor:
+    """tf.concat(axis=3) (slim/inception_model.py:127)."""
+    return torch.cat(list(xs), dim=3)
+
+
+def one_hot(labels: torch.Tensor, num_classes: int) -> torch.Tensor:
+    return F.one_hot(labels.long(), num_classes).to(torch.float32)
+
+
+# ----------------------------------------------------------------------------------------------
+# losses / metrics
+# ----------------------------------------------------------------------------------------------
+def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, label_smoothing: float = 0.0,
+                          weight: float = 1.0) -> torch.Tensor:
+    """weight * mean_n( -sum_c y'[n,c] log softmax(logits)[n,c] ),  y' = y(1-eps) + eps/C.
+
+    ``labels`` are class indices [N] (sparse form, cnn/cifar10.py:299) or dense targets [N, C]
+    (tf.losses.softmax_cross_entropy; slim/losses.py:142-174 for smoothing and weight)."""
+    if use_native(logits) and labels.dim() == 1:
+        from . import native_ops
+        return native_ops.softmax_xent(logits, labels, label_smoothing, weight)
+    logp = F.log_softmax(logits.float(), dim=1)
+    c = logits.shape[1]
+    if labels.dim() == 1:
+        target = F.one_hot(labels.long(), c).to(logp.dtype)
+    else:
+        target = labels.to(logp.dtype)
+    if label_smoothing > 0:
+        target = target * (1.0 - label_smoothing) + label_smoothing / c
+    return -(target * logp).sum(1).mean() * weight
+
+
+def in_top_k(logits: torch.Tensor, labels: torch.Tensor, k: int) -> torch.Tensor:
+    """tf.nn.in_top_k (cnn/cifar10_eval.py:129): target's score is among the k largest
+    (ties resolved as TF does: counts entries strictly greater than the target's score)."""
+    tgt = logits.gather(1, labels.long().view(-1, 1))
+    return (logits > tgt).sum(1) < k
+
+
+def zero_fraction(x: torch.Tensor) -> torch.Tensor:
+    """tf.nn.zero_fraction (cnn/cifar10.py:121)."""
+    return (x == 0).float().mean()
+
+
+def variance_scaling_std(fan_in: int) -> float:
+    """tf.variance_scaling_initializer() default: truncated normal, scale=1, fan_in
+    (stddev = sqrt(1/fan_in) / 0.87962566 after truncation correction)."""
+    return math.sqrt(1.0 / max(1, fan_in)) / 0.87962566103423978

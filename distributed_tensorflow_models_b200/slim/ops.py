@@ -1,0 +1,249 @@
+"""Layer library with the reference slim call signatures, executing eagerly on the current
+:class:`~.variables.VariableStore`.
+
+Counterparts in the reference (``inception/slim/ops.py``): ``batch_norm`` :46-135, ``conv2d`` :170-249,
+``fc`` :253-320, ``one_hot_encoding`` :323-341, ``max_pool`` :345-373, ``avg_pool`` :377-403,
+``dropout`` :407-424, ``flatten`` :427-446, ``repeat_op`` :449-476.  Variable names produced:
+``<scope|Conv[_k]>/weights``, ``/biases``, ``/BatchNorm/{beta,gamma,moving_mean,moving_variance}``,
+FC default scope ``FC``.  conv2d uses a bias only when no batch-norm follows (ops.py:234-246).
+
+The same functions also serve the ``tf.contrib.slim`` spellings used by the CIFAR models
+(``slim.conv2d(..., weights_initializer=, biases_initializer=, activation_fn=)``) through the thin
+aliases at the bottom of the file.
+
+Everything computes through ``ops.functional`` (NHWC; reference or native sm_100a kernels).  When the
+store is in *fused-BN* mode (``store.fuse_bn = True``, CUDA only) ``conv2d`` with ``batch_norm_params``
+hands the conv+BN+ReLU triple to ``native_ops.conv_bn_relu`` so statistics come out of the conv epilogue.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Sequence, Union
+
+import torch
+
+from ..ops import functional as Fn
+from . import losses
+from . import variables as V
+from .scopes import add_arg_scope
+
+UPDATE_OPS_COLLECTION = V.UPDATE_OPS_COLLECTION
+
+relu = Fn.relu
+
+
+def _two(v) -> Sequence[int]:
+    if isinstance(v, int):
+        return [v, v]
+    if len(v) == 1:
+        return [int(v[0]), int(v[0])]
+    return [int(v[0]), int(v[1])]
+
+
+def _is_relu(activation) -> bool:
+    return activation is relu or activation is torch.relu or activation is torch.nn.functional.relu
+
+
+@add_arg_scope
+def batch_norm(inputs: torch.Tensor, decay: float = 0.999, center: bool = True, scale: bool = False,
+               epsilon: float = 0.001, moving_vars: str = "moving_vars", activation: Optional[Callable] = None,
+               is_training: bool = True, trainable: bool = True, restore: bool = True,
+               scope: Optional[str] = None, reuse=None, update_moving: bool = True,
+               unbiased_moving_var: bool = False, names=("beta", "gamma", "moving_mean", "moving_variance")):
+    """Batch normalisation over all but the last axis (reference ops.py:46-135)."""
+    store = V.current_store()
+    c = inputs.shape[-1]
+    with store.scope(scope, "BatchNorm"):
+        beta = gamma = None
+        if center:
+            beta = V.variable(names[0], (c,), initializer=V.zeros_initializer(), trainable=trainable, restore=restore)
+        if scale:
+            gamma = V.variable(names[1], (c,), initializer=V.ones_initializer(), trainable=trainable, restore=restore)
+        colls = [moving_vars, V.MOVING_AVERAGE_VARIABLES]
+        mm = V.variable(names[2], (c,), initializer=V.zeros_initializer(), trainable=False, restore=restore,
+                        collections=colls)
+        mv = V.variable(names[3], (c,), initializer=V.ones_initializer(), trainable=False, restore=restore,
+                        collections=colls)
+    x = inputs if inputs.dim() == 4 else inputs.reshape(inputs.shape[0], 1, 1, c)
+    fuse_relu = _is_relu(activation)
+    y = Fn.batch_norm(x, gamma, beta, mm, mv, training=is_training, decay=decay, eps=epsilon, relu=fuse_relu,
+                      update_moving=update_moving, unbiased_moving_var=unbiased_moving_var)
+    y = y.reshape(inputs.shape)
+    if activation is not None and not fuse_relu:
+        y = activation(y)
+    return y
+
+
+@add_arg_scope
+def conv2d(inputs: torch.Tensor, num_filters_out: int, kernel_size, stride=1, padding="SAME",
+           activation: Optional[Callable] = relu, stddev: float = 0.01, bias: float = 0.0,
+           weight_decay: float = 0.0, batch_norm_params: Optional[dict] = None, is_training: bool = True,
+           trainable: bool = True, restore: bool = True, scope: Optional[str] = None, reuse=None,
+           weights_initializer: Optional[Callable] = None, biases_initializer: Optional[Callable] = None,
+           use_bias: bool = True, weights_name: str = "weights", biases_name: str = "biases"):
+    """2-D convolution (+BN | +bias) (+activation); NHWC in, NHWC out (reference ops.py:170-249)."""
+    store = V.current_store()
+    kh, kw = _two(kernel_size)
+    sh, sw = _two(stride)
+    cin = inputs.shape[-1]
+    with store.scope(scope, "Conv"):
+        w_init = weights_initializer or V.truncated_normal_initializer(stddev=stddev)
+        reg = losses.l2_regularizer(weight_decay) if weight_decay and weight_decay > 0 else None
+        w = V.variable(weights_name, (num_filters_out, kh, kw, cin), initializer=w_init, regularizer=reg,
+                       trainable=trainable, restore=restore, tf_layout="hwio",
+                       tf_shape=(kh, kw, cin, num_filters_out), fan_in=kh * kw * cin,
+                       fan_out=kh * kw * num_filters_out)
+        fuse_relu = _is_relu(activation)
+        if batch_norm_params is not None:
+            if getattr(store, "fuse_bn", False) and inputs.is_cuda and Fn.use_native(inputs) and is_training:
+                from ..ops import native_ops
+                bn = dict(batch_norm_params)
+                with store.scope(bn.pop("scope", None), "BatchNorm"):
+                    c = num_filters_out
+                    beta = V.variable("beta", (c,), initializer=V.zeros_initializer(), trainable=trainable,
+                                      restore=restore) if bn.get("center", True) else None
+                    gamma = V.variable("gamma", (c,), initializer=V.ones_initializer(), trainable=trainable,
+                                       restore=restore) if bn.get("scale", False) else None
+                    colls = [bn.get("moving_vars", "moving_vars"), V.MOVING_AVERAGE_VARIABLES]
+                    mm = V.variable("moving_mean", (c,), initializer=V.zeros_initializer(), trainable=False,
+                                    restore=restore, collections=colls)
+                    mv = V.variable("moving_variance", (c,), initializer=V.ones_initializer(), trainable=False,
+                                    restore=restore, collections=colls)
+                out = native_ops.conv_bn_act(inputs, w, (sh, sw), padding, gamma, beta, mm, mv,
+                                             decay=bn.get("decay", 0.999), eps=bn.get("epsilon", 0.001),
+                                             relu=fuse_relu)
+                if activation is not None and not fuse_relu:
+                    out = activation(out)
+                return out
+            y = Fn.conv2d(inputs, w, None, (sh, sw), padding)
+            y = batch_norm(y, is_training=is_training, trainable=trainable, restore=restore,
+                           activation=activation, **batch_norm_params)
+            return y
+        b = None
+        if use_bias:
+            b_init = biases_initializer or V.constant_initializer(bias)
+            b = V.variable(biases_name, (num_filters_out,), initializer=b_init, trainable=trainable, restore=restore)
+        y = Fn.conv2d(inputs, w, b, (sh, sw), padding, relu=fuse_relu)
+        if activation is not None and not fuse_relu:
+            y = activation(y)
+        return y
+
+
+@add_arg_scope
+def fc(inputs: torch.Tensor, num_units_out: int, activation: Optional[Callable] = relu, stddev: float = 0.01,
+       bias: float = 0.0, weight_decay: float = 0.0, batch_norm_params: Optional[dict] = None,
+       is_training: bool = True, trainable: bool = True, restore: bool = True, scope: Optional[str] = None,
+       reuse=None, weights_initializer: Optional[Callable] = None, biases_initializer: Optional[Callable] = None,
+       weights_name: str = "weights", biases_name: str = "biases"):
+    """Fully connected layer on [N, in] (reference ops.py:253-320)."""
+    store = V.current_store()
+    nin = inputs.shape[-1]
+    with store.scope(scope, "FC"):
+        w_init = weights_initializer or V.truncated_normal_initializer(stddev=stddev)
+        reg = losses.l2_regularizer(weight_decay) if weight_decay and weight_decay > 0 else None
+        w = V.variable(weights_name, (num_units_out, nin), initializer=w_init, regularizer=reg, trainable=trainable,
+                       restore=restore, tf_layout="io", tf_shape=(nin, num_units_out), fan_in=nin,
+                       fan_out=num_units_out)
+        fuse_relu = _is_relu(activation)
+        if batch_norm_params is not None:
+            y = Fn.linear(inputs, w, None)
+            return batch_norm(y, is_training=is_training, trainable=trainable, restore=restore,
+                              activation=activation, **batch_norm_params)
+        b_init = biases_initializer or V.constant_initializer(bias)
+        b = V.variable(biases_name, (num_units_out,), initializer=b_init, trainable=trainable, restore=restore)
+        y = Fn.linear(inputs, w, b, relu=fuse_relu)
+        if activation is not None and not fuse_relu:
+            y = activation(y)
+        return y
+
+
+def one_hot_encoding(labels: torch.Tensor, num_classes: int, scope: Optional[str] = None) -> torch.Tensor:
+    """Dense [N, num_classes] float one-hot (reference ops.py:323-341)."""
+    return Fn.one_hot(labels, num_classes)
+
+
+@add_arg_scope
+def max_pool(inputs: torch.Tensor, kernel_size, stride=2, padding="VALID", scope: Optional[str] = None):
+    """reference ops.py:345-373 (default stride 2, VALID)."""
+    return Fn.max_pool(inputs, _two(kernel_size), _two(stride), padding)
+
+
+@add_arg_scope
+def avg_pool(inputs: torch.Tensor, kernel_size, stride=2, padding="VALID", scope: Optional[str] = None):
+    """reference ops.py:377-403."""
+    return Fn.avg_pool(inputs, _two(kernel_size), _two(stride), padding)
+
+
+@add_arg_scope
+def dropout(inputs: torch.Tensor, keep_prob: float = 0.5, is_training: bool = True, scope: Optional[str] = None):
+    """Identity unless training and keep_prob < 1 (reference ops.py:407-424)."""
+    if is_training and keep_prob > 0:
+        return Fn.dropout(inputs, keep_prob, True)
+    return inputs
+
+
+def flatten(inputs: torch.Tensor, scope: Optional[str] = None) -> torch.Tensor:
+    """[N, ...] -> [N, k] (reference ops.py:427-446)."""
+    if inputs.dim() < 2:
+        raise ValueError("Inputs must be have a least 2 dimensions")
+    return Fn.flatten(inputs)
+
+
+def repeat_op(repetitions: int, inputs, op: Callable, *args, **kwargs):
+    """Apply ``op`` ``repetitions`` times, scopes ``<scope>_1 … _n`` (reference ops.py:449-476)."""
+    store = V.current_store()
+    scope = kwargs.pop("scope", None)
+    with store.scope(scope, "RepeatOp"):
+        tower = inputs
+        for _ in range(repetitions):
+            tower = op(tower, *args, **kwargs)
+        return tower
+
+
+def repeat(inputs, repetitions: int, layer: Callable, *args, **kwargs):
+    """``tf.contrib.slim.repeat``: scopes ``<scope>/<scope>_1 …`` (vgg/nets/vgg.py:190 → conv1/conv1_1)."""
+    store = V.current_store()
+    scope = kwargs.pop("scope", None)
+    with store.scope(scope, "Repeat"):
+        out = inputs
+        base = scope or "repeat"
+        for i in range(repetitions):
+            out = layer(out, *args, scope=f"{base}_{i + 1}", **kwargs)
+        return out
+
+
+# ---- tf.contrib.slim / tf.layers spellings used by the CIFAR models ---------------------------------
+@add_arg_scope
+def max_pool2d(inputs, kernel_size, stride=2, padding="VALID", scope=None):
+    """slim.max_pool2d (cifarnet/cifarnet.py:66, alexnet/alexnet.py:106, vgg/nets/vgg.py:191)."""
+    return Fn.max_pool(inputs, _two(kernel_size), _two(stride), padding)
+
+
+@add_arg_scope
+def avg_pool2d(inputs, kernel_size, stride=2, padding="VALID", scope=None):
+    return Fn.avg_pool(inputs, _two(kernel_size), _two(stride), padding)
+
+
+@add_arg_scope
+def fully_connected(inputs, num_outputs, activation_fn=relu, weights_initializer=None, biases_initializer=None,
+                    weights_regularizer=None, scope=None, trainable=True):
+    """slim.fully_connected: Xavier weights / zero biases by default (cifarnet/cifarnet.py:76-89)."""
+    wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
+    return fc(inputs, num_outputs, activation=activation_fn, weight_decay=wd,
+              weights_initializer=weights_initializer or V.xavier_initializer(),
+              biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope, trainable=trainable)
+
+
+@add_arg_scope
+def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", activation_fn=relu,
+                  weights_initializer=None, biases_initializer=None, weights_regularizer=None, scope=None,
+                  trainable=True, normalizer_fn=None, normalizer_params=None):
+    """slim.conv2d in its tf.contrib form (cifarnet/cifarnet.py:64, alexnet/alexnet.py:103, vgg.py:190)."""
+    wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
+    return conv2d(inputs, num_outputs, kernel_size, stride=stride, padding=padding, activation=activation_fn,
+                  weight_decay=wd, weights_initializer=weights_initializer or V.xavier_initializer(),
+                  biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope, trainable=trainable,
+                  batch_norm_params=normalizer_params if normalizer_fn is not None else None)
+
+
+def softmax(logits: torch.Tensor, scope=None) -> torch.Tensor:
+    return torch.softmax(logits, dim=-1)
