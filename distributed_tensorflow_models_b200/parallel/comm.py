@@ -1,0 +1,335 @@
+"""Transports for the parameter-server protocol (SPMD form: every rank is a worker *and* owns PS shards).
+
+The reference's L5 is re-expressed as three operations on flat buffers:
+
+``bsp_step``   push = owner obtains the mean of all workers' gradients for the ranges it owns and applies the
+               optimiser; pull = every worker refreshes its parameter copy from the owners
+               (SyncReplicasOptimizer semantics: one update per global step from exactly N gradients)
+``async_step`` push = the worker applies *its own* gradient to the owners' master ranges immediately
+               (Hogwild, ``use_locking=False``), global_step += 1 per worker step; pull = copy back
+``ssp_wait``   publish clock[rank] = step and block while step > min(clock) + bound
+               (replaces the Thrift ``check_staleness`` RPC loop, inception/ssp_manager.py:21-29)
+
+Back-ends
+---------
+``LocalComm``      world of one.
+``ThreadCluster``  fake cluster: N ranks are threads of this process sharing CPU tensors — peers' buffers are
+                   directly addressable, which makes it the CPU twin of the GPU symmetric-memory path (same
+                   one-sided protocol, testable without hardware; SURVEY §4 "what we must add").
+``TorchDistComm``  torch.distributed collectives (gloo on CPU, NCCL on GPU): BSP only.  This is the *baseline*
+                   arm (BASELINE.md B1 all-reduce, B2 reduce-scatter + all-gather), never the product path.
+``SymmComm``       (parallel/symm.py) peer-mapped HBM + our sm_100a push/pull kernels over NVLink.
+"""
+from __future__ import annotations
+
+import threading
+import time
+from typing import Callable, List, Optional, Sequence
+
+import torch
+
+from ..optim.updates import OptimizerConfig, ShardOptimizer
+from .layout import FlatLayout
+
+
+class StalenessTimeout(RuntimeError):
+    pass
+
+
+class Comm:
+    rank: int = 0
+    world: int = 1
+    supports_async = False
+
+    def setup(self, layout: FlatLayout, opt_cfg: OptimizerConfig) -> None:
+        raise NotImplementedError
+
+    # -- protocol -------------------------------------------------------------------------------
+    def bsp_step(self, lr: float, grad_scale: float = 1.0) -> int:
+        raise NotImplementedError
+
+    def async_step(self, lr: float, grad_scale: float = 1.0) -> int:
+        raise NotImplementedError("this transport has no one-sided path")
+
+    def ssp_wait(self, step: int, bound: int, timeout: float = 600.0) -> float:
+        raise NotImplementedError
+
+    # -- plumbing -------------------------------------------------------------------------------
+    def barrier(self) -> None:
+        pass
+
+    def broadcast_state(self, tensors: Sequence[torch.Tensor], src: int = 0) -> None:
+        pass
+
+    def global_step(self) -> int:
+        raise NotImplementedError
+
+    def set_global_step(self, v: int) -> None:
+        raise NotImplementedError
+
+    def max_over_ranks(self, v: float) -> float:
+        return v
+
+    def owned_optimizers(self) -> List[ShardOptimizer]:
+        raise NotImplementedError
+
+    def finish(self) -> None:
+        pass
+
+
+def _make_opts(layout: FlatLayout, cfg: OptimizerConfig, rank: int) -> List[ShardOptimizer]:
+    return [ShardOptimizer(cfg, layout.params, lo, hi, layout.wd_boundary) for lo, hi in layout.owned(rank)]
+
+
+# =================================================================================================
+class LocalComm(Comm):
+    """Single process: the PS shard is the whole buffer."""
+    supports_async = True
+
+    def __init__(self):
+        self.rank, self.world = 0, 1
+        self._gs = 0
+
+    def setup(self, layout, opt_cfg):
+        self.layout = layout
+        self.opts = _make_opts(layout, opt_cfg, 0)
+
+    def _apply(self, lr, grad_scale):
+        for o in self.opts:
+            o.apply(self.layout.grads[o.lo:o.hi], lr, grad_scale, num_updates=self._gs)
+        self._gs += 1
+        return self._gs
+
+    def bsp_step(self, lr, grad_scale=1.0):
+        return self._apply(lr, grad_scale)
+
+    def async_step(self, lr, grad_scale=1.0):
+        return self._apply(lr, grad_scale)
+
+    def ssp_wait(self, step, bound, timeout=600.0):
+        return 0.0
+
+    def global_step(self):
+        return self._gs
+
+    def set_global_step(self, v):
+        self._gs = int(v)
+
+    def owned_optimizers(self):
+        return self.opts
+
+
+# =================================================================================================
+class ThreadCluster:
+    """Shared state of an in-process fake cluster; hand one ``ThreadComm`` to each worker thread."""
+
+    def __init__(self, world: int):
+        self.world = world
+        self.barrier = threading.Barrier(world)
+        self.layouts: List[Optional[FlatLayout]] = [None] * world
+        self.opts: List[List[ShardOptimizer]] = [[] for _ in range(world)]
+        self.clock = [0] * world
+        self.clock_cv = threading.Condition()
+        self.gs = 0
+        self.gs_lock = threading.Lock()
+        self.max_lead_seen = 0          # protocol checker: largest (my step - min clock) observed at release
+        self.aborted = False
+
+    def comm(self, rank: int) -> "ThreadComm":
+        return ThreadComm(self, rank)
+
+    def run(self, fn: Callable[["ThreadComm"], object]) -> List[object]:
+        """Run ``fn(comm)`` on ``world`` threads; re-raises the first worker exception."""
+        results: List[object] = [None] * self.world
+        errors: List[BaseException] = []
+
+        def work(r):
+            try:
+                results[r] = fn(self.comm(r))
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+                self.aborted = True
+                self.barrier.abort()
+                with self.clock_cv:
+                    self.clock_cv.notify_all()
+
+        ts = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(self.world)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        if errors:
+            raise errors[0]
+        return results
+
+
+class ThreadComm(Comm):
+    supports_async = True
+
+    def __init__(self, cluster: ThreadCluster, rank: int):
+        self.c = cluster
+        self.rank = rank
+        self.world = cluster.world
+
+    def setup(self, layout, opt_cfg):
+        self.layout = layout
+        self.c.layouts[self.rank] = layout
+        self.c.opts[self.rank] = _make_opts(layout, opt_cfg, self.rank)
+        self.c.barrier.wait()
+        # chief's initial values win (Supervisor: chief initialises, others wait — cifarnet…bsp.py:93-106)
+        if self.rank != 0:
+            self.layout.params.copy_(self.c.layouts[0].params)
+        self.c.barrier.wait()
+
+    # -- BSP ------------------------------------------------------------------------------------
+    def bsp_step(self, lr, grad_scale=1.0):
+        c = self.c
+        c.barrier.wait()                                   # every worker's gradient is complete
+        gs = c.gs
+        for o in c.opts[self.rank]:
+            g = c.layouts[0].grads[o.lo:o.hi].clone()
+            for q in range(1, self.world):
+                g.add_(c.layouts[q].grads[o.lo:o.hi])
+            g.div_(self.world)                             # mean of N (SyncReplicas take_grad(N))
+            o.apply(g, lr, grad_scale, num_updates=gs)
+        c.barrier.wait()                                   # all owners updated
+        if self.rank == 0:
+            c.gs = gs + 1
+        self._pull()
+        c.barrier.wait()
+        return c.gs
+
+    def _pull(self):
+        for lo, hi, owner in self.layout.segments:
+            if owner != self.rank:
+                self.layout.params[lo:hi].copy_(self.c.layouts[owner].params[lo:hi])
+
+    # -- ASP / SSP ------------------------------------------------------------------------------
+    def async_step(self, lr, grad_scale=1.0):
+        c = self.c
+        with c.gs_lock:
+            gs = c.gs
+            c.gs = gs + 1
+        g_all = self.layout.grads
+        for owner in range(self.world):
+            for o in c.opts[owner]:
+                # pusher-side apply on the owner's master range; no lock (Hogwild, use_locking=False)
+                o.apply(g_all[o.lo:o.hi], lr, grad_scale, num_updates=gs)
+        self._pull()
+        return gs + 1
+
+    def ssp_wait(self, step, bound, timeout=600.0):
+        c = self.c
+        t0 = time.time()
+        with c.clock_cv:
+            c.clock[self.rank] = step
+            c.clock_cv.notify_all()
+            while step > min(c.clock) + bound:
+                if c.aborted:
+                    raise StalenessTimeout("cluster aborted")
+                if time.time() - t0 > timeout:
+                    raise StalenessTimeout(f"rank {self.rank} step {step} waited > {timeout}s (clocks {c.clock})")
+                c.clock_cv.wait(0.05)
+            c.max_lead_seen = max(c.max_lead_seen, step - min(c.clock))
+        return time.time() - t0
+
+    # -- plumbing -------------------------------------------------------------------------------
+    def barrier(self):
+        self.c.barrier.wait()
+
+    def broadcast_state(self, tensors, src=0):
+        if not hasattr(self.c, "_bcast"):
+            self.c._bcast = {}
+        self.c.barrier.wait()
+        if self.rank == src:
+            self.c._bcast["t"] = [t.detach().clone() for t in tensors]
+        self.c.barrier.wait()
+        if self.rank != src:
+            for dst, s in zip(tensors, self.c._bcast["t"]):
+                dst.copy_(s)
+        self.c.barrier.wait()
+
+    def global_step(self):
+        return self.c.gs
+
+    def set_global_step(self, v):
+        self.c.gs = int(v)
+
+    def max_over_ranks(self, v):
+        return v
+
+    def owned_optimizers(self):
+        return self.c.opts[self.rank]
+
+
+# =================================================================================================
+class TorchDistComm(Comm):
+    """BSP over torch.distributed collectives — the NCCL / gloo baseline arm.
+
+    ``algo='rs_ag'``: reduce-scatter -> unfused shard update -> all-gather ("NCCL-PS");
+    ``algo='allreduce'``: all-reduce -> every rank updates the whole buffer (DDP-style, B1).
+    Requires ``placement='flat'`` (equal contiguous shards)."""
+
+    def __init__(self, algo: str = "rs_ag", group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.algo = algo
+        self._gs = 0
+
+    def setup(self, layout, opt_cfg):
+        assert layout.placement == "flat", "collective transports need the flat placement"
+        self.layout = layout
+        dist = self.dist
+        dist.broadcast(layout.params, src=0, group=self.group)
+        self.is_gloo = dist.get_backend(self.group) == "gloo"
+        if self.algo == "allreduce" or self.is_gloo:
+            # whole-buffer optimiser on every rank
+            self.opts = [ShardOptimizer(opt_cfg, layout.params, 0, layout.total, layout.wd_boundary)]
+            self.shard = None
+        else:
+            s = layout.total // self.world
+            lo = self.rank * s
+            self.opts = [ShardOptimizer(opt_cfg, layout.params, lo, lo + s, layout.wd_boundary)]
+            self.shard = torch.empty(s, dtype=torch.float32, device=layout.params.device)
+
+    def bsp_step(self, lr, grad_scale=1.0):
+        dist, L = self.dist, self.layout
+        if self.shard is None:
+            dist.all_reduce(L.grads, group=self.group)
+            L.grads.div_(self.world)
+            self.opts[0].apply(L.grads, lr, grad_scale, num_updates=self._gs)
+        else:
+            dist.reduce_scatter_tensor(self.shard, L.grads, group=self.group)
+            self.shard.div_(self.world)
+            o = self.opts[0]
+            o.apply(self.shard, lr, grad_scale, num_updates=self._gs)
+            dist.all_gather_into_tensor(L.params, L.params[o.lo:o.hi].clone(), group=self.group)
+        self._gs += 1
+        return self._gs
+
+    def ssp_wait(self, step, bound, timeout=600.0):
+        return 0.0
+
+    def barrier(self):
+        self.dist.barrier(group=self.group)
+
+    def broadcast_state(self, tensors, src=0):
+        for t in tensors:
+            self.dist.broadcast(t, src=src, group=self.group)
+
+    def global_step(self):
+        return self._gs
+
+    def set_global_step(self, v):
+        self._gs = int(v)
+
+    def max_over_ranks(self, v):
+        t = torch.tensor([v], dtype=torch.float64, device=self.layout.params.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return float(t.item())
+
+    def owned_optimizers(self):
+        return self.opts
