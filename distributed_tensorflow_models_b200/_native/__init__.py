@@ -55,7 +55,7 @@ def available() -> bool:
     return LIB_PATH.exists()
 
 
-def build(force: bool = False) -> Path:
+def build_library(force: bool = False) -> Path:
     from . import build as _b
     return _b.build(force=force)
 
@@ -63,9 +63,7 @@ def build(force: bool = False) -> Path:
 def _declare(lib: C.CDLL) -> None:
     lib.dtf_version.restype = C.c_int
     lib.dtf_last_error.restype = C.c_char_p
-    for name in dir(lib):
-        pass
-    # every other entry point returns int; argument types are declared where they are wrapped
+    # every other entry point returns int; arguments are passed as explicit ctypes values by the wrappers
 
 
 def lib() -> C.CDLL:
@@ -77,7 +75,7 @@ def lib() -> C.CDLL:
         if _lib is not None:
             return _lib
         if not LIB_PATH.exists() or os.environ.get("DTF_REBUILD") == "1":
-            build(force=os.environ.get("DTF_REBUILD") == "1")
+            build_library(force=os.environ.get("DTF_REBUILD") == "1")
         l = C.CDLL(str(LIB_PATH))
         _declare(l)
         _lib = l
@@ -88,7 +86,20 @@ class NativeError(RuntimeError):
     pass
 
 
+_launches = [0]
+
+
+def launch_count() -> int:
+    """Number of native entry-point calls (each launches one kernel) since ``reset_launch_count``."""
+    return _launches[0]
+
+
+def reset_launch_count() -> None:
+    _launches[0] = 0
+
+
 def check(rc: int, what: str) -> None:
+    _launches[0] += 1
     if rc != 0:
         msg = lib().dtf_last_error()
         raise NativeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

@@ -82,6 +82,7 @@ def _conv(ctx: _Ctx, x: torch.Tensor, k: int, filters: int, stride: int) -> torc
 def residual_unit(ctx: _Ctx, x: torch.Tensor, convs: Sequence[ConvSpec], project: Optional[ConvSpec]) -> torch.Tensor:
     """One pre-activation unit (building_block :94-130 / bottleneck_block :133-175)."""
     if ctx.native:
+        # x is a (tensor, channel sums) pair: statistics travel with the tensor from the kernel that wrote it
         from ..ops import native_ops
         return native_ops.resnet_unit(ctx, x, convs, project, _bn_vars, _conv_var, _fixed_padding,
                                       BATCH_NORM_DECAY, BATCH_NORM_EPSILON)
@@ -110,7 +111,14 @@ def _stage(ctx: _Ctx, x, filters: int, bottleneck: bool, blocks: int, stride: in
 
 
 def _head(ctx: _Ctx, x, num_classes: int):
-    y = _bn_relu(ctx, x)
+    if ctx.native:
+        from ..ops import native_ops
+        x, st = x
+        gamma, beta, mm, mv = _bn_vars(ctx.store, x.shape[-1])
+        y = native_ops.batch_norm(x, gamma, beta, mm, mv, True, BATCH_NORM_DECAY, BATCH_NORM_EPSILON, True,
+                                  ctx.update_moving, True, stats=st)
+    else:
+        y = _bn_relu(ctx, x)
     y = Fn.global_avg_pool(y)
     store = ctx.store
     with store.scope(store.unique_name("dense")):
@@ -131,7 +139,14 @@ def cifar10_resnet_v2_generator(resnet_size: int, num_classes: int, data_format=
         store = V.current_store()
         ctx = _Ctx(store, is_training, update_moving)
         ctx.native = bool(getattr(store, "fuse_bn", False)) and inputs.is_cuda and Fn.use_native(inputs) and is_training
-        x = _conv(ctx, inputs, 3, 16, 1)
+        if ctx.native:
+            from ..ops import native_ops
+            w0 = _conv_var(store, inputs.shape[-1], 3, 16)
+            st0 = native_ops._zeros(32, inputs.device)
+            x = (native_ops.conv2d(inputs, w0, None, (1, 1), (1, 1), (inputs.shape[1], inputs.shape[2]), False,
+                                   stats=st0), st0)
+        else:
+            x = _conv(ctx, inputs, 3, 16, 1)
         for filters, stride in ((16, 1), (32, 2), (64, 2)):
             x = _stage(ctx, x, filters, False, num_blocks, stride)
         return _head(ctx, x, num_classes)

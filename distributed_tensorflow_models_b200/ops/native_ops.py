@@ -1,0 +1,525 @@
+"""Autograd wiring of the native sm_100a kernels (``libdtfb200.so``).
+
+Each public function mirrors one entry of ``ops.functional`` (same arguments, NHWC fp32) and is what that
+module dispatches to for CUDA tensors.  Forward and backward both run hand-written kernels:
+
+=====================  ==========================================================================
+conv2d / linear        tcgen05 implicit GEMM: fprop, dgrad (same kernel, transposed index map), wgrad
+batch_norm             stats (conv epilogue or ``bn_stats``) -> ``bn_finalize`` -> ``affine_act``;
+                       backward = ``bn_bwd_reduce`` + ``bn_bwd_apply``
+bn_relu_conv           BN-apply + ReLU fused into the conv's operand gather (ResNet pre-activation units)
+conv_bn_act            conv with statistics epilogue + BN (Inception's conv->BN->ReLU triple)
+max_pool / avg_pool    NHWC vector kernels, argmax byte map for the max-pool gradient
+lrn / dropout          channel-window kernel / counter-based mask regenerated in backward
+softmax_xent           loss and d(logits) in one pass
+fused_update           SGD / TF1-RMSProp / weight decay / EMA on a flat shard
+=====================  ==========================================================================
+
+Everything launches on the current torch stream and allocates through the torch caching allocator, so whole
+steps are CUDA-graph capturable.  Small per-channel scratch (BN sums) is carved from a :class:`ScratchArena`
+that is zeroed once per step.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from .. import _native as nat
+from . import conv_native as cn
+
+_vp = C.c_void_p
+
+
+def _p(t: Optional[torch.Tensor]):
+    return _vp(t.data_ptr()) if t is not None else None
+
+
+class PoolParams(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("N", "H", "W", "C", "OH", "OW", "kh", "kw", "sh", "sw", "ph", "pw",
+                                       "ld_in", "ld_out")]
+
+
+# ---------------------------------------------------------------------------------------------------
+# scratch arena for per-channel accumulators (zeroed once per step, graph friendly)
+# ---------------------------------------------------------------------------------------------------
+class ScratchArena:
+    def __init__(self, device, nfloats: int = 1 << 20):
+        self.buf = torch.zeros(nfloats, dtype=torch.float32, device=device)
+        self.off = 0
+
+    def reset(self) -> None:
+        self.buf.zero_()
+        self.off = 0
+
+    def take(self, n: int) -> torch.Tensor:
+        n4 = (n + 3) // 4 * 4
+        if self.off + n4 > self.buf.numel():
+            return torch.zeros(n, dtype=torch.float32, device=self.buf.device)
+        t = self.buf[self.off:self.off + n]
+        self.off += n4
+        return t
+
+
+_ARENAS = {}
+
+
+def _dev_index(device) -> int:
+    return device.index if device.index is not None else torch.cuda.current_device()
+
+
+def arena(device) -> ScratchArena:
+    key = _dev_index(device)
+    a = _ARENAS.get(key)
+    if a is None:
+        a = _ARENAS[key] = ScratchArena(device)
+    return a
+
+
+def begin_step(device) -> None:
+    """Zero the per-step scratch (call once before forward)."""
+    arena(device).reset()
+
+
+def _zeros(n: int, device) -> torch.Tensor:
+    return arena(device).take(n)
+
+
+# ---------------------------------------------------------------------------------------------------
+# convolution / linear
+# ---------------------------------------------------------------------------------------------------
+def _pad4(x: torch.Tensor, w: torch.Tensor):
+    """The gather reads 16-byte channel chunks: pad C_in to a multiple of 4 (3-channel stems)."""
+    c = x.shape[-1]
+    if c % 4 == 0:
+        return x, w
+    padc = (-c) % 4
+    return torch.nn.functional.pad(x, (0, padc)), torch.nn.functional.pad(w, (0, padc)).contiguous()
+
+
+class _ConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, stride, pad, out_hw, relu, stats):
+        x = x.contiguous() if x.stride(-1) != 1 else x
+        y = cn.conv_fprop(x, w, stride, pad, bias=bias, relu=relu, stats=stats, out_hw=out_hw)
+        ctx.save_for_backward(x, w, y if relu else None)
+        ctx.cfg = (stride, pad, relu, bias is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y = ctx.saved_tensors
+        stride, pad, relu, has_bias = ctx.cfg
+        dy = dy.contiguous()
+        if relu:
+            dy = torch.ops.aten.threshold_backward(dy, y, 0.0)
+        dx = dw = db = None
+        if has_bias and ctx.needs_input_grad[2]:
+            co = dy.shape[-1]
+            db = _zeros(co, dy.device)
+            nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db), nat.stream_ptr()),
+                      "dtf_colsum")
+        if ctx.needs_input_grad[0]:
+            dx = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
+        if ctx.needs_input_grad[1]:
+            dw = cn.conv_wgrad(x, dy, w.shape, stride, pad)
+        return dx, dw, db, None, None, None, None, None
+
+
+def conv2d(x, w, bias, stride, pad_before, out_hw, relu, stats=None):
+    cin = x.shape[-1]
+    if cin % 4 != 0:
+        x, w = _pad4(x, w)        # differentiable pads: the weight gradient is sliced back by autograd
+    return _ConvFn.apply(x, w, bias, tuple(stride), tuple(pad_before), tuple(out_hw), bool(relu), stats)
+
+
+def linear(x, w, bias, relu):
+    n, k = x.shape
+    y = conv2d(x.reshape(n, 1, 1, k), w.reshape(w.shape[0], 1, 1, k), bias, (1, 1), (0, 0), (1, 1), relu)
+    return y.reshape(n, w.shape[0])
+
+
+# ---------------------------------------------------------------------------------------------------
+# batch norm
+# ---------------------------------------------------------------------------------------------------
+class BnCoef:
+    """Per-channel (scale, shift, mean, invstd) of one batch-norm application."""
+
+    def __init__(self, scale, shift, mean, invstd, training):
+        self.scale, self.shift, self.mean, self.invstd, self.training = scale, shift, mean, invstd, training
+
+
+@torch.no_grad()
+def bn_prepare(stats: Optional[torch.Tensor], gamma, beta, mm, mv, count: int, eps: float, decay: float,
+               training: bool, update_moving: bool, unbiased: bool) -> BnCoef:
+    c = mm.numel()
+    dev = mm.device
+    buf = torch.empty(4 * c, dtype=torch.float32, device=dev)
+    scale, shift, mean, invstd = buf[:c], buf[c:2 * c], buf[2 * c:3 * c], buf[3 * c:]
+    if training:
+        nat.check(nat.lib().dtf_bn_finalize(_p(stats), _p(gamma), _p(beta), C.c_longlong(count), C.c_float(eps),
+                                            C.c_float(decay), int(update_moving), int(unbiased), _p(mm), _p(mv),
+                                            _p(scale), _p(shift), _p(mean), _p(invstd), c, nat.stream_ptr()),
+                  "dtf_bn_finalize")
+    else:
+        nat.check(nat.lib().dtf_bn_eval_affine(_p(gamma), _p(beta), _p(mm), _p(mv), C.c_float(eps), _p(scale),
+                                               _p(shift), c, nat.stream_ptr()), "dtf_bn_eval_affine")
+    return BnCoef(scale, shift, mean, invstd, training)
+
+
+def bn_stats(x: torch.Tensor) -> torch.Tensor:
+    c = x.shape[-1]
+    st = _zeros(2 * c, x.device)
+    m = x.numel() // c
+    nat.check(nat.lib().dtf_bn_stats(_p(x), C.c_longlong(m), c, c, _p(st), nat.stream_ptr()), "dtf_bn_stats")
+    return st
+
+
+def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: bool, add=None):
+    """Shared BN(+ReLU) backward: returns (dx, dgamma, dbeta)."""
+    c = x.shape[-1]
+    m = x.numel() // c
+    dx = torch.empty_like(x)
+    if not coef.training:
+        nat.check(nat.lib().dtf_affine_act_bwd(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu),
+                                               C.c_longlong(m), c, c, c, c, _p(dx), nat.stream_ptr()),
+                  "dtf_affine_act_bwd")
+        if add is not None:
+            dx = dx + add
+        # frozen statistics: dgamma/dbeta via the same reduction
+    sums = _zeros(2 * c, x.device)
+    nat.check(nat.lib().dtf_bn_bwd_reduce(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m),
+                                          c, c, c, _p(sums), nat.stream_ptr()), "dtf_bn_bwd_reduce")
+    dg = torch.empty(c, dtype=torch.float32, device=x.device) if has_gamma else None
+    db = torch.empty(c, dtype=torch.float32, device=x.device) if has_beta else None
+    if coef.training:
+        nat.check(nat.lib().dtf_bn_bwd_apply(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), _p(coef.mean),
+                                             _p(coef.invstd), _p(sums), int(relu), C.c_longlong(m), c, c, c, c,
+                                             _p(add), c if add is not None else 0, _p(dx), _p(dg), _p(db),
+                                             nat.stream_ptr()), "dtf_bn_bwd_apply")
+    else:
+        if db is not None:
+            db.copy_(sums[:c])
+        if dg is not None:
+            # d/dgamma of gamma*invstd*(x-mean): invstd * (sum g*x - mean * sum g), with moving statistics
+            dg.copy_(coef.invstd_eval * (sums[c:] - coef.mean_eval * sums[:c]))
+    return dx, dg, db
+
+
+class _BnApplyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, coef, relu):
+        x = x.contiguous()
+        c = x.shape[-1]
+        m = x.numel() // c
+        y = torch.empty_like(x)
+        nat.check(nat.lib().dtf_affine_act(_p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m), c, c, c,
+                                           _p(y), nat.stream_ptr()), "dtf_affine_act")
+        ctx.save_for_backward(x)
+        ctx.coef, ctx.relu = coef, relu
+        ctx.has = (gamma is not None, beta is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dx, dg, db = _bn_backward(dy.contiguous(), x, ctx.coef, ctx.relu, ctx.has[0], ctx.has[1])
+        return dx, dg, db, None, None
+
+
+def batch_norm(x, gamma, beta, mm, mv, training, decay, eps, relu, update_moving, unbiased, stats=None):
+    """Stand-alone BN (+ReLU).  ``stats`` may carry sums already produced by a conv epilogue."""
+    shape = x.shape
+    c = shape[-1]
+    x4 = x if x.dim() == 4 else x.reshape(shape[0], 1, 1, c)
+    x4 = x4.contiguous()
+    count = x4.numel() // c
+    if training and stats is None:
+        stats = bn_stats(x4)
+    coef = bn_prepare(stats, gamma, beta, mm, mv, count, eps, decay, training, update_moving, unbiased)
+    if not training:
+        coef.mean_eval = mm
+        coef.invstd_eval = torch.rsqrt(mv + eps)
+    y = _BnApplyFn.apply(x4, gamma, beta, coef, bool(relu))
+    return y.reshape(shape)
+
+
+def conv_bn_act(x, w, stride, padding, gamma, beta, mm, mv, decay, eps, relu):
+    """conv -> BN(train) -> ReLU with the statistics taken from the conv epilogue (one pass less over y)."""
+    from .functional import resolve_padding
+    co, r, s, _ = w.shape
+    oh, ow, ph, pw = resolve_padding(x.shape[1], x.shape[2], r, s, stride, padding)
+    stats = _zeros(2 * co, x.device)
+    y = conv2d(x, w, None, stride, (ph[0], pw[0]), (oh, ow), False, stats=stats)
+    return batch_norm(y, gamma, beta, mm, mv, True, decay, eps, relu, True, False, stats=stats)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BN-ReLU fused into the consumer convolution (ResNet pre-activation units)
+# ---------------------------------------------------------------------------------------------------
+class _BnReluConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, w, residual, coef, stride, pad, out_hw, stats_out):
+        y = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
+                          in_relu=True, stats=stats_out, out_hw=out_hw)
+        ctx.save_for_backward(x, w)
+        ctx.coef = coef
+        ctx.cfg = (stride, pad, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        stride, pad, has_res = ctx.cfg
+        coef = ctx.coef
+        dy = dy.contiguous()
+        dw = cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
+        da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
+        dx, dg, db = _bn_backward(da, x, coef, True, True, True)
+        return dx, dg, db, dw, (dy if has_res else None), None, None, None, None, None
+
+
+def bn_relu_conv(x, gamma, beta, w, coef: BnCoef, stride, padding, residual=None, want_stats=True):
+    from .functional import resolve_padding
+    co, r, s, _ = w.shape
+    stride = (stride, stride) if isinstance(stride, int) else tuple(stride)
+    oh, ow, ph, pw = resolve_padding(x.shape[1], x.shape[2], r, s, stride, padding)
+    stats = _zeros(2 * co, x.device) if want_stats else None
+    y = _BnReluConvFn.apply(x, gamma, beta, w, residual, coef, stride, (ph[0], pw[0]), (oh, ow), stats)
+    return y, stats
+
+
+def resnet_unit(ctx, x_and_stats, convs, project, bn_vars, conv_var, fixed_padding, decay, eps):
+    """One pre-activation residual unit on the fused path.  ``x_and_stats`` = (x, stats of x)."""
+    x, st = x_and_stats
+    store = ctx.store
+    count = x.numel() // x.shape[-1]
+    gamma, beta, mm, mv = bn_vars(store, x.shape[-1])
+    coef = bn_prepare(st, gamma, beta, mm, mv, count, eps, decay, True, ctx.update_moving, True)
+    shortcut = x
+    if project is not None:
+        k, f, s = project
+        wp = conv_var(store, x.shape[-1], k, f)
+        shortcut, _ = bn_relu_conv(x, gamma, beta, wp, coef, s, fixed_padding(k, s), want_stats=False)
+    y, yst = x, st
+    n = len(convs)
+    for i, (k, f, s) in enumerate(convs):
+        if i > 0:
+            gamma, beta, mm, mv = bn_vars(store, y.shape[-1])
+            coef = bn_prepare(yst, gamma, beta, mm, mv, y.numel() // y.shape[-1], eps, decay, True,
+                              ctx.update_moving, True)
+        w = conv_var(store, y.shape[-1], k, f)
+        last = i == n - 1
+        y, yst = bn_relu_conv(y, gamma, beta, w, coef, s, fixed_padding(k, s),
+                              residual=shortcut if last else None, want_stats=True)
+    return y, yst
+
+
+# ---------------------------------------------------------------------------------------------------
+# pooling
+# ---------------------------------------------------------------------------------------------------
+def _pool_params(x, k, stride, pad, out_hw, c_out_ld):
+    p = PoolParams()
+    n, h, w, c = x.shape
+    p.N, p.H, p.W, p.C = n, h, w, c
+    p.OH, p.OW = out_hw
+    p.kh, p.kw = k
+    p.sh, p.sw = stride
+    p.ph, p.pw = pad
+    p.ld_in, p.ld_out = c, c_out_ld
+    return p
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad, out_hw):
+        x = x.contiguous()
+        n, h, w, c = x.shape
+        y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
+        arg = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.uint8, device=x.device)
+        p = _pool_params(x, k, stride, pad, out_hw, c)
+        nat.check(nat.lib().dtf_max_pool_fwd(C.byref(p), _p(x), _p(y), _p(arg), nat.stream_ptr()), "dtf_max_pool_fwd")
+        ctx.save_for_backward(arg)
+        ctx.p = p
+        ctx.in_shape = x.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (arg,) = ctx.saved_tensors
+        dy = dy.contiguous()
+        c = ctx.in_shape[-1]
+        dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dy.device)
+        nat.check(nat.lib().dtf_max_pool_bwd(C.byref(ctx.p), _p(dy), c, _p(arg), _p(dx), c, nat.stream_ptr()),
+                  "dtf_max_pool_bwd")
+        return dx, None, None, None, None
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad, out_hw):
+        x = x.contiguous()
+        n, h, w, c = x.shape
+        y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
+        p = _pool_params(x, k, stride, pad, out_hw, c)
+        nat.check(nat.lib().dtf_avg_pool_fwd(C.byref(p), _p(x), _p(y), nat.stream_ptr()), "dtf_avg_pool_fwd")
+        ctx.p = p
+        ctx.in_shape = x.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous()
+        c = ctx.in_shape[-1]
+        dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dy.device)
+        nat.check(nat.lib().dtf_avg_pool_bwd(C.byref(ctx.p), _p(dy), c, _p(dx), c, nat.stream_ptr()),
+                  "dtf_avg_pool_bwd")
+        return dx, None, None, None, None
+
+
+def max_pool(x, k, stride, pad_before, out_hw):
+    if x.shape[-1] % 4 != 0:
+        raise RuntimeError("native max_pool needs C % 4 == 0")
+    return _MaxPoolFn.apply(x, tuple(k), tuple(stride), tuple(pad_before), tuple(out_hw))
+
+
+def avg_pool(x, k, stride, pad_before, out_hw):
+    if x.shape[-1] % 4 != 0:
+        raise RuntimeError("native avg_pool needs C % 4 == 0")
+    return _AvgPoolFn.apply(x, tuple(k), tuple(stride), tuple(pad_before), tuple(out_hw))
+
+
+# ---------------------------------------------------------------------------------------------------
+# LRN / dropout / loss
+# ---------------------------------------------------------------------------------------------------
+class _LrnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, radius, bias, alpha, beta):
+        x = x.contiguous()
+        c = x.shape[-1]
+        y = torch.empty_like(x)
+        nat.check(nat.lib().dtf_lrn_fwd(_p(x), _p(y), C.c_longlong(x.numel() // c), c, radius, C.c_float(bias),
+                                        C.c_float(alpha), C.c_float(beta), nat.stream_ptr()), "dtf_lrn_fwd")
+        ctx.save_for_backward(x)
+        ctx.cfg = (radius, bias, alpha, beta)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        radius, bias, alpha, beta = ctx.cfg
+        c = x.shape[-1]
+        dy = dy.contiguous()
+        dx = torch.empty_like(x)
+        nat.check(nat.lib().dtf_lrn_bwd(_p(x), _p(dy), _p(dx), C.c_longlong(x.numel() // c), c, radius,
+                                        C.c_float(bias), C.c_float(alpha), C.c_float(beta), nat.stream_ptr()),
+                  "dtf_lrn_bwd")
+        return dx, None, None, None, None
+
+
+def lrn(x, radius, bias, alpha, beta):
+    return _LrnFn.apply(x, int(radius), float(bias), float(alpha), float(beta))
+
+
+_SEEDS = {}
+_SALT = [0]
+
+
+def dropout_seed(device) -> torch.Tensor:
+    """Device-resident step counter feeding the dropout generator (bumped by ``advance_dropout_seed``)."""
+    key = _dev_index(device)
+    t = _SEEDS.get(key)
+    if t is None:
+        t = _SEEDS[key] = torch.full((1,), 0x5DEECE66D, dtype=torch.int64, device=device)
+    return t
+
+
+def advance_dropout_seed(device) -> None:
+    dropout_seed(device).add_(1)
+    _SALT[0] = 0
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, keep, salt):
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        seed = dropout_seed(x.device)
+        nat.check(nat.lib().dtf_dropout(_p(x), _p(y), C.c_longlong(x.numel()), C.c_float(keep), _p(seed),
+                                        C.c_ulonglong(salt), nat.stream_ptr()), "dtf_dropout")
+        ctx.cfg = (keep, salt)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        keep, salt = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty_like(dy)
+        seed = dropout_seed(dy.device)
+        nat.check(nat.lib().dtf_dropout(_p(dy), _p(dx), C.c_longlong(dy.numel()), C.c_float(keep), _p(seed),
+                                        C.c_ulonglong(salt), nat.stream_ptr()), "dtf_dropout")
+        return dx, None, None
+
+
+def dropout(x, keep_prob):
+    _SALT[0] += 1
+    return _DropoutFn.apply(x, float(keep_prob), _SALT[0] * 0x9E3779B1)
+
+
+class _XentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, smoothing, weight):
+        logits = logits.contiguous()
+        n, c = logits.shape
+        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+        dlog = torch.empty_like(logits)
+        nat.check(nat.lib().dtf_softmax_xent(_p(logits), _p(labels), n, c, C.c_float(smoothing), C.c_float(weight),
+                                             _p(loss), _p(dlog), None, nat.stream_ptr()), "dtf_softmax_xent")
+        ctx.save_for_backward(dlog)
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dlog,) = ctx.saved_tensors
+        return dlog * dloss, None, None, None
+
+
+def softmax_xent(logits, labels, smoothing, weight):
+    return _XentFn.apply(logits, labels.to(torch.int64).contiguous(), float(smoothing), float(weight))
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused optimiser update
+# ---------------------------------------------------------------------------------------------------
+def hyper_tensor(opt, device) -> torch.Tensor:
+    h = getattr(opt, "_hyper", None)
+    if h is None:
+        h = opt._hyper = torch.zeros(8, dtype=torch.float32, device=device)
+        opt._hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory()
+    return h
+
+
+def set_hyper(opt, lr: float, grad_scale: float, ema_decay: float) -> torch.Tensor:
+    cfg = opt.cfg
+    h = hyper_tensor(opt, opt.w.device)
+    vals = (float(lr), float(grad_scale), float(cfg.weight_decay), float(cfg.rms_decay), float(cfg.momentum),
+            float(cfg.epsilon), float(ema_decay), 0.0)
+    if getattr(opt, "_hyper_vals", None) != vals:
+        opt._hyper_vals = vals
+        opt._hyper_host.copy_(torch.tensor(vals, dtype=torch.float32))
+        h.copy_(opt._hyper_host, non_blocking=True)
+    return h
+
+
+def fused_update(opt, g: torch.Tensor, lr: float, grad_scale: float, num_updates, use_ema: bool) -> None:
+    from ..optim.schedule import ema_decay as _ema_decay
+    d = -1.0
+    if opt.ema is not None and use_ema:
+        d = _ema_decay(opt.cfg.ema.decay, num_updates if opt.cfg.ema.use_num_updates else None)
+    h = set_hyper(opt, lr, grad_scale, d)
+    kind = 0 if opt.cfg.kind == "sgd" else 1
+    n = opt.w.numel()
+    nat.check(nat.lib().dtf_fused_update(_p(opt.w), _p(g), _p(opt.slots.get("RMSProp")), _p(opt.slots.get("RMSProp_1")),
+                                         _p(opt.ema), C.c_longlong(n), C.c_longlong(opt.n_decayed), _p(h), kind,
+                                         nat.stream_ptr()), "dtf_fused_update")

@@ -109,6 +109,8 @@ class Trainer:
         self.setup = setup.resolved()
         self.comm = comm or LocalComm()
         self.device = device or torch.device("cpu")
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.p = self.setup.preset
         spec = registry.MODEL_SPECS[self.setup.model]
         self.spec = spec
@@ -135,6 +137,7 @@ class Trainer:
         self.local_step = 0
         self._graph = None
         self._static = None
+        self.graph_kernel_launches = 0      # native kernels inside one replay of the captured step
         self.last_timing: Dict[str, float] = {}
 
     # ---- helpers ---------------------------------------------------------------------------------
@@ -175,6 +178,10 @@ class Trainer:
 
     # ---- one step --------------------------------------------------------------------------------
     def _fwd_bwd(self, x, y):
+        if self.device.type == "cuda" and Fn.get_backend() != "torch":
+            from ..ops import native_ops
+            native_ops.begin_step(self.device)
+            native_ops.advance_dropout_seed(self.device)
         self.layout.zero_grads()
         loss, logits = self._run_forward(x, y, True)
         total = loss
@@ -195,9 +202,12 @@ class Trainer:
                     self._fwd_bwd(*self._static)
             torch.cuda.current_stream().wait_stream(s)
             self._undo_warmup_side_effects()
+            from .. import _native as nat
+            before = nat.launch_count()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._out = self._fwd_bwd(*self._static)
+            self.graph_kernel_launches = nat.launch_count() - before
             self._graph = g
         self._static[0].copy_(x, non_blocking=True)
         self._static[1].copy_(y, non_blocking=True)

@@ -62,7 +62,7 @@ int dtf_conv_gemm(const dtf_conv_gemm_params* p, void* stream);
 /* Weight gradient: dW[n][k] (+)= sum_m dY[m, n] * A[m, k], A gathered exactly as in fprop
  * (with the same optional fused input activation).  Split over m across CTAs; partial sums
  * are combined with red.global.add.f32, so dW must be zeroed (or hold the value to
- * accumulate into) before the call.  Optional dbias[n] += sum_m dY[m, n]. */
+ * accumulate into) before the call. */
 typedef struct {
   const float* src; int srcH, srcW, srcC, src_ld;
   int N, OH, OW;
@@ -77,6 +77,85 @@ int dtf_conv_wgrad(const dtf_conv_wgrad_params* p, void* stream);
 
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* K7  batch norm on [M = N*H*W, C] views of NHWC tensors (C % 4 == 0)                    */
+/*     replaces slim ops.batch_norm (inception/slim/ops.py:46-135) and                   */
+/*     tf.layers.batch_normalization(fused=True) (resnet/resnet_model.py:41-50)          */
+/* ------------------------------------------------------------------------------------ */
+/* stats[0..C) += sum_m x, stats[C..2C) += sum_m x^2 (atomic; zero the buffer first) */
+int dtf_bn_stats(const float* x, long long M, int C, int ld_x, float* stats, void* stream);
+/* sums -> scale = gamma*invstd, shift = beta - mean*scale (+ mean, invstd for backward);
+ * moving = moving*decay + batch*(1-decay) when update_moving (variance Bessel-corrected when asked) */
+int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, long long count, float eps,
+                    float decay, int update_moving, int unbiased_moving_var, float* moving_mean,
+                    float* moving_var, float* scale, float* shift, float* mean_out, float* invstd_out, int C,
+                    void* stream);
+int dtf_bn_eval_affine(const float* gamma, const float* beta, const float* moving_mean, const float* moving_var,
+                       float eps, float* scale, float* shift, int C, void* stream);
+/* y = act(x*scale + shift) */
+int dtf_affine_act(const float* x, const float* scale, const float* shift, int relu, long long M, int C, int ld_x,
+                   int ld_y, float* y, void* stream);
+/* sums[0..C) += sum g, sums[C..2C) += sum g*x with g = dy * [x*scale+shift > 0] (when relu) */
+int dtf_bn_bwd_reduce(const float* dy, const float* x, const float* scale, const float* shift, int relu,
+                      long long M, int C, int ld_x, int ld_dy, float* sums, void* stream);
+/* dx (+= add) from the reduced sums; also writes dgamma / dbeta (either may be NULL) */
+int dtf_bn_bwd_apply(const float* dy, const float* x, const float* scale, const float* shift, const float* mean,
+                     const float* invstd, const float* sums, int relu, long long M, int C, int ld_x, int ld_dy,
+                     int ld_dx, const float* add, int ld_add, float* dx, float* dgamma, float* dbeta, void* stream);
+/* frozen-statistics backward: dx = scale * dy * mask */
+int dtf_affine_act_bwd(const float* dy, const float* x, const float* scale, const float* shift, int relu,
+                       long long M, int C, int ld_x, int ld_dy, int ld_dx, float* dx, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* K4/K5  pooling (NHWC, C % 4 == 0); tf.nn.max_pool / avg_pool semantics                 */
+/*     (cnn/cifar10.py:228, inception/slim/ops.py:370,400, resnet/resnet_model.py:271)   */
+/* ------------------------------------------------------------------------------------ */
+typedef struct {
+  int N, H, W, C, OH, OW, kh, kw, sh, sw, ph, pw, ld_in, ld_out;
+} dtf_pool_params;
+int dtf_max_pool_fwd(const dtf_pool_params* p, const float* x, float* y, unsigned char* argmax, void* stream);
+int dtf_max_pool_bwd(const dtf_pool_params* p, const float* dy, int ld_dy, const unsigned char* argmax, float* dx,
+                     int ld_dx, void* stream);
+int dtf_avg_pool_fwd(const dtf_pool_params* p, const float* x, float* y, void* stream);
+int dtf_avg_pool_bwd(const dtf_pool_params* p, const float* dy, int ld_dy, float* dx, int ld_dx, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* K6 LRN, K9 softmax-xent, K10 dropout, K2 bias gradient                                 */
+/*     (cnn/cifar10.py:231,299; inception/slim/losses.py:142-174; slim/ops.py:422)       */
+/* ------------------------------------------------------------------------------------ */
+int dtf_lrn_fwd(const float* x, float* y, long long M, int C, int radius, float bias, float alpha, float beta,
+                void* stream);
+int dtf_lrn_bwd(const float* x, const float* dy, float* dx, long long M, int C, int radius, float bias,
+                float alpha, float beta, void* stream);
+/* loss[0] = weight * mean_n xent(smoothed target); dlogits = weight/N * (softmax - target) (may be NULL) */
+int dtf_softmax_xent(const float* logits, const long long* labels, int N, int C, float smoothing, float weight,
+                     float* loss, float* dlogits, float* row_loss, void* stream);
+/* y = x * keep(i) / keep_prob; the mask is a pure function of (*seed_ptr, salt, i) */
+int dtf_dropout(const float* x, float* y, long long n, float keep_prob, const unsigned long long* seed_ptr,
+                unsigned long long salt, void* stream);
+/* out[c] += sum_m x[m*ld + c] */
+int dtf_colsum(const float* x, long long M, int C, int ld, float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* K16 + C1..C5  parameter-server update / push / pull / clocks                           */
+/*     hyper[7] (device): lr, grad_scale, weight_decay, rms_decay, momentum, epsilon,    */
+/*     ema_decay (< 0 disables EMA).  kind: 0 SGD, 1 TF1 RMSProp with momentum.          */
+/* ------------------------------------------------------------------------------------ */
+int dtf_fused_update(float* w, const float* g, float* ms, float* mom, float* ema, long long n,
+                     long long n_decayed, const float* hyper, int kind, void* stream);
+/* One BSP step over peer-mapped buffers (reduce-scatter + update + all-gather in one kernel per rank). */
+int dtf_ps_bsp_step(const float* const* peer_grads, float* const* peer_params, unsigned int* const* peer_flags,
+                    unsigned int* local_counter, unsigned int* status, int rank, int world, long long shard,
+                    long long wd_boundary, float* ms, float* mom, float* ema, const float* hyper, int kind,
+                    unsigned int* epoch_ptr, void* stream);
+/* One ASP/SSP step: one-sided apply of the local gradient on every owner's range, then refresh the replica. */
+int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms, float* const* peer_mom,
+                      float* const* peer_ema, unsigned long long* global_step, int rank, int world, long long shard,
+                      long long wd_boundary, const float* hyper, int kind, void* stream);
+/* SSP: publish clock[rank] = step to every peer, wait while step > min(clock) + bound (status 2 on timeout). */
+int dtf_ssp_clock(unsigned int* const* peer_clocks, int rank, int world, unsigned int step, unsigned int bound,
+                  double timeout_s, unsigned int* status, unsigned int* waited_polls, void* stream);
 
 #ifdef __cplusplus
 }

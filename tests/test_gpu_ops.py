@@ -1,0 +1,166 @@
+"""Numerics of every native sm_100a op against the plain PyTorch fp32 reference of the same op
+(forward and gradients).  tf32 tensor-core ops are compared at tf32 tolerance, the rest at fp32."""
+import pytest
+import torch
+
+from distributed_tensorflow_models_b200.ops import functional as Fn
+
+pytestmark = pytest.mark.gpu
+
+TF32_TOL = 5e-3
+FP32_TOL = 2e-5
+
+
+def _rel(a, b):
+    """Relative Frobenius error (robust to the few ReLU-mask flips tf32 rounding causes near zero)."""
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def _both(fn, inputs, tol, grad_inputs=None):
+    """Run fn(*inputs) on the native and the reference backend; compare outputs and input gradients."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    outs, grads = [], []
+    g = torch.Generator(device="cpu").manual_seed(7)
+    dy = None
+    for backend in ("auto", "torch"):
+        Fn.set_backend(backend)
+        try:
+            ins = [t.detach().clone().requires_grad_(t.is_floating_point()) if isinstance(t, torch.Tensor) else t
+                   for t in inputs]
+            y = fn(*ins)
+            if dy is None:
+                dy = torch.randn(y.shape, generator=g).to(y.device)
+            y.backward(dy)
+            outs.append(y.detach())
+            grads.append([t.grad for t in ins if isinstance(t, torch.Tensor) and t.requires_grad])
+        finally:
+            Fn.set_backend("auto")
+    assert _rel(outs[0], outs[1]) < tol, f"forward mismatch {_rel(outs[0], outs[1])}"
+    for a, b in zip(grads[0], grads[1]):
+        if a is None and b is None:
+            continue
+        assert _rel(a, b) < tol, f"grad mismatch {_rel(a, b)}"
+
+
+def _r(*shape, seed=0, scale=1.0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).cuda()
+
+
+@pytest.mark.parametrize("cfg", [
+    (4, 32, 32, 3, 16, 3, 1, "SAME", False, False),     # stem: 3 input channels (padded to 4 internally)
+    (4, 32, 32, 16, 32, 3, 2, ((1, 1), (1, 1)), False, False),
+    (4, 24, 24, 3, 64, 5, 1, "SAME", True, True),
+    (2, 35, 35, 48, 64, 5, 1, "SAME", False, False),
+    (2, 12, 12, 64, 64, 3, 2, "SAME", True, True),      # asymmetric SAME padding
+    (2, 32, 32, 3, 64, 11, 1, "VALID", True, True),
+])
+def test_conv2d(cfg):
+    n, h, w, ci, co, k, s, pad, bias, relu = cfg
+    x = _r(n, h, w, ci, seed=1)
+    wt = _r(co, k, k, ci, seed=2, scale=(k * k * ci) ** -0.5)
+    b = (torch.sign(_r(co, seed=3)) * 6.0) if bias else None     # keeps pre-activations away from the ReLU kink
+    if bias:
+        _both(lambda x, wt, b: Fn.conv2d(x, wt, b, s, pad, relu=relu), [x, wt, b], TF32_TOL)
+    else:
+        _both(lambda x, wt: Fn.conv2d(x, wt, None, s, pad, relu=relu), [x, wt], TF32_TOL)
+
+
+def test_conv_rect_kernels():
+    x = _r(2, 17, 17, 128, seed=1)
+    for kh, kw in ((1, 7), (7, 1), (1, 3), (3, 1)):
+        wt = _r(96, kh, kw, 128, seed=2, scale=(kh * kw * 128) ** -0.5)
+        _both(lambda x, wt: Fn.conv2d(x, wt, None, 1, "SAME"), [x, wt], TF32_TOL)
+
+
+@pytest.mark.parametrize("n,k,m", [(128, 2304, 384), (128, 64, 10), (32, 2048, 1001), (8, 192, 10)])
+def test_linear(n, k, m):
+    x, w, b = _r(n, k, seed=1), _r(m, k, seed=2, scale=k ** -0.5), torch.sign(_r(m, seed=3)) * 6.0
+    _both(lambda x, w, b: Fn.linear(x, w, b, relu=True), [x, w, b], TF32_TOL)
+
+
+@pytest.mark.parametrize("c,relu,has_gamma", [(16, True, True), (64, False, True), (80, True, False), (448, True, False)])
+def test_batch_norm_train(c, relu, has_gamma):
+    x = _r(8, 9, 9, c, seed=1) * 2 + 0.5
+    gamma = (_r(c, seed=2) * 0.1 + 1.0) if has_gamma else None
+    beta = _r(c, seed=3) * 0.1
+    mms, mvs = [], []
+
+    def run(x, *gb):
+        mm = torch.zeros(c, device="cuda")
+        mv = torch.ones(c, device="cuda")
+        gam = gb[0] if has_gamma else None
+        bet = gb[-1]
+        y = Fn.batch_norm(x, gam, bet, mm, mv, training=True, decay=0.9, eps=1e-3, relu=relu,
+                          unbiased_moving_var=True)
+        mms.append(mm)
+        mvs.append(mv)
+        return y
+    ins = [x] + ([gamma] if has_gamma else []) + [beta]
+    _both(run, ins, 2e-4)
+    assert _rel(mms[0], mms[1]) < 1e-4 and _rel(mvs[0], mvs[1]) < 1e-4
+
+
+def test_batch_norm_eval():
+    c = 32
+    x = _r(4, 5, 5, c, seed=1)
+    mm, mv = _r(c, seed=4) * 0.2, (_r(c, seed=5).abs() + 0.5)
+    beta = _r(c, seed=3)
+    _both(lambda x, beta: Fn.batch_norm(x, None, beta, mm, mv, training=False, decay=0.9, eps=1e-3, relu=True),
+          [x, beta], 1e-4)
+
+
+@pytest.mark.parametrize("k,s,pad", [(3, 2, "SAME"), (2, 2, "VALID"), (3, 2, "VALID"), (3, 1, "SAME")])
+def test_pools(k, s, pad):
+    x = _r(3, 13, 13, 32, seed=1)
+    _both(lambda x: Fn.max_pool(x, k, s, pad), [x], FP32_TOL)
+    _both(lambda x: Fn.avg_pool(x, k, s, pad), [x], FP32_TOL)
+
+
+def test_global_avg_pool():
+    x = _r(16, 8, 8, 64, seed=1)
+    _both(lambda x: Fn.global_avg_pool(x), [x], FP32_TOL)
+
+
+def test_lrn():
+    x = _r(4, 12, 12, 64, seed=1) * 3
+    _both(lambda x: Fn.lrn(x, 4, 1.0, 0.001 / 9.0, 0.75), [x], 1e-4)
+
+
+@pytest.mark.parametrize("c,smooth,weight", [(10, 0.0, 1.0), (1001, 0.1, 0.4)])
+def test_softmax_xent(c, smooth, weight):
+    logits = _r(32, c, seed=1) * 3
+    labels = torch.randint(0, c, (32,), generator=torch.Generator().manual_seed(1)).cuda()
+    _both(lambda z: Fn.softmax_cross_entropy(z, labels, smooth, weight), [logits], 1e-4)
+
+
+def test_dropout_statistics_and_backward_mask():
+    from distributed_tensorflow_models_b200.ops import native_ops
+    x = torch.ones(1 << 16, device="cuda", requires_grad=True)
+    y = Fn.dropout(x, 0.8, True)
+    kept = (y > 0).float().mean().item()
+    assert abs(kept - 0.8) < 0.01
+    assert torch.allclose(y[y > 0], torch.full_like(y[y > 0], 1 / 0.8))
+    y.sum().backward()
+    assert torch.equal(x.grad > 0, y > 0)        # same mask regenerated in backward
+    native_ops.advance_dropout_seed(x.device)
+    y2 = Fn.dropout(x, 0.8, True)
+    assert not torch.equal(y2 > 0, y > 0)
+
+
+def test_fused_update_matches_reference():
+    from distributed_tensorflow_models_b200.optim import EmaConfig, OptimizerConfig, ShardOptimizer
+    for kind in ("sgd", "rmsprop"):
+        cfg = OptimizerConfig(kind=kind, weight_decay=2e-3, ema=EmaConfig(0.9999))
+        w0 = _r(5000, seed=1)
+        opts = []
+        for dev in ("cuda", "cpu"):
+            w = w0.to(dev).clone()
+            o = ShardOptimizer(cfg, w, 0, 5000, 3000)
+            for step in range(3):
+                g = _r(5000, seed=10 + step).to(dev)
+                o.apply(g, 0.05, 1.0, num_updates=step)
+            opts.append(o)
+        assert _rel(opts[0].w.cpu(), opts[1].w) < 1e-5
+        assert _rel(opts[0].ema.cpu(), opts[1].ema) < 1e-5
