@@ -261,6 +261,41 @@ extern "C" int dtf_bn_finalize(const float* stats, const float* gamma, const flo
   return 0;
 }
 
+// Training-mode batch norm forward as one call: zero scratch -> column sums -> statistics / moving update ->
+// y = act(x*scale + shift).  `scratch` (2*C floats) holds the per-channel sums; `coef` (4*C floats) receives
+// scale | shift | mean | invstd for the backward pass.
+static int bn_forward_train_impl(const float* x, long long M, int C, int ld_x, const float* gamma, const float* beta,
+                                 float eps, float decay, int update_moving, int unbiased_moving_var,
+                                 float* moving_mean, float* moving_var, int relu, float* scratch, float* coef,
+                                 float* y, int ld_y, cudaStream_t stream) {
+  DTF_REQUIRE(C % 4 == 0 && ld_x % 4 == 0 && ld_y % 4 == 0, "channel count / pitch must be multiples of 4");
+  if (M == 0) return 0;
+  DTF_CHECK(cudaMemsetAsync(scratch, 0, 2 * (size_t)C * sizeof(float), stream));
+  int rpb;
+  const int grid = reduce_grid(M, &rpb);
+  col_reduce_kernel<0><<<grid, 256, 256 * 8 * sizeof(float), stream>>>(x, nullptr, nullptr, nullptr, 0, M, C, ld_x, 0,
+                                                                        rpb, scratch);
+  DTF_CHECK(cudaGetLastError());
+  const float unbias = (unbiased_moving_var && M > 1) ? (float)M / (float)(M - 1) : 1.f;
+  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(scratch, gamma, beta, 1.f / (float)M, unbias, eps, decay,
+                                                           update_moving, moving_mean, moving_var, coef, coef + C,
+                                                           coef + 2 * C, coef + 3 * C, C);
+  DTF_CHECK(cudaGetLastError());
+  const long long total4 = M * (C / 4);
+  affine_act_kernel<<<ew_grid(total4), 256, 0, stream>>>(x, coef, coef + C, relu, total4, C / 4, ld_x, ld_y, y);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_bn_forward_train(const float* x, long long M, int C, int ld_x, const float* gamma,
+                                    const float* beta, float eps, float decay, int update_moving,
+                                    int unbiased_moving_var, float* moving_mean, float* moving_var, int relu,
+                                    float* scratch, float* coef, float* y, int ld_y, void* stream_) {
+  return bn_forward_train_impl(x, M, C, ld_x, gamma, beta, eps, decay, update_moving, unbiased_moving_var,
+                               moving_mean, moving_var, relu, scratch, coef, y, ld_y,
+                               reinterpret_cast<cudaStream_t>(stream_));
+}
+
 extern "C" int dtf_bn_eval_affine(const float* gamma, const float* beta, const float* moving_mean,
                                   const float* moving_var, float eps, float* scale, float* shift, int C,
                                   void* stream_) {

@@ -143,6 +143,14 @@ def linear(x, w, bias, relu):
 # ---------------------------------------------------------------------------------------------------
 # batch norm
 # ---------------------------------------------------------------------------------------------------
+class _BnTrainSpec:
+    """Arguments of a training-mode BN whose statistics are still to be computed."""
+
+    def __init__(self, mm, mv, eps, decay, update_moving, unbiased):
+        self.mm, self.mv, self.eps, self.decay = mm, mv, eps, decay
+        self.update_moving, self.unbiased = update_moving, unbiased
+
+
 class BnCoef:
     """Per-channel (scale, shift, mean, invstd) of one batch-norm application."""
 
@@ -214,8 +222,19 @@ class _BnApplyFn(torch.autograd.Function):
         c = x.shape[-1]
         m = x.numel() // c
         y = torch.empty_like(x)
-        nat.check(nat.lib().dtf_affine_act(_p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m), c, c, c,
-                                           _p(y), nat.stream_ptr()), "dtf_affine_act")
+        if isinstance(coef, _BnTrainSpec):
+            # statistics, moving-average update and apply in one native call
+            sp = coef
+            buf = torch.empty(4 * c, dtype=torch.float32, device=x.device)
+            scratch = torch.empty(2 * c, dtype=torch.float32, device=x.device)
+            nat.check(nat.lib().dtf_bn_forward_train(_p(x), C.c_longlong(m), c, c, _p(gamma), _p(beta),
+                                                     C.c_float(sp.eps), C.c_float(sp.decay), int(sp.update_moving),
+                                                     int(sp.unbiased), _p(sp.mm), _p(sp.mv), int(relu), _p(scratch),
+                                                     _p(buf), _p(y), c, nat.stream_ptr()), "dtf_bn_forward_train")
+            coef = BnCoef(buf[:c], buf[c:2 * c], buf[2 * c:3 * c], buf[3 * c:], True)
+        else:
+            nat.check(nat.lib().dtf_affine_act(_p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m), c, c,
+                                               c, _p(y), nat.stream_ptr()), "dtf_affine_act")
         ctx.save_for_backward(x)
         ctx.coef, ctx.relu = coef, relu
         ctx.has = (gamma is not None, beta is not None)
@@ -236,7 +255,8 @@ def batch_norm(x, gamma, beta, mm, mv, training, decay, eps, relu, update_moving
     x4 = x4.contiguous()
     count = x4.numel() // c
     if training and stats is None:
-        stats = bn_stats(x4)
+        y = _BnApplyFn.apply(x4, gamma, beta, _BnTrainSpec(mm, mv, eps, decay, update_moving, unbiased), bool(relu))
+        return y.reshape(shape)
     coef = bn_prepare(stats, gamma, beta, mm, mv, count, eps, decay, training, update_moving, unbiased)
     if not training:
         coef.mean_eval = mm

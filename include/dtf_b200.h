@@ -91,6 +91,11 @@ int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, l
                     float decay, int update_moving, int unbiased_moving_var, float* moving_mean,
                     float* moving_var, float* scale, float* shift, float* mean_out, float* invstd_out, int C,
                     void* stream);
+/* Training-mode forward in one call (stats -> finalize -> apply).  scratch: 2*C floats (zeroed by the call);
+ * coef: 4*C floats out = scale | shift | mean | invstd (kept for the backward kernels). */
+int dtf_bn_forward_train(const float* x, long long M, int C, int ld_x, const float* gamma, const float* beta,
+                         float eps, float decay, int update_moving, int unbiased_moving_var, float* moving_mean,
+                         float* moving_var, int relu, float* scratch, float* coef, float* y, int ld_y, void* stream);
 int dtf_bn_eval_affine(const float* gamma, const float* beta, const float* moving_mean, const float* moving_var,
                        float eps, float* scale, float* shift, int C, void* stream);
 /* y = act(x*scale + shift) */
