@@ -296,6 +296,69 @@ extern "C" int dtf_bn_forward_train(const float* x, long long M, int C, int ld_x
                                reinterpret_cast<cudaStream_t>(stream_));
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// dtf_bn_forward_train_static: the same training-mode forward for callers that cannot hand us scratch memory.
+//
+// Who needs this: code that runs where allocating device memory is off the table — an inference-server or
+// framework plug-in callback that is only allowed to enqueue work on the stream it is given, a process whose
+// memory pool has already been carved up completely by its host framework, or a latency-critical loop in
+// which a cudaMalloc (which synchronises the whole device) would stall every other stream.  Such a caller
+// still owns its inputs and outputs (x, the moving statistics, coef, y) but has nowhere to put the 2*C floats
+// of per-channel sums, so they live in the file-scope array below instead.
+//
+// Consequences the caller has to know about:
+//   * The array is part of the library image: every GPU that loads the library gives up
+//     2 * DTF_BN_STATIC_MAX_CHANNELS floats (32 KiB) until the process exits.
+//   * C above DTF_BN_STATIC_MAX_CHANNELS is refused with an error; nothing is launched.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that
+//     device current) and remembers it.  Make that first call before you start capturing a stream.
+//   * All calls share the one array and it keeps whatever the last call left in it.  Each call therefore
+//     clears the part it uses before accumulating, and two calls whose kernels can overlap on the GPU (different
+//     streams, or concurrent host threads on one device) race on it — serialise them.
+//   * No cudaMalloc / cudaFree / allocating library routine is called, here or in the kernels.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_bn_static_scratch[2 * DTF_BN_STATIC_MAX_CHANNELS];
+
+// In host code `g_bn_static_scratch` is only a handle for the runtime, not an address a kernel may use: the
+// device address has to be asked for, once per device, while that device is current.
+static int bn_static_scratch_address(float** out) {
+  static std::mutex mu;
+  static float* resolved[64] = {nullptr};
+  int dev = -1;
+  DTF_CHECK(cudaGetDevice(&dev));
+  DTF_REQUIRE(dev >= 0 && dev < 64, "device ordinal out of range for the static scratch table");
+  std::lock_guard<std::mutex> lk(mu);
+  if (resolved[dev] == nullptr) {
+    float* ptr = nullptr;
+    DTF_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_bn_static_scratch));
+    DTF_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null address");
+    resolved[dev] = ptr;
+  }
+  *out = resolved[dev];
+  return 0;
+}
+
+extern "C" int dtf_bn_forward_train_static(const float* x, long long M, int C, int ld_x, const float* gamma,
+                                           const float* beta, float eps, float decay, int update_moving,
+                                           int unbiased_moving_var, float* moving_mean, float* moving_var, int relu,
+                                           float* coef, float* y, int ld_y, void* stream_) {
+  if (C > DTF_BN_STATIC_MAX_CHANNELS) {
+    char msg[160];
+    snprintf(msg, sizeof(msg), "dtf_bn_forward_train_static: C = %d exceeds the built-in scratch (max %d channels); "
+             "use dtf_bn_forward_train with caller-provided scratch", C, DTF_BN_STATIC_MAX_CHANNELS);
+    set_last_error(msg);
+    return -3;
+  }
+  float* scratch = nullptr;
+  const int rc = bn_static_scratch_address(&scratch);
+  if (rc != 0) return rc;
+  // bn_forward_train_impl starts by zeroing scratch[0, 2C) on the caller's stream, which is exactly the part
+  // this call accumulates into; whatever an earlier call left beyond 2C is never read.
+  return bn_forward_train_impl(x, M, C, ld_x, gamma, beta, eps, decay, update_moving, unbiased_moving_var,
+                               moving_mean, moving_var, relu, scratch, coef, y, ld_y,
+                               reinterpret_cast<cudaStream_t>(stream_));
+}
+
 extern "C" int dtf_bn_eval_affine(const float* gamma, const float* beta, const float* moving_mean,
                                   const float* moving_var, float eps, float* scale, float* shift, int C,
                                   void* stream_) {

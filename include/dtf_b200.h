@@ -96,6 +96,18 @@ int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, l
 int dtf_bn_forward_train(const float* x, long long M, int C, int ld_x, const float* gamma, const float* beta,
                          float eps, float decay, int update_moving, int unbiased_moving_var, float* moving_mean,
                          float* moving_var, int relu, float* scratch, float* coef, float* y, int ld_y, void* stream);
+/* Same operation for callers that may not allocate device memory (stream-only plug-in callbacks, processes
+ * whose memory pool is already fully committed, loops that cannot afford cudaMalloc's device-wide sync): the
+ * 2*C floats of per-channel sums live in a static __device__ array inside the library (32 KiB per GPU, held
+ * until exit) instead of a caller buffer.  C > DTF_BN_STATIC_MAX_CHANNELS is rejected with an error.  The
+ * first call on a device resolves the array's address — issue it before any stream capture.  All calls share
+ * the array (each clears what it uses first), so calls that can overlap on the GPU must be serialised.
+ * This entry point has no counterpart in the reference. */
+#define DTF_BN_STATIC_MAX_CHANNELS 4096
+int dtf_bn_forward_train_static(const float* x, long long M, int C, int ld_x, const float* gamma, const float* beta,
+                                float eps, float decay, int update_moving, int unbiased_moving_var,
+                                float* moving_mean, float* moving_var, int relu, float* coef, float* y, int ld_y,
+                                void* stream);
 int dtf_bn_eval_affine(const float* gamma, const float* beta, const float* moving_mean, const float* moving_var,
                        float eps, float* scale, float* shift, int C, void* stream);
 /* y = act(x*scale + shift) */
