@@ -31,7 +31,9 @@ constexpr int NUM_PRODUCERS = 256;   // warps 4..11
 constexpr int NUM_THREADS = 128 + NUM_PRODUCERS + 32;
 constexpr int PRODUCER_T0 = 128;
 constexpr int MMA_WARP = (128 + NUM_PRODUCERS) / 32;
-constexpr int ROWS_PER_THREAD = BM * 8 / NUM_PRODUCERS;   // 4
+constexpr int PRODUCER_GROUPS = 4;
+constexpr int GROUP_THREADS = NUM_PRODUCERS / PRODUCER_GROUPS;   // 64
+constexpr int ROWS_PER_THREAD = BM * 8 / GROUP_THREADS;   // 16
 
 struct GemmCfg {
   int BN;          // UMMA N (multiple of 16, <= 256)
@@ -41,11 +43,19 @@ struct GemmCfg {
   int tmem_cols;   // power of two >= 2*BN
   int M;
   int Ktot;
+  int active_groups;   // producer groups in use: min(PRODUCER_GROUPS, stages)
   int all_live;    // every k-block touches at least one in-range tap
   int vec_out;     // 16-byte stores allowed
   int vec_res;
-  FastDiv d_ohow, d_ow, d_c, d_s;
+  FastDiv d_ohow, d_ow, d_c, d_s, d_divh, d_divw;
 };
+
+// Optional timeline trace (debug / profiling aid): when armed through dtf_debug_set_trace, CTA 0 stamps
+// globaltimer-free SM clocks at the pipeline hand-offs of its first tile into a caller buffer.
+__device__ long long* g_trace = nullptr;
+__device__ __forceinline__ void trace_stamp(int slot) {
+  if (g_trace != nullptr && blockIdx.x == 0 && slot < 4096) g_trace[slot] = clock64();
+}
 
 __device__ __forceinline__ bool tap_live_1d(int r, int a, int b, int c, int div, int O, int srcDim) {
   const int lo = b + r * c;
@@ -86,15 +96,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* csum = reinterpret_cast<float*>(tmem_slot + 4);   // [256]
   float* csq = csum + 256;                                 // [256]
+  int4* row_table = reinterpret_cast<int4*>(csq + 256);    // [PRODUCER_GROUPS][BM]
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
+  if (tid == 0) trace_stamp(3);
 
   if (warp == MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < stages; ++i) {
-        mbar_init(&full_bar[i], NUM_PRODUCERS);
+        mbar_init(&full_bar[i], GROUP_THREADS);
         mbar_init(&empty_bar[i], 1);
       }
       for (int i = 0; i < 2; ++i) {
@@ -116,114 +128,140 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) trace_stamp(4);
 
   const int num_tiles = cfg.m_tiles * cfg.n_tiles;
 
   if (warp >= 4 && warp < MMA_WARP) {
     // =========================== producers =================================================
-    // Thread pt owns 16-byte chunk j of rows rbase + 32*i.  Loads for k-block n+1 are issued before
-    // the stores of k-block n, so global latency overlaps the smem/barrier traffic.
+    // Four groups of two warps; group g owns every 4th live k-block (sequence number q with q % 4 == g), so
+    // four k-blocks are being gathered at any time.  Inside a group the order is strictly
+    //   wait(slot free) -> TMA(B) + 16 x LDG.128 per thread -> [BN-apply + ReLU] -> STS -> proxy fence -> arrive.
+    // The fence (MEMBAR + FENCE.VIEW.ASYNC) waits for *all* of the thread's outstanding memory operations, so a
+    // thread must not have loads of a later k-block in flight when it fences; overlap comes from the other groups.
+    // The gather is instruction-bound, so everything that depends only on the output pixel (row) is computed
+    // once per tile into a per-group shared-memory table {element offset of the row's origin pixel, ih0, iw0};
+    // per k-block a row then costs one LDS.128, two adds, two unsigned compares, one 64-bit add and the LDG.
     const int pt = tid - PRODUCER_T0;
-    const int j = pt & 7;
-    const int rbase = pt >> 3;     // 0..31
+    const int grp = pt >> 6;                 // 0..3
+    const int gt = pt & 63;
+    const int j = gt & 7;
+    const int rgrp = gt >> 3;                // rows rgrp*16 .. rgrp*16+15
     const bool has_aff = p.in_scale != nullptr;
-    int stage = 0; uint32_t phase = 0;
-
-    int hb[ROWS_PER_THREAD], wb[ROWS_PER_THREAD], pixbase[ROWS_PER_THREAD];
-
-    // raw loads only (no dependent math): the affine is applied at store time so that all of a
-    // thread's LDG.128 are in flight together.
-    auto issue_loads = [&](int kb, float4 (&v)[ROWS_PER_THREAD], uint32_t& okmask, float4& sc, float4& sh) {
-      const int k = kb * BK + j * 4;
-      const bool kvalid = k < cfg.Ktot;
-      int c = 0, dh = 0, dw = 0;
-      sc = make_float4(1.f, 1.f, 1.f, 1.f); sh = make_float4(0.f, 0.f, 0.f, 0.f);
-      okmask = 0;
-      if (kvalid) {
-        const int tap = (int)fdiv((uint32_t)k, cfg.d_c);
-        c = k - tap * p.srcC;
-        const int r = (int)fdiv((uint32_t)tap, cfg.d_s);
-        const int s = tap - r * p.S;
-        dh = r * p.c_h;
-        dw = s * p.c_w;
-        if (has_aff) {
-          sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
-          sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-        int ih = hb[i] + dh, iw = wb[i] + dw;
-        bool valid = kvalid && ih >= 0 && iw >= 0;
-        if (p.div_h > 1) { valid = valid && (ih % p.div_h == 0); ih /= p.div_h; }
-        if (p.div_w > 1) { valid = valid && (iw % p.div_w == 0); iw /= p.div_w; }
-        valid = valid && ih < p.srcH && iw < p.srcW;
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid) {
-          const size_t off = (size_t)(pixbase[i] + ih * p.srcW + iw) * (size_t)p.src_ld + c;
-          x = __ldg(reinterpret_cast<const float4*>(p.src + off));
-          okmask |= 1u << i;
-        }
-        v[i] = x;
-      }
-    };
-    auto next_live = [&](int kb) {
-      while (kb < cfg.num_kb && !kb_live(p, cfg, kb)) ++kb;
-      return kb;
-    };
+    const bool div1 = (p.div_h == 1) && (p.div_w == 1);
+    int4* rtab = row_table + grp * BM;
+    int q = 0, q_grp = 0, stage = 0; uint32_t phase = 0;
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
       const int m0 = mt * BM, n0 = nt * BN;
+      // ---- per-tile row table (two rows per thread) ----
+      named_bar_sync(2 + grp, GROUP_THREADS);          // everyone is done with the previous tile's table
 #pragma unroll
-      for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-        const int m = m0 + rbase + 32 * i;
+      for (int rr = 0; rr < 2; ++rr) {
+        const int row = gt * 2 + rr;
+        const int m = m0 + row;
+        int4 e = make_int4(0, -(1 << 24), -(1 << 24), 0);
         if (m < cfg.M) {
           const int img = (int)fdiv((uint32_t)m, cfg.d_ohow);
           const int rem = m - img * p.OH * p.OW;
           const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
           const int ow = rem - oh * p.OW;
-          hb[i] = oh * p.a_h + p.b_h;
-          wb[i] = ow * p.a_w + p.b_w;
-          pixbase[i] = img * p.srcH * p.srcW;
-        } else {
-          hb[i] = -(1 << 28); wb[i] = 0; pixbase[i] = 0;
+          e.y = oh * p.a_h + p.b_h;
+          e.z = ow * p.a_w + p.b_w;
+          if (div1) e.x = ((img * p.srcH + e.y) * p.srcW + e.z) * p.src_ld;   // may be "negative": only used when valid
+          else e.x = img * p.srcH * p.srcW;                                 // pixel index of the image origin
         }
+        rtab[row] = e;
       }
-      float4 cur[ROWS_PER_THREAD], nxt[ROWS_PER_THREAD];
-      uint32_t cur_ok = 0, nxt_ok = 0;
-      float4 cur_sc, cur_sh, nxt_sc, nxt_sh;
-      int kb = next_live(0);
-      if (kb < cfg.num_kb) issue_loads(kb, cur, cur_ok, cur_sc, cur_sh);
-      while (kb < cfg.num_kb) {
-        const int nkb = next_live(kb + 1);
-        if (nkb < cfg.num_kb) issue_loads(nkb, nxt, nxt_ok, nxt_sc, nxt_sh);
-        mbar_wait(&empty_bar[stage], phase ^ 1u);
-        uint8_t* a_stage = sA + stage * A_STAGE_BYTES;
-        if (pt == 0) {
-          mbar_expect_tx(&full_bar[stage], (uint32_t)b_stage_bytes);
-          tma_load_2d(sB + stage * b_stage_bytes, &tmapB, &full_bar[stage], kb * BK, n0);
-        }
-#pragma unroll
-        for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-          const int row = rbase + 32 * i;
-          float4 x = cur[i];
-          if (has_aff && ((cur_ok >> i) & 1u)) {
-            x.x = fmaf(x.x, cur_sc.x, cur_sh.x); x.y = fmaf(x.y, cur_sc.y, cur_sh.y);
-            x.z = fmaf(x.z, cur_sc.z, cur_sh.z); x.w = fmaf(x.w, cur_sc.w, cur_sh.w);
-            if (p.in_relu) {
-              x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+      named_bar_sync(2 + grp, GROUP_THREADS);
+      const bool tr = (pt == 0) && (tile == (int)blockIdx.x);
+      if (tr) trace_stamp(0);
+      for (int kb = 0; kb < cfg.num_kb; ++kb) {
+        if (!kb_live(p, cfg, kb)) continue;
+        // A group may only run one ring-phase ahead of the consumer (mbarrier waits see a single parity bit),
+        // which holds as long as there are at least as many stages as active groups.
+        if (q_grp == grp) {
+          if (tr) trace_stamp(16 + 8 * (q >> 2) + 0);
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (tr) trace_stamp(16 + 8 * (q >> 2) + 1);
+          uint8_t* a_stage = sA + stage * A_STAGE_BYTES;
+          if (gt == 0) {
+            mbar_expect_tx(&full_bar[stage], (uint32_t)b_stage_bytes);
+            tma_load_2d(sB + stage * b_stage_bytes, &tmapB, &full_bar[stage], kb * BK, n0);
+          }
+          const int k = kb * BK + j * 4;
+          const bool kvalid = k < cfg.Ktot;
+          int c = 0, dh = -(1 << 24), dw = 0;
+          float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (kvalid) {
+            const int tap = (int)fdiv((uint32_t)k, cfg.d_c);
+            c = k - tap * p.srcC;
+            const int r = (int)fdiv((uint32_t)tap, cfg.d_s);
+            const int s_ = tap - r * p.S;
+            dh = r * p.c_h;
+            dw = s_ * p.c_w;
+            if (has_aff) {
+              sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
+              sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
             }
           }
-          *reinterpret_cast<float4*>(a_stage + row * 128 + ((j ^ (row & 7)) << 4)) = x;
-        }
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[stage]);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
+          float4 v[ROWS_PER_THREAD];
+          uint32_t okmask = 0;
+          const int4* rt = rtab + rgrp * ROWS_PER_THREAD;
+          if (div1) {
+            const int tap_off = (dh * p.srcW + dw) * p.src_ld + c;
+            const float* srcc = p.src + tap_off;
 #pragma unroll
-        for (int i = 0; i < ROWS_PER_THREAD; ++i) cur[i] = nxt[i];
-        cur_ok = nxt_ok; cur_sc = nxt_sc; cur_sh = nxt_sh;
-        kb = nkb;
+            for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+              const int4 e = rt[i];
+              const bool valid = (unsigned)(e.y + dh) < (unsigned)p.srcH && (unsigned)(e.z + dw) < (unsigned)p.srcW;
+              float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (valid) {
+                x = __ldg(reinterpret_cast<const float4*>(srcc + e.x));
+                okmask |= 1u << i;
+              }
+              v[i] = x;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+              const int4 e = rt[i];
+              const int ihn = e.y + dh, iwn = e.z + dw;
+              const int ih = (int)fdiv((uint32_t)(ihn < 0 ? 0 : ihn), cfg.d_divh);
+              const int iw = (int)fdiv((uint32_t)(iwn < 0 ? 0 : iwn), cfg.d_divw);
+              const bool valid = ihn >= 0 && iwn >= 0 && ih * p.div_h == ihn && iw * p.div_w == iwn &&
+                                 ih < p.srcH && iw < p.srcW;
+              float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (valid) {
+                const size_t off = (size_t)(e.x + ih * p.srcW + iw) * (size_t)p.src_ld + c;
+                x = __ldg(reinterpret_cast<const float4*>(p.src + off));
+                okmask |= 1u << i;
+              }
+              v[i] = x;
+            }
+          }
+          if (tr) trace_stamp(16 + 8 * (q >> 2) + 2);
+#pragma unroll
+          for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+            const int row = rgrp * ROWS_PER_THREAD + i;
+            float4 x = v[i];
+            if (has_aff && ((okmask >> i) & 1u)) {
+              x.x = fmaf(x.x, sc.x, sh.x); x.y = fmaf(x.y, sc.y, sh.y);
+              x.z = fmaf(x.z, sc.z, sh.z); x.w = fmaf(x.w, sc.w, sh.w);
+              if (p.in_relu) {
+                x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+              }
+            }
+            *reinterpret_cast<float4*>(a_stage + row * 128 + ((j ^ (row & 7)) << 4)) = x;
+          }
+          fence_proxy_async_smem();
+          if (tr) trace_stamp(16 + 8 * (q >> 2) + 3);
+          mbar_arrive(&full_bar[stage]);
+        }
+        ++q;
+        if (++q_grp == cfg.active_groups) q_grp = 0;
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == MMA_WARP) {
@@ -238,9 +276,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
       uint32_t accumulate = 0;
+      int seq = 0;
+      const bool tr = (lane == 0) && (local == 0);
       for (int kb = 0; kb < cfg.num_kb; ++kb) {
         if (!kb_live(p, cfg, kb)) continue;
         mbar_wait(&full_bar[stage], phase);
+        if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 4);
         tc_fence_after();
         if (lane == 0) {
           const uint64_t adesc = make_desc_k_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
@@ -251,9 +292,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
             accumulate = 1;
           }
           umma_commit(&empty_bar[stage]);
+          if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 5);
         }
         __syncwarp();
         accumulate = 1;
+        ++seq;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
       if (lane == 0) umma_commit(&tfull_bar[acc]);
@@ -269,6 +312,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       const int acc = local & 1;
       const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
       mbar_wait(&tfull_bar[acc], acc_phase);
+      if (tid == 0 && local == 0) trace_stamp(1);
       tc_fence_after();
       const int m = m0 + tid;
       const bool mvalid = m < cfg.M;
@@ -341,6 +385,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
+      if (tid == 0 && local == 0) trace_stamp(2);
       if (do_stats && cfg.n_tiles > 1) {
         // several n-tiles share the smem accumulators: flush after every tile
         named_bar_sync(1, 128);
@@ -417,6 +462,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(p.src) & 15) == 0, "source must be 16-byte aligned");
   DTF_REQUIRE(p.div_h >= 1 && p.div_w >= 1 && p.a_h >= 1 && p.a_w >= 1, "bad index map");
   DTF_REQUIRE(p.Nout >= 1 && p.R >= 1 && p.S >= 1, "bad shape");
+  DTF_REQUIRE((long long)p.N * p.srcH * p.srcW * p.src_ld < (1LL << 31), "source tensor too large for 32-bit offsets");
   if (p.in_scale) DTF_REQUIRE(p.in_shift != nullptr, "in_scale without in_shift");
 
   GemmCfg cfg;
@@ -429,11 +475,13 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.num_kb = ceil_div(cfg.Ktot, BK);
   cfg.tmem_cols = next_pow2_cols(2 * cfg.BN);
   const int stage_bytes = A_STAGE_BYTES + cfg.BN * BK * 4;
-  int stages = (196 * 1024) / stage_bytes;
+  const int fixed_smem = 1024 + 16 * 2 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int4);
+  int stages = (227 * 1024 - fixed_smem) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages > cfg.num_kb + 1) stages = cfg.num_kb + 1;
   if (stages < 2) stages = 2;
   cfg.stages = stages;
+  cfg.active_groups = stages < PRODUCER_GROUPS ? stages : PRODUCER_GROUPS;
   // liveness: every tap reaches at least one in-range source pixel?
   int all_live = 1;
   for (int r = 0; r < p.R && all_live; ++r) {
@@ -449,13 +497,16 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.d_ow = make_fastdiv((uint32_t)p.OW);
   cfg.d_c = make_fastdiv((uint32_t)p.srcC);
   cfg.d_s = make_fastdiv((uint32_t)p.S);
+  cfg.d_divh = make_fastdiv((uint32_t)p.div_h);
+  cfg.d_divw = make_fastdiv((uint32_t)p.div_w);
   cfg.vec_out = (p.out_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
   cfg.vec_res = p.residual && (p.res_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0);
 
   const CUtensorMap* tm = get_tmap_2d_f32_sw128(p.wt, p.Nout, cfg.Ktot, cfg.BN);
   if (!tm) return -2;
 
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + (2 * stages + 4) * sizeof(uint64_t) + 16 + 2 * 256 * 4;
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + (2 * stages + 4) * sizeof(uint64_t) + 16 + 2 * 256 * 4 +
+                      PRODUCER_GROUPS * BM * sizeof(int4);
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -467,6 +518,11 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   const int grid = tiles < num_sms() ? tiles : num_sms();
   conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, p, cfg);
   DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_debug_set_trace(long long* buf) {
+  DTF_CHECK(cudaMemcpyToSymbol(g_trace, &buf, sizeof(buf)));
   return 0;
 }
 

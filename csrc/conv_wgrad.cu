@@ -55,7 +55,7 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
   if (warp == WG_MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < stages; ++i) {
-        mbar_init(&full_bar[i], WG_PRODUCERS);
+        mbar_init(&full_bar[i], WG_PRODUCERS / 2);
         mbar_init(&empty_bar[i], 1);
       }
       for (int i = 0; i < 2; ++i) {
@@ -77,63 +77,20 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
 
   if (warp >= 4 && warp < WG_MMA_WARP) {
     // =========================== producers =================================================
-    // Thread pt owns pixel chunk pc (4 consecutive output pixels) and 4-row chunk rc0 of the A tile
-    // (one filter tap, 4 consecutive input channels), plus up to two 4-row chunks of the dY tile.
+    // Two groups of four warps alternate k-blocks (32 output pixels each): while one group waits for its
+    // global loads the other is transposing / storing.  Within a group the order is strictly
+    //   wait(slot free) -> LDG.128 x (8 + 4*nB) -> 4x4 register transposes -> STS -> proxy fence -> arrive
+    // (the proxy fence drains all of a thread's outstanding memory operations, so a thread never has loads
+    // of a later k-block in flight when it fences).
+    // Thread gt owns pixel chunk pc (4 consecutive output pixels) and 4-row chunks rc0 + 16*i of the A tile
+    // (one filter tap, 4 consecutive input channels each) and of the dY tile.
     const int pt = tid - 128;
-    const int pc = pt & 7;
-    const int rc0 = pt >> 3;      // 0..31
+    const int grp = pt >> 7;      // 0..1
+    const int gt = pt & 127;
+    const int pc = gt & 7;
+    const int rc0 = gt >> 3;      // 0..15
     const bool has_aff = p.in_scale != nullptr;
-    int stage = 0; uint32_t phase = 0;
-
-    bool a_ok = false; int a_c = 0, a_r = 0, a_s = 0;
-    float4 a_sc = make_float4(1.f, 1.f, 1.f, 1.f), a_sh = make_float4(0.f, 0.f, 0.f, 0.f);
-    int n0 = 0;
-
-    auto issue_loads = [&](int kb, float4 (&xa)[4], uint32_t& okmask, float4 (&yb)[2][4]) {
-      const int mbase = kb * WG_BK + pc * 4;
-      okmask = 0;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int m = mbase + q;
-        const bool mok = m < cfg.M;
-        const int mm = mok ? m : 0;
-        const int img = (int)fdiv((uint32_t)mm, cfg.d_ohow);
-        const int rem = mm - img * p.OH * p.OW;
-        const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
-        const int ow = rem - oh * p.OW;
-        const int ih = oh * p.stride_h - p.pad_h + a_r;
-        const int iw = ow * p.stride_w - p.pad_w + a_s;
-        const bool valid = a_ok && mok && ih >= 0 && iw >= 0 && ih < p.srcH && iw < p.srcW;
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid) {
-          const size_t off = (size_t)((img * p.srcH + ih) * p.srcW + iw) * (size_t)p.src_ld + a_c;
-          x = __ldg(reinterpret_cast<const float4*>(p.src + off));
-          okmask |= 1u << q;
-        }
-        xa[q] = x;
-      }
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int rc = rc0 + 32 * i;
-        const int co = n0 + rc * 4;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (rc * 4 < BN && (mbase + q) < cfg.M && co < p.Nout) {
-            const float* src = p.dy + (size_t)(mbase + q) * p.dy_ld + co;
-            if (cfg.vec_dy && co + 3 < p.Nout) {
-              t = __ldg(reinterpret_cast<const float4*>(src));
-            } else {
-              t.x = __ldg(src);
-              if (co + 1 < p.Nout) t.y = __ldg(src + 1);
-              if (co + 2 < p.Nout) t.z = __ldg(src + 2);
-              if (co + 3 < p.Nout) t.w = __ldg(src + 3);
-            }
-          }
-          yb[i][q] = t;
-        }
-      }
-    };
+    int q = 0, stage = 0; uint32_t phase = 0;
 
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int split = unit % cfg.splits;
@@ -142,80 +99,143 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
       const int kb0 = split * cfg.kb_per_split;
       int kb1 = kb0 + cfg.kb_per_split;
       if (kb1 > cfg.kb_total) kb1 = cfg.kb_total;
-      {
-        const int k = mt * WG_BM + rc0 * 4;
-        a_ok = k < cfg.Ktot;
-        const int tap = a_ok ? (int)fdiv((uint32_t)k, cfg.d_c) : 0;
-        a_c = a_ok ? k - tap * p.srcC : 0;
-        a_r = (int)fdiv((uint32_t)tap, cfg.d_s);
-        a_s = tap - a_r * p.S;
-        a_sc = make_float4(1.f, 1.f, 1.f, 1.f);
-        a_sh = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (has_aff && a_ok) {
-          a_sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + a_c));
-          a_sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + a_c));
+      bool a_ok[2]; int a_c[2], a_r[2], a_s[2], a_off[2];
+      float4 a_sc[2], a_sh[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int k = mt * WG_BM + (rc0 + 16 * i) * 4;
+        a_ok[i] = k < cfg.Ktot;
+        const int tap = a_ok[i] ? (int)fdiv((uint32_t)k, cfg.d_c) : 0;
+        a_c[i] = a_ok[i] ? k - tap * p.srcC : 0;
+        a_r[i] = (int)fdiv((uint32_t)tap, cfg.d_s);
+        a_s[i] = tap - a_r[i] * p.S;
+        a_off[i] = (a_r[i] * p.srcW + a_s[i]) * p.src_ld + a_c[i];
+        a_sc[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+        a_sh[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (has_aff && a_ok[i]) {
+          a_sc[i] = __ldg(reinterpret_cast<const float4*>(p.in_scale + a_c[i]));
+          a_sh[i] = __ldg(reinterpret_cast<const float4*>(p.in_shift + a_c[i]));
         }
       }
-      n0 = nt * BN;
-      float4 xa[4], xn[4], yb[2][4], yn[2][4];
-      uint32_t ok_cur = 0, ok_nxt = 0;
-      if (kb0 < kb1) issue_loads(kb0, xa, ok_cur, yb);
+      const int n0 = nt * BN;
       for (int kb = kb0; kb < kb1; ++kb) {
-        if (kb + 1 < kb1) issue_loads(kb + 1, xn, ok_nxt, yn);
-        mbar_wait(&empty_bar[stage], phase ^ 1u);
-        uint8_t* a_stage = sA + stage * WG_A_STAGE_BYTES;
-        uint8_t* b_stage = sB + stage * b_stage_bytes;
-        if (has_aff) {
+        if ((q & 1) == grp) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* a_stage = sA + stage * WG_A_STAGE_BYTES;
+          uint8_t* b_stage = sB + stage * b_stage_bytes;
+          // the four pixels of this thread's chunk: origin offset (elements) and origin coordinates
+          int pixoff[4], ihb[4], iwb[4];
+          bool mok[4];
+          const int mbase = kb * WG_BK + pc * 4;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            if ((ok_cur >> q) & 1u) {
-              float4 x = xa[q];
-              x.x = fmaf(x.x, a_sc.x, a_sh.x); x.y = fmaf(x.y, a_sc.y, a_sh.y);
-              x.z = fmaf(x.z, a_sc.z, a_sh.z); x.w = fmaf(x.w, a_sc.w, a_sh.w);
-              if (p.in_relu) {
-                x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+          for (int qq = 0; qq < 4; ++qq) {
+            const int m = mbase + qq;
+            mok[qq] = m < cfg.M;
+            const int mm = mok[qq] ? m : 0;
+            const int img = (int)fdiv((uint32_t)mm, cfg.d_ohow);
+            const int rem = mm - img * p.OH * p.OW;
+            const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
+            const int ow = rem - oh * p.OW;
+            ihb[qq] = mok[qq] ? oh * p.stride_h - p.pad_h : -(1 << 24);
+            iwb[qq] = ow * p.stride_w - p.pad_w;
+            pixoff[qq] = ((img * p.srcH + ihb[qq]) * p.srcW + iwb[qq]) * p.src_ld;
+          }
+          float4 xa[2][4];
+          uint32_t okm = 0;
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            if (a_ok[i]) {                      // rows beyond R*S*C are never read back: skip them entirely
+              const float* srct = p.src + a_off[i];
+#pragma unroll
+              for (int qq = 0; qq < 4; ++qq) {
+                const bool valid = (unsigned)(ihb[qq] + a_r[i]) < (unsigned)p.srcH &&
+                                   (unsigned)(iwb[qq] + a_s[i]) < (unsigned)p.srcW;
+                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (valid) {
+                  x = __ldg(reinterpret_cast<const float4*>(srct + pixoff[qq]));
+                  okm |= 1u << (i * 4 + qq);
+                }
+                xa[i][qq] = x;
               }
-              xa[q] = x;
             }
           }
-        }
-        {
-          // 4x4 transpose in registers: row e <- channel e of the 4 pixels
-          const int row0 = rc0 * 4;
-          const float4 t0 = make_float4(xa[0].x, xa[1].x, xa[2].x, xa[3].x);
-          const float4 t1 = make_float4(xa[0].y, xa[1].y, xa[2].y, xa[3].y);
-          const float4 t2 = make_float4(xa[0].z, xa[1].z, xa[2].z, xa[3].z);
-          const float4 t3 = make_float4(xa[0].w, xa[1].w, xa[2].w, xa[3].w);
-          *reinterpret_cast<float4*>(a_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
-          *reinterpret_cast<float4*>(a_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
-          *reinterpret_cast<float4*>(a_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
-          *reinterpret_cast<float4*>(a_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
-        }
+          // dY rows (output channels): up to 4 chunks of 4 channels per thread, two at a time
+          for (int ib = 0; ib < 4; ib += 2) {
+            float4 yb[2][4];
+            bool any = false;
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int rc = rc0 + 32 * i;
-          if (rc * 4 < BN) {
-            const int row0 = rc * 4;
-            const float4 t0 = make_float4(yb[i][0].x, yb[i][1].x, yb[i][2].x, yb[i][3].x);
-            const float4 t1 = make_float4(yb[i][0].y, yb[i][1].y, yb[i][2].y, yb[i][3].y);
-            const float4 t2 = make_float4(yb[i][0].z, yb[i][1].z, yb[i][2].z, yb[i][3].z);
-            const float4 t3 = make_float4(yb[i][0].w, yb[i][1].w, yb[i][2].w, yb[i][3].w);
-            *reinterpret_cast<float4*>(b_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
-            *reinterpret_cast<float4*>(b_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
-            *reinterpret_cast<float4*>(b_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
-            *reinterpret_cast<float4*>(b_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+            for (int i = 0; i < 2; ++i) {
+              const int rc = rc0 + 16 * (ib + i);
+              const int co = n0 + rc * 4;
+              const bool rowok = rc * 4 < BN;
+              any = any || rowok;
+#pragma unroll
+              for (int qq = 0; qq < 4; ++qq) {
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (rowok && mok[qq] && co < p.Nout) {
+                  const float* src = p.dy + (size_t)(mbase + qq) * p.dy_ld + co;
+                  if (cfg.vec_dy && co + 3 < p.Nout) {
+                    t = __ldg(reinterpret_cast<const float4*>(src));
+                  } else {
+                    t.x = __ldg(src);
+                    if (co + 1 < p.Nout) t.y = __ldg(src + 1);
+                    if (co + 2 < p.Nout) t.z = __ldg(src + 2);
+                    if (co + 3 < p.Nout) t.w = __ldg(src + 3);
+                  }
+                }
+                yb[i][qq] = t;
+              }
+            }
+            if (!any) break;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              const int rc = rc0 + 16 * (ib + i);
+              if (rc * 4 < BN) {
+                const int row0 = rc * 4;
+                const float4 t0 = make_float4(yb[i][0].x, yb[i][1].x, yb[i][2].x, yb[i][3].x);
+                const float4 t1 = make_float4(yb[i][0].y, yb[i][1].y, yb[i][2].y, yb[i][3].y);
+                const float4 t2 = make_float4(yb[i][0].z, yb[i][1].z, yb[i][2].z, yb[i][3].z);
+                const float4 t3 = make_float4(yb[i][0].w, yb[i][1].w, yb[i][2].w, yb[i][3].w);
+                *reinterpret_cast<float4*>(b_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
+                *reinterpret_cast<float4*>(b_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
+                *reinterpret_cast<float4*>(b_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
+                *reinterpret_cast<float4*>(b_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+              }
+            }
           }
-        }
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[stage]);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          xa[q] = xn[q];
-          yb[0][q] = yn[0][q];
-          yb[1][q] = yn[1][q];
+          for (int i = 0; i < 2; ++i) {
+            if (!a_ok[i]) continue;
+            if (has_aff) {
+#pragma unroll
+              for (int qq = 0; qq < 4; ++qq) {
+                if ((okm >> (i * 4 + qq)) & 1u) {
+                  float4 x = xa[i][qq];
+                  x.x = fmaf(x.x, a_sc[i].x, a_sh[i].x); x.y = fmaf(x.y, a_sc[i].y, a_sh[i].y);
+                  x.z = fmaf(x.z, a_sc[i].z, a_sh[i].z); x.w = fmaf(x.w, a_sc[i].w, a_sh[i].w);
+                  if (p.in_relu) {
+                    x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+                  }
+                  xa[i][qq] = x;
+                }
+              }
+            }
+            // 4x4 transpose in registers: row e <- channel e of the 4 pixels
+            const int row0 = (rc0 + 16 * i) * 4;
+            const float4 t0 = make_float4(xa[i][0].x, xa[i][1].x, xa[i][2].x, xa[i][3].x);
+            const float4 t1 = make_float4(xa[i][0].y, xa[i][1].y, xa[i][2].y, xa[i][3].y);
+            const float4 t2 = make_float4(xa[i][0].z, xa[i][1].z, xa[i][2].z, xa[i][3].z);
+            const float4 t3 = make_float4(xa[i][0].w, xa[i][1].w, xa[i][2].w, xa[i][3].w);
+            *reinterpret_cast<float4*>(a_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
+            *reinterpret_cast<float4*>(a_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
+            *reinterpret_cast<float4*>(a_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
+            *reinterpret_cast<float4*>(a_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+          }
+          fence_proxy_async_smem();
+          mbar_arrive(&full_bar[stage]);
         }
-        ok_cur = ok_nxt;
+        ++q;
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == WG_MMA_WARP) {
@@ -309,6 +329,7 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   const dtf_conv_wgrad_params& p = *pp;
   DTF_REQUIRE(p.srcC % 4 == 0 && p.src_ld % 4 == 0, "source channels / pitch must be multiples of 4");
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(p.src) & 15) == 0, "source must be 16-byte aligned");
+  DTF_REQUIRE((long long)p.N * p.srcH * p.srcW * p.src_ld < (1LL << 31), "source tensor too large for 32-bit offsets");
   WgradCfg cfg;
   cfg.Ktot = p.R * p.S * p.srcC;
   cfg.M = p.N * p.OH * p.OW;
@@ -328,9 +349,9 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   while (tc < 2 * cfg.BN) tc <<= 1;
   cfg.tmem_cols = tc;
   const int stage_bytes = WG_A_STAGE_BYTES + cfg.BN * WG_BK * 4;
-  int stages = (196 * 1024) / stage_bytes;
+  int stages = (224 * 1024) / stage_bytes;
   if (stages > 6) stages = 6;
-  if (stages < 2) stages = 2;
+  if (stages < 2) stages = 2;     // >= number of producer groups (2): a group runs at most one ring-phase ahead
   cfg.stages = stages;
   cfg.d_ohow = make_fastdiv((uint32_t)(p.OH * p.OW));
   cfg.d_ow = make_fastdiv((uint32_t)p.OW);

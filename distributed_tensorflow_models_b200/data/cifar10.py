@@ -1,0 +1,198 @@
+"""CIFAR-10 input pipeline (role of the five copies of ``cifar10_input.py`` in the reference).
+
+* record format: 1 label byte + 3072 image bytes stored CHW -> HWC uint8 (cnn/cifar10_input.py:68-95);
+  files ``data_batch_{1..5}.bin`` / ``test_batch.bin`` under ``<data_dir>/cifar-10-batches-bin`` (:156-157,223)
+* training distortion (:145-203): random crop to ``image_size`` (24 for the plain CNN, 32 = identity for the
+  others), random left-right flip, ``random_brightness(max_delta=63)``, ``random_contrast(0.2, 1.8)``,
+  ``per_image_standardization``
+* eval (:206-257): centre crop / pad to ``image_size`` + standardisation
+* batching: a background thread keeps a bounded queue of ready batches (the reference's 16 queue-runner
+  threads and ``capacity = 0.4*50000 + 3*batch`` shuffle queue); ``shuffle`` is honoured (the reference forces
+  ``shuffle=False`` in four of five copies, Q9) and every rank reads a disjoint stride of the records when
+  ``world > 1`` (the reference has no sharding; documented deviation).
+
+All augmentation is vectorised torch-on-CPU over the whole batch; output is NHWC float32 in pinned memory
+when CUDA is present so the trainer's H2D copy is asynchronous.
+"""
+from __future__ import annotations
+
+import os
+import queue
+import threading
+from typing import Iterator, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+IMAGE_SIZE = 24                 # cnn/cifar10_input.py:30 (the other models use 32)
+NUM_CLASSES = 10
+NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN = 50000
+NUM_EXAMPLES_PER_EPOCH_FOR_EVAL = 10000
+RECORD_BYTES = 1 + 32 * 32 * 3
+
+
+def data_files(data_dir: str, eval_data: bool) -> List[str]:
+    d = os.path.join(data_dir, "cifar-10-batches-bin")
+    names = ["test_batch.bin"] if eval_data else [f"data_batch_{i}.bin" for i in range(1, 6)]
+    files = [os.path.join(d, n) for n in names]
+    for f in files:
+        if not os.path.exists(f):
+            raise ValueError("Failed to find file: " + f)
+    return files
+
+
+def dataset_available(data_dir: str) -> bool:
+    try:
+        data_files(data_dir, False)
+        return True
+    except ValueError:
+        return False
+
+
+def maybe_download_and_extract(data_dir: str) -> bool:
+    """The reference downloads cifar-10-binary.tar.gz here (cnn/cifar10.py:394-411).  This box has no
+    network: report whether the dataset is present so the caller can fall back to synthetic data."""
+    return dataset_available(data_dir)
+
+
+def read_records(files: List[str]) -> Tuple[np.ndarray, np.ndarray]:
+    """-> (labels int64 [N], images uint8 [N,32,32,3])"""
+    raw = np.concatenate([np.fromfile(f, dtype=np.uint8) for f in files])
+    if raw.size % RECORD_BYTES:
+        raise ValueError("corrupt CIFAR-10 binary file (size is not a multiple of the record length)")
+    rec = raw.reshape(-1, RECORD_BYTES)
+    labels = rec[:, 0].astype(np.int64)
+    images = rec[:, 1:].reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1)
+    return labels, np.ascontiguousarray(images)
+
+
+def per_image_standardization(x: torch.Tensor) -> torch.Tensor:
+    """(x - mean) / max(stddev, 1/sqrt(num_elements)) per image (tf.image.per_image_standardization)."""
+    n = x[0].numel()
+    flat = x.reshape(x.shape[0], -1)
+    mean = flat.mean(1, keepdim=True)
+    std = flat.std(1, unbiased=False, keepdim=True).clamp_min(1.0 / n ** 0.5)
+    return ((flat - mean) / std).reshape(x.shape)
+
+
+def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator) -> torch.Tensor:
+    """uint8 [B,32,32,3] -> float32 [B,image_size,image_size,3] with the training distortions."""
+    b = images_u8.shape[0]
+    x = images_u8.to(torch.float32)
+    if image_size < 32:
+        oy = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+        ox = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+        idx_y = oy[:, None] + torch.arange(image_size)[None, :]
+        idx_x = ox[:, None] + torch.arange(image_size)[None, :]
+        x = x[torch.arange(b)[:, None, None], idx_y[:, :, None], idx_x[:, None, :]]
+    flip = torch.rand(b, generator=gen) < 0.5
+    x = torch.where(flip[:, None, None, None], x.flip(2), x)
+    delta = (torch.rand(b, generator=gen) * 2 - 1) * 63.0
+    x = x + delta[:, None, None, None]
+    factor = 0.2 + torch.rand(b, generator=gen) * 1.6
+    mean = x.mean(dim=(1, 2), keepdim=True)
+    x = (x - mean) * factor[:, None, None, None] + mean
+    return per_image_standardization(x)
+
+
+def center_batch(images_u8: torch.Tensor, image_size: int) -> torch.Tensor:
+    """Eval preprocessing: resize_image_with_crop_or_pad + standardisation (cnn/cifar10_input.py:242-247)."""
+    x = images_u8.to(torch.float32)
+    if image_size < 32:
+        o = (32 - image_size) // 2
+        x = x[:, o:o + image_size, o:o + image_size]
+    elif image_size > 32:
+        p = image_size - 32
+        x = torch.nn.functional.pad(x, (0, 0, p // 2, p - p // 2, p // 2, p - p // 2))
+    return per_image_standardization(x)
+
+
+class _Prefetcher:
+    def __init__(self, make_batch, depth: int):
+        self.q: "queue.Queue" = queue.Queue(maxsize=depth)
+        self.stop = False
+        self.t = threading.Thread(target=self._run, args=(make_batch,), daemon=True)
+        self.t.start()
+
+    def _run(self, make_batch):
+        while not self.stop:
+            item = make_batch()
+            while not self.stop:
+                try:
+                    self.q.put(item, timeout=0.1)
+                    break
+                except queue.Full:
+                    continue
+            if item is None:
+                return
+
+    def get(self):
+        return self.q.get()
+
+    def close(self):
+        self.stop = True
+
+
+class Cifar10Batches:
+    """Iterator of ``(images float32 NHWC, labels int64)`` host batches."""
+
+    def __init__(self, data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, train: bool = True,
+                 shuffle: bool = True, rank: int = 0, world: int = 1, seed: int = 0, prefetch: int = 4,
+                 repeat: bool = True):
+        labels, images = read_records(data_files(data_dir, eval_data=not train))
+        if world > 1 and train:
+            labels, images = labels[rank::world], images[rank::world]
+        self.labels = torch.from_numpy(labels)
+        self.images = torch.from_numpy(images)
+        self.bs, self.size, self.train, self.shuffle, self.repeat = batch_size, image_size, train, shuffle, repeat
+        self.gen = torch.Generator().manual_seed(seed + 7919 * rank)
+        self.pos = 0
+        self.order = self._new_order()
+        self.pin = torch.cuda.is_available()
+        self.pf = _Prefetcher(self._make, prefetch)
+
+    def _new_order(self):
+        n = self.labels.numel()
+        return torch.randperm(n, generator=self.gen) if (self.shuffle and self.train) else torch.arange(n)
+
+    def _make(self):
+        n = self.labels.numel()
+        if self.pos >= n:
+            if not self.repeat:
+                return None
+            self.pos = 0
+            self.order = self._new_order()
+        idx = self.order[self.pos:self.pos + self.bs]
+        if idx.numel() < self.bs and self.repeat:
+            idx = torch.cat([idx, self.order[: self.bs - idx.numel()]])
+        self.pos += self.bs
+        img = self.images[idx]
+        x = distort_batch(img, self.size, self.gen) if self.train else center_batch(img, self.size)
+        y = self.labels[idx].clone()
+        if self.pin:
+            x, y = x.pin_memory(), y.pin_memory()
+        return x, y
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        item = self.pf.get()
+        if item is None:
+            raise StopIteration
+        return item
+
+    def close(self):
+        self.pf.close()
+
+
+def distorted_inputs(data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, **kw) -> Cifar10Batches:
+    """Training batches (reference ``cifar10.distorted_inputs``, cnn/cifar10.py:165)."""
+    return Cifar10Batches(data_dir, batch_size, image_size, train=True, **kw)
+
+
+def inputs(eval_data: bool, data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, **kw) -> Cifar10Batches:
+    """Evaluation batches (reference ``cifar10.inputs``, cnn/cifar10.py:183)."""
+    kw.setdefault("repeat", False)
+    return Cifar10Batches(data_dir, batch_size, image_size, train=not eval_data, shuffle=False, **kw) if not eval_data \
+        else Cifar10Batches(data_dir, batch_size, image_size, train=False, shuffle=False, **kw)

@@ -75,6 +75,9 @@ typedef struct {
 
 int dtf_conv_wgrad(const dtf_conv_wgrad_params* p, void* stream);
 
+/* Debug aid: arm (buf != NULL, >= 4096 int64) or disarm the in-kernel timeline trace of dtf_conv_gemm. */
+int dtf_debug_set_trace(long long* buf);
+
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
 
