@@ -1,0 +1,170 @@
+"""Checkpoints keyed by the reference's TensorFlow variable names.
+
+What ``tf.train.Saver`` + ``Supervisor`` do for the reference:
+
+* files ``<train_dir>/model.ckpt-<global_step>`` plus the text-proto state file ``<train_dir>/checkpoint``
+  (``model_checkpoint_path: "model.ckpt-N"`` / ``all_model_checkpoint_paths: ...``), which is how the eval
+  scripts find the newest checkpoint and parse the step from the suffix (cnn/cifar10_eval.py:73-80);
+* every variable under its full logical name in **TensorFlow layout** (conv kernels HWIO, FC ``[in, out]``),
+  independent of how it was sharded over parameter servers;
+* optimizer slots ``<var>/RMSProp`` (ms) and ``<var>/RMSProp_1`` (mom), EMA shadows
+  ``<var>/ExponentialMovingAverage``, and the global step under the trainer's name for it;
+* keep-N policy (``max_to_keep``: 5 by default, 1 for ResNet — resnet/cifar10_resnet_bsp.py:107).
+
+The container is a NumPy ``.npz`` (one array per name).  Writing real TF V2 bundles (``.index`` SSTable +
+``.data``) is out of scope; a TF-side loader only needs ``np.load`` + ``assign`` because names and layouts
+already match.
+"""
+from __future__ import annotations
+
+import os
+import re
+import shutil
+import time
+from typing import Dict, Iterable, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..slim.variables import Variable, VariableStore
+
+STATE_FILE = "checkpoint"
+PREFIX = "model.ckpt"
+EMA_SUFFIX = "/ExponentialMovingAverage"
+
+
+class CheckpointState:
+    def __init__(self, model_checkpoint_path: str, all_model_checkpoint_paths: List[str]):
+        self.model_checkpoint_path = model_checkpoint_path
+        self.all_model_checkpoint_paths = all_model_checkpoint_paths
+
+
+def _write_state(train_dir: str, paths: List[str]) -> None:
+    tmp = os.path.join(train_dir, STATE_FILE + ".tmp")
+    with open(tmp, "w") as f:
+        f.write('model_checkpoint_path: "%s"\n' % paths[-1])
+        for p in paths:
+            f.write('all_model_checkpoint_paths: "%s"\n' % p)
+    os.replace(tmp, os.path.join(train_dir, STATE_FILE))
+
+
+def get_checkpoint_state(checkpoint_dir: str) -> Optional[CheckpointState]:
+    """``tf.train.get_checkpoint_state``: parse ``<dir>/checkpoint`` (None when absent)."""
+    path = os.path.join(checkpoint_dir, STATE_FILE)
+    if not os.path.exists(path):
+        return None
+    latest, allp = None, []
+    with open(path) as f:
+        for line in f:
+            m = re.match(r'\s*(\w+):\s*"(.*)"', line)
+            if not m:
+                continue
+            if m.group(1) == "model_checkpoint_path":
+                latest = m.group(2)
+            elif m.group(1) == "all_model_checkpoint_paths":
+                allp.append(m.group(2))
+    if latest is None:
+        return None
+
+    def absolutise(p):
+        return p if os.path.isabs(p) else os.path.join(checkpoint_dir, p)
+    return CheckpointState(absolutise(latest), [absolutise(p) for p in allp])
+
+
+def latest_checkpoint(checkpoint_dir: str) -> Optional[str]:
+    st = get_checkpoint_state(checkpoint_dir)
+    return st.model_checkpoint_path if st else None
+
+
+def step_of(path: str) -> int:
+    """global step from ``.../model.ckpt-1234`` (cnn/cifar10_eval.py:80)."""
+    return int(path.split("/")[-1].split("-")[-1].split(".")[0])
+
+
+def _file(path: str) -> str:
+    return path if path.endswith(".npz") else path + ".npz"
+
+
+def collect_tensors(store: VariableStore, slot_flats: Optional[Dict[str, torch.Tensor]] = None,
+                    layout=None, global_step: int = 0, global_step_name: str = "global_step") -> Dict[str, np.ndarray]:
+    """name -> array in TF layout.  ``slot_flats``: full-length flat tensors per slot
+    ('RMSProp', 'RMSProp_1', 'ExponentialMovingAverage') gathered from the PS shards."""
+    out: Dict[str, np.ndarray] = {}
+    for v in store.all():
+        if v.name == "global_step":
+            continue
+        out[v.name] = v.to_tf().cpu().numpy()
+    if slot_flats and layout is not None:
+        for slot, flat in slot_flats.items():
+            for e in layout.entries:
+                v = store.get(e.name)
+                t = flat[e.offset:e.offset + e.numel].view(e.shape)
+                tmp = Variable(e.name, t, True, tf_layout=v.tf_layout)
+                out[f"{e.name}/{slot}"] = tmp.to_tf().cpu().numpy()
+    out[global_step_name] = np.asarray(global_step, dtype=np.int64)
+    return out
+
+
+def save(train_dir: str, tensors: Dict[str, np.ndarray], global_step: int, max_to_keep: int = 5) -> str:
+    os.makedirs(train_dir, exist_ok=True)
+    name = f"{PREFIX}-{int(global_step)}"
+    tmp = os.path.join(train_dir, name + ".tmp.npz")
+    np.savez(tmp, **{k.replace("/", "|"): v for k, v in tensors.items()})
+    os.replace(tmp, os.path.join(train_dir, name + ".npz"))
+    st = get_checkpoint_state(train_dir)
+    paths = [os.path.basename(p) for p in (st.all_model_checkpoint_paths if st else [])]
+    paths = [p for p in paths if p != name and os.path.exists(_file(os.path.join(train_dir, p)))] + [name]
+    while max_to_keep and len(paths) > max_to_keep:
+        old = paths.pop(0)
+        try:
+            os.remove(_file(os.path.join(train_dir, old)))
+        except OSError:
+            pass
+    _write_state(train_dir, paths)
+    return os.path.join(train_dir, name)
+
+
+def load(path: str) -> Dict[str, np.ndarray]:
+    with np.load(_file(path)) as z:
+        return {k.replace("|", "/"): z[k] for k in z.files}
+
+
+def restore(store: VariableStore, tensors: Dict[str, np.ndarray], use_ema: bool = False,
+            strict: bool = True) -> List[str]:
+    """Assign checkpoint values to the store's variables.  ``use_ema``: prefer the shadow value
+    ``<name>/ExponentialMovingAverage`` when present (``variable_averages.variables_to_restore()``,
+    cnn/cifar10_eval.py:132-135).  Returns the names restored."""
+    done = []
+    for v in store.get_variables_to_restore():
+        if v.name == "global_step":
+            continue
+        key = v.name
+        if use_ema and (v.name + EMA_SUFFIX) in tensors:
+            key = v.name + EMA_SUFFIX
+        if key not in tensors:
+            if strict:
+                raise KeyError(f"checkpoint has no tensor named {key}")
+            continue
+        v.from_tf(torch.from_numpy(np.asarray(tensors[key])))
+        done.append(v.name)
+    return done
+
+
+def wipe(train_dir: str) -> None:
+    """CIFAR chiefs delete and recreate train_dir at start (cifarnet/cifar10_cifarnet_bsp.py:45-48)."""
+    if os.path.isdir(train_dir):
+        shutil.rmtree(train_dir)
+    os.makedirs(train_dir, exist_ok=True)
+
+
+def wait_for_checkpoint(checkpoint_dir: str, poll_secs: float = 1.0, timeout: Optional[float] = None) -> Optional[str]:
+    """Poll until a checkpoint exists (re-reading the state each time — the reference's wait loops do not,
+    cifarnet/cifar10_cifarnet_eval.py:75-82)."""
+    t0 = time.time()
+    while True:
+        p = latest_checkpoint(checkpoint_dir)
+        if p and os.path.exists(_file(p)):
+            return p
+        if timeout is not None and time.time() - t0 > timeout:
+            return None
+        time.sleep(poll_secs)

@@ -16,9 +16,11 @@ when CUDA is present so the trainer's H2D copy is asynchronous.
 """
 from __future__ import annotations
 
+import atexit
 import os
 import queue
 import threading
+import weakref
 from typing import Iterator, List, Optional, Tuple
 
 import numpy as np
@@ -107,11 +109,23 @@ def center_batch(images_u8: torch.Tensor, image_size: int) -> torch.Tensor:
     return per_image_standardization(x)
 
 
+_LIVE_PREFETCHERS: "weakref.WeakSet" = weakref.WeakSet()
+
+
+def _shutdown_prefetchers():
+    for p in list(_LIVE_PREFETCHERS):
+        p.close(join=True)
+
+
+atexit.register(_shutdown_prefetchers)
+
+
 class _Prefetcher:
     def __init__(self, make_batch, depth: int):
         self.q: "queue.Queue" = queue.Queue(maxsize=depth)
         self.stop = False
         self.t = threading.Thread(target=self._run, args=(make_batch,), daemon=True)
+        _LIVE_PREFETCHERS.add(self)
         self.t.start()
 
     def _run(self, make_batch):
@@ -129,8 +143,15 @@ class _Prefetcher:
     def get(self):
         return self.q.get()
 
-    def close(self):
+    def close(self, join: bool = False):
         self.stop = True
+        if join and self.t.is_alive():
+            try:
+                while True:
+                    self.q.get_nowait()
+            except queue.Empty:
+                pass
+            self.t.join(timeout=2.0)
 
 
 class Cifar10Batches:

@@ -54,3 +54,29 @@ def write_cifar10_binary(data_dir: str, train_per_file: int = 64, test: int = 64
         dump(os.path.join(d, f"data_batch_{i}.bin"), train_per_file)
     dump(os.path.join(d, "test_batch.bin"), test)
     return d
+
+
+class SyntheticCifarBatches:
+    """Random 32x32x3 uint8 records pushed through the real CIFAR training distortion
+    (``cifar10.distort_batch``): what a worker sees when no dataset is on disk."""
+
+    def __init__(self, batch_size: int, image_size: int, seed: int = 0, pool: int = 8):
+        from . import cifar10
+        g = torch.Generator().manual_seed(seed)
+        self.pool = []
+        for _ in range(pool):
+            raw = torch.randint(0, 256, (batch_size, 32, 32, 3), generator=g, dtype=torch.uint8)
+            x = cifar10.distort_batch(raw, image_size, g)
+            y = torch.randint(0, 10, (batch_size,), generator=g)
+            if torch.cuda.is_available():
+                x, y = x.pin_memory(), y.pin_memory()
+            self.pool.append((x, y))
+        self.i = 0
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        b = self.pool[self.i % len(self.pool)]
+        self.i += 1
+        return b

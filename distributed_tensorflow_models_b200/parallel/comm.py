@@ -73,6 +73,17 @@ class Comm:
     def owned_optimizers(self) -> List[ShardOptimizer]:
         raise NotImplementedError
 
+    def gather_slot_flats(self) -> dict:
+        """Full-length flat tensors of the optimizer slots / EMA shadows (for the chief's checkpoint;
+        SURVEY C8).  Default: this rank owns everything it needs (single rank or replicated optimiser)."""
+        L = self.layout
+        out = {}
+        for o in self.owned_optimizers():
+            for name, t in o.state_tensors().items():
+                flat = out.setdefault(name, torch.zeros(L.total, dtype=torch.float32, device=t.device))
+                flat[o.lo:o.hi].copy_(t)
+        return out
+
     def finish(self) -> None:
         pass
 
@@ -261,6 +272,16 @@ class ThreadComm(Comm):
     def owned_optimizers(self):
         return self.c.opts[self.rank]
 
+    def gather_slot_flats(self):
+        L = self.layout
+        out = {}
+        for r in range(self.world):
+            for o in self.c.opts[r]:
+                for name, t in o.state_tensors().items():
+                    flat = out.setdefault(name, torch.zeros(L.total, dtype=torch.float32))
+                    flat[o.lo:o.hi].copy_(t)
+        return out
+
 
 # =================================================================================================
 class TorchDistComm(Comm):
@@ -333,3 +354,14 @@ class TorchDistComm(Comm):
 
     def owned_optimizers(self):
         return self.opts
+
+    def gather_slot_flats(self):
+        if self.shard is None:
+            return Comm.gather_slot_flats(self)
+        L = self.layout
+        out = {}
+        for name, t in self.opts[0].state_tensors().items():
+            flat = torch.empty(L.total, dtype=torch.float32, device=t.device)
+            self.dist.all_gather_into_tensor(flat, t.contiguous(), group=self.group)
+            out[name] = flat
+        return out

@@ -127,7 +127,8 @@ class Trainer:
         self.store.to(self.device)
         # ---- PS layout + optimiser -------------------------------------------------------------
         wd = self.p.weight_decay if self.p.decay_all_trainables else None
-        self.layout = FlatLayout(self.store, self.comm.world, self.setup.placement, self.device,
+        owners = getattr(self.comm, "owners", self.comm.world)     # PS tasks (== workers in the SPMD transports)
+        self.layout = FlatLayout(self.store, owners, self.setup.placement, self.device,
                                  default_weight_decay=wd)
         ema = EmaConfig(self.p.ema_decay) if self.p.ema_decay else None
         self.opt_cfg = OptimizerConfig(kind=self.p.optimizer, weight_decay=self.layout.weight_decay, ema=ema)

@@ -179,6 +179,14 @@ class SymmComm(Comm):
     def owned_optimizers(self) -> List[ShardOptimizer]:
         return [self.opt]
 
+    def gather_slot_flats(self):
+        out = {}
+        for name, t in self.opt.state_tensors().items():
+            flat = torch.empty(self.layout.total, dtype=torch.float32, device=t.device)
+            self.dist.all_gather_into_tensor(flat, t.contiguous().clone(), group=self.group)
+            out[name] = flat
+        return out
+
     def finish(self):
         torch.cuda.synchronize()
         self.check_status()

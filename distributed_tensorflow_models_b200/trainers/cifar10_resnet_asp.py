@@ -1,0 +1,18 @@
+"""resnet / ASP trainer entry point.  The reference ships no script for this pair (README.md:23 'some <model>-<mode> pairs are not yet available'); here every pair runs.
+
+    python -m distributed_tensorflow_models_b200.trainers.cifar10_resnet_asp --job_name=worker --task_id=0 \\
+        --ps_hosts=h1:22222 --worker_hosts=h2:22223,h3:22223
+
+All behaviour lives in ``trainers/common.py``; hyper-parameters come from ``config.PRESETS['resnet']``.
+"""
+import sys
+
+from .common import main as _main
+
+
+def main(argv=None):
+    return _main(argv, model="resnet", mode="asp")
+
+
+if __name__ == "__main__":
+    sys.exit(main())

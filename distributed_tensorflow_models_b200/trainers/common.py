@@ -1,0 +1,280 @@
+"""The trainer program behind every ``<model> x <mode>`` entry point.
+
+One parametrised implementation of the skeleton that each reference trainer script repeats (SURVEY §2.2,
+call stack §3.2): parse ``--ps_hosts/--worker_hosts/--job_name/--task_id`` -> bring up the cluster -> the
+chief (worker 0) wipes ``train_dir`` (CIFAR models) or resumes (Inception) -> build model + PS layout ->
+wait for the chief's initial values -> loop ``max_steps`` times: batch, step, log line -> periodic
+checkpoints by the chief (``save_model_secs`` 60 / ``save_interval_secs`` 600) -> NaN guard (Inception) ->
+train-batch accuracy every 200 steps (ResNet).
+
+Roles and transports
+--------------------
+* GPU box: workers are SPMD ranks that also own the PS shards (``--backend symm``: our NVLink push/pull
+  kernels; ``nccl``: collective baseline).  ``--job_name=ps`` processes have nothing to host and exit at once.
+* CPU / multi-host plumbing (``--backend gloo``): dedicated PS processes as in the reference
+  (``parallel/ps_process.py``), SSP through the TCP clock service on PS 0's host.
+* ``--backend local``: single process.
+"""
+from __future__ import annotations
+
+import math
+import os
+import sys
+import time
+from typing import Optional
+
+import torch
+
+from .. import config as cfg
+from ..ckpt import store as ckpt
+from ..data.synthetic import SyntheticBatches
+from ..models.registry import MODEL_SPECS
+from ..ops import functional as Fn
+from ..parallel.comm import Comm, LocalComm
+from ..parallel.engine import Trainer, TrainSetup
+from ..utils.logs import ChromeTrace, MetricsWriter, format_step, log
+
+GLOBAL_STEP_NAME = {"cnn": "Variable", "cifarnet": "partitioned_space/Variable",
+                    "alexnet": "partitioned_space/Variable", "vgg": "root/Variable", "resnet": "Variable",
+                    "inception": "global_step"}
+
+
+def _host_port(hp: str, default_port: int):
+    if ":" in hp:
+        h, p = hp.rsplit(":", 1)
+        return h, int(p)
+    return hp, default_port
+
+
+def resolve_backend(args) -> str:
+    if args.backend != "auto":
+        return args.backend
+    nw = max(1, len(args.worker_host_list))
+    if torch.cuda.is_available():
+        return "symm" if (nw > 1 or int(os.environ.get("WORLD_SIZE", "1")) > 1) else "local"
+    if nw > 1 or args.ps_host_list:
+        return "gloo"
+    return "local"
+
+
+def make_setup(args, num_workers: int) -> TrainSetup:
+    return TrainSetup(model=args.model, mode=args.mode, batch_size=args.batch_size, num_workers=num_workers,
+                      staleness=args.staleness, resnet_size=args.resnet_size, ref_compat=args.ref_compat,
+                      placement=args.placement, seed=args.seed, initial_lr=args.initial_learning_rate,
+                      epochs_per_decay=args.num_epochs_per_decay, decay_factor=args.learning_rate_decay_factor,
+                      cuda_graph=bool(args.cuda_graph), preset=args.preset)
+
+
+def make_batches(args, spec, rank: int, world: int):
+    """Real data when present (and not ``--synthetic``), synthetic batches of the model's shape otherwise."""
+    use_synth = args.synthetic
+    if spec.dataset == "cifar10":
+        from ..data import cifar10
+        if use_synth is None:
+            use_synth = not cifar10.maybe_download_and_extract(args.data_dir)
+        if not use_synth:
+            return cifar10.distorted_inputs(args.data_dir, args.batch_size, spec.image_size, rank=rank, world=world,
+                                            seed=args.seed)
+    else:
+        from ..data import imagenet
+        if use_synth is None:
+            use_synth = not imagenet.ImagenetData(args.subset, args.data_dir).available()
+        if not use_synth:
+            return imagenet.distorted_inputs(imagenet.ImagenetData(args.subset, args.data_dir), args.batch_size,
+                                             image_size=spec.image_size, num_preprocess_threads=args.num_preprocess_threads,
+                                             rank=rank, world=world, seed=args.seed)
+    if spec.dataset == "cifar10":
+        # synthetic 32x32 records run through the real distortion pipeline (random crop to 24 for the plain
+        # CNN, flip, brightness, contrast, standardisation) — BASELINE.json config 1 / SURVEY Q10
+        from ..data.synthetic import SyntheticCifarBatches
+        return SyntheticCifarBatches(args.batch_size, spec.image_size, seed=args.seed + rank)
+    return SyntheticBatches(args.batch_size, spec.image_size, spec.num_classes, seed=args.seed + rank)
+
+
+def _init_gloo(args, backend_rank: int, world: int) -> None:
+    import torch.distributed as dist
+    host, port = _host_port(args.ps_host_list[0] if args.ps_host_list else args.worker_host_list[0], cfg.PS_PORT)
+    if host in ("localhost",):
+        host = "127.0.0.1"
+    dist.init_process_group("gloo", init_method=f"tcp://{host}:{port + 1000}", rank=backend_rank, world_size=world)
+
+
+def run_ps(args) -> int:
+    """``--job_name=ps``."""
+    backend = resolve_backend(args)
+    if backend != "gloo":
+        log("ps task %d: parameter-server shards live on the worker GPUs in this mode (backend=%s); nothing to host"
+            % (args.task_id, backend))
+        return 0
+    from ..parallel.layout import FlatLayout
+    from ..parallel.ps_process import ParameterServer
+    P, W = len(args.ps_host_list), len(args.worker_host_list)
+    _init_gloo(args, args.task_id, P + W)
+    # build the same variables as the workers to learn the layout (values come from the chief)
+    t = Trainer(make_setup(args, W), _LayoutOnlyComm(P), torch.device("cpu"))
+    host, _ = _host_port(args.ps_host_list[0], cfg.PS_PORT)
+    ps = ParameterServer(args.task_id, P, W, t.layout, t.opt_cfg, mode=args.mode, ssp_host="0.0.0.0",
+                         ssp_port=cfg.SSP_PORT, staleness=args.staleness)
+    log("ps task %d serving %d workers (%s, %s)" % (args.task_id, W, args.mode, t.layout.describe()))
+    steps = ps.serve()
+    log("ps task %d done after %d updates" % (args.task_id, steps))
+    import torch.distributed as dist
+    dist.destroy_process_group()
+    return 0
+
+
+class _LayoutOnlyComm(LocalComm):
+    """Used by PS processes: they need the model's layout, not a worker transport."""
+
+    def __init__(self, owners: int):
+        super().__init__()
+        self.owners = owners
+
+    def setup(self, layout, opt_cfg):
+        self.layout = layout
+        self.opts = []
+
+
+def make_comm(args, backend: str, num_workers: int):
+    """-> (comm, device, rank, world)"""
+    if backend == "local":
+        dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
+        return LocalComm(), dev, 0, 1
+    if backend == "gloo":
+        from ..parallel.ps_process import PsWorkerComm
+        P, W = len(args.ps_host_list), len(args.worker_host_list)
+        if P == 0:
+            raise SystemExit("--backend gloo needs --ps_hosts (dedicated parameter servers)")
+        _init_gloo(args, P + args.task_id, P + W)
+        host, _ = _host_port(args.ps_host_list[0], cfg.PS_PORT)
+        if host == "localhost":
+            host = "127.0.0.1"
+        comm = PsWorkerComm(P, W, args.task_id, ssp_host=host, ssp_port=cfg.SSP_PORT, mode=args.mode,
+                            staleness=args.staleness)
+        return comm, torch.device("cpu"), args.task_id, W
+    # GPU SPMD transports
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", str(num_workers)))
+    rank = int(os.environ.get("RANK", str(args.task_id)))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank % max(1, torch.cuda.device_count()))))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if not dist.is_initialized():
+        if "MASTER_ADDR" not in os.environ:
+            host, port = _host_port(args.worker_host_list[0], cfg.WORKER_PORT)
+            os.environ["MASTER_ADDR"] = "127.0.0.1" if host == "localhost" else host
+            os.environ["MASTER_PORT"] = str(port + 1000)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    if backend == "symm":
+        from ..parallel.symm import SymmComm
+        return SymmComm(), dev, rank, world
+    from ..parallel.comm import TorchDistComm
+    return TorchDistComm("rs_ag"), dev, rank, world
+
+
+def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int) -> Optional[str]:
+    """Chief-side save (all ranks must call: gathering the sharded slots is collective)."""
+    comm = trainer.comm
+    slots = comm.gather_slot_flats()
+    if comm.rank != 0:
+        return None
+    gs = comm.global_step()
+    tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME[trainer.setup.model])
+    return ckpt.save(train_dir, tensors, gs, max_to_keep)
+
+
+def run_worker(args) -> int:
+    backend = resolve_backend(args)
+    num_workers = max(1, len(args.worker_host_list)) if backend in ("gloo", "local") else \
+        int(os.environ.get("WORLD_SIZE", str(max(1, len(args.worker_host_list)))))
+    Fn.set_backend("torch" if args.kernels == "torch" else "auto")
+    comm, device, rank, world = make_comm(args, backend, num_workers)
+    p = args.preset
+    is_chief = rank == 0
+    # ---- chief: train_dir policy ----
+    if is_chief and p.save_secs is not None:
+        if p.wipe_train_dir and not args.resume:
+            ckpt.wipe(args.train_dir)
+        else:
+            os.makedirs(args.train_dir, exist_ok=True)
+    trainer = Trainer(make_setup(args, world), comm, device)
+    spec = trainer.spec
+    log("worker %d/%d on %s: %s, mode=%s backend=%s" % (rank, world, device, trainer.layout.describe(), args.mode, backend))
+    # ---- resume ----
+    if (args.resume or not p.wipe_train_dir) and p.save_secs is not None:
+        latest = ckpt.latest_checkpoint(args.train_dir)
+        if latest and os.path.exists(latest + ".npz"):
+            tensors = ckpt.load(latest)
+            ckpt.restore(trainer.store, tensors, strict=False)
+            comm.set_global_step(ckpt.step_of(latest))
+            log("restored %s" % latest)
+    batches = make_batches(args, spec, rank, world)
+    metrics = MetricsWriter(args.metrics_jsonl if is_chief else "")
+    trace = ChromeTrace(args.trace, pid=rank)
+    last_save = time.time()
+    t_run0 = time.time()
+    for step in range(0, args.max_steps):          # init_global_step := 0
+        t0 = time.time()
+        images, labels = next(batches)
+        t1 = time.time()
+        out = trainer.train_step(images.to(device, non_blocking=True), labels.to(device, non_blocking=True),
+                                 batch_size=args.batch_size)
+        want_log = (step % max(1, args.log_every) == 0) or step == args.max_steps - 1
+        if want_log or p.nan_guard:
+            loss_value = float(out["loss"])             # D2H read (also the NaN guard, inception…bsp.py:191)
+            if p.nan_guard:
+                assert not math.isnan(loss_value), "Model diverged with loss = NaN"
+        t2 = time.time()
+        trace.add("input", t0 - t_run0, t1 - t0, step=step)
+        trace.add("train_step", t1 - t_run0, t2 - t1, step=step)
+        if want_log:
+            duration = max(t2 - t0, 1e-9)
+            log(format_step(p.log_style, step, out["global_step"], loss_value, args.batch_size / duration, duration))
+            metrics.write(step=step, global_step=out["global_step"], loss=loss_value, lr=out["lr"],
+                          examples_per_sec=args.batch_size / duration, sec_per_batch=duration,
+                          ssp_wait_s=out["ssp_wait_s"], time=t2)
+        if p.accuracy_every and step % p.accuracy_every == 0:
+            acc = float((out["logits"].argmax(1) == labels.to(device)).float().mean())
+            log("step %d, train-batch accuracy = %.4f" % (step, acc))
+        if p.save_secs is not None and args.save_interval_secs and backend != "gloo":
+            # time-based like Supervisor(save_model_secs); every rank takes the same decision from the chief's clock
+            due = time.time() - last_save >= args.save_interval_secs
+            if world > 1:
+                flag = torch.tensor([1.0 if (due and is_chief) else 0.0], device=device)
+                comm.broadcast_state([flag], src=0)
+                due = bool(flag.item() > 0)
+            if due:
+                path = save_checkpoint(trainer, args.train_dir, p.max_to_keep)
+                last_save = time.time()
+                if path:
+                    log("saved %s" % path)
+    # final checkpoint + shutdown
+    if p.save_secs is not None and backend != "gloo":
+        path = save_checkpoint(trainer, args.train_dir, p.max_to_keep)
+        if path:
+            log("saved %s" % path)
+    elif p.save_secs is not None and is_chief:
+        # dedicated-PS mode: the chief's replica is fresh after its last pull; slots live on the PS processes
+        tensors = ckpt.collect_tensors(trainer.store, None, None, comm.global_step(), GLOBAL_STEP_NAME[args.model])
+        log("saved %s" % ckpt.save(args.train_dir, tensors, comm.global_step(), p.max_to_keep))
+    comm.finish()
+    trace.save()
+    metrics.close()
+    if hasattr(batches, "close"):
+        batches.close()
+    if backend in ("gloo", "symm", "nccl"):
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    return 0
+
+
+def main(argv=None, model: Optional[str] = None, mode: Optional[str] = None) -> int:
+    args = cfg.parse_args(argv, model, mode)
+    if args.job_name == "ps":
+        return run_ps(args)
+    return run_worker(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
