@@ -80,3 +80,34 @@ class SyntheticCifarBatches:
         b = self.pool[self.i % len(self.pool)]
         self.i += 1
         return b
+
+
+def write_imagenet_tfrecords(data_dir: str, subset: str = "train", num_images: int = 16, num_shards: int = 2,
+                             size: int = 64, num_classes: int = 1000, seed: int = 0):
+    """Tiny random-JPEG ImageNet look-alike in the real TFRecord/Example format (for offline tests)."""
+    import io
+
+    from PIL import Image
+
+    from .build_image_data import convert_to_example
+    from .tfrecord import TFRecordWriter
+    rng = np.random.RandomState(seed)
+    os.makedirs(data_dir, exist_ok=True)
+    paths = []
+    per = (num_images + num_shards - 1) // num_shards
+    k = 0
+    for s in range(num_shards):
+        p = os.path.join(data_dir, "%s-%.5d-of-%.5d" % (subset, s, num_shards))
+        with TFRecordWriter(p) as w:
+            for _ in range(per):
+                if k >= num_images:
+                    break
+                arr = rng.randint(0, 256, size=(size, size + 8, 3)).astype(np.uint8)
+                buf = io.BytesIO()
+                Image.fromarray(arr).save(buf, format="JPEG")
+                label = int(rng.randint(1, num_classes + 1))
+                w.write(convert_to_example("img_%d.JPEG" % k, buf.getvalue(), label, "synthetic", size, size + 8,
+                                           [[0.1, 0.1, 0.9, 0.9]]))
+                k += 1
+        paths.append(p)
+    return paths
