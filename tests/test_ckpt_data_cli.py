@@ -1,0 +1,203 @@
+"""Checkpoint store, eval loop, input pipelines, flags/presets and launcher helpers."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from distributed_tensorflow_models_b200 import config as cfg
+from distributed_tensorflow_models_b200.ckpt import store as ckpt
+from distributed_tensorflow_models_b200.data import cifar10, imagenet, synthetic, tfrecord
+from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+from distributed_tensorflow_models_b200.trainers import common
+from distributed_tensorflow_models_b200.utils import logs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---- checkpoints ------------------------------------------------------------------------------------------------
+def test_checkpoint_names_layouts_slots_and_state_file(tmp_path):
+    t = Trainer(TrainSetup(model="cifarnet", batch_size=4))
+    x = torch.randn(4, 32, 32, 3)
+    y = torch.randint(0, 10, (4,))
+    t.train_step(x, y)
+    path = common.save_checkpoint(t, str(tmp_path), max_to_keep=2)
+    assert path.endswith("model.ckpt-1") and os.path.exists(path + ".npz")
+    tensors = ckpt.load(path)
+    # TF names under the trainer's variable scope, TF layouts (HWIO / [in, out])
+    assert tensors["partitioned_space/CifarNet/conv1/weights"].shape == (5, 5, 3, 64)
+    assert tensors["partitioned_space/CifarNet/fc3/weights"].shape == (4096, 384)
+    assert tensors["partitioned_space/CifarNet/conv1/weights/ExponentialMovingAverage"].shape == (5, 5, 3, 64)
+    assert int(tensors["partitioned_space/Variable"]) == 1
+    st = ckpt.get_checkpoint_state(str(tmp_path))
+    assert st.model_checkpoint_path == path and ckpt.step_of(path) == 1
+    assert 'model_checkpoint_path: "model.ckpt-1"' in open(tmp_path / "checkpoint").read()
+    # keep-N
+    for _ in range(3):
+        t.train_step(x, y)
+        common.save_checkpoint(t, str(tmp_path), max_to_keep=2)
+    kept = sorted(f for f in os.listdir(tmp_path) if f.endswith(".npz"))
+    assert kept == ["model.ckpt-3.npz", "model.ckpt-4.npz"]
+    # round trip into a fresh replica, raw and EMA-restored
+    t2 = Trainer(TrainSetup(model="cifarnet", batch_size=4, seed=99))
+    tensors = ckpt.load(ckpt.latest_checkpoint(str(tmp_path)))
+    ckpt.restore(t2.store, tensors)
+    assert torch.equal(t2.layout.params[: t.layout.used], t.layout.params[: t.layout.used])
+    ckpt.restore(t2.store, tensors, use_ema=True)
+    ema = t.comm.opts[0].ema
+    assert torch.allclose(t2.layout.params[: t.layout.used], ema[: t.layout.used])
+
+
+def test_rmsprop_slot_names_and_inception_global_step(tmp_path):
+    t = Trainer(TrainSetup(model="cnn", batch_size=2, preset=cfg.PRESETS["cnn"].__class__(
+        **{**cfg.PRESETS["cnn"].__dict__, "optimizer": "rmsprop"})))
+    t.train_step(torch.randn(2, 24, 24, 3), torch.randint(0, 10, (2,)))
+    slots = t.comm.gather_slot_flats()
+    tensors = ckpt.collect_tensors(t.store, slots, t.layout, 7, "global_step")
+    assert "conv1/weights/RMSProp" in tensors and "conv1/weights/RMSProp_1" in tensors
+    assert tensors["conv1/weights/RMSProp"].shape == (5, 5, 3, 64) and int(tensors["global_step"]) == 7
+
+
+def test_eval_once_on_saved_checkpoint(tmp_path):
+    rc = subprocess.run([sys.executable, "-m", "distributed_tensorflow_models_b200.trainers.cifar10_resnet_bsp",
+                         "--max_steps=2", "--batch_size=4", f"--train_dir={tmp_path}/t", "--synthetic"],
+                        cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert rc.returncode == 0, rc.stderr
+    assert "(gs 2), loss=" in rc.stderr and "samples/s" in rc.stderr               # resnet log format
+    assert "train-batch accuracy" in rc.stderr
+    rc = subprocess.run([sys.executable, "-m", "distributed_tensorflow_models_b200.eval.cifar10_resnet_eval",
+                         f"--checkpoint_dir={tmp_path}/t", f"--eval_dir={tmp_path}/e", "--run_once", "--num_examples=16",
+                         "--synthetic"], cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert rc.returncode == 0, rc.stderr
+    assert "precision @ 1 = " in rc.stderr and "global_step: 2" in rc.stderr
+    assert os.path.exists(tmp_path / "e" / "eval.jsonl")
+
+
+# ---- CIFAR-10 -----------------------------------------------------------------------------------------------------
+def test_cifar10_binary_reader_and_pipeline(tmp_path):
+    synthetic.write_cifar10_binary(str(tmp_path), train_per_file=20, test=12)
+    labels, images = cifar10.read_records(cifar10.data_files(str(tmp_path), eval_data=False))
+    assert labels.shape == (100,) and images.shape == (100, 32, 32, 3) and images.dtype == np.uint8
+    raw = np.fromfile(tmp_path / "cifar-10-batches-bin" / "data_batch_1.bin", dtype=np.uint8).reshape(-1, 3073)
+    assert labels[0] == raw[0, 0]
+    assert np.array_equal(images[0, :, :, 0], raw[0, 1:1025].reshape(32, 32))      # CHW on disk -> HWC
+    it = cifar10.distorted_inputs(str(tmp_path), 8, image_size=24, seed=1)
+    x, y = next(it)
+    it.close()
+    assert tuple(x.shape) == (8, 24, 24, 3) and x.dtype == torch.float32 and y.dtype == torch.int64
+    assert torch.allclose(x.reshape(8, -1).mean(1), torch.zeros(8), atol=1e-4)       # per-image standardisation
+    assert torch.allclose(x.reshape(8, -1).std(1, unbiased=False), torch.ones(8), atol=1e-3)
+    ev = cifar10.inputs(True, str(tmp_path), 5, image_size=32)
+    assert sum(b[0].shape[0] for b in ev) == 12
+    with pytest.raises(ValueError):
+        cifar10.data_files(str(tmp_path / "nope"), False)
+    assert not cifar10.maybe_download_and_extract(str(tmp_path / "nope"))
+    # disjoint per-rank shards
+    a = cifar10.Cifar10Batches(str(tmp_path), 4, 32, rank=0, world=2, shuffle=False)
+    b = cifar10.Cifar10Batches(str(tmp_path), 4, 32, rank=1, world=2, shuffle=False)
+    assert a.labels.numel() + b.labels.numel() == 100
+    a.close(), b.close()
+
+
+# ---- TFRecords / ImageNet ----------------------------------------------------------------------------------------
+def test_tfrecord_and_example_roundtrip(tmp_path):
+    assert tfrecord.crc32c(b"123456789") == 0xE3069283
+    feats = {"image/encoded": [b"\xff\xd8abc"], "image/class/label": [7], "image/class/text": [b"tench"],
+             "image/object/bbox/xmin": [0.1, 0.25], "neg": [-3, 1 << 40]}
+    rec = tfrecord.encode_example(feats)
+    out = tfrecord.decode_example(rec)
+    assert out["image/encoded"] == [b"\xff\xd8abc"] and out["image/class/label"] == [7]
+    assert out["image/object/bbox/xmin"] == pytest.approx([0.1, 0.25]) and out["neg"] == [-3, 1 << 40]
+    p = str(tmp_path / "x-00000-of-00001")
+    with tfrecord.TFRecordWriter(p) as w:
+        w.write(rec)
+        w.write(b"second")
+    assert list(tfrecord.read_records(p, check_crc=True)) == [rec, b"second"]
+    try:
+        from google.protobuf import descriptor  # noqa: F401
+    except Exception:
+        pass
+
+
+def test_imagenet_pipeline_and_builders(tmp_path):
+    synthetic.write_imagenet_tfrecords(str(tmp_path), "train", 10, 2, size=40)
+    ds = imagenet.ImagenetData("train", str(tmp_path))
+    assert ds.available() and ds.num_classes() == 1000 and ds.num_examples_per_epoch() == 1281167
+    it = imagenet.distorted_inputs(ds, 4, image_size=32, num_preprocess_threads=2, shuffle_buffer=2)
+    x, y = next(it)
+    it.close()
+    assert tuple(x.shape) == (4, 32, 32, 3) and float(x.min()) >= -1.0 and float(x.max()) <= 1.0
+    assert all(1 <= int(v) <= 1000 for v in y)
+    import random
+    assert imagenet.sample_distorted_bounding_box(100, 80, np.zeros((0, 4), np.float32), random.Random(0))[2] <= 100
+    img = torch.rand(50, 60, 3)
+    assert tuple(imagenet.eval_image(img, 32, 32).shape) == (32, 32, 3)
+    hsv = imagenet.rgb_to_hsv(img)
+    assert torch.allclose(imagenet.hsv_to_rgb(hsv), img, atol=1e-5)
+    # folder tree -> TFRecords -> reader
+    from PIL import Image
+    from distributed_tensorflow_models_b200.data import build_image_data as bid
+    for lab in ("daisy", "rose"):
+        os.makedirs(tmp_path / "raw" / lab)
+        for i in range(3):
+            Image.fromarray(np.random.randint(0, 255, (20, 24, 3), np.uint8)).save(tmp_path / "raw" / lab / f"{i}.png")
+    f, t, l = bid.find_image_files(str(tmp_path / "raw"), ["daisy", "rose"])
+    assert sorted(set(l)) == [1, 2] and len(f) == 6
+    outs = bid.process_image_files("train", f, t, l, 2, str(tmp_path / "out"), 2)
+    recs = [r for p in outs for r in tfrecord.read_records(p)]
+    assert len(recs) == 6
+    image, label, bbox, text = imagenet.parse_example_proto(recs[0])
+    assert image[:3] == b"\xff\xd8\xff" and text in (b"daisy", b"rose")              # PNG re-encoded as JPEG
+
+
+def test_bounding_box_xml_to_csv(tmp_path):
+    from distributed_tensorflow_models_b200.data import process_bounding_boxes as pbb
+    d = tmp_path / "n01440764"
+    d.mkdir()
+    (d / "n01440764_1.xml").write_text(
+        "<annotation><size><width>200</width><height>100</height></size>"
+        "<object><name>n01440764</name><bndbox><xmin>20</xmin><ymin>10</ymin><xmax>220</xmax><ymax>50</ymax></bndbox></object>"
+        "<object><name>n99999999</name><bndbox><xmin>1</xmin><ymin>1</ymin><xmax>2</xmax><ymax>2</ymax></bndbox></object>"
+        "</annotation>")
+    assert list(pbb.process(str(tmp_path))) == ["n01440764_1.JPEG,0.1000,0.1000,1.0000,0.5000"]
+
+
+# ---- flags / presets / launcher ------------------------------------------------------------------------------------
+def test_flags_and_presets_match_reference_defaults():
+    a = cfg.parse_args(["--job_name=worker", "--task_id=1", "--ps_hosts=a:22222", "--worker_hosts=b:22223,c:22223"],
+                       model="inception", mode="ssp")
+    assert (a.batch_size, a.max_steps, a.initial_learning_rate, a.staleness) == (32, 1000000, 0.045, 5)
+    assert a.learning_rate_decay_factor == 0.94 and a.num_epochs_per_decay == 2.0 and a.save_interval_secs == 600.0
+    assert a.worker_host_list == ["b:22223", "c:22223"] and a.task_id == 1
+    assert a.preset.optimizer == "rmsprop" and a.preset.ema_decay is None and not a.preset.lr_times_workers_in_bsp
+    p = cfg.PRESETS
+    assert (p["cnn"].initial_lr, p["cnn"].lr_times_workers_in_bsp) == (0.32, False)
+    assert (p["resnet"].weight_decay, p["resnet"].epochs_per_decay, p["resnet"].max_to_keep) == (2e-3, 32.0, 1)
+    assert p["vgg"].save_secs is None and p["vgg"].ema_decay is None
+    assert cfg.preset_for("vgg", "asp").ema_decay == 0.9999
+    assert cfg.parse_args(["--run_once=True", "--synthetic"], model="cnn").run_once is True
+    assert (cfg.PS_PORT, cfg.WORKER_PORT, cfg.SSP_PORT) == (22222, 22223, 8000)
+
+
+def test_log_line_formats():
+    s = logs.format_step("cifar", 3, 7, 2.345, 1234.56, 0.1037, now=0.0)
+    assert s.startswith("time: 0.0; ") and s.endswith(": step 3 (global_step 7), loss = 2.35 (1234.6 examples/sec; 0.104 sec/batch)")
+    assert "step 3 (gs 7), loss= 2.35 (1234.6 samples/s; 0.104 s/batch)" in logs.format_step("resnet", 3, 7, 2.345, 1234.56, 0.1037)
+    assert not logs.format_step("cnn", 1, 1, 1.0, 1.0, 1.0).startswith("time:")
+    assert logs.format_precision(0.8312, 99).endswith("precision @ 1 = 0.831, global_step: 99")
+
+
+def test_launcher_host_lists_usage_and_all_pairs():
+    from distributed_tensorflow_models_b200 import launcher
+    ps, wk = launcher.host_lists(["h1", "h2"], ["h3", "h3", "h4"])
+    assert ps == ["h1:22222", "h2:22222"] and wk == ["h3:22223", "h3:22233", "h4:22223"]
+    r = subprocess.run(["bash", os.path.join(ROOT, "train.sh")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "please specify" in r.stdout
+    import importlib
+    for m, base in launcher.TRAINER.items():
+        for mode in cfg.MODES:
+            assert hasattr(importlib.import_module(f"distributed_tensorflow_models_b200.trainers.{base}_{mode}"), "main")
+    for mod in launcher.EVALUATOR.values():
+        importlib.import_module(f"distributed_tensorflow_models_b200.eval.{mod}")
