@@ -154,8 +154,10 @@ bn_bwd_apply_kernel(const float* __restrict__ dy, const float* __restrict__ x, c
   if (blockIdx.x == 0) {
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       const float sg = sums[c], sgx = sums[C + c];
-      if (dbeta) dbeta[c] = sg;
-      if (dgamma) dgamma[c] = invstd[c] * (sgx - mean[c] * sg);
+      // accumulate: the destination is the (pre-zeroed) flat gradient buffer, and a BN whose output feeds two
+      // convolutions (residual projection + first conv of the unit) receives two contributions
+      if (dbeta) dbeta[c] += sg;
+      if (dgamma) dgamma[c] += invstd[c] * (sgx - mean[c] * sg);
     }
   }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;

@@ -28,6 +28,7 @@ constexpr int WG_MMA_WARP = (128 + WG_PRODUCERS) / 32;
 struct WgradCfg {
   int BN, stages, m_tiles, n_tiles, splits, kb_total, kb_per_split, tmem_cols, M, Ktot;
   int vec_dy;
+  int active_groups;     // producer groups in use: min(4, stages)
   FastDiv d_ohow, d_ow, d_c, d_s;
 };
 
@@ -55,7 +56,7 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
   if (warp == WG_MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < stages; ++i) {
-        mbar_init(&full_bar[i], WG_PRODUCERS / 2);
+        mbar_init(&full_bar[i], WG_PRODUCERS / 4);
         mbar_init(&empty_bar[i], 1);
       }
       for (int i = 0; i < 2; ++i) {
@@ -77,20 +78,32 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
 
   if (warp >= 4 && warp < WG_MMA_WARP) {
     // =========================== producers =================================================
-    // Two groups of four warps alternate k-blocks (32 output pixels each): while one group waits for its
-    // global loads the other is transposing / storing.  Within a group the order is strictly
-    //   wait(slot free) -> LDG.128 x (8 + 4*nB) -> 4x4 register transposes -> STS -> proxy fence -> arrive
-    // (the proxy fence drains all of a thread's outstanding memory operations, so a thread never has loads
-    // of a later k-block in flight when it fences).
-    // Thread gt owns pixel chunk pc (4 consecutive output pixels) and 4-row chunks rc0 + 16*i of the A tile
-    // (one filter tap, 4 consecutive input channels each) and of the dY tile.
+    // Four groups of two warps; group g owns every 4th k-block (32 output pixels), so four k-blocks are being
+    // gathered at any time.  Within a group the order is strictly
+    //   wait(slot free) -> LDG.128 (dY chunks, A chunks) -> 4x4 register transposes -> STS -> proxy fence -> arrive
+    // (the proxy fence drains all of a thread's outstanding memory operations, so a thread never has loads of a
+    // later k-block in flight when it fences; the overlap comes from the other groups).
+    // Thread gt owns pixel chunk pc (4 consecutive output pixels) and 4-row chunks rc0 + 8*i of the A tile
+    // (one filter tap, 4 consecutive input channels each; i < 4) and of the dY tile (rows = output channels).
     const int pt = tid - 128;
-    const int grp = pt >> 7;      // 0..1
-    const int gt = pt & 127;
+    const int grp = pt >> 6;      // 0..3
+    const int gt = pt & 63;
     const int pc = gt & 7;
-    const int rc0 = gt >> 3;      // 0..15
+    const int rc0 = gt >> 3;      // 0..7
     const bool has_aff = p.in_scale != nullptr;
-    int q = 0, stage = 0; uint32_t phase = 0;
+    int q_grp = 0, stage = 0; uint32_t phase = 0;
+
+    auto store4x4 = [&](uint8_t* tile, int row0, const float4 (&v)[4]) {
+      // 4x4 transpose in registers: row e <- component e of the 4 pixels
+      const float4 t0 = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
+      const float4 t1 = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+      const float4 t2 = make_float4(v[0].z, v[1].z, v[2].z, v[3].z);
+      const float4 t3 = make_float4(v[0].w, v[1].w, v[2].w, v[3].w);
+      *reinterpret_cast<float4*>(tile + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
+      *reinterpret_cast<float4*>(tile + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
+      *reinterpret_cast<float4*>(tile + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
+      *reinterpret_cast<float4*>(tile + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+    };
 
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int split = unit % cfg.splits;
@@ -99,27 +112,20 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
       const int kb0 = split * cfg.kb_per_split;
       int kb1 = kb0 + cfg.kb_per_split;
       if (kb1 > cfg.kb_total) kb1 = cfg.kb_total;
-      bool a_ok[2]; int a_c[2], a_r[2], a_s[2], a_off[2];
-      float4 a_sc[2], a_sh[2];
+      bool a_ok[4]; int a_r[4], a_s[4], a_off[4], a_c[4];
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int k = mt * WG_BM + (rc0 + 16 * i) * 4;
+      for (int i = 0; i < 4; ++i) {
+        const int k = mt * WG_BM + (rc0 + 8 * i) * 4;
         a_ok[i] = k < cfg.Ktot;
         const int tap = a_ok[i] ? (int)fdiv((uint32_t)k, cfg.d_c) : 0;
         a_c[i] = a_ok[i] ? k - tap * p.srcC : 0;
         a_r[i] = (int)fdiv((uint32_t)tap, cfg.d_s);
         a_s[i] = tap - a_r[i] * p.S;
         a_off[i] = (a_r[i] * p.srcW + a_s[i]) * p.src_ld + a_c[i];
-        a_sc[i] = make_float4(1.f, 1.f, 1.f, 1.f);
-        a_sh[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (has_aff && a_ok[i]) {
-          a_sc[i] = __ldg(reinterpret_cast<const float4*>(p.in_scale + a_c[i]));
-          a_sh[i] = __ldg(reinterpret_cast<const float4*>(p.in_shift + a_c[i]));
-        }
       }
       const int n0 = nt * BN;
       for (int kb = kb0; kb < kb1; ++kb) {
-        if ((q & 1) == grp) {
+        if (q_grp == grp) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* a_stage = sA + stage * WG_A_STAGE_BYTES;
           uint8_t* b_stage = sB + stage * b_stage_bytes;
@@ -140,101 +146,85 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
             iwb[qq] = ow * p.stride_w - p.pad_w;
             pixoff[qq] = ((img * p.srcH + ihb[qq]) * p.srcW + iwb[qq]) * p.src_ld;
           }
-          float4 xa[2][4];
-          uint32_t okm = 0;
+          auto load_a = [&](int i, float4 (&v)[4]) {
+            const float* srct = p.src + a_off[i];
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            if (a_ok[i]) {                      // rows beyond R*S*C are never read back: skip them entirely
-              const float* srct = p.src + a_off[i];
-#pragma unroll
-              for (int qq = 0; qq < 4; ++qq) {
-                const bool valid = (unsigned)(ihb[qq] + a_r[i]) < (unsigned)p.srcH &&
-                                   (unsigned)(iwb[qq] + a_s[i]) < (unsigned)p.srcW;
-                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (valid) {
-                  x = __ldg(reinterpret_cast<const float4*>(srct + pixoff[qq]));
-                  okm |= 1u << (i * 4 + qq);
-                }
-                xa[i][qq] = x;
-              }
+            for (int qq = 0; qq < 4; ++qq) {
+              const bool valid = (unsigned)(ihb[qq] + a_r[i]) < (unsigned)p.srcH &&
+                                 (unsigned)(iwb[qq] + a_s[i]) < (unsigned)p.srcW;
+              v[qq] = valid ? __ldg(reinterpret_cast<const float4*>(srct + pixoff[qq]))
+                            : make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);   // NaN tag = "padding"
             }
-          }
-          // dY rows (output channels): up to 4 chunks of 4 channels per thread, two at a time
-          for (int ib = 0; ib < 4; ib += 2) {
-            float4 yb[2][4];
-            bool any = false;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              const int rc = rc0 + 16 * (ib + i);
-              const int co = n0 + rc * 4;
-              const bool rowok = rc * 4 < BN;
-              any = any || rowok;
-#pragma unroll
-              for (int qq = 0; qq < 4; ++qq) {
-                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (rowok && mok[qq] && co < p.Nout) {
-                  const float* src = p.dy + (size_t)(mbase + qq) * p.dy_ld + co;
-                  if (cfg.vec_dy && co + 3 < p.Nout) {
-                    t = __ldg(reinterpret_cast<const float4*>(src));
-                  } else {
-                    t.x = __ldg(src);
-                    if (co + 1 < p.Nout) t.y = __ldg(src + 1);
-                    if (co + 2 < p.Nout) t.z = __ldg(src + 2);
-                    if (co + 3 < p.Nout) t.w = __ldg(src + 3);
-                  }
-                }
-                yb[i][qq] = t;
-              }
-            }
-            if (!any) break;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              const int rc = rc0 + 16 * (ib + i);
-              if (rc * 4 < BN) {
-                const int row0 = rc * 4;
-                const float4 t0 = make_float4(yb[i][0].x, yb[i][1].x, yb[i][2].x, yb[i][3].x);
-                const float4 t1 = make_float4(yb[i][0].y, yb[i][1].y, yb[i][2].y, yb[i][3].y);
-                const float4 t2 = make_float4(yb[i][0].z, yb[i][1].z, yb[i][2].z, yb[i][3].z);
-                const float4 t3 = make_float4(yb[i][0].w, yb[i][1].w, yb[i][2].w, yb[i][3].w);
-                *reinterpret_cast<float4*>(b_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
-                *reinterpret_cast<float4*>(b_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
-                *reinterpret_cast<float4*>(b_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
-                *reinterpret_cast<float4*>(b_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
-              }
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            if (!a_ok[i]) continue;
+          };
+          auto finish_a = [&](int i, float4 (&v)[4]) {
+            float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
             if (has_aff) {
+              sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + a_c[i]));
+              sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + a_c[i]));
+            }
 #pragma unroll
-              for (int qq = 0; qq < 4; ++qq) {
-                if ((okm >> (i * 4 + qq)) & 1u) {
-                  float4 x = xa[i][qq];
-                  x.x = fmaf(x.x, a_sc[i].x, a_sh[i].x); x.y = fmaf(x.y, a_sc[i].y, a_sh[i].y);
-                  x.z = fmaf(x.z, a_sc[i].z, a_sh[i].z); x.w = fmaf(x.w, a_sc[i].w, a_sh[i].w);
-                  if (p.in_relu) {
-                    x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-                  }
-                  xa[i][qq] = x;
+            for (int qq = 0; qq < 4; ++qq) {
+              float4 x = v[qq];
+              if (x.x != x.x) {                     // padding tap: contributes zeros (never activated)
+                x = make_float4(0.f, 0.f, 0.f, 0.f);
+              } else if (has_aff) {
+                x.x = fmaf(x.x, sc.x, sh.x); x.y = fmaf(x.y, sc.y, sh.y);
+                x.z = fmaf(x.z, sc.z, sh.z); x.w = fmaf(x.w, sc.w, sh.w);
+                if (p.in_relu) {
+                  x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
                 }
               }
+              v[qq] = x;
             }
-            // 4x4 transpose in registers: row e <- channel e of the 4 pixels
-            const int row0 = (rc0 + 16 * i) * 4;
-            const float4 t0 = make_float4(xa[i][0].x, xa[i][1].x, xa[i][2].x, xa[i][3].x);
-            const float4 t1 = make_float4(xa[i][0].y, xa[i][1].y, xa[i][2].y, xa[i][3].y);
-            const float4 t2 = make_float4(xa[i][0].z, xa[i][1].z, xa[i][2].z, xa[i][3].z);
-            const float4 t3 = make_float4(xa[i][0].w, xa[i][1].w, xa[i][2].w, xa[i][3].w);
-            *reinterpret_cast<float4*>(a_stage + (row0 + 0) * 128 + ((pc ^ ((row0 + 0) & 7)) << 4)) = t0;
-            *reinterpret_cast<float4*>(a_stage + (row0 + 1) * 128 + ((pc ^ ((row0 + 1) & 7)) << 4)) = t1;
-            *reinterpret_cast<float4*>(a_stage + (row0 + 2) * 128 + ((pc ^ ((row0 + 2) & 7)) << 4)) = t2;
-            *reinterpret_cast<float4*>(a_stage + (row0 + 3) * 128 + ((pc ^ ((row0 + 3) & 7)) << 4)) = t3;
+            store4x4(a_stage, (rc0 + 8 * i) * 4, v);
+          };
+          auto load_b = [&](int i, float4 (&v)[4]) {
+            const int rc = rc0 + 8 * i;
+            const int co = n0 + rc * 4;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+              float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (mok[qq] && co < p.Nout) {
+                const float* src = p.dy + (size_t)(mbase + qq) * p.dy_ld + co;
+                if (cfg.vec_dy && co + 3 < p.Nout) {
+                  t = __ldg(reinterpret_cast<const float4*>(src));
+                } else {
+                  t.x = __ldg(src);
+                  if (co + 1 < p.Nout) t.y = __ldg(src + 1);
+                  if (co + 2 < p.Nout) t.z = __ldg(src + 2);
+                  if (co + 3 < p.Nout) t.w = __ldg(src + 3);
+                }
+              }
+              v[qq] = t;
+            }
+          };
+          // ---- issue: dY chunks 0,1 + A chunks 0,1; then A chunks 2,3 reuse the dY registers ----
+          float4 vb0[4], vb1[4], va0[4], va1[4];
+          const bool b0 = (rc0) * 4 < BN, b1 = (rc0 + 8) * 4 < BN;
+          if (b0) load_b(0, vb0);
+          if (b1) load_b(1, vb1);
+          if (a_ok[0]) load_a(0, va0);
+          if (a_ok[1]) load_a(1, va1);
+          if (b0) store4x4(b_stage, rc0 * 4, vb0);
+          if (b1) store4x4(b_stage, (rc0 + 8) * 4, vb1);
+          if (a_ok[2]) load_a(2, vb0);
+          if (a_ok[3]) load_a(3, vb1);
+          if (a_ok[0]) finish_a(0, va0);
+          if (a_ok[1]) finish_a(1, va1);
+          if (a_ok[2]) finish_a(2, vb0);
+          if (a_ok[3]) finish_a(3, vb1);
+          // wide outputs (BN > 64): remaining dY chunks, two at a time
+          for (int ib = 2; (rc0 + 8 * ib) * 4 < BN; ib += 2) {
+            load_b(ib, va0);
+            const bool more = (rc0 + 8 * (ib + 1)) * 4 < BN;
+            if (more) load_b(ib + 1, va1);
+            store4x4(b_stage, (rc0 + 8 * ib) * 4, va0);
+            if (more) store4x4(b_stage, (rc0 + 8 * (ib + 1)) * 4, va1);
           }
           fence_proxy_async_smem();
           mbar_arrive(&full_bar[stage]);
         }
-        ++q;
+        if (++q_grp == cfg.active_groups) q_grp = 0;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -351,8 +341,9 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   const int stage_bytes = WG_A_STAGE_BYTES + cfg.BN * WG_BK * 4;
   int stages = (224 * 1024) / stage_bytes;
   if (stages > 6) stages = 6;
-  if (stages < 2) stages = 2;     // >= number of producer groups (2): a group runs at most one ring-phase ahead
+  if (stages < 2) stages = 2;
   cfg.stages = stages;
+  cfg.active_groups = stages < 4 ? stages : 4;     // a group may run at most one ring-phase ahead of the MMA
   cfg.d_ohow = make_fastdiv((uint32_t)(p.OH * p.OW));
   cfg.d_ow = make_fastdiv((uint32_t)p.OW);
   cfg.d_c = make_fastdiv((uint32_t)p.srcC);

@@ -105,6 +105,7 @@ class _ConvFn(torch.autograd.Function):
         y = cn.conv_fprop(x, w, stride, pad, bias=bias, relu=relu, stats=stats, out_hw=out_hw)
         ctx.save_for_backward(x, w, y if relu else None)
         ctx.cfg = (stride, pad, relu, bias is not None)
+        ctx.params = (w, bias)
         return y
 
     @staticmethod
@@ -115,15 +116,23 @@ class _ConvFn(torch.autograd.Function):
         if relu:
             dy = torch.ops.aten.threshold_backward(dy, y, 0.0)
         dx = dw = db = None
+        wparam, bparam = ctx.params
         if has_bias and ctx.needs_input_grad[2]:
             co = dy.shape[-1]
-            db = _zeros(co, dy.device)
+            slot = _grad_slot(bparam)
+            db = slot if slot is not None else _zeros(co, dy.device)
             nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db), nat.stream_ptr()),
                       "dtf_colsum")
+            if slot is not None:
+                db = None
         if ctx.needs_input_grad[0]:
             dx = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
         if ctx.needs_input_grad[1]:
-            dw = cn.conv_wgrad(x, dy, w.shape, stride, pad)
+            slot = _grad_slot(wparam)
+            if slot is not None:
+                cn.conv_wgrad(x, dy, w.shape, stride, pad, out=slot)      # red.add straight into the flat buffer
+            else:
+                dw = cn.conv_wgrad(x, dy, w.shape, stride, pad)
         return dx, dw, db, None, None, None, None, None
 
 
@@ -184,8 +193,21 @@ def bn_stats(x: torch.Tensor) -> torch.Tensor:
     return st
 
 
-def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: bool, add=None):
-    """Shared BN(+ReLU) backward: returns (dx, dgamma, dbeta)."""
+def _grad_slot(p):
+    """The parameter's pre-allocated .grad (a view of the flat PS gradient buffer) when it can be accumulated
+    into directly — saves one elementwise add kernel per parameter per step."""
+    if p is None or not isinstance(p, torch.nn.Parameter):
+        return None
+    g = p.grad
+    if g is None or not g.is_contiguous() or g.shape != p.shape:
+        return None
+    return g
+
+
+def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: bool, add=None, gamma=None,
+                 beta=None):
+    """Shared BN(+ReLU) backward: returns (dx, dgamma, dbeta); dgamma/dbeta are None when they were accumulated
+    straight into the parameters' .grad."""
     c = x.shape[-1]
     m = x.numel() // c
     dx = torch.empty_like(x)
@@ -199,8 +221,13 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
     sums = _zeros(2 * c, x.device)
     nat.check(nat.lib().dtf_bn_bwd_reduce(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m),
                                           c, c, c, _p(sums), nat.stream_ptr()), "dtf_bn_bwd_reduce")
-    dg = torch.empty(c, dtype=torch.float32, device=x.device) if has_gamma else None
-    db = torch.empty(c, dtype=torch.float32, device=x.device) if has_beta else None
+    gslot, bslot = _grad_slot(gamma), _grad_slot(beta)
+    direct = coef.training and (not has_gamma or gslot is not None) and (not has_beta or bslot is not None)
+    if direct:
+        dg, db = gslot if has_gamma else None, bslot if has_beta else None
+    else:
+        dg = torch.zeros(c, dtype=torch.float32, device=x.device) if has_gamma else None
+        db = torch.zeros(c, dtype=torch.float32, device=x.device) if has_beta else None
     if coef.training:
         nat.check(nat.lib().dtf_bn_bwd_apply(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), _p(coef.mean),
                                              _p(coef.invstd), _p(sums), int(relu), C.c_longlong(m), c, c, c, c,
@@ -212,6 +239,8 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
         if dg is not None:
             # d/dgamma of gamma*invstd*(x-mean): invstd * (sum g*x - mean * sum g), with moving statistics
             dg.copy_(coef.invstd_eval * (sums[c:] - coef.mean_eval * sums[:c]))
+    if direct:
+        return dx, None, None
     return dx, dg, db
 
 
@@ -238,12 +267,14 @@ class _BnApplyFn(torch.autograd.Function):
         ctx.save_for_backward(x)
         ctx.coef, ctx.relu = coef, relu
         ctx.has = (gamma is not None, beta is not None)
+        ctx.params = (gamma, beta)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
-        dx, dg, db = _bn_backward(dy.contiguous(), x, ctx.coef, ctx.relu, ctx.has[0], ctx.has[1])
+        dx, dg, db = _bn_backward(dy.contiguous(), x, ctx.coef, ctx.relu, ctx.has[0], ctx.has[1],
+                                  gamma=ctx.params[0], beta=ctx.params[1])
         return dx, dg, db, None, None
 
 
@@ -286,6 +317,7 @@ class _BnReluConvFn(torch.autograd.Function):
         ctx.save_for_backward(x, w)
         ctx.coef = coef
         ctx.cfg = (stride, pad, residual is not None)
+        ctx.params = (gamma, beta, w)
         return y
 
     @staticmethod
@@ -293,10 +325,16 @@ class _BnReluConvFn(torch.autograd.Function):
         x, w = ctx.saved_tensors
         stride, pad, has_res = ctx.cfg
         coef = ctx.coef
+        gamma, beta, wparam = ctx.params
         dy = dy.contiguous()
-        dw = cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
+        slot = _grad_slot(wparam)
+        dw = None
+        if slot is not None:
+            cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True, out=slot)
+        else:
+            dw = cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
         da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
-        dx, dg, db = _bn_backward(da, x, coef, True, True, True)
+        dx, dg, db = _bn_backward(da, x, coef, True, True, True, gamma=gamma, beta=beta)
         return dx, dg, db, dw, (dy if has_res else None), None, None, None, None, None
 
 

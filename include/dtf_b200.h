@@ -119,7 +119,7 @@ int dtf_affine_act(const float* x, const float* scale, const float* shift, int r
 /* sums[0..C) += sum g, sums[C..2C) += sum g*x with g = dy * [x*scale+shift > 0] (when relu) */
 int dtf_bn_bwd_reduce(const float* dy, const float* x, const float* scale, const float* shift, int relu,
                       long long M, int C, int ld_x, int ld_dy, float* sums, void* stream);
-/* dx (+= add) from the reduced sums; also writes dgamma / dbeta (either may be NULL) */
+/* dx (+= add) from the reduced sums; dgamma / dbeta (either may be NULL) are ACCUMULATED into */
 int dtf_bn_bwd_apply(const float* dy, const float* x, const float* scale, const float* shift, const float* mean,
                      const float* invstd, const float* sums, int relu, long long M, int C, int ld_x, int ld_dy,
                      int ld_dx, const float* add, int ld_add, float* dx, float* dgamma, float* dbeta, void* stream);
