@@ -48,14 +48,16 @@ struct GemmCfg {
   int vec_out;     // 16-byte stores allowed
   int vec_res;
   FastDiv d_ohow, d_ow, d_c, d_s, d_divh, d_divw;
+  long long* trace;  // optional timeline buffer (debug)
 };
 
-// Optional timeline trace (debug / profiling aid): when armed through dtf_debug_set_trace, CTA 0 stamps
-// globaltimer-free SM clocks at the pipeline hand-offs of its first tile into a caller buffer.
-__device__ long long* g_trace = nullptr;
-__device__ __forceinline__ void trace_stamp(int slot) {
-  if (g_trace != nullptr && blockIdx.x == 0 && slot < 4096) g_trace[slot] = clock64();
-}
+// Optional timeline trace (debug / profiling aid): when armed through dtf_debug_set_trace, CTA 0 stamps SM
+// clocks at the pipeline hand-offs of its first tile into a caller buffer (scripts/trace_conv.py).
+static long long* g_trace_host = nullptr;     // armed by dtf_debug_set_trace, passed to the kernel in GemmCfg
+#define trace_stamp(slot)                                                              \
+  do {                                                                                 \
+    if (cfg.trace != nullptr && blockIdx.x == 0 && (slot) < 4096) cfg.trace[(slot)] = clock64(); \
+  } while (0)
 
 __device__ __forceinline__ bool tap_live_1d(int r, int a, int b, int c, int div, int O, int srcDim) {
   const int lo = b + r * c;
@@ -96,7 +98,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* csum = reinterpret_cast<float*>(tmem_slot + 4);   // [256]
   float* csq = csum + 256;                                 // [256]
-  int4* row_table = reinterpret_cast<int4*>(csq + 256);    // [PRODUCER_GROUPS][BM]
+  int2* row_table = reinterpret_cast<int2*>(csq + 256);    // [PRODUCER_GROUPS][BM]
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -149,7 +151,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
     const int rgrp = gt >> 3;                // rows rgrp*16 .. rgrp*16+15
     const bool has_aff = p.in_scale != nullptr;
     const bool div1 = (p.div_h == 1) && (p.div_w == 1);
-    int4* rtab = row_table + grp * BM;
+    int2* rtab = row_table + grp * BM;
     int q = 0, q_grp = 0, stage = 0; uint32_t phase = 0;
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -161,15 +163,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       for (int rr = 0; rr < 2; ++rr) {
         const int row = gt * 2 + rr;
         const int m = m0 + row;
-        int4 e = make_int4(0, -(1 << 24), -(1 << 24), 0);
+        // entry = { element offset of the row's origin pixel (div1) | pixel index of its image (strided dgrad),
+        //           (ih0 << 16) | (iw0 & 0xffff) }   — ih0 = -32768 marks a row past the end of the tensor
+        int2 e = make_int2(0, (int)0x80000000);
         if (m < cfg.M) {
           const int img = (int)fdiv((uint32_t)m, cfg.d_ohow);
           const int rem = m - img * p.OH * p.OW;
           const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
           const int ow = rem - oh * p.OW;
-          e.y = oh * p.a_h + p.b_h;
-          e.z = ow * p.a_w + p.b_w;
-          if (div1) e.x = ((img * p.srcH + e.y) * p.srcW + e.z) * p.src_ld;   // may be "negative": only used when valid
+          const int ih0 = oh * p.a_h + p.b_h, iw0 = ow * p.a_w + p.b_w;
+          e.y = (ih0 << 16) | (iw0 & 0xffff);
+          if (div1) e.x = ((img * p.srcH + ih0) * p.srcW + iw0) * p.src_ld;   // may be "negative": only used when valid
           else e.x = img * p.srcH * p.srcW;                                 // pixel index of the image origin
         }
         rtab[row] = e;
@@ -192,7 +196,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
           }
           const int k = kb * BK + j * 4;
           const bool kvalid = k < cfg.Ktot;
-          int c = 0, dh = -(1 << 24), dw = 0;
+          int c = 0, dh = -(1 << 20), dw = 0;
           float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
           if (kvalid) {
             const int tap = (int)fdiv((uint32_t)k, cfg.d_c);
@@ -208,26 +212,55 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
           }
           float4 v[ROWS_PER_THREAD];
           uint32_t okmask = 0;
-          const int4* rt = rtab + rgrp * ROWS_PER_THREAD;
-          if (div1) {
+          const int2* rt = rtab + rgrp * ROWS_PER_THREAD;
+          if (div1 && !has_aff) {
+            // ---- asynchronous path (no fused activation): LDGSTS straight into the swizzled tile ----
             const int tap_off = (dh * p.srcW + dw) * p.src_ld + c;
-            const float* srcc = p.src + tap_off;
+            const uint32_t a_base = smem_u32(a_stage) + (uint32_t)(rgrp * ROWS_PER_THREAD) * 128u;
+            // phase 1 (plain ALU + LDS, freely schedulable): element offsets and validity bits
+            int off[ROWS_PER_THREAD];
 #pragma unroll
             for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-              const int4 e = rt[i];
-              const bool valid = (unsigned)(e.y + dh) < (unsigned)p.srcH && (unsigned)(e.z + dw) < (unsigned)p.srcW;
+              const int2 e = rt[i];
+              const int ih = (e.y >> 16) + dh;
+              const int iw = (int)(short)(e.y & 0xffff) + dw;
+              const bool valid = (unsigned)ih < (unsigned)p.srcH && (unsigned)iw < (unsigned)p.srcW;
+              if (valid) okmask |= 1u << i;
+              off[i] = valid ? e.x + tap_off : 0;
+            }
+            // phase 2: sixteen LDGSTS back to back
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_THREAD; ++i)
+              cp_async_16(a_base + (uint32_t)i * 128u + (uint32_t)((j ^ (i & 7)) << 4), p.src + off[i],
+                          ((okmask >> i) & 1u) ? 16u : 0u);
+            if (tr) trace_stamp(16 + 8 * (q >> 2) + 2);
+            cp_async_mbar_arrive_noinc(&full_bar[stage]);
+            if (tr) trace_stamp(16 + 8 * (q >> 2) + 3);
+          } else {
+          if (div1) {
+            // phase 1: table -> 32-bit element offsets + validity bits (cheap ALU, no long-latency dependence)
+            const int tap_off = (dh * p.srcW + dw) * p.src_ld + c;
+            int off[ROWS_PER_THREAD];
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+              const int2 e = rt[i];
+              const int ih = (e.y >> 16) + dh;
+              const int iw = (int)(short)(e.y & 0xffff) + dw;
+              if ((unsigned)ih < (unsigned)p.srcH && (unsigned)iw < (unsigned)p.srcW) okmask |= 1u << i;
+              off[i] = e.x + tap_off;
+            }
+            // phase 2: all loads back to back
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_THREAD; ++i) {
               float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (valid) {
-                x = __ldg(reinterpret_cast<const float4*>(srcc + e.x));
-                okmask |= 1u << i;
-              }
+              if ((okmask >> i) & 1u) x = __ldg(reinterpret_cast<const float4*>(p.src + off[i]));
               v[i] = x;
             }
           } else {
 #pragma unroll
             for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-              const int4 e = rt[i];
-              const int ihn = e.y + dh, iwn = e.z + dw;
+              const int2 e = rt[i];
+              const int ihn = (e.y >> 16) + dh, iwn = (int)(short)(e.y & 0xffff) + dw;
               const int ih = (int)fdiv((uint32_t)(ihn < 0 ? 0 : ihn), cfg.d_divh);
               const int iw = (int)fdiv((uint32_t)(iwn < 0 ? 0 : iwn), cfg.d_divw);
               const bool valid = ihn >= 0 && iwn >= 0 && ih * p.div_h == ihn && iw * p.div_w == iwn &&
@@ -258,6 +291,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
           fence_proxy_async_smem();
           if (tr) trace_stamp(16 + 8 * (q >> 2) + 3);
           mbar_arrive(&full_bar[stage]);
+          }
         }
         ++q;
         if (++q_grp == cfg.active_groups) q_grp = 0;
@@ -267,6 +301,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   } else if (warp == MMA_WARP) {
     // =========================== MMA issuer ================================================
     const uint32_t idesc = make_idesc_tf32(BM, (uint32_t)BN);
+    const uint64_t adesc0 = make_desc_k_sw128(smem_u32(sA));
+    const uint64_t bdesc0 = make_desc_k_sw128(smem_u32(sB));
     int stage = 0; uint32_t phase = 0;
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
@@ -282,24 +318,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
         if (!kb_live(p, cfg, kb)) continue;
         mbar_wait(&full_bar[stage], phase);
         if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 4);
+        if (tr && seq < 512) trace_stamp(2048 + 2 * seq);
         tc_fence_after();
-        if (lane == 0) {
-          const uint64_t adesc = make_desc_k_sw128(smem_u32(sA + stage * A_STAGE_BYTES));
-          const uint64_t bdesc = make_desc_k_sw128(smem_u32(sB + stage * b_stage_bytes));
+        {
+          // descriptors are warp-uniform (derived from `stage` only): compute them outside the elected branch so
+          // they can live in uniform registers instead of being broadcast per MMA
+          const uint64_t adesc = adesc0 + (uint64_t)((uint32_t)(stage * A_STAGE_BYTES) >> 4);
+          const uint64_t bdesc = bdesc0 + (uint64_t)((uint32_t)(stage * b_stage_bytes) >> 4);
+          if (elect_one()) {        // elect.sync: the compiler knows exactly one lane issues (no waterfall loops)
 #pragma unroll
-          for (int kk = 0; kk < BK / 8; ++kk) {
-            umma_tf32_ss(d_tmem, desc_advance(adesc, kk * 32), desc_advance(bdesc, kk * 32), idesc, accumulate);
-            accumulate = 1;
+            for (int kk = 0; kk < BK / 8; ++kk) {
+              umma_tf32_ss(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, accumulate);
+              accumulate = 1;
+            }
+            umma_commit(&empty_bar[stage]);
+            if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 5);
+            if (tr && seq < 512) trace_stamp(2049 + 2 * seq);
           }
-          umma_commit(&empty_bar[stage]);
-          if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 5);
         }
         __syncwarp();
         accumulate = 1;
         ++seq;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
-      if (lane == 0) umma_commit(&tfull_bar[acc]);
+      if (elect_one()) umma_commit(&tfull_bar[acc]);
       __syncwarp();
     }
   } else {
@@ -475,7 +517,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.num_kb = ceil_div(cfg.Ktot, BK);
   cfg.tmem_cols = next_pow2_cols(2 * cfg.BN);
   const int stage_bytes = A_STAGE_BYTES + cfg.BN * BK * 4;
-  const int fixed_smem = 1024 + 16 * 2 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int4);
+  const int fixed_smem = 1024 + 16 * 2 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int2);
   int stages = (227 * 1024 - fixed_smem) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages > cfg.num_kb + 1) stages = cfg.num_kb + 1;
@@ -499,6 +541,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.d_s = make_fastdiv((uint32_t)p.S);
   cfg.d_divh = make_fastdiv((uint32_t)p.div_h);
   cfg.d_divw = make_fastdiv((uint32_t)p.div_w);
+  cfg.trace = g_trace_host;
   cfg.vec_out = (p.out_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
   cfg.vec_res = p.residual && (p.res_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0);
 
@@ -506,7 +549,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   if (!tm) return -2;
 
   const size_t smem = 1024 + (size_t)stages * stage_bytes + (2 * stages + 4) * sizeof(uint64_t) + 16 + 2 * 256 * 4 +
-                      PRODUCER_GROUPS * BM * sizeof(int4);
+                      PRODUCER_GROUPS * BM * sizeof(int2);
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -522,7 +565,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
 }
 
 extern "C" int dtf_debug_set_trace(long long* buf) {
-  DTF_CHECK(cudaMemcpyToSymbol(g_trace, &buf, sizeof(buf)));
+  g_trace_host = buf;
   return 0;
 }
 

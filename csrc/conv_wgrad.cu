@@ -231,6 +231,8 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
   } else if (warp == WG_MMA_WARP) {
     // =========================== MMA issuer ================================================
     const uint32_t idesc = make_idesc_tf32(WG_BM, (uint32_t)BN);
+    const uint64_t adesc0 = make_desc_k_sw128(smem_u32(sA));
+    const uint64_t bdesc0 = make_desc_k_sw128(smem_u32(sB));
     int stage = 0; uint32_t phase = 0;
     int local = 0;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++local) {
@@ -247,21 +249,23 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint64_t adesc = make_desc_k_sw128(smem_u32(sA + stage * WG_A_STAGE_BYTES));
-          const uint64_t bdesc = make_desc_k_sw128(smem_u32(sB + stage * b_stage_bytes));
+        {
+          const uint64_t adesc = adesc0 + (uint64_t)((uint32_t)(stage * WG_A_STAGE_BYTES) >> 4);
+          const uint64_t bdesc = bdesc0 + (uint64_t)((uint32_t)(stage * b_stage_bytes) >> 4);
+          if (elect_one()) {        // elect.sync: one known issuing lane => descriptors stay in uniform registers
 #pragma unroll
-          for (int kk = 0; kk < WG_BK / 8; ++kk) {
-            umma_tf32_ss(d_tmem, desc_advance(adesc, kk * 32), desc_advance(bdesc, kk * 32), idesc, accumulate);
-            accumulate = 1;
+            for (int kk = 0; kk < WG_BK / 8; ++kk) {
+              umma_tf32_ss(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, accumulate);
+              accumulate = 1;
+            }
+            umma_commit(&empty_bar[stage]);
           }
-          umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
         accumulate = 1;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
-      if (lane == 0) umma_commit(&tfull_bar[acc]);
+      if (elect_one()) umma_commit(&tfull_bar[acc]);
       __syncwarp();
     }
   } else {

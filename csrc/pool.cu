@@ -159,6 +159,39 @@ avg_pool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, PoolGe
   }
 }
 
+// Global average pool (window == whole map, e.g. the 8x8 heads of ResNet / Inception): one block per image,
+// thread (slice, chunk) sums a strided subset of the pixels for 4 channels, slices are combined in smem.
+__global__ void __launch_bounds__(256)
+global_avg_pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int HW, int C, int ld_in, int ld_out) {
+  extern __shared__ float4 part[];            // [slices][chunks]
+  const int chunks = C >> 2;
+  const int n = blockIdx.x;
+  const float inv = 1.f / (float)HW;
+  for (int c0 = 0; c0 < chunks; c0 += 256) {
+    const int cw = chunks - c0 < 256 ? chunks - c0 : 256;       // chunks handled in this pass
+    const int slices = 256 / cw;
+    const int cc = threadIdx.x % cw, sl = threadIdx.x / cw;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (sl < slices) {
+      for (int p = sl; p < HW; p += slices) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(x + ((long long)n * HW + p) * ld_in) + c0 + cc);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+      part[sl * cw + cc] = a;
+    }
+    __syncthreads();
+    if (sl == 0) {
+      for (int k = 1; k < slices; ++k) {
+        const float4 v = part[k * cw + cc];
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+      a.x *= inv; a.y *= inv; a.z *= inv; a.w *= inv;
+      reinterpret_cast<float4*>(y + (long long)n * ld_out)[c0 + cc] = a;
+    }
+    __syncthreads();
+  }
+}
+
 static int pool_grid(long long total4) {
   long long b = (total4 + 255) / 256;
   const long long cap = 16LL * num_sms();
@@ -204,6 +237,12 @@ extern "C" int dtf_avg_pool_fwd(const dtf_pool_params* p, const float* x, float*
   DTF_REQUIRE(p->C % 4 == 0 && p->ld_in % 4 == 0 && p->ld_out % 4 == 0, "channels / pitches must be multiples of 4");
   const long long total4 = (long long)p->N * p->OH * p->OW * (p->C / 4);
   if (total4 == 0) return 0;
+  if (p->OH == 1 && p->OW == 1 && p->kh == p->H && p->kw == p->W && p->ph == 0 && p->pw == 0) {
+    global_avg_pool_fwd_kernel<<<p->N, 256, 256 * sizeof(float4), stream>>>(x, y, p->H * p->W, p->C, p->ld_in,
+                                                                           p->ld_out);
+    DTF_CHECK(cudaGetLastError());
+    return 0;
+  }
   avg_pool_fwd_kernel<<<pool_grid(total4), 256, 0, stream>>>(x, y, make_geom(*p), total4);
   DTF_CHECK(cudaGetLastError());
   return 0;

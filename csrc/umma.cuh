@@ -82,6 +82,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ---------------------------------------------------------------------------------------
+// cp.async (LDGSTS): 16-byte global -> shared copies that bypass registers.  src_bytes = 0 zero-fills.
+// Completion is reported straight to an mbarrier (no proxy fence, no register staging), which is what lets a
+// gather producer run several pipeline stages ahead of the tensor core.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* gsrc, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+// The barrier receives one arrival from this thread once all of its prior cp.async copies have landed
+// (.noinc: that arrival is one of the barrier's expected arrivals).
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------
 // TMA
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {

@@ -21,3 +21,5 @@ for name, (n, h, c, co) in {"64ch_8x8_b128": (128, 8, 64, 64), "16ch_32x32_b128"
         b = 16 + 8 * kb
         if t[b] == 0: break
         print(f" {kb:2d} | {t[b]-t0:8d} {t[b+1]-t0:8d} {t[b+2]-t0:8d} {t[b+3]-t0:8d} | {t[b+4]-t0:8d} {t[b+5]-t0:8d}")
+    mm = [(t[2048 + 2 * i] - t0, t[2049 + 2 * i] - t0) for i in range(24) if t[2048 + 2 * i]]
+    print(" MMA per k-block (full_ok, committed):", mm)
