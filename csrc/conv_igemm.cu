@@ -414,8 +414,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
         }
         if (do_stats) {
           float sq[16];
+          if (p.bnb_x != nullptr) {
+            // fused BN-backward reduction: g = d(act) * [bn(x) > 0];  accumulate sum g and sum g*x
+            const float* xrow = p.bnb_x + (size_t)m * p.bnb_ld + nb;
 #pragma unroll
-          for (int e = 0; e < 16; ++e) sq[e] = v[e] * v[e];
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const int n = nb + q4 * 4;
+              float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
+              float4 sc = xv, sh = xv;
+              if (mvalid && n + 3 < p.Nout) {
+                xv = __ldg(reinterpret_cast<const float4*>(xrow + q4 * 4));
+                sc = __ldg(reinterpret_cast<const float4*>(p.bnb_scale + n));
+                sh = __ldg(reinterpret_cast<const float4*>(p.bnb_shift + n));
+              }
+              const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+              const float ss[4] = {sc.x, sc.y, sc.z, sc.w};
+              const float hs[4] = {sh.x, sh.y, sh.z, sh.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float g = fmaf(xs[e], ss[e], hs[e]) > 0.f ? v[q4 * 4 + e] : 0.f;
+                v[q4 * 4 + e] = g;
+                sq[q4 * 4 + e] = g * xs[e];
+              }
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) sq[e] = v[e] * v[e];
+          }
           int col;
           const float s1 = warp_colsum16(v, lane, col);
           const float s2 = warp_colsum16(sq, lane, col);
@@ -506,6 +531,10 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   DTF_REQUIRE(p.Nout >= 1 && p.R >= 1 && p.S >= 1, "bad shape");
   DTF_REQUIRE((long long)p.N * p.srcH * p.srcW * p.src_ld < (1LL << 31), "source tensor too large for 32-bit offsets");
   if (p.in_scale) DTF_REQUIRE(p.in_shift != nullptr, "in_scale without in_shift");
+  if (p.bnb_x) {
+    DTF_REQUIRE(p.stats && p.bnb_scale && p.bnb_shift, "fused BN-backward reduction needs stats/scale/shift");
+    DTF_REQUIRE(p.Nout % 4 == 0 && p.bnb_ld % 4 == 0, "fused BN-backward reduction needs C % 4 == 0");
+  }
 
   GemmCfg cfg;
   cfg.Ktot = p.R * p.S * p.srcC;

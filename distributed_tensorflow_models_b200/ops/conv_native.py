@@ -64,14 +64,19 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
     p.res_ld = _pitch(residual) if residual is not None else 0
     p.out_relu = int(relu)
     p.stats = nat.ptr(stats)
+    p.bnb_x = p.bnb_scale = p.bnb_shift = None
+    p.bnb_ld = 0
     nat.check(nat.lib().dtf_conv_gemm(C.byref(p), nat.stream_ptr()), "dtf_conv_gemm(fprop)")
     return out
 
 
 def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
-               pad: Tuple[int, int], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+               pad: Tuple[int, int], out: Optional[torch.Tensor] = None, bn_bwd=None) -> torch.Tensor:
     """dx = conv_transpose(dy, w).  ``w_t`` is the dgrad operand ``[C_in, R, S, C_out]``
-    (``weight_transpose`` of the OHWI weights)."""
+    (``weight_transpose`` of the OHWI weights).
+
+    ``bn_bwd = (x, scale, shift, sums)``: the layer's forward input was ``relu(x*scale+shift)``; the epilogue
+    then also accumulates ``sum g`` / ``sum g*x`` (g = dx masked by the ReLU) into ``sums`` (2*C_in floats)."""
     n, p_, q_, co = dy.shape
     ci, r, s, co2 = w_t.shape
     assert co2 == co and w_t.is_contiguous()
@@ -99,6 +104,13 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
     p.res_ld = 0
     p.out_relu = 0
     p.stats = None
+    p.bnb_x = p.bnb_scale = p.bnb_shift = None
+    p.bnb_ld = 0
+    if bn_bwd is not None:
+        bx, bsc, bsh, sums = bn_bwd
+        p.bnb_x, p.bnb_ld = bx.data_ptr(), _pitch(bx)
+        p.bnb_scale, p.bnb_shift = bsc.data_ptr(), bsh.data_ptr()
+        p.stats = sums.data_ptr()
     nat.check(nat.lib().dtf_conv_gemm(C.byref(p), nat.stream_ptr()), "dtf_conv_gemm(dgrad)")
     return out
 

@@ -205,7 +205,7 @@ def _grad_slot(p):
 
 
 def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: bool, add=None, gamma=None,
-                 beta=None):
+                 beta=None, sums=None):
     """Shared BN(+ReLU) backward: returns (dx, dgamma, dbeta); dgamma/dbeta are None when they were accumulated
     straight into the parameters' .grad."""
     c = x.shape[-1]
@@ -218,9 +218,11 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
         if add is not None:
             dx = dx + add
         # frozen statistics: dgamma/dbeta via the same reduction
-    sums = _zeros(2 * c, x.device)
-    nat.check(nat.lib().dtf_bn_bwd_reduce(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m),
-                                          c, c, c, _p(sums), nat.stream_ptr()), "dtf_bn_bwd_reduce")
+    if sums is None:          # (the dgrad epilogue may already have produced the reductions)
+        sums = _zeros(2 * c, x.device)
+        nat.check(nat.lib().dtf_bn_bwd_reduce(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu),
+                                              C.c_longlong(m), c, c, c, _p(sums), nat.stream_ptr()),
+                  "dtf_bn_bwd_reduce")
     gslot, bslot = _grad_slot(gamma), _grad_slot(beta)
     direct = coef.training and (not has_gamma or gslot is not None) and (not has_beta or bslot is not None)
     if direct:
@@ -333,8 +335,10 @@ class _BnReluConvFn(torch.autograd.Function):
             cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True, out=slot)
         else:
             dw = cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
-        da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
-        dx, dg, db = _bn_backward(da, x, coef, True, True, True, gamma=gamma, beta=beta)
+        sums = _zeros(2 * x.shape[-1], x.device)
+        da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad,
+                           bn_bwd=(x, coef.scale, coef.shift, sums))
+        dx, dg, db = _bn_backward(da, x, coef, True, True, True, gamma=gamma, beta=beta, sums=sums)
         return dx, dg, db, dw, (dy if has_res else None), None, None, None, None, None
 
 

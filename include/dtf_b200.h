@@ -41,7 +41,8 @@ const char* dtf_last_error(void);
  *   act(x) = in_relu ? max(x*in_scale[c] + in_shift[c], 0) : x*in_scale[c] + in_shift[c]
  *            when in_scale != NULL (fused batch-norm apply of the producer layer).
  *   epilogue: + bias[n], + residual[m, n], ReLU, per-channel sum / sum-of-squares of the
- *             stored value into stats[0..Nout) / stats[Nout..2Nout) (atomic adds).
+ *             stored value into stats[0..Nout) / stats[Nout..2Nout) (atomic adds); or, for dgrad,
+ *             the batch-norm backward reductions of the layer below (see bnb_x).
  */
 typedef struct {
   const float* src; int srcH, srcW, srcC, src_ld;
@@ -55,6 +56,10 @@ typedef struct {
   const float* in_scale; const float* in_shift; int in_relu;
   const float* bias; const float* residual; int res_ld; int out_relu;
   float* stats;
+  /* dgrad + fused batch-norm backward reduction: when bnb_x != NULL the kernel output is d(act) for a layer
+   * whose forward input was act = relu(bnb_x*bnb_scale + bnb_shift); `stats` then receives
+   * sum_m g and sum_m g*x with g = out * [act > 0] (the two reductions dtf_bn_bwd_apply needs). */
+  const float* bnb_x; int bnb_ld; const float* bnb_scale; const float* bnb_shift;
 } dtf_conv_gemm_params;
 
 int dtf_conv_gemm(const dtf_conv_gemm_params* p, void* stream);

@@ -164,3 +164,26 @@ def test_fused_update_matches_reference():
             opts.append(o)
         assert _rel(opts[0].w.cpu(), opts[1].w) < 1e-5
         assert _rel(opts[0].ema.cpu(), opts[1].ema) < 1e-5
+
+
+def test_dgrad_epilogue_bn_backward_sums_match_reduce_kernel():
+    """The fused BN-backward reductions of the dgrad epilogue equal the stand-alone reduce kernel."""
+    import ctypes as C
+    from distributed_tensorflow_models_b200 import _native as nat
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    n, h, w, ci, co = 8, 16, 16, 32, 64
+    x = _r(n, h, w, ci, seed=1)
+    wt = _r(co, 3, 3, ci, seed=2, scale=0.05)
+    dy = _r(n, h, w, co, seed=3)
+    scale, shift = _r(ci, seed=4).abs() + 0.5, _r(ci, seed=5) * 0.3
+    w_t = cn.weight_transpose(wt)
+    sums = torch.zeros(2 * ci, device="cuda")
+    da = cn.conv_dgrad(dy, w_t, (h, w), (1, 1), (1, 1), bn_bwd=(x, scale, shift, sums))
+    ref = torch.zeros(2 * ci, device="cuda")
+    vp = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    nat.check(nat.lib().dtf_bn_bwd_reduce(vp(da), vp(x), vp(scale), vp(shift), 1, C.c_longlong(n * h * w), ci, ci, ci,
+                                          vp(ref), nat.stream_ptr()), "reduce")
+    torch.cuda.synchronize()
+    assert _rel(sums, ref) < 1e-4
+    mask = (x * scale + shift > 0).float()
+    assert _rel(sums[:ci], (da * mask).reshape(-1, ci).sum(0)) < 1e-4
