@@ -93,12 +93,26 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def _protect_stdout():
+    """Route everything libraries print to stdout (e.g. NCCL's version banner) to stderr, and return a
+    writer for the real stdout so that exactly ONE line — the JSON result — appears there."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
+
+    def emit(line: str) -> None:
+        os.write(real, (line + "\n").encode())
+    return emit
+
+
 def main():
     args = parse()
+    emit = _protect_stdout()
     if args.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable":
-                          "reference is Python-2/TensorFlow-1.x (tf.contrib.slim, Supervisor, SyncReplicasOptimizer, "
-                          "thrift) with no setup.py; it cannot be installed or run offline on this image (DESIGN.md)"}))
+        emit(json.dumps({"impl": "reference", "unavailable":
+                         "reference is Python-2/TensorFlow-1.x (tf.contrib.slim, Supervisor, SyncReplicasOptimizer, "
+                         "thrift) with no setup.py; it cannot be installed or run offline on this image (DESIGN.md)"}))
         return 0
 
     import torch
@@ -215,7 +229,7 @@ def main():
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": last_loss,
             "impl": "ours",
         }
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if world > 1:
         comm.finish()
         dist.destroy_process_group()
