@@ -204,45 +204,49 @@ ps_async_step_kernel(const AsyncArgs a) {
   const Hyper h = load_hyper(a.hyper);
   const int W = a.W, me = a.rank;
   const long long total = a.shard * W;
+  float* mine = a.peer_params[me];
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd_system(a.global_step, 1ull);
-  // ---- push: apply my gradient to every owner's master range (owner order staggered by rank) -----------
+  // ---- push: apply my gradient to every owner's master range (owner order staggered by rank).
+  // Only one-way traffic crosses NVLink for SGD: the weight-decay term uses this worker's replica of w (what
+  // the gradient was computed from), so the update is a single red.global.add.f32 per element on the owner.
   for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total;
        j += (long long)gridDim.x * blockDim.x) {
     const int k = (int)(j / a.shard);
     const long long i = j - (long long)k * a.shard;
     const int owner = (me + k) % W;
     const long long gi = (long long)owner * a.shard + i;
-    float* wp = a.peer_params[owner] + gi;
-    const float w = *wp;
     float g = a.grads[gi] * h.gscale;
-    if (gi < a.wd_boundary) g = fmaf(h.wd, w, g);
-    float nw;
+    if (gi < a.wd_boundary) g = fmaf(h.wd, mine[gi], g);
+    float* wp = a.peer_params[owner] + gi;
     if (a.kind == 0) {
-      atomicAdd(wp, -h.lr * g);                       // one-sided red.add on the owner's HBM
-      nw = w - h.lr * g;
+      atomicAdd(wp, -h.lr * g);                       // one-sided red.add on the owner's HBM (Hogwild)
     } else {
-      float* msp = a.peer_ms[owner] + i;
-      float* mop = a.peer_mom[owner] + i;
+      float* msp = a.peer_ms[owner] + i;              // slots live with the owner; racy RMW is the semantics
+      float* mop = a.peer_mom[owner] + i;             // of use_locking=False
       const float m2 = h.rms_decay * (*msp) + (1.f - h.rms_decay) * g * g;
       const float mo = h.momentum * (*mop) + h.lr * g * rsqrtf(m2 + h.eps);
       *msp = m2;
       *mop = mo;
       atomicAdd(wp, -mo);
-      nw = w - mo;
-    }
-    if (a.peer_ema && h.ema_decay >= 0.f) {
-      float* ep = a.peer_ema[owner] + i;
-      *ep -= (1.f - h.ema_decay) * (*ep - nw);
     }
   }
   // ---- pull: refresh my replica from the masters (no barrier: stale reads are the semantics) ------------
   __threadfence_system();
-  float* mine = a.peer_params[me];
   for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total;
        j += (long long)gridDim.x * blockDim.x) {
     const int owner = (int)(j / a.shard);
     if (owner == me) continue;
     mine[j] = *reinterpret_cast<volatile const float*>(a.peer_params[owner] + j);
+  }
+  // ---- EMA of my own range, owner side (local traffic only).  The reference applies the average after
+  // every worker's step; the owner sees W such steps per step of its own, so the host passes decay^W.
+  if (a.peer_ema && h.ema_decay >= 0.f) {
+    float* ema = a.peer_ema[me];
+    const float* wm = mine + (long long)me * a.shard;
+    const float k = 1.f - h.ema_decay;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.shard;
+         i += (long long)gridDim.x * blockDim.x)
+      ema[i] -= k * (ema[i] - wm[i]);
   }
 }
 
