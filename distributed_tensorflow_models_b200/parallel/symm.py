@@ -105,11 +105,11 @@ class SymmComm(Comm):
         self.dist.barrier(group=self.group)
 
     # ------------------------------------------------------------------------------------------
-    def _hyper(self, lr, grad_scale, num_updates):
+    def _hyper(self, lr, grad_scale, num_updates, ema_power: int = 1):
         from ..ops import native_ops
         d = -1.0
         if self.opt.ema is not None:
-            d = _ema_decay(self.cfg.ema.decay, num_updates if self.cfg.ema.use_num_updates else None)
+            d = _ema_decay(self.cfg.ema.decay, num_updates if self.cfg.ema.use_num_updates else None) ** ema_power
         return native_ops.set_hyper(self.opt, lr, grad_scale, d)
 
     def bsp_step(self, lr, grad_scale=1.0):
@@ -126,7 +126,7 @@ class SymmComm(Comm):
         return self._gs
 
     def async_step(self, lr, grad_scale=1.0):
-        h = self._hyper(lr, grad_scale, self._gs)
+        h = self._hyper(lr, grad_scale, self._gs, ema_power=self.world)
         kind = 0 if self.cfg.kind == "sgd" else 1
         has_ema = self.opt.ema is not None
         nat.check(nat.lib().dtf_ps_async_step(_p(self.layout.grads), _p(self.t_params),
