@@ -28,9 +28,11 @@ constexpr int BM = 128;              // pixels per tile (UMMA M)
 constexpr int BK = 32;               // k per stage: 32 tf32 = one 128-byte swizzle row
 constexpr int A_STAGE_BYTES = BM * BK * 4;
 constexpr int NUM_PRODUCERS = 256;   // warps 4..11
-constexpr int NUM_THREADS = 128 + NUM_PRODUCERS + 32;
+constexpr int NUM_THREADS = 128 + NUM_PRODUCERS + 64;
 constexpr int PRODUCER_T0 = 128;
 constexpr int MMA_WARP = (128 + NUM_PRODUCERS) / 32;
+constexpr int TMA_WARP = MMA_WARP + 1;
+constexpr int A_HALF_BYTES = A_STAGE_BYTES / 2;   // one 16-channel (64-byte swizzle) im2col box
 constexpr int PRODUCER_GROUPS = 4;
 constexpr int GROUP_THREADS = NUM_PRODUCERS / PRODUCER_GROUPS;   // 64
 constexpr int ROWS_PER_THREAD = BM * 8 / GROUP_THREADS;   // 16
@@ -47,12 +49,21 @@ struct GemmCfg {
   int all_live;    // every k-block touches at least one in-range tap
   int vec_out;     // 16-byte stores allowed
   int vec_res;
+  // hardware im2col (TMA) feed of the A operand
+  int tma_a;       // 0: software gather by the producer warps   1: cp.async.bulk.tensor im2col loads
+  int cb;          // channels per im2col load: 32 (128-byte swizzle) or 16 (two 64-byte-swizzle halves per stage)
+  int cblocks;     // srcC / cb
+  int n_units;     // R * S * cblocks im2col loads per tile
+  int lw, lh;      // base-pixel origin (bounding-box lower corner), W and H
+  int flip_w, flip_h;   // tap offset counts down (dgrad: the index map steps by -1 per tap)
+  FastDiv d_cblk;
   FastDiv d_ohow, d_ow, d_c, d_s, d_divh, d_divw;
   long long* trace;  // optional timeline buffer (debug)
 };
 
 // Optional timeline trace (debug / profiling aid): when armed through dtf_debug_set_trace, CTA 0 stamps SM
 // clocks at the pipeline hand-offs of its first tile into a caller buffer (scripts/trace_conv.py).
+static int g_conv_tma_enabled = 1;            // dtf_debug_set_conv_tma(0) forces the software gather (A/B tests)
 static long long* g_trace_host = nullptr;     // armed by dtf_debug_set_trace, passed to the kernel in GemmCfg
 #define trace_stamp(slot)                                                              \
   do {                                                                                 \
@@ -81,7 +92,8 @@ __device__ __forceinline__ bool kb_live(const dtf_conv_gemm_params& p, const Gem
 }
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_params p, const GemmCfg cfg) {
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ CUtensorMap tmapA,
+                 const dtf_conv_gemm_params p, const GemmCfg cfg) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -95,7 +107,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tfull_bar = empty_bar + stages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* tma_bar = tempty_bar + 2;                      // [stages] im2col tile landed, waiting for the transform
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tma_bar + stages);
   float* csum = reinterpret_cast<float*>(tmem_slot + 4);   // [256]
   float* csq = csum + 256;                                 // [256]
   int2* row_table = reinterpret_cast<int2*>(csq + 256);    // [PRODUCER_GROUPS][BM]
@@ -107,9 +120,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
 
   if (warp == MMA_WARP) {
     if (lane == 0) {
+      // arrivals that complete a stage: the gathering group's threads | the TMA issuer | one per transform warp
+      const uint32_t full_count = !cfg.tma_a ? (uint32_t)GROUP_THREADS
+                                             : (p.in_scale != nullptr ? (uint32_t)(NUM_PRODUCERS / 32) : 1u);
       for (int i = 0; i < stages; ++i) {
-        mbar_init(&full_bar[i], GROUP_THREADS);
+        mbar_init(&full_bar[i], full_count);
         mbar_init(&empty_bar[i], 1);
+        mbar_init(&tma_bar[i], 1);
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull_bar[i], 1);
@@ -126,6 +143,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
     csq[tid] = 0.f;  csq[tid + 128] = 0.f;
   }
   if (tid == PRODUCER_T0) tma_prefetch_desc(&tmapB);
+  if (tid == TMA_WARP * 32 && cfg.tma_a) tma_prefetch_desc(&tmapA);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -134,8 +152,136 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
 
   const int num_tiles = cfg.m_tiles * cfg.n_tiles;
 
-  if (warp >= 4 && warp < MMA_WARP) {
-    // =========================== producers =================================================
+  if (warp >= 4 && warp < MMA_WARP && cfg.tma_a) {
+    // =========================== transform warps (TMA feed + fused BN-apply/ReLU) ===========
+    // The im2col tile lands raw, with out-of-image pixels filled by the NaN marker.  Each warp rewrites its
+    // 16 rows in place as relu(scale * x + shift), turning the marker into the zero padding the convolution
+    // wants, then publishes the stage to the tensor core.  Without a fused input transform the TMA completes the
+    // stage by itself and these warps have nothing to do.
+    if (p.in_scale != nullptr) {
+      const int pw = warp - 4;
+      const bool relu = p.in_relu != 0;
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int kb = 0; kb < cfg.num_kb; ++kb) {
+          if (!kb_live(p, cfg, kb)) continue;
+          uint8_t* a_stage = sA + stage * A_STAGE_BYTES;
+          if (cfg.cb == 32) {
+            const int j = lane & 7;
+            const int tap = (int)fdiv((uint32_t)kb, cfg.d_cblk);
+            const int c = (kb - tap * cfg.cblocks) * 32 + j * 4;
+            const float4 sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
+            const float4 sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
+            mbar_wait(&tma_bar[stage], phase);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int row = pw * 16 + i * 4 + (lane >> 3);
+              float4* ptr = reinterpret_cast<float4*>(a_stage + row * 128 + ((j ^ (row & 7)) << 4));
+              float4 x = *ptr;
+              float4 y;
+              y.x = fmaf(x.x, sc.x, sh.x); y.y = fmaf(x.y, sc.y, sh.y);
+              y.z = fmaf(x.z, sc.z, sh.z); y.w = fmaf(x.w, sc.w, sh.w);
+              if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+              y.x = (x.x == x.x) ? y.x : 0.f; y.y = (x.y == x.y) ? y.y : 0.f;
+              y.z = (x.z == x.z) ? y.z : 0.f; y.w = (x.w == x.w) ? y.w : 0.f;
+              *ptr = y;
+            }
+          } else {
+            const int jj = lane & 3, rs = lane >> 2;
+            const int u0 = kb * 2;
+            const int nu = cfg.n_units - u0 < 2 ? cfg.n_units - u0 : 2;
+            float4 sc[2], sh[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int u = h < nu ? u0 + h : u0;
+              const int tap = (int)fdiv((uint32_t)u, cfg.d_cblk);
+              const int c = (u - tap * cfg.cblocks) * 16 + jj * 4;
+              sc[h] = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
+              sh[h] = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
+            }
+            mbar_wait(&tma_bar[stage], phase);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              if (h < nu) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                  const int row = pw * 16 + i * 8 + rs;
+                  float4* ptr = reinterpret_cast<float4*>(a_stage + h * A_HALF_BYTES + row * 64 +
+                                                          ((jj ^ ((row >> 1) & 3)) << 4));
+                  float4 x = *ptr;
+                  float4 y;
+                  y.x = fmaf(x.x, sc[h].x, sh[h].x); y.y = fmaf(x.y, sc[h].y, sh[h].y);
+                  y.z = fmaf(x.z, sc[h].z, sh[h].z); y.w = fmaf(x.w, sc[h].w, sh[h].w);
+                  if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+                  y.x = (x.x == x.x) ? y.x : 0.f; y.y = (x.y == x.y) ? y.y : 0.f;
+                  y.z = (x.z == x.z) ? y.z : 0.f; y.w = (x.w == x.w) ? y.w : 0.f;
+                  *ptr = y;
+                }
+              }
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full_bar[stage]);
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == TMA_WARP) {
+    // =========================== TMA issuer (hardware im2col feed) ===========================
+    // Per k-block: wait for the slot, then one elected lane posts the byte count and issues the weight-tile load
+    // plus one (32-channel) or two (16-channel) im2col loads.  The engine generates the addresses, applies the
+    // convolution stride, zero/NaN-fills the padding and writes the swizzled K-major tile.
+    if (cfg.tma_a) {
+      const bool has_aff = p.in_scale != nullptr;
+      int stage = 0; uint32_t phase = 0;
+      int gseq = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
+        const int m0 = mt * BM, n0 = nt * BN;
+        const int img = (int)fdiv((uint32_t)m0, cfg.d_ohow);
+        const int rem = m0 - img * p.OH * p.OW;
+        const int oh = (int)fdiv((uint32_t)rem, cfg.d_ow);
+        const int ow = rem - oh * p.OW;
+        const int w0 = ow * p.a_w + cfg.lw, h0 = oh * p.a_h + cfg.lh;
+        for (int kb = 0; kb < cfg.num_kb; ++kb) {
+          if (!kb_live(p, cfg, kb)) continue;
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
+            if (gseq < 512) trace_stamp(1024 + gseq);
+            uint64_t* bar = has_aff ? &tma_bar[stage] : &full_bar[stage];
+            const uint32_t a_dst = smem_u32(sA + stage * A_STAGE_BYTES);
+            if (cfg.cb == 32) {
+              mbar_arrive_expect_tx(bar, (uint32_t)(b_stage_bytes + A_STAGE_BYTES));
+              const int tap = (int)fdiv((uint32_t)kb, cfg.d_cblk);
+              const int c0 = (kb - tap * cfg.cblocks) * 32;
+              const int r = (int)fdiv((uint32_t)tap, cfg.d_s), s_ = tap - r * p.S;
+              tma_load_im2col_4d(a_dst, &tmapA, bar, c0, w0, h0, img,
+                                 (uint16_t)(cfg.flip_w ? p.S - 1 - s_ : s_), (uint16_t)(cfg.flip_h ? p.R - 1 - r : r));
+            } else {
+              const int u0 = kb * 2;
+              const int nu = cfg.n_units - u0 < 2 ? cfg.n_units - u0 : 2;
+              mbar_arrive_expect_tx(bar, (uint32_t)(b_stage_bytes + nu * A_HALF_BYTES));
+              for (int h = 0; h < nu; ++h) {
+                const int u = u0 + h;
+                const int tap = (int)fdiv((uint32_t)u, cfg.d_cblk);
+                const int c0 = (u - tap * cfg.cblocks) * 16;
+                const int r = (int)fdiv((uint32_t)tap, cfg.d_s), s_ = tap - r * p.S;
+                tma_load_im2col_4d(a_dst + (uint32_t)(h * A_HALF_BYTES), &tmapA, bar, c0, w0, h0, img,
+                                   (uint16_t)(cfg.flip_w ? p.S - 1 - s_ : s_),
+                                   (uint16_t)(cfg.flip_h ? p.R - 1 - r : r));
+              }
+            }
+            tma_load_2d(sB + stage * b_stage_bytes, &tmapB, bar, kb * BK, n0);
+          }
+          __syncwarp();
+          ++gseq;
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp >= 4 && warp < MMA_WARP) {
+    // =========================== producers (software gather) =================================
     // Four groups of two warps; group g owns every 4th live k-block (sequence number q with q % 4 == g), so
     // four k-blocks are being gathered at any time.  Inside a group the order is strictly
     //   wait(slot free) -> TMA(B) + 16 x LDG.128 per thread -> [BN-apply + ReLU] -> STS -> proxy fence -> arrive.
@@ -301,10 +447,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
   } else if (warp == MMA_WARP) {
     // =========================== MMA issuer ================================================
     const uint32_t idesc = make_idesc_tf32(BM, (uint32_t)BN);
-    const uint64_t adesc0 = make_desc_k_sw128(smem_u32(sA));
+    const bool sw64 = cfg.tma_a && cfg.cb == 16;     // A stage = two 64-byte-swizzled halves (one filter tap each)
+    const uint64_t adesc0 = sw64 ? make_desc_k_sw64(smem_u32(sA)) : make_desc_k_sw128(smem_u32(sA));
     const uint64_t bdesc0 = make_desc_k_sw128(smem_u32(sB));
     int stage = 0; uint32_t phase = 0;
     int local = 0;
+    int gseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int acc = local & 1;
       const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
@@ -318,27 +466,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
         if (!kb_live(p, cfg, kb)) continue;
         mbar_wait(&full_bar[stage], phase);
         if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 4);
-        if (tr && seq < 512) trace_stamp(2048 + 2 * seq);
+        if (lane == 0 && gseq < 512) trace_stamp(2048 + 2 * gseq);
         tc_fence_after();
         {
           // descriptors are warp-uniform (derived from `stage` only): compute them outside the elected branch so
           // they can live in uniform registers instead of being broadcast per MMA
           const uint64_t adesc = adesc0 + (uint64_t)((uint32_t)(stage * A_STAGE_BYTES) >> 4);
           const uint64_t bdesc = bdesc0 + (uint64_t)((uint32_t)(stage * b_stage_bytes) >> 4);
+          // a 16-channel feed whose unit count is odd leaves the second half of the last k-block unloaded
+          const int nmma = (sw64 && cfg.n_units - kb * 2 < 2) ? 2 : BK / 8;
           if (elect_one()) {        // elect.sync: the compiler knows exactly one lane issues (no waterfall loops)
 #pragma unroll
             for (int kk = 0; kk < BK / 8; ++kk) {
-              umma_tf32_ss(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, accumulate);
-              accumulate = 1;
+              if (kk < nmma) {
+                const uint32_t aoff = sw64 ? (uint32_t)((kk >> 1) * (A_HALF_BYTES >> 4) + (kk & 1) * 2) : (uint32_t)(kk * 2);
+                umma_tf32_ss(d_tmem, adesc + (uint64_t)aoff, bdesc + (uint64_t)(kk * 2), idesc, accumulate);
+                accumulate = 1;
+              }
             }
             umma_commit(&empty_bar[stage]);
             if (tr && (seq & 3) == 0) trace_stamp(16 + 8 * (seq >> 2) + 5);
-            if (tr && seq < 512) trace_stamp(2049 + 2 * seq);
+            if (gseq < 512) trace_stamp(2049 + 2 * gseq);
           }
         }
         __syncwarp();
         accumulate = 1;
         ++seq;
+        ++gseq;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
       if (elect_one()) umma_commit(&tfull_bar[acc]);
@@ -355,6 +509,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
       mbar_wait(&tfull_bar[acc], acc_phase);
       if (tid == 0 && local == 0) trace_stamp(1);
+      if (tid == 0 && local < 128) trace_stamp(512 + 2 * local);
       tc_fence_after();
       const int m = m0 + tid;
       const bool mvalid = m < cfg.M;
@@ -453,6 +608,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
       if (tid == 0 && local == 0) trace_stamp(2);
+      if (tid == 0 && local < 128) trace_stamp(513 + 2 * local);
       if (do_stats && cfg.n_tiles > 1) {
         // several n-tiles share the smem accumulators: flush after every tile
         named_bar_sync(1, 128);
@@ -480,6 +636,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_
 
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) trace_stamp(5);
   if (warp == MMA_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, (uint32_t)cfg.tmem_cols);
@@ -546,7 +703,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.num_kb = ceil_div(cfg.Ktot, BK);
   cfg.tmem_cols = next_pow2_cols(2 * cfg.BN);
   const int stage_bytes = A_STAGE_BYTES + cfg.BN * BK * 4;
-  const int fixed_smem = 1024 + 16 * 2 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int2);
+  const int fixed_smem = 1024 + 16 * 3 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int2);
   int stages = (227 * 1024 - fixed_smem) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages > cfg.num_kb + 1) stages = cfg.num_kb + 1;
@@ -577,7 +734,37 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   const CUtensorMap* tm = get_tmap_2d_f32_sw128(p.wt, p.Nout, cfg.Ktot, cfg.BN);
   if (!tm) return -2;
 
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + (2 * stages + 4) * sizeof(uint64_t) + 16 + 2 * 256 * 4 +
+  // ---- A operand feed: hardware im2col when the index map is a unit-step stencil over >= 16-channel pixels ----
+  cfg.tma_a = 0; cfg.cb = 32; cfg.cblocks = 1; cfg.n_units = 0; cfg.lw = cfg.lh = 0; cfg.flip_w = cfg.flip_h = 0;
+  cfg.d_cblk = make_fastdiv(1u);
+  const CUtensorMap* tma = nullptr;
+  const bool unit_h = (p.R == 1) || p.c_h == 1 || p.c_h == -1;
+  const bool unit_w = (p.S == 1) || p.c_w == 1 || p.c_w == -1;
+  if (g_conv_tma_enabled && p.div_h == 1 && p.div_w == 1 && unit_h && unit_w && p.srcC % 16 == 0 &&
+      p.R <= 256 && p.S <= 256) {
+    Im2colSpec sp;
+    sp.ptr = p.src; sp.N = p.N; sp.H = p.srcH; sp.W = p.srcW; sp.C = p.srcC; sp.ld = p.src_ld;
+    const int flip_h = (p.R > 1 && p.c_h < 0), flip_w = (p.S > 1 && p.c_w < 0);
+    sp.lower_h = flip_h ? p.b_h - (p.R - 1) : p.b_h;
+    sp.lower_w = flip_w ? p.b_w - (p.S - 1) : p.b_w;
+    sp.upper_h = sp.lower_h + (p.OH - 1) * p.a_h + 1 - p.srcH;
+    sp.upper_w = sp.lower_w + (p.OW - 1) * p.a_w + 1 - p.srcW;
+    sp.th = p.a_h; sp.tw = p.a_w;
+    sp.channels = (p.srcC % 32 == 0) ? 32 : 16;
+    sp.nan_fill = p.in_scale != nullptr;
+    tma = get_tmap_im2col_f32(sp);
+    if (tma) {
+      cfg.tma_a = 1;
+      cfg.cb = sp.channels;
+      cfg.cblocks = p.srcC / cfg.cb;
+      cfg.n_units = p.R * p.S * cfg.cblocks;
+      cfg.lw = sp.lower_w; cfg.lh = sp.lower_h;
+      cfg.flip_w = flip_w; cfg.flip_h = flip_h;
+      cfg.d_cblk = make_fastdiv((uint32_t)cfg.cblocks);
+    }
+  }
+
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + (3 * stages + 4) * sizeof(uint64_t) + 16 + 2 * 256 * 4 +
                       PRODUCER_GROUPS * BM * sizeof(int2);
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -588,8 +775,13 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   }
   const int tiles = cfg.m_tiles * cfg.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, p, cfg);
+  conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, tma ? *tma : *tm, p, cfg);
   DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_debug_set_conv_tma(int enabled) {
+  g_conv_tma_enabled = enabled;
   return 0;
 }
 

@@ -103,6 +103,89 @@ const CUtensorMap* get_tmap_2d_f32_sw128(const float* ptr, int rows, int cols, i
   return tm;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col_fn() {
+  static EncodeIm2colFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<EncodeIm2colFn>(p);
+  }
+  return fn;
+}
+
+struct Im2colKey {
+  Im2colSpec s;
+  int dev;
+  bool operator==(const Im2colKey& o) const { return dev == o.dev && memcmp(&s, &o.s, sizeof(Im2colSpec)) == 0; }
+};
+struct Im2colKeyHash {
+  size_t operator()(const Im2colKey& k) const {
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(&k.s);
+    size_t h = 1469598103934665603ull ^ (size_t)k.dev;
+    for (size_t i = 0; i < sizeof(Im2colSpec); ++i) h = (h ^ b[i]) * 1099511628211ull;
+    return h;
+  }
+};
+
+const CUtensorMap* get_tmap_im2col_f32(const Im2colSpec& spec) {
+  static std::unordered_map<Im2colKey, CUtensorMap*, Im2colKeyHash> cache;
+  static std::mutex mu;
+  Im2colKey key;
+  memset(&key, 0, sizeof(key));          // padding bytes take part in the comparison
+  key.s.ptr = spec.ptr;
+  key.s.N = spec.N; key.s.H = spec.H; key.s.W = spec.W; key.s.C = spec.C; key.s.ld = spec.ld;
+  key.s.lower_w = spec.lower_w; key.s.lower_h = spec.lower_h; key.s.upper_w = spec.upper_w; key.s.upper_h = spec.upper_h;
+  key.s.tw = spec.tw; key.s.th = spec.th; key.s.channels = spec.channels; key.s.nan_fill = spec.nan_fill;
+  cudaGetDevice(&key.dev);
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  EncodeIm2colFn enc = get_encode_im2col_fn();
+  if (!enc) return nullptr;
+  const Im2colSpec& s = key.s;
+  if ((reinterpret_cast<uintptr_t>(s.ptr) & 15) != 0 || (s.ld % 4) != 0) return nullptr;
+  if (s.channels != 16 && s.channels != 32) return nullptr;
+  if (s.lower_w < -128 || s.lower_w > 127 || s.lower_h < -128 || s.lower_h > 127) return nullptr;
+  if (s.upper_w < -128 || s.upper_w > 127 || s.upper_h < -128 || s.upper_h > 127) return nullptr;
+  if (s.tw < 1 || s.tw > 8 || s.th < 1 || s.th > 8) return nullptr;
+  void* mem = nullptr;
+  if (posix_memalign(&mem, 64, sizeof(CUtensorMap)) != 0) return nullptr;
+  CUtensorMap* tm = reinterpret_cast<CUtensorMap*>(mem);
+  cuuint64_t gdim[4] = {(cuuint64_t)s.C, (cuuint64_t)s.W, (cuuint64_t)s.H, (cuuint64_t)s.N};
+  cuuint64_t gstride[3] = {(cuuint64_t)s.ld * 4ull, (cuuint64_t)s.ld * 4ull * (cuuint64_t)s.W,
+                           (cuuint64_t)s.ld * 4ull * (cuuint64_t)s.W * (cuuint64_t)s.H};
+  int lower[2] = {s.lower_w, s.lower_h};
+  int upper[2] = {s.upper_w, s.upper_h};
+  cuuint32_t estr[4] = {1u, (cuuint32_t)s.tw, (cuuint32_t)s.th, 1u};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(s.ptr), gdim, gstride, lower, upper,
+                   (cuuint32_t)s.channels, 128u, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   s.channels == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   s.nan_fill ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    free(mem);
+    cache.emplace(key, nullptr);         // remember: this shape uses the gather path
+    return nullptr;
+  }
+  // Drivers up to CUDA 13.1 set a descriptor bit that breaks im2col loads of tensors smaller than 128 KB; the
+  // vendored CUTLASS tree (cute/atom/copy_traits_sm90_im2col.hpp) clears it the same way.
+  int drv = 0;
+  if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010) {
+    const unsigned long long bytes = (unsigned long long)s.N * s.H * s.W * s.ld * 4ull;
+    if (bytes < 131072ull) reinterpret_cast<uint64_t*>(tm)[1] &= ~(1ull << 21);
+  }
+  cache.emplace(key, tm);
+  return tm;
+}
+
 }  // namespace dtf
 
 extern "C" int dtf_version(void) { return 100; }

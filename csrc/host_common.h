@@ -39,6 +39,21 @@ int num_sms();
 // Returns nullptr (and sets last error) on failure.  Cached per (ptr, rows, cols, box_rows).
 const CUtensorMap* get_tmap_2d_f32_sw128(const float* ptr, int rows, int cols, int box_rows);
 
+// NHWC fp32 activation [N][H][W][ld >= C] as an im2col-mode tensor map: one load brings `channels` (16 -> 64-byte
+// swizzle, 32 -> 128-byte swizzle) channels of 128 consecutive output pixels for one filter tap; the hardware
+// walks the base pixels along W, H, N with traversal strides (tw, th), adds the tap offset given with the copy,
+// and fills out-of-range pixels with zeros (nan_fill = false) or the NaN marker (true).
+// lower/upper are the bounding-box corner offsets in [W, H] order.  nullptr when the shape is not encodable.
+struct Im2colSpec {
+  const float* ptr;
+  int N, H, W, C, ld;
+  int lower_w, lower_h, upper_w, upper_h;
+  int tw, th;
+  int channels;
+  int nan_fill;
+};
+const CUtensorMap* get_tmap_im2col_f32(const Im2colSpec& s);
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
 

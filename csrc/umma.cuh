@@ -110,6 +110,19 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
       : "memory");
 }
 
+// im2col-mode load of an NHWC activation (tensor map from get_tmap_im2col_f32): `channels` channels starting at c0
+// for 128 consecutive output pixels beginning at base pixel (w, h, n) — coordinates of the receptive field's
+// corner in the input frame, i.e. lower corner + output index * stride — shifted by the filter tap (off_w, off_h).
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0,
+                                                   int w, int h, int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(w), "r"(h), "r"(n),
+      "h"(off_w), "h"(off_h)
+      : "memory");
+}
+
 // ---------------------------------------------------------------------------------------
 // tcgen05: TMEM management
 // ---------------------------------------------------------------------------------------
@@ -167,6 +180,17 @@ __device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(1024 >> 4) << 32;
   d |= static_cast<uint64_t>(1) << 46;
   d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// Same for a K-major tile whose rows are 64 bytes (16 tf32) stored with the 64-byte swizzle (16-byte chunk index
+// XOR ((row >> 1) & 3)); 8-row groups are 512 bytes apart.  Layout type 4 = SWIZZLE_64B.
+__device__ __forceinline__ uint64_t make_desc_k_sw64(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(512 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(4) << 61;
   return d;
 }
 // Advance a K-major SW128 descriptor by `bytes` along K inside the 128-byte swizzle span.

@@ -83,6 +83,10 @@ int dtf_conv_wgrad(const dtf_conv_wgrad_params* p, void* stream);
 /* Debug aid: arm (buf != NULL, >= 4096 int64) or disarm the in-kernel timeline trace of dtf_conv_gemm. */
 int dtf_debug_set_trace(long long* buf);
 
+/* Debug aid: 0 forces dtf_conv_gemm onto the software-gather producers even where the hardware im2col (TMA)
+ * feed applies; 1 (default) restores the automatic choice. */
+int dtf_debug_set_conv_tma(int enabled);
+
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
 

@@ -36,12 +36,24 @@ CASES = [
     ("alex_fc6_dead_taps", 16, 1, 1, 256, 512, 5, 5, 1, (2, 2), {"bias": True}),
     ("alex_11x11_valid", 4, 32, 32, 4, 64, 11, 11, 1, (0, 0), {}),
     ("big_res_batch128", 128, 32, 32, 16, 16, 3, 3, 1, (1, 1), {"stats": True}),
+    # hardware-im2col coverage: both swizzle widths, fused input transform, strides, odd unit counts, tails
+    ("b128_res16_inaff", 128, 32, 32, 16, 16, 3, 3, 1, (1, 1), {"in_affine": True, "stats": True}),
+    ("b128_res32_inaff", 128, 16, 16, 32, 32, 3, 3, 1, (1, 1), {"in_affine": True, "stats": True}),
+    ("b128_res64_inaff", 128, 8, 8, 64, 64, 3, 3, 1, (1, 1), {"in_affine": True, "stats": True}),
+    ("b128_res16_32_s2_inaff", 128, 32, 32, 16, 32, 3, 3, 2, (1, 1), {"in_affine": True}),
+    ("b128_res32_64_s2_inaff", 128, 16, 16, 32, 64, 3, 3, 2, (1, 1), {"in_affine": True}),
+    ("inc_c48_5x5_tail", 3, 35, 35, 48, 64, 5, 5, 1, (2, 2), {"in_affine": True}),
+    ("inc_c80_3x3_valid_tail", 3, 73, 73, 80, 192, 3, 3, 1, (0, 0), {}),
+    ("inc7x1_160_inaff", 5, 17, 17, 160, 192, 7, 1, 1, (3, 0), {"in_affine": True}),
+    ("vgg3x3_64_64_224", 2, 112, 112, 64, 64, 3, 3, 1, (1, 1), {"bias": True, "relu": True}),
+    ("alex_5x5_s1_64_192", 8, 27, 27, 64, 192, 5, 5, 1, (2, 2), {"bias": True, "relu": True}),
 ]
 
 
 def run_cases(start: int, end: int) -> None:
     import torch
     import torch.nn.functional as F
+    from distributed_tensorflow_models_b200 import _native as nat
     from distributed_tensorflow_models_b200.ops import conv_native as cn
 
     torch.backends.cudnn.allow_tf32 = False
@@ -98,19 +110,44 @@ def run_cases(start: int, end: int) -> None:
         res["wgrad_rel"] = rel(dw, wr.grad)
         # timing (device events) of the three kernels
         def timeit(fn, iters=20):
+            # replay a captured graph of `iters` launches: the Python / ctypes launch cost (~10 us) would
+            # otherwise hide kernels this short
             for _ in range(3):
                 fn()
             torch.cuda.synchronize()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                fn()
+                with torch.cuda.graph(graph, stream=side):
+                    for _ in range(iters):
+                        fn()
+            torch.cuda.synchronize()
+            graph.replay()
+            torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            for _ in range(iters):
-                fn()
+            graph.replay()
             e1.record()
             torch.cuda.synchronize()
             return e0.elapsed_time(e1) / iters * 1e3
-        res["us_fprop"] = timeit(lambda: cn.conv_fprop(x, wt, (st, st), pad, out=y))
-        res["us_dgrad"] = timeit(lambda: cn.conv_dgrad(dy, w_t, (h, w), (st, st), pad, out=dx))
+        fp = lambda: cn.conv_fprop(x, wt, (st, st), pad, out=y, in_scale=in_scale, in_shift=in_shift,
+                                   in_relu=in_scale is not None)
+        dg = lambda: cn.conv_dgrad(dy, w_t, (h, w), (st, st), pad, out=dx)
+        res["us_fprop"] = timeit(fp)
+        res["us_dgrad"] = timeit(dg)
         res["us_wgrad"] = timeit(lambda: cn.conv_wgrad(x, dy, wt.shape, (st, st), pad, out=dw))
+        # the same two kernels on the software-gather producers (A/B for the hardware im2col feed)
+        nat.lib().dtf_debug_set_conv_tma(0)
+        y2 = cn.conv_fprop(x, wt, (st, st), pad, bias=bias, residual=residual, relu=bool(ex.get("relu")),
+                           in_scale=in_scale, in_shift=in_shift, in_relu=in_scale is not None)
+        dx2 = cn.conv_dgrad(dy, w_t, (h, w), (st, st), pad)
+        res["fprop_rel_gather"] = rel(y2, ref)
+        res["dgrad_rel_gather"] = rel(dx2, xr.grad)
+        res["us_fprop_gather"] = timeit(fp)
+        res["us_dgrad_gather"] = timeit(dg)
+        nat.lib().dtf_debug_set_conv_tma(1)
         res["us_cudnn_fprop"] = timeit(lambda: F.conv2d(xa.permute(0, 3, 1, 2), wt.permute(0, 3, 1, 2), None,
                                                          stride=st, padding=pad))
         ok = res["fprop_rel"] < 5e-3 and res["dgrad_rel"] < 5e-3 and res["wgrad_rel"] < 5e-3

@@ -1,3 +1,6 @@
+"""Pipeline timeline of CTA 0 of dtf_conv_gemm (SM clock stamps written by the kernel when armed through
+dtf_debug_set_trace): when the TMA issuer got each slot, when the MMA warp saw each stage full and committed it,
+and when the epilogue started / finished each tile."""
 import sys, os, ctypes as C
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -6,20 +9,22 @@ from distributed_tensorflow_models_b200.ops import conv_native as cn
 dev = torch.device("cuda:0")
 g = torch.Generator().manual_seed(0)
 def r(*s): return torch.randn(*s, generator=g).to(dev)
-for name, (n, h, c, co) in {"64ch_8x8_b128": (128, 8, 64, 64), "16ch_32x32_b128": (128, 32, 16, 16)}.items():
+CASES = {"16ch_32x32_b128": (128, 32, 16, 16, False), "16ch_32x32_b128_inaff": (128, 32, 16, 16, True),
+         "64ch_8x8_b128": (128, 8, 64, 64, False), "32ch_16x16_b128_inaff": (128, 16, 32, 32, True)}
+for name, (n, h, c, co, aff) in CASES.items():
     x = r(n, h, h, c); w = r(co, 3, 3, c) * 0.1
-    for _ in range(3): cn.conv_fprop(x, w, (1, 1), (1, 1))
+    kw = dict(in_scale=torch.rand(c, device=dev) + 0.5, in_shift=torch.randn(c, device=dev) * 0.1, in_relu=True) if aff else {}
+    for _ in range(3): cn.conv_fprop(x, w, (1, 1), (1, 1), **kw)
     buf = torch.zeros(4096, dtype=torch.int64, device=dev)
     nat.lib().dtf_debug_set_trace(C.c_void_p(buf.data_ptr()))
-    cn.conv_fprop(x, w, (1, 1), (1, 1)); torch.cuda.synchronize()
+    cn.conv_fprop(x, w, (1, 1), (1, 1), **kw); torch.cuda.synchronize()
     nat.lib().dtf_debug_set_trace(None)
     t = buf.cpu().tolist()
     t0 = t[3]
-    print(f"== {name}: kernel start->post-setup {t[4]-t0} cyc; producer tile start {t[0]-t0}; epilogue begin {t[1]-t0} end {t[2]-t0}")
-    print(" kb | P:loads_issued  empty_ok  stored  fenced | M:full_ok  committed")
-    for kb in range(20):
-        b = 16 + 8 * kb
-        if t[b] == 0: break
-        print(f" {kb:2d} | {t[b]-t0:8d} {t[b+1]-t0:8d} {t[b+2]-t0:8d} {t[b+3]-t0:8d} | {t[b+4]-t0:8d} {t[b+5]-t0:8d}")
-    mm = [(t[2048 + 2 * i] - t0, t[2049 + 2 * i] - t0) for i in range(24) if t[2048 + 2 * i]]
-    print(" MMA per k-block (full_ok, committed):", mm)
+    print(f"== {name}: setup done {t[4]-t0} cyc; kernel end {t[5]-t0} cyc")
+    iss = [t[1024 + i] - t0 for i in range(512) if t[1024 + i]]
+    mm = [(t[2048 + 2 * i] - t0, t[2049 + 2 * i] - t0) for i in range(512) if t[2048 + 2 * i]]
+    ep = [(t[512 + 2 * i] - t0, t[513 + 2 * i] - t0) for i in range(128) if t[512 + 2 * i]]
+    print(" TMA issue times      :", iss[:48])
+    print(" MMA (full, committed):", mm[:48])
+    print(" epilogue (begin, end):", ep)
