@@ -21,6 +21,7 @@
 #include "../include/dtf_b200.h"
 #include "host_common.h"
 #include "umma.cuh"
+#include "conv_epilogue.cuh"
 
 namespace dtf {
 
@@ -64,7 +65,7 @@ struct GemmCfg {
 // Optional timeline trace (debug / profiling aid): when armed through dtf_debug_set_trace, CTA 0 stamps SM
 // clocks at the pipeline hand-offs of its first tile into a caller buffer (scripts/trace_conv.py).
 static int g_conv_tma_enabled = 1;            // dtf_debug_set_conv_tma(0) forces the software gather (A/B tests)
-static long long* g_trace_host = nullptr;     // armed by dtf_debug_set_trace, passed to the kernel in GemmCfg
+long long* g_trace_host = nullptr;     // armed by dtf_debug_set_trace, passed to the kernel in GemmCfg
 #define trace_stamp(slot)                                                              \
   do {                                                                                 \
     if (cfg.trace != nullptr && blockIdx.x == 0 && (slot) < 4096) cfg.trace[(slot)] = clock64(); \
@@ -513,98 +514,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constan
       tc_fence_after();
       const int m = m0 + tid;
       const bool mvalid = m < cfg.M;
-      float* orow = p.out + (size_t)m * p.out_ld;
-      const float* rrow = p.residual ? p.residual + (size_t)m * p.res_ld : nullptr;
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
-      for (int cc = 0; cc < BN; cc += 16) {
-        float v[16];
-        tmem_ld16(t_row + (uint32_t)cc, v);
-        const int nb = n0 + cc;
-        if (nb >= p.Nout) break;    // uniform across the CTA
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int n = nb + q * 4;
-          float4 x = make_float4(v[q * 4 + 0], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
-          const bool full4 = n + 3 < p.Nout;
-          if (p.bias) {
-            if (full4) {
-              x.x += __ldg(p.bias + n); x.y += __ldg(p.bias + n + 1);
-              x.z += __ldg(p.bias + n + 2); x.w += __ldg(p.bias + n + 3);
-            } else {
-              if (n < p.Nout) x.x += __ldg(p.bias + n);
-              if (n + 1 < p.Nout) x.y += __ldg(p.bias + n + 1);
-              if (n + 2 < p.Nout) x.z += __ldg(p.bias + n + 2);
-            }
-          }
-          if (rrow && mvalid) {
-            if (full4 && cfg.vec_res) {
-              const float4 r4 = __ldg(reinterpret_cast<const float4*>(rrow + n));
-              x.x += r4.x; x.y += r4.y; x.z += r4.z; x.w += r4.w;
-            } else {
-              if (n < p.Nout) x.x += __ldg(rrow + n);
-              if (n + 1 < p.Nout) x.y += __ldg(rrow + n + 1);
-              if (n + 2 < p.Nout) x.z += __ldg(rrow + n + 2);
-              if (n + 3 < p.Nout) x.w += __ldg(rrow + n + 3);
-            }
-          }
-          if (p.out_relu) {
-            x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-          }
-          if (mvalid) {
-            if (full4 && cfg.vec_out) {
-              *reinterpret_cast<float4*>(orow + n) = x;
-            } else {
-              if (n < p.Nout) orow[n] = x.x;
-              if (n + 1 < p.Nout) orow[n + 1] = x.y;
-              if (n + 2 < p.Nout) orow[n + 2] = x.z;
-              if (n + 3 < p.Nout) orow[n + 3] = x.w;
-            }
-          }
-          // keep masked values for the statistics
-          const bool rowok = mvalid;
-          v[q * 4 + 0] = (rowok && n < p.Nout) ? x.x : 0.f;
-          v[q * 4 + 1] = (rowok && n + 1 < p.Nout) ? x.y : 0.f;
-          v[q * 4 + 2] = (rowok && n + 2 < p.Nout) ? x.z : 0.f;
-          v[q * 4 + 3] = (rowok && n + 3 < p.Nout) ? x.w : 0.f;
-        }
-        if (do_stats) {
-          float sq[16];
-          if (p.bnb_x != nullptr) {
-            // fused BN-backward reduction: g = d(act) * [bn(x) > 0];  accumulate sum g and sum g*x
-            const float* xrow = p.bnb_x + (size_t)m * p.bnb_ld + nb;
-#pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-              const int n = nb + q4 * 4;
-              float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
-              float4 sc = xv, sh = xv;
-              if (mvalid && n + 3 < p.Nout) {
-                xv = __ldg(reinterpret_cast<const float4*>(xrow + q4 * 4));
-                sc = __ldg(reinterpret_cast<const float4*>(p.bnb_scale + n));
-                sh = __ldg(reinterpret_cast<const float4*>(p.bnb_shift + n));
-              }
-              const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
-              const float ss[4] = {sc.x, sc.y, sc.z, sc.w};
-              const float hs[4] = {sh.x, sh.y, sh.z, sh.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float g = fmaf(xs[e], ss[e], hs[e]) > 0.f ? v[q4 * 4 + e] : 0.f;
-                v[q4 * 4 + e] = g;
-                sq[q4 * 4 + e] = g * xs[e];
-              }
-            }
-          } else {
-#pragma unroll
-            for (int e = 0; e < 16; ++e) sq[e] = v[e] * v[e];
-          }
-          int col;
-          const float s1 = warp_colsum16(v, lane, col);
-          const float s2 = warp_colsum16(sq, lane, col);
-          if ((lane & 1) == 0) {
-            atomicAdd(&csum[cc + col], s1);
-            atomicAdd(&csq[cc + col], s2);
-          }
-        }
-      }
+      conv_epilogue_row(p, BN, n0, mvalid, (size_t)m, t_row, cfg.vec_out, cfg.vec_res, do_stats, csum, csq, lane);
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
       if (tid == 0 && local == 0) trace_stamp(2);
@@ -676,6 +587,9 @@ static int next_pow2_cols(int c) {
 
 }  // namespace dtf
 
+namespace dtf {
+int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched);
+}
 using namespace dtf;
 
 extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
@@ -697,6 +611,12 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.Ktot = p.R * p.S * p.srcC;
   cfg.M = p.N * p.OH * p.OW;
   if (cfg.M == 0) return 0;
+  {
+    // small-channel stride-1 stencils: the sliding-window kernel reads each activation once (conv_win.cu)
+    bool launched = false;
+    const int rc = try_conv_win(p, stream, &launched);
+    if (rc != 0 || launched) return rc;
+  }
   cfg.BN = pick_bn(p.Nout);
   cfg.n_tiles = ceil_div(p.Nout, cfg.BN);
   cfg.m_tiles = ceil_div(cfg.M, BM);

@@ -159,6 +159,39 @@ __device__ __forceinline__ void umma_tf32_ss(uint32_t tmem_d, uint64_t adesc, ui
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with the two descriptors given as 32-bit halves: the high words (strides, layout type) are kernel-uniform
+// constants, so only the low words (start addresses) have to travel from vector to uniform registers per MMA.
+// ACC is a compile-time accumulate flag (no predicate register to materialise).
+template <int ACC>
+__device__ __forceinline__ void umma_tf32_ss_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                  uint32_t b_hi, uint32_t idesc) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " .reg .b64 da, db;\n"
+      " mov.b64 da, {%1, %2};\n"
+      " mov.b64 db, {%3, %4};\n"
+      " setp.ne.b32 p, %6, 0;\n"
+      " tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(ACC)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32_ss_lohi_p(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                    uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " .reg .b64 da, db;\n"
+      " mov.b64 da, {%1, %2};\n"
+      " mov.b64 db, {%3, %4};\n"
+      " setp.ne.b32 p, %6, 0;\n"
+      " tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // Arrive on an mbarrier once all previously issued MMAs of this thread have completed.
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {

@@ -87,6 +87,10 @@ int dtf_debug_set_trace(long long* buf);
  * feed applies; 1 (default) restores the automatic choice. */
 int dtf_debug_set_conv_tma(int enabled);
 
+/* Debug aid: sliding-window convolution kernel (stride-1 stencils): 0 never, 1 automatic (default: sources of up
+ * to 64 channels), 2 whenever the shape is eligible. */
+int dtf_debug_set_conv_win(int mode);
+
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
 

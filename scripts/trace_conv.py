@@ -25,6 +25,10 @@ for name, (n, h, c, co, aff) in CASES.items():
     iss = [t[1024 + i] - t0 for i in range(512) if t[1024 + i]]
     mm = [(t[2048 + 2 * i] - t0, t[2049 + 2 * i] - t0) for i in range(512) if t[2048 + 2 * i]]
     ep = [(t[512 + 2 * i] - t0, t[513 + 2 * i] - t0) for i in range(128) if t[512 + 2 * i]]
-    print(" TMA issue times      :", iss[:48])
+    if len(iss) and t[1025]:      # window kernel: (slot free, fill issued) per window; MMA (window full, tile committed)
+        print(" fill (slot free, issued):", [(t[1024 + 2 * i] - t0, t[1025 + 2 * i] - t0) for i in range(64) if t[1024 + 2 * i]])
+    else:
+        print(" TMA issue times      :", iss[:48])
     print(" MMA (full, committed):", mm[:48])
     print(" epilogue (begin, end):", ep)
+    print(" epilogue detail (acc loaded, stored, stats):", [tuple(t[3072 + 4 * i + k] - t0 for k in range(3)) for i in range(16) if t[3072 + 4 * i]])
