@@ -589,6 +589,7 @@ static int next_pow2_cols(int c) {
 
 namespace dtf {
 int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched);
+int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched);
 }
 using namespace dtf;
 
@@ -614,7 +615,9 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   {
     // small-channel stride-1 stencils: the sliding-window kernel reads each activation once (conv_win.cu)
     bool launched = false;
-    const int rc = try_conv_win(p, stream, &launched);
+    int rc = try_conv_wint(p, stream, &launched);     // <= 64 output channels: channels on M, pixels on N
+    if (rc != 0 || launched) return rc;
+    rc = try_conv_win(p, stream, &launched);
     if (rc != 0 || launched) return rc;
   }
   cfg.BN = pick_bn(p.Nout);

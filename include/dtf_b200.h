@@ -91,6 +91,10 @@ int dtf_debug_set_conv_tma(int enabled);
  * to 64 channels), 2 whenever the shape is eligible. */
 int dtf_debug_set_conv_win(int mode);
 
+/* Debug aid: channel-major sliding-window kernel (C_in, C_out in {16, 32, 64}): mode 0 off / 1 on (default),
+ * UMMA M (64 or 128), and which TMEM row -> lane mapping to assume for M = 64. */
+int dtf_debug_set_conv_wint(int mode, int umma_m, int lane_mode);
+
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
 

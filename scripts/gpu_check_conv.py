@@ -62,12 +62,17 @@ def run_cases(start: int, end: int) -> None:
     g = torch.Generator(device="cpu").manual_seed(1234)
     WIN_MODE = int(os.environ.get("DTF_CHECK_WIN_MODE", "2"))     # 2: every eligible shape takes the window kernel
     nat.lib().dtf_debug_set_conv_win(WIN_MODE)
+    WINT = [int(v) for v in os.environ.get("DTF_CHECK_WINT", "1,64,1").split(",")]
+    nat.lib().dtf_debug_set_conv_wint(*WINT)
 
     def rel(a, b):
         return float((a - b).abs().max() / (b.abs().max() + 1e-12))
 
+    only = os.environ.get("DTF_CHECK_ONLY")
     for idx in range(start, min(end, len(CASES))):
         name, n, h, w, ci, co, r, s, st, pad, ex = CASES[idx]
+        if only and only not in name:
+            continue
         print(json.dumps({"begin": idx, "name": name}), flush=True)
         x = torch.randn(n, h, w, ci, generator=g).to(dev)
         wt = (torch.randn(co, r, s, ci, generator=g) / (r * s * ci) ** 0.5).to(dev)
@@ -142,6 +147,14 @@ def run_cases(start: int, end: int) -> None:
         res["us_wgrad"] = timeit(lambda: cn.conv_wgrad(x, dy, wt.shape, (st, st), pad, out=dw))
         # A/B: the same two kernels with the sliding-window kernel off (hardware-im2col feed), then with the
         # software-gather producers
+        nat.lib().dtf_debug_set_conv_wint(0, WINT[1], WINT[2])
+        yw = cn.conv_fprop(x, wt, (st, st), pad, bias=bias, residual=residual, relu=bool(ex.get("relu")),
+                           in_scale=in_scale, in_shift=in_shift, in_relu=in_scale is not None)
+        dxw = cn.conv_dgrad(dy, w_t, (h, w), (st, st), pad)
+        res["fprop_rel_win"] = rel(yw, ref)
+        res["dgrad_rel_win"] = rel(dxw, xr.grad)
+        res["us_fprop_win"] = timeit(fp)
+        res["us_dgrad_win"] = timeit(dg)
         nat.lib().dtf_debug_set_conv_win(0)
         y1 = cn.conv_fprop(x, wt, (st, st), pad, bias=bias, residual=residual, relu=bool(ex.get("relu")),
                            in_scale=in_scale, in_shift=in_shift, in_relu=in_scale is not None)
@@ -160,6 +173,7 @@ def run_cases(start: int, end: int) -> None:
         res["us_dgrad_gather"] = timeit(dg)
         nat.lib().dtf_debug_set_conv_tma(1)
         nat.lib().dtf_debug_set_conv_win(WIN_MODE)
+        nat.lib().dtf_debug_set_conv_wint(*WINT)
         res["us_cudnn_fprop"] = timeit(lambda: F.conv2d(xa.permute(0, 3, 1, 2), wt.permute(0, 3, 1, 2), None,
                                                          stride=st, padding=pad))
         ok = all(res[k] < 5e-3 for k in res if "_rel" in k)
@@ -170,7 +184,7 @@ def run_cases(start: int, end: int) -> None:
 def driver() -> int:
     out_dir = os.path.join(ROOT, "gpurun_out")
     os.makedirs(out_dir, exist_ok=True)
-    log_path = os.path.join(out_dir, "conv_check.log")
+    log_path = os.path.join(out_dir, os.environ.get("DTF_CHECK_LOG", "conv_check.log"))
     start = 0
     results = {}
     with open(log_path, "w") as log:
