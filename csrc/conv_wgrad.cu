@@ -316,6 +316,9 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
 
 }  // namespace dtf
 
+namespace dtf {
+int try_conv_wgrad_mn(const dtf_conv_wgrad_params& p, cudaStream_t stream, bool* launched);
+}
 using namespace dtf;
 
 extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
@@ -324,6 +327,12 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   DTF_REQUIRE(p.srcC % 4 == 0 && p.src_ld % 4 == 0, "source channels / pitch must be multiples of 4");
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(p.src) & 15) == 0, "source must be 16-byte aligned");
   DTF_REQUIRE((long long)p.N * p.srcH * p.srcW * p.src_ld < (1LL << 31), "source tensor too large for 32-bit offsets");
+  {
+    // copy-only producers with MN-major operands (conv_wgrad_mn.cu) whenever the gradient rows are 16-byte chunks
+    bool launched = false;
+    const int rc = try_conv_wgrad_mn(p, stream, &launched);
+    if (rc != 0 || launched) return rc;
+  }
   WgradCfg cfg;
   cfg.Ktot = p.R * p.S * p.srcC;
   cfg.M = p.N * p.OH * p.OW;

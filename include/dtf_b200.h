@@ -80,6 +80,10 @@ typedef struct {
 
 int dtf_conv_wgrad(const dtf_conv_wgrad_params* p, void* stream);
 
+/* Debug aid: 0 keeps dtf_conv_wgrad on the register-transposing producers (K-major operands); 1 (default) lets it
+ * use the copy-only producers with MN-major operands where the shape allows. */
+int dtf_debug_set_wgrad_mn(int enabled);
+
 /* Debug aid: arm (buf != NULL, >= 4096 int64) or disarm the in-kernel timeline trace of dtf_conv_gemm. */
 int dtf_debug_set_trace(long long* buf);
 

@@ -144,7 +144,15 @@ def run_cases(start: int, end: int) -> None:
         dg = lambda: cn.conv_dgrad(dy, w_t, (h, w), (st, st), pad, out=dx)
         res["us_fprop"] = timeit(fp)
         res["us_dgrad"] = timeit(dg)
-        res["us_wgrad"] = timeit(lambda: cn.conv_wgrad(x, dy, wt.shape, (st, st), pad, out=dw))
+        wg = lambda: cn.conv_wgrad(x, dy, wt.shape, (st, st), pad, out=dw, in_scale=in_scale, in_shift=in_shift,
+                                   in_relu=in_scale is not None)
+        res["us_wgrad"] = timeit(wg)
+        nat.lib().dtf_debug_set_wgrad_mn(0)
+        dw0 = cn.conv_wgrad(x, dy, wt.shape, (st, st), pad, in_scale=in_scale, in_shift=in_shift,
+                            in_relu=in_scale is not None)
+        res["wgrad_rel_reg"] = rel(dw0, wr.grad)
+        res["us_wgrad_reg"] = timeit(wg)
+        nat.lib().dtf_debug_set_wgrad_mn(1)
         # A/B: the same two kernels with the sliding-window kernel off (hardware-im2col feed), then with the
         # software-gather producers
         nat.lib().dtf_debug_set_conv_wint(0, WINT[1], WINT[2])
