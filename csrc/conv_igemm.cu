@@ -588,8 +588,8 @@ static int next_pow2_cols(int c) {
 }  // namespace dtf
 
 namespace dtf {
-int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched);
-int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched);
+int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched, bool dry_run);
+int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched, bool dry_run);
 }
 using namespace dtf;
 
@@ -615,9 +615,9 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   {
     // small-channel stride-1 stencils: the sliding-window kernel reads each activation once (conv_win.cu)
     bool launched = false;
-    int rc = try_conv_wint(p, stream, &launched);     // <= 64 output channels: channels on M, pixels on N
+    int rc = try_conv_wint(p, stream, &launched, false);     // <= 64 output channels: channels on M, pixels on N
     if (rc != 0 || launched) return rc;
-    rc = try_conv_win(p, stream, &launched);
+    rc = try_conv_win(p, stream, &launched, false);
     if (rc != 0 || launched) return rc;
   }
   cfg.BN = pick_bn(p.Nout);
@@ -700,6 +700,15 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   const int grid = tiles < num_sms() ? tiles : num_sms();
   conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, tma ? *tma : *tm, p, cfg);
   DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_conv_gemm_writes_act(const dtf_conv_gemm_params* pp) {
+  const dtf_conv_gemm_params& p = *pp;
+  if (p.in_scale == nullptr || p.srcC % 4 != 0 || p.src_ld % 4 != 0 || p.N * p.OH * p.OW == 0) return 0;
+  bool would = false;
+  if (try_conv_wint(p, nullptr, &would, true) == 0 && would) return 1;
+  if (try_conv_win(p, nullptr, &would, true) == 0 && would) return 1;
   return 0;
 }
 

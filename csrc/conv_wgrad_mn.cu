@@ -9,11 +9,12 @@
 // (layout type 1): rows of 128 bytes = 32 consecutive k (or n) values of ONE pixel, four pixel rows per 512-byte
 // atom, 32-byte chunk index XOR (pixel & 3).  An im2col row of a pixel is exactly such a row, so the producers
 // become pure 16-byte cp.async copies (zero-filled for padding) — the same gather the forward kernel uses, no
-// registers, no transposes — and, when the producer layer's batch-norm + ReLU is fused in, an in-place fix-up of
-// the thread's own chunks once they have landed.
+// registers, no transposes.  When the producer layer's batch-norm + ReLU is fused in, padding is copied from a NaN
+// marker instead and the (otherwise idle) epilogue warps rewrite each landed tile in place as
+// relu(scale * x + shift), NaN -> 0, before handing it to the tensor core.
 //
-//   warps 0-3   epilogue : accumulator row = k; 32 lanes add 32 consecutive k of one output channel (coalesced
-//                          red.global.add.f32 into dW[n][k])
+//   warps 0-3   fix-up (fused input transform only) and epilogue: accumulator row = k; 32 lanes add 32
+//                          consecutive k of one output channel (coalesced red.global.add.f32 into dW[n][k])
 //   warps 4-11  producers: 4 groups x 64 threads, group g owns every 4th 32-pixel block
 //   warp  12    MMA      : 4 x tcgen05.mma.kind::tf32 (M=128, N=C_out tile, K=8 pixels) per block, both operands
 //                          MN-major
@@ -31,8 +32,9 @@ constexpr int MN_BKP = 32;            // pixels per stage
 constexpr int MN_ATOM_BYTES = MN_BKP * 128;        // one 32-wide MN atom column: 32 pixel rows x 128 B
 constexpr int MN_A_STAGE_BYTES = 4 * MN_ATOM_BYTES;
 constexpr int MN_PRODUCERS = 256;
-constexpr int MN_THREADS = 128 + MN_PRODUCERS + 32;
 constexpr int MN_MMA_WARP = (128 + MN_PRODUCERS) / 32;
+constexpr int MN_FIX_WORKERS = 8;     // fix-up warps: the 4 epilogue warps + 4 dedicated ones after the MMA warp
+constexpr int MN_THREADS = 128 + MN_PRODUCERS + 32 + 128;
 
 struct WgradMnCfg {
   int BN, n_atoms;       // output-channel tile (multiple of 16, <= 256) and its 32-wide atoms
@@ -52,6 +54,10 @@ __device__ __forceinline__ uint64_t make_desc_mn_sw128_32b(uint32_t smem_addr, u
   d |= static_cast<uint64_t>(1) << 61;       // SWIZZLE_128B_BASE32B
   return d;
 }
+
+// Source of "padding" chunks when the tile is fixed up after landing (fused batch-norm apply + ReLU): the fix-up
+// maps NaN to 0, so out-of-image taps contribute zeros and are never activated.
+__device__ __align__(16) const uint32_t g_nan_chunk[4] = {0x7fc00000u, 0x7fc00000u, 0x7fc00000u, 0x7fc00000u};
 
 // byte offset of 16-byte chunk j (0..7) of pixel row `row` inside an atom column
 __device__ __forceinline__ uint32_t mn_chunk_off(int row, int j) {
@@ -73,8 +79,10 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tfull_bar = empty_bar + stages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  int4* ptab = reinterpret_cast<int4*>(tmem_slot + 4);      // [4 groups][32] {pixel offset, ih0, iw0, valid}
+  uint64_t* raw_bar = tempty_bar + 2;                       // [stages] copies landed, waiting for the fix-up warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(raw_bar + stages);
+  int4* ptab = reinterpret_cast<int4*>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~static_cast<uintptr_t>(15));
+  // ^ [4 groups][32] {pixel offset, ih0, iw0, valid}
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -83,8 +91,10 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
   if (warp == MN_MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < stages; ++i) {
-        mbar_init(&full_bar[i], MN_PRODUCERS / 4);
+        // a stage is complete after its producer group (plain copy) or after the 128 fix-up threads
+        mbar_init(&full_bar[i], p.in_scale != nullptr ? 32 : MN_PRODUCERS / 4);
         mbar_init(&empty_bar[i], 1);
+        mbar_init(&raw_bar[i], MN_PRODUCERS / 4);
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull_bar[i], 1);
@@ -102,6 +112,47 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
   const uint32_t tmem_base = *tmem_slot;
 
   const int num_units = cfg.m_tiles * cfg.n_tiles * cfg.splits;
+
+  // Fix-up of landed im2col tiles (fused batch-norm apply + ReLU): worker w of MN_FIX_WORKERS warps owns every
+  // MN_FIX_WORKERS-th 32-pixel block; lane = 16-byte chunk j (fixed filter tap / channels for the unit), all 32
+  // pixel rows.  In place: relu(scale * x + shift), NaN marker -> 0; then the stage is published to the MMA warp.
+  auto fixup_unit = [&](int w, int mt, int kb0, int& seq, int& fstage, uint32_t& fphase) {
+    int kb1 = kb0 + cfg.kb_per_split;
+    if (kb1 > cfg.kb_total) kb1 = cfg.kb_total;
+    const int j = lane;
+    const int k = mt * MN_BM + j * 4;
+    float4 sc = make_float4(0.f, 0.f, 0.f, 0.f), sh = sc;
+    if (k < cfg.Ktot) {
+      const int tap = (int)fdiv((uint32_t)k, cfg.d_c);
+      const int c = k - tap * p.srcC;
+      sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
+      sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
+    }
+    const bool relu = p.in_relu != 0;
+    const uint32_t col = (uint32_t)((j >> 3) * MN_ATOM_BYTES);
+    for (int kb = kb0; kb < kb1; ++kb) {
+      if (seq == w) {
+        mbar_wait(&raw_bar[fstage], fphase);
+        uint8_t* a_stage = sA + fstage * MN_A_STAGE_BYTES + col;
+#pragma unroll 8
+        for (int row = 0; row < MN_BKP; ++row) {
+          float4* ptr = reinterpret_cast<float4*>(a_stage + mn_chunk_off(row, j & 7));
+          const float4 x = *ptr;
+          float4 y;
+          y.x = fmaf(x.x, sc.x, sh.x); y.y = fmaf(x.y, sc.y, sh.y);
+          y.z = fmaf(x.z, sc.z, sh.z); y.w = fmaf(x.w, sc.w, sh.w);
+          if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+          y.x = (x.x == x.x) ? y.x : 0.f; y.y = (x.y == x.y) ? y.y : 0.f;
+          y.z = (x.z == x.z) ? y.z : 0.f; y.w = (x.w == x.w) ? y.w : 0.f;
+          *ptr = y;
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[fstage]);
+      }
+      if (++seq == MN_FIX_WORKERS) seq = 0;
+      if (++fstage == stages) { fstage = 0; fphase ^= 1u; }
+    }
+  };
 
   if (warp >= 4 && warp < MN_MMA_WARP) {
     // =========================== producers =================================================
@@ -133,11 +184,6 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
       const int r = (int)fdiv((uint32_t)tap, cfg.d_s);
       const int s_ = tap - r * p.S;
       const int tap_off = (r * p.srcW + s_) * p.src_ld + c;
-      float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (has_aff && k_ok) {
-        sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + c));
-        sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + c));
-      }
       const int n0 = nt * BN;
       const uint32_t a_col = (uint32_t)((j >> 3) * MN_ATOM_BYTES);       // atom column of this thread's chunk
       const int jj = j & 7;
@@ -163,15 +209,17 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
           uint8_t* a_stage = sA + stage * MN_A_STAGE_BYTES;
           uint8_t* b_stage = sB + stage * b_stage_bytes;
           const uint32_t a_base = smem_u32(a_stage) + a_col;
-          uint32_t okmask = 0;
           // ---- im2col chunks: 16 pixels per thread ----
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const int row = half + 2 * i;
             const int4 e = gtab[row];
             const bool valid = k_ok && (unsigned)(e.y + r) < (unsigned)p.srcH && (unsigned)(e.z + s_) < (unsigned)p.srcW;
-            if (valid) okmask |= 1u << i;
-            cp_async_16(a_base + mn_chunk_off(row, jj), p.src + (valid ? e.x + tap_off : 0), valid ? 16u : 0u);
+            if (has_aff)
+              cp_async_16(a_base + mn_chunk_off(row, jj),
+                          valid ? (const void*)(p.src + e.x + tap_off) : (const void*)g_nan_chunk, 16u);
+            else
+              cp_async_16(a_base + mn_chunk_off(row, jj), p.src + (valid ? e.x + tap_off : 0), valid ? 16u : 0u);
           }
           // ---- dY chunks: 32 pixels x dyc chunks spread over the group's 64 threads ----
           for (int idx = gt; idx < MN_BKP * dyc; idx += 64) {
@@ -182,28 +230,9 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
             cp_async_16(smem_u32(b_stage) + (uint32_t)((cj >> 3) * MN_ATOM_BYTES) + mn_chunk_off(row, cj & 7),
                         p.dy + (valid ? (size_t)m * p.dy_ld + co : 0), valid ? 16u : 0u);
           }
-          if (!has_aff) {
-            cp_async_mbar_arrive_noinc(&full_bar[stage]);
-          } else {
-            // fused batch-norm apply + ReLU: fix up this thread's own chunks once they have landed
-            asm volatile("cp.async.wait_all;" ::: "memory");
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              if ((okmask >> i) & 1u) {
-                const int row = half + 2 * i;
-                float4* ptr = reinterpret_cast<float4*>(a_stage + a_col + mn_chunk_off(row, jj));
-                float4 x = *ptr;
-                x.x = fmaf(x.x, sc.x, sh.x); x.y = fmaf(x.y, sc.y, sh.y);
-                x.z = fmaf(x.z, sc.z, sh.z); x.w = fmaf(x.w, sc.w, sh.w);
-                if (p.in_relu) {
-                  x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-                }
-                *ptr = x;
-              }
-            }
-            fence_proxy_async_smem();
-            mbar_arrive(&full_bar[stage]);
-          }
+          // the barrier hears from this thread once its copies have landed: the stage itself when the data is
+          // used as is, the fix-up warps' barrier when batch-norm + ReLU is applied first
+          cp_async_mbar_arrive_noinc(has_aff ? &raw_bar[stage] : &full_bar[stage]);
         }
         if (++q_grp == cfg.active_groups) q_grp = 0;
         if (++stage == stages) { stage = 0; phase ^= 1u; }
@@ -251,15 +280,29 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
       if (elect_one()) umma_commit(&tfull_bar[acc]);
       __syncwarp();
     }
+  } else if (warp > MN_MMA_WARP) {
+    // =========================== dedicated fix-up warps =====================================
+    if (p.in_scale != nullptr) {
+      int fstage = 0, fseq = 0; uint32_t fphase = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int split = unit % cfg.splits;
+        const int tile = unit / cfg.splits;
+        const int mt = tile / cfg.n_tiles;
+        fixup_unit(4 + (warp - MN_MMA_WARP - 1), mt, split * cfg.kb_per_split, fseq, fstage, fphase);
+      }
+    }
   } else {
     // =========================== epilogue ==================================================
     int local = 0;
+    const bool has_aff = p.in_scale != nullptr;
+    int fstage = 0, fseq = 0; uint32_t fphase = 0;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++local) {
       const int split = unit % cfg.splits;
       const int tile = unit / cfg.splits;
       const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
       const int kb0 = split * cfg.kb_per_split;
       const bool nonempty = kb0 < cfg.kb_total;
+      if (has_aff) fixup_unit(warp, mt, kb0, fseq, fstage, fphase);
       const int acc = local & 1;
       const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -323,7 +366,7 @@ int try_conv_wgrad_mn(const dtf_conv_wgrad_params& p, cudaStream_t stream, bool*
   while (tc < 2 * cfg.BN) tc <<= 1;
   cfg.tmem_cols = tc;
   const int stage_bytes = MN_A_STAGE_BYTES + cfg.n_atoms * MN_ATOM_BYTES;
-  const int fixed = 1024 + (2 * 8 + 4) * 8 + 16 + 4 * MN_BKP * 16;
+  const int fixed = 1024 + (3 * 8 + 4) * 8 + 32 + 4 * MN_BKP * 16;
   int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return 0;

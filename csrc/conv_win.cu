@@ -153,6 +153,7 @@ conv_win_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_p
     const int istep = W_FILL_THREADS / planes;
     const bool has_aff = p.in_scale != nullptr;
     const bool relu = p.in_relu != 0;
+    const bool write_act = has_aff && p.act_out != nullptr && cfg.cblocks >= 1;
     const int hpwp = cfg.Hp * cfg.Wp;
     int wslot = 0; uint32_t wphase = 0;
     int fseq = 0;
@@ -215,6 +216,9 @@ conv_win_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_p
                 }
               }
               if (i < cfg.win) *reinterpret_cast<float4*>(wbase + (size_t)i * 16) = x;
+              // side output act(src): each tile stores the pixels of its own range (no halo), once
+              if (write_act && ok[u] && (unsigned)(i + cfg.lin_min) < (unsigned)WBM)
+                *reinterpret_cast<float4*>(p.act_out + off[u]) = x;
             }
           }
         }
@@ -388,7 +392,7 @@ static int win_pick_bn(int nout) {
 
 // Launches the window kernel when the problem fits it (*launched = true); otherwise leaves *launched false and the
 // caller uses the implicit-GEMM kernel.  Returns 0 or an error code.
-int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched) {
+int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched, bool dry_run) {
   *launched = false;
   if (g_conv_win_mode == 0) return 0;
   if (p.a_h != 1 || p.a_w != 1 || p.div_h != 1 || p.div_w != 1) return 0;
@@ -460,6 +464,10 @@ int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launc
   cfg.vec_out = (p.out_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
   cfg.vec_res = p.residual && (p.res_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0);
 
+  if (dry_run) {
+    *launched = true;
+    return 0;
+  }
   const int Ktot = p.R * p.S * C;
   const CUtensorMap* tm = get_tmap_2d_f32_sw128(p.wt, p.Nout, Ktot, cfg.BN);
   if (!tm) return -2;

@@ -143,6 +143,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
     const int istep = T_FILL_THREADS / planes;
     const bool has_aff = p.in_scale != nullptr;
     const bool relu = p.in_relu != 0;
+    const bool write_act = has_aff && p.act_out != nullptr && cfg.cblocks >= 1;
     const int hpwp = cfg.Hp * cfg.Wp;
     int wslot = 0; uint32_t wphase = 0;
     int fseq = 0;
@@ -207,6 +208,9 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
                 }
               }
               if (i < cfg.win) *reinterpret_cast<float4*>(wbase + (size_t)i * 16) = x;
+              // side output act(src): each tile stores the pixels of its own range (no halo), once
+              if (write_act && ok[u] && (unsigned)(i + cfg.lin_min) < (unsigned)TN)
+                *reinterpret_cast<float4*>(p.act_out + off[u]) = x;
             }
           }
         }
@@ -446,7 +450,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
 
 static int g_wint_mode = 1;        // 0 off, 1 on
 
-int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched) {
+int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launched, bool dry_run) {
   *launched = false;
   if (g_wint_mode == 0) return 0;
   if (p.a_h != 1 || p.a_w != 1 || p.div_h != 1 || p.div_w != 1) return 0;
@@ -533,6 +537,10 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
   cfg.d_kbpt = make_fastdiv((uint32_t)(CB >= 32 ? CB / 32 : 1));
   cfg.trace = g_trace_host;
 
+  if (dry_run) {
+    *launched = true;
+    return 0;
+  }
   const int Ktot = p.R * p.S * C;
   const CUtensorMap* tm = get_tmap_2d_f32_sw128(p.wt, p.Nout, Ktot, cfg.rows_b);
   if (!tm) return -2;

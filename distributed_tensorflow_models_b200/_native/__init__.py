@@ -35,6 +35,7 @@ class ConvGemmParams(C.Structure):
         ("bias", C.c_void_p), ("residual", C.c_void_p), ("res_ld", C.c_int), ("out_relu", C.c_int),
         ("stats", C.c_void_p),
         ("bnb_x", C.c_void_p), ("bnb_ld", C.c_int), ("bnb_scale", C.c_void_p), ("bnb_shift", C.c_void_p),
+        ("act_out", C.c_void_p),
     ]
 
 

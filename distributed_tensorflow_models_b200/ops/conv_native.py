@@ -36,11 +36,15 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
                relu: bool = False, in_scale: Optional[torch.Tensor] = None,
                in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
                stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-               out_hw: Optional[Tuple[int, int]] = None) -> torch.Tensor:
+               out_hw: Optional[Tuple[int, int]] = None, want_act: bool = False):
     """y = epilogue(conv(act(x), w)); see ``dtf_conv_gemm`` in include/dtf_b200.h.
 
     ``pad`` is the padding *before* (top, left); with TensorFlow 'SAME' the padding after may be one
-    larger, which is expressed by passing the output size explicitly in ``out_hw``."""
+    larger, which is expressed by passing the output size explicitly in ``out_hw``.
+
+    ``want_act``: also return ``act(x)`` (or ``None`` when the kernel chosen for this shape does not produce it) —
+    the sliding-window kernels read every input pixel once and can store the transformed value on the way, which
+    spares the weight-gradient pass the transform."""
     n, h, wd, c = x.shape
     co, r, s, ci = w.shape
     assert ci == c and w.is_contiguous() and x.dtype == torch.float32 and w.dtype == torch.float32
@@ -66,8 +70,13 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
     p.stats = nat.ptr(stats)
     p.bnb_x = p.bnb_scale = p.bnb_shift = None
     p.bnb_ld = 0
+    p.act_out = None
+    act = None
+    if want_act and in_scale is not None and x.is_contiguous() and nat.lib().dtf_conv_gemm_writes_act(C.byref(p)):
+        act = torch.empty_like(x)
+        p.act_out = act.data_ptr()
     nat.check(nat.lib().dtf_conv_gemm(C.byref(p), nat.stream_ptr()), "dtf_conv_gemm(fprop)")
-    return out
+    return (out, act) if want_act else out
 
 
 def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
@@ -106,6 +115,7 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
     p.stats = None
     p.bnb_x = p.bnb_scale = p.bnb_shift = None
     p.bnb_ld = 0
+    p.act_out = None
     if bn_bwd is not None:
         bx, bsc, bsh, sums = bn_bwd
         p.bnb_x, p.bnb_ld = bx.data_ptr(), _pitch(bx)

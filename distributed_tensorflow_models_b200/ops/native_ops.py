@@ -314,9 +314,13 @@ def conv_bn_act(x, w, stride, padding, gamma, beta, mm, mv, decay, eps, relu):
 class _BnReluConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, w, residual, coef, stride, pad, out_hw, stats_out):
-        y = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
-                          in_relu=True, stats=stats_out, out_hw=out_hw)
+        # the window kernels hand back relu(bn(x)) as a by-product: the weight gradient then copies it instead of
+        # re-applying the transform to every im2col element
+        y, act = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
+                               in_relu=True, stats=stats_out, out_hw=out_hw,
+                               want_act=any(ctx.needs_input_grad))
         ctx.save_for_backward(x, w)
+        ctx.act = act
         ctx.coef = coef
         ctx.cfg = (stride, pad, residual is not None)
         ctx.params = (gamma, beta, w)
@@ -331,10 +335,15 @@ class _BnReluConvFn(torch.autograd.Function):
         dy = dy.contiguous()
         slot = _grad_slot(wparam)
         dw = None
-        if slot is not None:
-            cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True, out=slot)
+        if ctx.act is not None:
+            wsrc, waff = ctx.act, dict()
         else:
-            dw = cn.conv_wgrad(x, dy, w.shape, stride, pad, in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
+            wsrc, waff = x, dict(in_scale=coef.scale, in_shift=coef.shift, in_relu=True)
+        if slot is not None:
+            cn.conv_wgrad(wsrc, dy, w.shape, stride, pad, out=slot, **waff)
+        else:
+            dw = cn.conv_wgrad(wsrc, dy, w.shape, stride, pad, **waff)
+        ctx.act = None
         sums = _zeros(2 * x.shape[-1], x.device)
         da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad,
                            bn_bwd=(x, coef.scale, coef.shift, sums))

@@ -60,9 +60,16 @@ typedef struct {
    * whose forward input was act = relu(bnb_x*bnb_scale + bnb_shift); `stats` then receives
    * sum_m g and sum_m g*x with g = out * [act > 0] (the two reductions dtf_bn_bwd_apply needs). */
   const float* bnb_x; int bnb_ld; const float* bnb_scale; const float* bnb_shift;
+  /* optional side output (fused input transform only): act(src) in the layout of src, written by the kernels that
+   * read every source pixel exactly once (the sliding-window kernels).  The weight-gradient pass can then copy the
+   * activated input instead of re-applying the transform.  Check dtf_conv_gemm_writes_act first. */
+  float* act_out;
 } dtf_conv_gemm_params;
 
 int dtf_conv_gemm(const dtf_conv_gemm_params* p, void* stream);
+
+/* 1 if dtf_conv_gemm would run a kernel that fills act_out for this problem (act_out itself may be NULL), else 0. */
+int dtf_conv_gemm_writes_act(const dtf_conv_gemm_params* p);
 
 /* Weight gradient: dW[n][k] (+)= sum_m dY[m, n] * A[m, k], A gathered exactly as in fprop
  * (with the same optional fused input activation).  Split over m across CTAs; partial sums

@@ -95,6 +95,14 @@ def run_cases(start: int, end: int) -> None:
                           in_scale=in_scale, in_shift=in_shift, in_relu=in_scale is not None, stats=stats)
         torch.cuda.synchronize()
         res = {"idx": idx, "name": name, "fprop_rel": rel(y, ref), "ms_first": (time.time() - t0) * 1e3}
+        if in_scale is not None:
+            y3, act = cn.conv_fprop(x, wt, (st, st), pad, in_scale=in_scale, in_shift=in_shift, in_relu=True,
+                                    want_act=True)
+            res["act_written"] = act is not None
+            if act is not None:
+                res["act_rel"] = rel(act, xa)
+                res["fprop_rel_act"] = rel(y3, F.conv2d(xa.permute(0, 3, 1, 2), wt.permute(0, 3, 1, 2), None, stride=st,
+                                                        padding=pad).permute(0, 2, 3, 1))
         if stats is not None:
             s1 = ref.reshape(-1, co).sum(0)
             s2 = (ref.reshape(-1, co) ** 2).sum(0)
