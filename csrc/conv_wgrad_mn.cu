@@ -40,7 +40,7 @@ struct WgradMnCfg {
   int BN, n_atoms;       // output-channel tile (multiple of 16, <= 256) and its 32-wide atoms
   int stages, m_tiles, n_tiles, splits, kb_total, kb_per_split, tmem_cols, M, Ktot;
   int active_groups;
-  FastDiv d_ohow, d_ow, d_c, d_s;
+  FastDiv d_ohow, d_ow, d_c, d_s, d_dyc;
 };
 
 // MN-major operand, 128-byte swizzle with 32-byte atoms: 32 MN elements (128 B) per pixel row, 4 rows per atom.
@@ -209,21 +209,54 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
           uint8_t* a_stage = sA + stage * MN_A_STAGE_BYTES;
           uint8_t* b_stage = sB + stage * b_stage_bytes;
           const uint32_t a_base = smem_u32(a_stage) + a_col;
-          // ---- im2col chunks: 16 pixels per thread ----
+          // ---- im2col chunks: 16 pixels per thread.  Phase 1 (table reads + ALU, freely schedulable) collects the
+          // source offsets; phase 2 issues the 16 LDGSTS back to back (each asm statement is a compiler barrier, so
+          // interleaving the table reads with the copies would serialise them on the shared-memory latency) ----
+          int soff[16];
+          uint32_t okmask = 0;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const int row = half + 2 * i;
-            const int4 e = gtab[row];
+            const int4 e = gtab[half + 2 * i];
             const bool valid = k_ok && (unsigned)(e.y + r) < (unsigned)p.srcH && (unsigned)(e.z + s_) < (unsigned)p.srcW;
-            if (has_aff)
-              cp_async_16(a_base + mn_chunk_off(row, jj),
-                          valid ? (const void*)(p.src + e.x + tap_off) : (const void*)g_nan_chunk, 16u);
-            else
-              cp_async_16(a_base + mn_chunk_off(row, jj), p.src + (valid ? e.x + tap_off : 0), valid ? 16u : 0u);
+            if (valid) okmask |= 1u << i;
+            soff[i] = e.x + tap_off;
           }
-          // ---- dY chunks: 32 pixels x dyc chunks spread over the group's 64 threads ----
-          for (int idx = gt; idx < MN_BKP * dyc; idx += 64) {
-            const int row = idx / dyc, cj = idx - row * dyc;
+          // dY chunks: this thread's (row, chunk) pairs, offsets first
+          const int n_dy = MN_BKP * dyc;
+          int dyoff[4];
+          uint32_t dymask = 0;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int idx = gt + 64 * t;
+            const int row = (int)fdiv((uint32_t)idx, cfg.d_dyc), cj = idx - row * dyc;
+            const int m = kb * MN_BKP + row;
+            const bool valid = idx < n_dy && m < cfg.M && n0 + cj * 4 < p.Nout;
+            if (valid) dymask |= 1u << t;
+            dyoff[t] = valid ? m * p.dy_ld + n0 + cj * 4 : 0;
+          }
+          if (has_aff) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj),
+                          ((okmask >> i) & 1u) ? (const void*)(p.src + soff[i]) : (const void*)g_nan_chunk, 16u);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj), p.src + (((okmask >> i) & 1u) ? soff[i] : 0),
+                          ((okmask >> i) & 1u) ? 16u : 0u);
+          }
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int idx = gt + 64 * t;
+            if (idx < n_dy) {
+              const int row = (int)fdiv((uint32_t)idx, cfg.d_dyc), cj = idx - row * dyc;
+              cp_async_16(smem_u32(b_stage) + (uint32_t)((cj >> 3) * MN_ATOM_BYTES) + mn_chunk_off(row, cj & 7),
+                          p.dy + dyoff[t], ((dymask >> t) & 1u) ? 16u : 0u);
+            }
+          }
+          // wide gradient tiles (more than 8 chunks per pixel row): the rest, one at a time
+          for (int idx = gt + 256; idx < n_dy; idx += 64) {
+            const int row = (int)fdiv((uint32_t)idx, cfg.d_dyc), cj = idx - row * dyc;
             const int m = kb * MN_BKP + row;
             const int co = n0 + cj * 4;
             const bool valid = m < cfg.M && co < p.Nout;
@@ -376,6 +409,8 @@ int try_conv_wgrad_mn(const dtf_conv_wgrad_params& p, cudaStream_t stream, bool*
   cfg.d_ow = make_fastdiv((uint32_t)p.OW);
   cfg.d_c = make_fastdiv((uint32_t)p.srcC);
   cfg.d_s = make_fastdiv((uint32_t)p.S);
+  cfg.d_dyc = make_fastdiv((uint32_t)(cfg.BN / 4));
+  if ((long long)cfg.M * p.dy_ld >= (1LL << 31)) return 0;      // 32-bit gradient offsets
 
   const size_t smem = (size_t)fixed + (size_t)stages * stage_bytes;
   static bool attr_set[64] = {false};
