@@ -145,6 +145,10 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
     const bool relu = p.in_relu != 0;
     const bool write_act = has_aff && p.act_out != nullptr && cfg.cblocks >= 1;
     const int hpwp = cfg.Hp * cfg.Wp;
+    const int step_q = istep / cfg.Wp, step_r = istep - step_q * cfg.Wp;
+    const int step_off = (step_q * p.srcW + step_r) * p.src_ld;       // offset change of (dy, dx) = (step_q, step_r)
+    const int wrap_x_off = (p.srcW - cfg.Wp) * p.src_ld;              // column wrapped: x -= Wp, y += 1
+    const int wrap_y_off = (p.srcH - cfg.Hp) * p.srcW * p.src_ld;     // row wrapped:    y -= Hp, n += 1
     int wslot = 0; uint32_t wphase = 0;
     int fseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -162,7 +166,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
         const uint32_t wbase_s = smem_u32(wbase);
         // frame coordinates of this thread's first window pixel; later pixels follow incrementally (the frame
         // index is biased by one image so that the few pixels before the tensor decode without negative division)
-        int fn, fy, fx;
+        int fn, fy, fx, foff;
         {
           const int u0 = pbase + i0 + hpwp;
           fn = (int)fdiv((uint32_t)u0, cfg.d_hpwp);
@@ -170,6 +174,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
           fy = (int)fdiv((uint32_t)rem, cfg.d_wp);
           fx = rem - fy * cfg.Wp;
           fn -= 1;
+          foff = ((fn * p.srcH + fy) * p.srcW + fx) * p.src_ld + cbase;     // meaningful only where the pixel is valid
         }
         for (int ib = i0; ib < cfg.win; ib += 4 * istep) {
           int off[4];
@@ -177,11 +182,13 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int i = ib + u * istep;
-            ok[u] = i < cfg.win && fn >= 0 && fn < p.N && fy < p.srcH && fx < p.srcW;
-            off[u] = ok[u] ? ((fn * p.srcH + fy) * p.srcW + fx) * p.src_ld + cbase : 0;
-            fx += istep;
-            while (fx >= cfg.Wp) { fx -= cfg.Wp; ++fy; }
-            while (fy >= cfg.Hp) { fy -= cfg.Hp; ++fn; }
+            ok[u] = i < cfg.win && (unsigned)fn < (unsigned)p.N && fy < p.srcH && fx < p.srcW;
+            off[u] = ok[u] ? foff : 0;
+            // advance by istep frame pixels without divisions or loops: istep = step_q * Wp + step_r, and one step
+            // can wrap the column once and the row once (step_q + 1 <= Hp)
+            fx += step_r; fy += step_q; foff += step_off;
+            if (fx >= cfg.Wp) { fx -= cfg.Wp; fy += 1; foff += wrap_x_off; }
+            if (fy >= cfg.Hp) { fy -= cfg.Hp; fn += 1; foff += wrap_y_off; }
           }
           if (!has_aff) {
 #pragma unroll
@@ -484,6 +491,7 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
   const long long M = (long long)p.N * p.OH * p.OW;
   if (M == 0) return 0;
   if (Q > (1LL << 30) || Q * 10 > M * 16) return 0;
+  if (32 / cfg.Wp + 1 > cfg.Hp) return 0;             // the fill's incremental frame walk wraps at most one row per step
   cfg.Q = (int)Q;
   // tile width: one wave over the SMs when the problem is small, 256 pixels otherwise; at most T_MAX_ITEMS items
   // per epilogue thread; then shrink until two accumulator patches, two windows and the weights fit
