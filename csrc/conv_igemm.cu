@@ -570,6 +570,35 @@ __global__ void weight_transpose_kernel(const float* __restrict__ w, float* __re
   }
 }
 
+// All layers' weight transposes of a training step in one launch: entry e owns blocks [blk0, blk0 + its tile count).
+struct WtEntry {
+  const float* w;
+  float* wt;
+  int Nout, RS, C, blk0;
+};
+
+__global__ void weight_transpose_batched_kernel(const WtEntry* __restrict__ tab, int n_entries) {
+  __shared__ float tile[32][33];
+  int e = 0;
+  while (e + 1 < n_entries && (int)blockIdx.x >= tab[e + 1].blk0) ++e;
+  const WtEntry en = tab[e];
+  const int cx = (en.C + 31) / 32, ny = (en.Nout + 31) / 32;
+  int b = (int)blockIdx.x - en.blk0;
+  const int rs = b / (cx * ny);
+  b -= rs * cx * ny;
+  const int by = b / cx, bx = b - by * cx;
+  const int c0 = bx * 32, n0 = by * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int n = n0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (n < en.Nout && c < en.C) ? en.w[((size_t)n * en.RS + rs) * en.C + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, n = n0 + threadIdx.x;
+    if (c < en.C && n < en.Nout) en.wt[((size_t)c * en.RS + rs) * en.Nout + n] = tile[threadIdx.x][i];
+  }
+}
+
 static int pick_bn(int nout) {
   if (nout <= 256) return round_up(nout, 16);
   // prefer the widest tile that divides evenly; otherwise 128 keeps the tail small
@@ -719,6 +748,15 @@ extern "C" int dtf_debug_set_conv_tma(int enabled) {
 
 extern "C" int dtf_debug_set_trace(long long* buf) {
   g_trace_host = buf;
+  return 0;
+}
+
+extern "C" int dtf_weight_transpose_batched(const void* table, int n_entries, int total_blocks, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (n_entries <= 0 || total_blocks <= 0) return 0;
+  weight_transpose_batched_kernel<<<total_blocks, dim3(32, 8), 0, stream>>>(reinterpret_cast<const WtEntry*>(table),
+                                                                          n_entries);
+  DTF_CHECK(cudaGetLastError());
   return 0;
 }
 

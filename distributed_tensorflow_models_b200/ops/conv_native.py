@@ -125,6 +125,83 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
     return out
 
 
+class WeightTransposeBatch:
+    """dgrad operands ``[C_in,R,S,C_out]`` of every convolution of a step, produced by ONE kernel launch.
+
+    Convolutions register their weights during the forward pass; the first backward convolution that asks for a
+    transposed weight triggers the batched launch for all of them.  The record table lives on the device and is
+    rebuilt only when the set of registered weights changes, so a captured CUDA graph replays a single launch."""
+
+    def __init__(self):
+        self.entries = {}          # data_ptr -> (shape, index)
+        self.order = []            # (data_ptr, shape)
+        self.table = None
+        self.out = None
+        self.views = {}
+        self.total_blocks = 0
+        self.fresh = False         # transposes valid for the current step
+        self.dirty = True
+
+    def register(self, w: torch.Tensor) -> None:
+        key = (w.data_ptr(), tuple(w.shape))
+        if key not in self.entries:
+            self.entries[key] = len(self.order)
+            self.order.append((key, w.device))
+            self.dirty = True
+        self.fresh = False         # a forward pass is running: weights may have changed since the last backward
+
+    def _rebuild(self) -> None:
+        import struct
+        dev = self.order[0][1]
+        total = sum(s[0] * s[1] * s[2] * s[3] for (_, s), _ in self.order)
+        self.out = torch.empty(total, dtype=torch.float32, device=dev)
+        recs, off, blk = [], 0, 0
+        self.views = {}
+        for (ptr, shape), _ in self.order:
+            co, r, s, ci = shape
+            view = self.out[off:off + co * r * s * ci].view(ci, r, s, co)
+            self.views[(ptr, shape)] = view
+            recs.append(struct.pack("<QQiiii", ptr, view.data_ptr(), co, r * s, ci, blk))
+            blk += ((ci + 31) // 32) * ((co + 31) // 32) * r * s
+            off += co * r * s * ci
+        raw = b"".join(recs)
+        self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self.total_blocks = blk
+        self.dirty = False
+
+    def get(self, w: torch.Tensor) -> torch.Tensor:
+        key = (w.data_ptr(), tuple(w.shape))
+        if key not in self.entries:
+            return weight_transpose(w)
+        if self.dirty:
+            self._rebuild()
+        if not self.fresh:
+            nat.check(nat.lib().dtf_weight_transpose_batched(C.c_void_p(self.table.data_ptr()), len(self.order),
+                                                             self.total_blocks, nat.stream_ptr()),
+                      "dtf_weight_transpose_batched")
+            self.fresh = True
+        return self.views[key]
+
+
+_current_wt_batch: Optional[WeightTransposeBatch] = None
+
+
+def set_wt_batch(batch: Optional[WeightTransposeBatch]) -> None:
+    """Install the batch that convolutions register with (the engine owns one per model; ``None`` = one transpose
+    kernel per layer)."""
+    global _current_wt_batch
+    _current_wt_batch = batch
+
+
+def wt_register(w: torch.Tensor) -> None:
+    if _current_wt_batch is not None:
+        _current_wt_batch.register(w)
+
+
+def wt_get(w: torch.Tensor) -> torch.Tensor:
+    return _current_wt_batch.get(w) if _current_wt_batch is not None else weight_transpose(w)
+
+
 def weight_transpose(w: torch.Tensor) -> torch.Tensor:
     """OHWI ``[C_out,R,S,C_in]`` -> ``[C_in,R,S,C_out]`` (B operand of the dgrad GEMM)."""
     co, r, s, ci = w.shape

@@ -103,6 +103,8 @@ class _ConvFn(torch.autograd.Function):
     def forward(ctx, x, w, bias, stride, pad, out_hw, relu, stats):
         x = x.contiguous() if x.stride(-1) != 1 else x
         y = cn.conv_fprop(x, w, stride, pad, bias=bias, relu=relu, stats=stats, out_hw=out_hw)
+        if ctx.needs_input_grad[0]:
+            cn.wt_register(w)          # its dgrad operand comes from the step's batched transpose
         ctx.save_for_backward(x, w, y if relu else None)
         ctx.cfg = (stride, pad, relu, bias is not None)
         ctx.params = (w, bias)
@@ -126,7 +128,7 @@ class _ConvFn(torch.autograd.Function):
             if slot is not None:
                 db = None
         if ctx.needs_input_grad[0]:
-            dx = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad)
+            dx = cn.conv_dgrad(dy, cn.wt_get(w), (x.shape[1], x.shape[2]), stride, pad)
         if ctx.needs_input_grad[1]:
             slot = _grad_slot(wparam)
             if slot is not None:
@@ -319,6 +321,8 @@ class _BnReluConvFn(torch.autograd.Function):
         y, act = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
                                in_relu=True, stats=stats_out, out_hw=out_hw,
                                want_act=any(ctx.needs_input_grad))
+        if ctx.needs_input_grad[0]:
+            cn.wt_register(w)
         ctx.save_for_backward(x, w)
         ctx.act = act
         ctx.coef = coef
@@ -345,7 +349,7 @@ class _BnReluConvFn(torch.autograd.Function):
             dw = cn.conv_wgrad(wsrc, dy, w.shape, stride, pad, **waff)
         ctx.act = None
         sums = _zeros(2 * x.shape[-1], x.device)
-        da = cn.conv_dgrad(dy, cn.weight_transpose(w), (x.shape[1], x.shape[2]), stride, pad,
+        da = cn.conv_dgrad(dy, cn.wt_get(w), (x.shape[1], x.shape[2]), stride, pad,
                            bn_bwd=(x, coef.scale, coef.shift, sums))
         dx, dg, db = _bn_backward(da, x, coef, True, True, True, gamma=gamma, beta=beta, sums=sums)
         return dx, dg, db, dw, (dy if has_res else None), None, None, None, None, None

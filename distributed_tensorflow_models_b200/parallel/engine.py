@@ -137,6 +137,7 @@ class Trainer:
         self.comm.broadcast_state([v.tensor for v in self.store.all() if not v.trainable], src=0)
         self.local_step = 0
         self._graph = None
+        self._wt_batch = None
         self._static = None
         self.graph_kernel_launches = 0      # native kernels inside one replay of the captured step
         self.last_timing: Dict[str, float] = {}
@@ -179,16 +180,24 @@ class Trainer:
 
     # ---- one step --------------------------------------------------------------------------------
     def _fwd_bwd(self, x, y):
-        if self.device.type == "cuda" and Fn.get_backend() != "torch":
-            from ..ops import native_ops
+        native = self.device.type == "cuda" and Fn.get_backend() != "torch"
+        if native:
+            from ..ops import conv_native, native_ops
             native_ops.begin_step(self.device)
             native_ops.advance_dropout_seed(self.device)
-        self.layout.zero_grads()
-        loss, logits = self._run_forward(x, y, True)
-        total = loss
-        if not self.setup.fused_l2:
-            total = loss + self.l2_term()
-        total.backward()
+            if self._wt_batch is None:
+                self._wt_batch = conv_native.WeightTransposeBatch()
+            conv_native.set_wt_batch(self._wt_batch)      # dgrad operands of all layers: one launch per step
+        try:
+            self.layout.zero_grads()
+            loss, logits = self._run_forward(x, y, True)
+            total = loss
+            if not self.setup.fused_l2:
+                total = loss + self.l2_term()
+            total.backward()
+        finally:
+            if native:
+                conv_native.set_wt_batch(None)
         return loss.detach(), logits.detach()
 
     def _fwd_bwd_graphed(self, x, y):

@@ -109,6 +109,12 @@ int dtf_debug_set_conv_wint(int mode, int umma_m, int lane_mode);
 /* [Nout][R*S][C] -> [C][R*S][Nout]: builds the dgrad B operand from OHWI weights. */
 int dtf_weight_transpose(const float* w, float* wt, int Nout, int RS, int C, void* stream);
 
+/* The same for a whole list of layers in one launch.  `table` is a device array of n_entries records
+ *   { const float* w; float* wt; int Nout, RS, C, blk0; }   (32 bytes each)
+ * where blk0 is the running sum of ceil(C/32) * ceil(Nout/32) * RS over the preceding entries and total_blocks
+ * that sum over all entries. */
+int dtf_weight_transpose_batched(const void* table, int n_entries, int total_blocks, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* K7  batch norm on [M = N*H*W, C] views of NHWC tensors (C % 4 == 0)                    */
 /*     replaces slim ops.batch_norm (inception/slim/ops.py:46-135) and                   */
