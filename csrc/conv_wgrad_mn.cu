@@ -234,16 +234,20 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
             if (valid) dymask |= 1u << t;
             dyoff[t] = valid ? m * p.dy_ld + n0 + cj * 4 : 0;
           }
-          if (has_aff) {
+          // columns past the end of the filter (tail tile) are not copied at all: their accumulator rows are
+          // never stored, so whatever the stage holds there is harmless
+          if (k_ok) {
+            if (has_aff) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj),
-                          ((okmask >> i) & 1u) ? (const void*)(p.src + soff[i]) : (const void*)g_nan_chunk, 16u);
-          } else {
+              for (int i = 0; i < 16; ++i)
+                cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj),
+                            ((okmask >> i) & 1u) ? (const void*)(p.src + soff[i]) : (const void*)g_nan_chunk, 16u);
+            } else {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj), p.src + (((okmask >> i) & 1u) ? soff[i] : 0),
-                          ((okmask >> i) & 1u) ? 16u : 0u);
+              for (int i = 0; i < 16; ++i)
+                cp_async_16(a_base + mn_chunk_off(half + 2 * i, jj), p.src + (((okmask >> i) & 1u) ? soff[i] : 0),
+                            ((okmask >> i) & 1u) ? 16u : 0u);
+            }
           }
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
