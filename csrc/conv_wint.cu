@@ -176,48 +176,58 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
           fn -= 1;
           foff = ((fn * p.srcH + fy) * p.srcW + fx) * p.src_ld + cbase;     // meaningful only where the pixel is valid
         }
-        for (int ib = i0; ib < cfg.win; ib += 4 * istep) {
-          int off[4];
-          bool ok[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int i = ib + u * istep;
-            ok[u] = i < cfg.win && (unsigned)fn < (unsigned)p.N && fy < p.srcH && fx < p.srcW;
-            off[u] = ok[u] ? foff : 0;
-            // advance by istep frame pixels without divisions or loops: istep = step_q * Wp + step_r, and one step
-            // can wrap the column once and the row once (step_q + 1 <= Hp)
-            fx += step_r; fy += step_q; foff += step_off;
-            if (fx >= cfg.Wp) { fx -= cfg.Wp; fy += 1; foff += wrap_x_off; }
-            if (fy >= cfg.Hp) { fy -= cfg.Hp; fn += 1; foff += wrap_y_off; }
+        // Pass 0 issues every copy of the window (zero-filled where the frame has padding): all of them are in
+        // flight at once, so the window costs one memory latency.  With a fused batch-norm + ReLU, pass 1 walks the
+        // same pixels again once the thread's copies have landed and rewrites them in place (padding stays zero),
+        // storing act(src) for the tile's own pixel range on request.
+        const int fn0 = fn, fy0 = fy, fx0 = fx, foff0 = foff;
+        for (int pass = 0; pass < (has_aff ? 2 : 1); ++pass) {
+          if (pass == 1) {
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            fn = fn0; fy = fy0; fx = fx0; foff = foff0;
           }
-          if (!has_aff) {
+          for (int ib = i0; ib < cfg.win; ib += 4 * istep) {
+            int off[4];
+            bool ok[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int i = ib + u * istep;
-              if (i < cfg.win) cp_async_16(wbase_s + (uint32_t)i * 16u, p.src + off[u], ok[u] ? 16u : 0u);
+              ok[u] = i < cfg.win && (unsigned)fn < (unsigned)p.N && fy < p.srcH && fx < p.srcW;
+              off[u] = ok[u] ? foff : 0;
+              // advance by istep frame pixels without divisions or loops: istep = step_q * Wp + step_r, and one
+              // step can wrap the column once and the row once (step_q + 1 <= Hp)
+              fx += step_r; fy += step_q; foff += step_off;
+              if (fx >= cfg.Wp) { fx -= cfg.Wp; fy += 1; foff += wrap_x_off; }
+              if (fy >= cfg.Hp) { fy -= cfg.Hp; fn += 1; foff += wrap_y_off; }
             }
-          } else {
-            float4 v[4];
+            if (pass == 0) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (ok[u]) v[u] = __ldg(reinterpret_cast<const float4*>(p.src + off[u]));
-            }
+              for (int u = 0; u < 4; ++u) {
+                const int i = ib + u * istep;
+                if (i < cfg.win) cp_async_16(wbase_s + (uint32_t)i * 16u, p.src + off[u], ok[u] ? 16u : 0u);
+              }
+            } else {
+              float4 v[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int i = ib + u * istep;
-              float4 x = v[u];
-              if (ok[u]) {
-                x.x = fmaf(x.x, sc.x, sh.x); x.y = fmaf(x.y, sc.y, sh.y);
-                x.z = fmaf(x.z, sc.z, sh.z); x.w = fmaf(x.w, sc.w, sh.w);
-                if (relu) {
-                  x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+              for (int u = 0; u < 4; ++u) {
+                const int i = ib + u * istep;
+                if (ok[u]) v[u] = *reinterpret_cast<const float4*>(wbase + (size_t)i * 16);
+              }
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                if (ok[u]) {
+                  const int i = ib + u * istep;
+                  float4 x = v[u];
+                  x.x = fmaf(x.x, sc.x, sh.x); x.y = fmaf(x.y, sc.y, sh.y);
+                  x.z = fmaf(x.z, sc.z, sh.z); x.w = fmaf(x.w, sc.w, sh.w);
+                  if (relu) {
+                    x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+                  }
+                  *reinterpret_cast<float4*>(wbase + (size_t)i * 16) = x;
+                  if (write_act && (unsigned)(i + cfg.lin_min) < (unsigned)TN)
+                    *reinterpret_cast<float4*>(p.act_out + off[u]) = x;
                 }
               }
-              if (i < cfg.win) *reinterpret_cast<float4*>(wbase + (size_t)i * 16) = x;
-              // side output act(src): each tile stores the pixels of its own range (no halo), once
-              if (write_act && ok[u] && (unsigned)(i + cfg.lin_min) < (unsigned)TN)
-                *reinterpret_cast<float4*>(p.act_out + off[u]) = x;
             }
           }
         }

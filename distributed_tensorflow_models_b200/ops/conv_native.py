@@ -89,6 +89,13 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
     n, p_, q_, co = dy.shape
     ci, r, s, co2 = w_t.shape
     assert co2 == co and w_t.is_contiguous()
+    if (stride[0] > 1 or stride[1] > 1) and r * s > 1 and co in (16, 32, 64) and ci in (16, 32, 64):
+        # Strided stencil: insert the zeros explicitly (dy at the even positions of a stride-times larger grid) and
+        # run the stride-1 sliding-window kernel on that.  The generic path would gather every tap of every pixel
+        # and zero-fill the 1 - 1/(sh*sw) of them that do not divide, element by element.
+        dyu = torch.zeros((n, p_ * stride[0], q_ * stride[1], co), device=dy.device, dtype=torch.float32)
+        dyu[:, ::stride[0], ::stride[1], :] = dy
+        return conv_dgrad(dyu, w_t, in_hw, (1, 1), pad, out=out, bn_bwd=bn_bwd)
     if co % 4 != 0:
         # the gather reads 16-byte channel chunks and TMA needs a 16-byte row pitch: zero-pad the
         # (tiny: logits layers only) gradient and weight operand to a multiple of 4 channels
