@@ -315,7 +315,13 @@ def conv_bn_act(x, w, stride, padding, gamma, beta, mm, mv, decay, eps, relu):
 # ---------------------------------------------------------------------------------------------------
 class _BnReluConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, w, residual, coef, stride, pad, out_hw, stats_out):
+    def forward(ctx, x, gamma, beta, w, residual, coef, stride, pad, out_hw, stats_out, res_link=None,
+                link_first=False, link_last=False):
+        # res_link: identity-shortcut units hand the shortcut's gradient from the unit's last convolution (which
+        # received it as `residual`) to its first one, whose batch-norm backward adds it while writing dx —
+        # instead of autograd summing the two contributions to x with a separate elementwise kernel.
+        ctx.res_link = res_link
+        ctx.link_first, ctx.link_last = link_first, link_last
         # the window kernels hand back relu(bn(x)) as a by-product: the weight gradient then copies it instead of
         # re-applying the transform to every im2col element
         y, act = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
@@ -351,17 +357,27 @@ class _BnReluConvFn(torch.autograd.Function):
         sums = _zeros(2 * x.shape[-1], x.device)
         da = cn.conv_dgrad(dy, cn.wt_get(w), (x.shape[1], x.shape[2]), stride, pad,
                            bn_bwd=(x, coef.scale, coef.shift, sums))
-        dx, dg, db = _bn_backward(da, x, coef, True, True, True, gamma=gamma, beta=beta, sums=sums)
-        return dx, dg, db, dw, (dy if has_res else None), None, None, None, None, None
+        add = None
+        d_res = dy if has_res else None
+        if ctx.res_link is not None:
+            if ctx.link_last:
+                ctx.res_link["g"] = dy          # the shortcut is the unit's own input: pass its gradient on
+                d_res = None
+            if ctx.link_first:
+                add = ctx.res_link.pop("g", None)
+        dx, dg, db = _bn_backward(da, x, coef, True, True, True, add=add, gamma=gamma, beta=beta, sums=sums)
+        return dx, dg, db, dw, d_res, None, None, None, None, None, None, None, None
 
 
-def bn_relu_conv(x, gamma, beta, w, coef: BnCoef, stride, padding, residual=None, want_stats=True):
+def bn_relu_conv(x, gamma, beta, w, coef: BnCoef, stride, padding, residual=None, want_stats=True, res_link=None,
+                 link_first=False, link_last=False):
     from .functional import resolve_padding
     co, r, s, _ = w.shape
     stride = (stride, stride) if isinstance(stride, int) else tuple(stride)
     oh, ow, ph, pw = resolve_padding(x.shape[1], x.shape[2], r, s, stride, padding)
     stats = _zeros(2 * co, x.device) if want_stats else None
-    y = _BnReluConvFn.apply(x, gamma, beta, w, residual, coef, stride, (ph[0], pw[0]), (oh, ow), stats)
+    y = _BnReluConvFn.apply(x, gamma, beta, w, residual, coef, stride, (ph[0], pw[0]), (oh, ow), stats, res_link,
+                            link_first, link_last)
     return y, stats
 
 
@@ -379,6 +395,9 @@ def resnet_unit(ctx, x_and_stats, convs, project, bn_vars, conv_var, fixed_paddi
         shortcut, _ = bn_relu_conv(x, gamma, beta, wp, coef, s, fixed_padding(k, s), want_stats=False)
     y, yst = x, st
     n = len(convs)
+    # identity shortcut: its gradient rides from the last convolution's backward to the first one's (see
+    # _BnReluConvFn); needs autograd to be recording and the unit input to want a gradient
+    link = {} if (project is None and torch.is_grad_enabled() and x.requires_grad) else None
     for i, (k, f, s) in enumerate(convs):
         if i > 0:
             gamma, beta, mm, mv = bn_vars(store, y.shape[-1])
@@ -387,7 +406,8 @@ def resnet_unit(ctx, x_and_stats, convs, project, bn_vars, conv_var, fixed_paddi
         w = conv_var(store, y.shape[-1], k, f)
         last = i == n - 1
         y, yst = bn_relu_conv(y, gamma, beta, w, coef, s, fixed_padding(k, s),
-                              residual=shortcut if last else None, want_stats=True)
+                              residual=shortcut if last else None, want_stats=True, res_link=link,
+                              link_first=(i == 0), link_last=last)
     return y, yst
 
 
