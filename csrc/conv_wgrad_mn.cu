@@ -279,6 +279,8 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
     // =========================== MMA issuer ================================================
     // both operands MN-major: bit 15 (A) and bit 16 (B) of the instruction descriptor
     const uint32_t idesc = make_idesc_tf32(MN_BM, (uint32_t)BN) | (1u << 15) | (1u << 16);
+    // a last tile with at most 64 valid k rows runs as M = 64: half the A-operand stream per instruction
+    const uint32_t idesc64 = make_idesc_tf32(64, (uint32_t)BN) | (1u << 15) | (1u << 16);
     const uint64_t adesc0 = make_desc_mn_sw128_32b(smem_u32(sA), MN_ATOM_BYTES, 512);
     const uint64_t bdesc0 = make_desc_mn_sw128_32b(smem_u32(sB), MN_ATOM_BYTES, 512);
     int stage = 0; uint32_t phase = 0;
@@ -293,6 +295,7 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
       mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      const bool use64 = cfg.Ktot - ((unit / cfg.splits) / cfg.n_tiles) * MN_BM <= 64;
       uint32_t accumulate = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full_bar[stage], phase);
@@ -304,7 +307,8 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
 #pragma unroll
             for (int kk = 0; kk < MN_BKP / 8; ++kk) {
               // 8 pixels further along the reduction = 8 rows of 128 bytes
-              umma_tf32_ss(d_tmem, adesc + (uint64_t)(kk * 64), bdesc + (uint64_t)(kk * 64), idesc, accumulate);
+              umma_tf32_ss(d_tmem, adesc + (uint64_t)(kk * 64), bdesc + (uint64_t)(kk * 64), use64 ? idesc64 : idesc,
+                           accumulate);
               accumulate = 1;
             }
             umma_commit(&empty_bar[stage]);
@@ -344,8 +348,12 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
       const uint32_t acc_phase = (uint32_t)(local >> 1) & 1u;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      const int k = mt * MN_BM + tid;
-      const bool kvalid = nonempty && k < cfg.Ktot;
+      // accumulator row of this thread: M = 128 -> lane r holds row r; M = 64 (short last tile) -> rows
+      // 16g..16g+15 sit in lanes 0..15 of quadrant g
+      const bool use64 = cfg.Ktot - mt * MN_BM <= 64;
+      const int krow = use64 ? (lane < 16 ? warp * 16 + lane : MN_BM) : tid;
+      const int k = mt * MN_BM + krow;
+      const bool kvalid = nonempty && krow < MN_BM && k < cfg.Ktot;
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
       for (int cc = 0; cc < BN; cc += 16) {
         const int nb = nt * BN + cc;
