@@ -187,3 +187,139 @@ def test_dgrad_epilogue_bn_backward_sums_match_reduce_kernel():
     assert _rel(sums, ref) < 1e-4
     mask = (x * scale + shift > 0).float()
     assert _rel(sums[:ci], (da * mask).reshape(-1, ci).sum(0)) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------
+# every convolution kernel path against the fp32 reference (the dispatcher's choices can be forced off)
+# ---------------------------------------------------------------------------------------------------
+def _conv_ref(x, wt, stride, pad, scale=None, shift=None):
+    import torch.nn.functional as F
+    xa = x if scale is None else torch.relu(x * scale + shift)
+    y = F.conv2d(xa.permute(0, 3, 1, 2), wt.permute(0, 3, 1, 2), None, stride=stride, padding=pad)
+    return xa, y.permute(0, 2, 3, 1).contiguous()
+
+
+class _Paths:
+    """Context manager: select the fprop/dgrad kernel (wint | win | tma | gather) through the debug switches."""
+
+    def __init__(self, path):
+        self.path = path
+
+    def __enter__(self):
+        from distributed_tensorflow_models_b200 import _native as nat
+        lib = nat.lib()
+        lib.dtf_debug_set_conv_wint(1 if self.path == "wint" else 0, 64, 1)
+        lib.dtf_debug_set_conv_win(2 if self.path == "win" else 0)
+        lib.dtf_debug_set_conv_tma(0 if self.path == "gather" else 1)
+        return self
+
+    def __exit__(self, *exc):
+        from distributed_tensorflow_models_b200 import _native as nat
+        lib = nat.lib()
+        lib.dtf_debug_set_conv_wint(1, 64, 1)
+        lib.dtf_debug_set_conv_win(1)
+        lib.dtf_debug_set_conv_tma(1)
+
+
+@pytest.mark.parametrize("path", ["wint", "win", "tma", "gather"])
+@pytest.mark.parametrize("shape", [(8, 32, 32, 16, 16, 3), (8, 16, 16, 32, 32, 3), (9, 8, 8, 64, 64, 3),
+                                   (3, 12, 12, 64, 32, 5)])
+def test_conv_kernel_paths_fprop_dgrad(path, shape):
+    """Sliding-window (channel-major and pixel-major), hardware-im2col and software-gather kernels: same result."""
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    torch.backends.cudnn.allow_tf32 = False
+    n, h, w, ci, co, k = shape
+    pad = (k - 1) // 2
+    x = _r(n, h, w, ci, seed=1)
+    wt = _r(co, k, k, ci, seed=2, scale=(k * k * ci) ** -0.5)
+    scale, shift = _r(ci, seed=4).abs() + 0.5, _r(ci, seed=5) * 0.3
+    dy = _r(n, h, w, co, seed=3)
+    for aff in (False, True):
+        xa, ref = _conv_ref(x, wt, 1, pad, scale if aff else None, shift if aff else None)
+        xr = xa.clone().requires_grad_(True)
+        _conv_ref(xr, wt, 1, pad)[1].backward(dy)
+        with _Paths(path):
+            kw = dict(in_scale=scale, in_shift=shift, in_relu=True) if aff else {}
+            stats = torch.zeros(2 * co, device="cuda")
+            res = _r(n, h, w, co, seed=6)
+            y = cn.conv_fprop(x, wt, (1, 1), (pad, pad), residual=res, stats=stats, **kw)
+            dx = cn.conv_dgrad(dy, cn.weight_transpose(wt), (h, w), (1, 1), (pad, pad))
+        torch.cuda.synchronize()
+        assert _rel(y, ref + res) < TF32_TOL
+        assert _rel(stats[:co], (ref + res).reshape(-1, co).sum(0)) < TF32_TOL
+        assert _rel(stats[co:], ((ref + res) ** 2).reshape(-1, co).sum(0)) < TF32_TOL
+        assert _rel(dx, xr.grad) < TF32_TOL
+
+
+def test_window_kernel_act_side_output():
+    """The window kernels return relu(scale * x + shift) as a by-product (exact: fp32 FMA + max)."""
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    for (n, h, c) in ((128, 32, 16), (16, 16, 32), (5, 8, 64)):
+        x = _r(n, h, h, c, seed=1)
+        wt = _r(c, 3, 3, c, seed=2, scale=0.1)
+        scale, shift = _r(c, seed=4).abs() + 0.5, _r(c, seed=5) * 0.3
+        y, act = cn.conv_fprop(x, wt, (1, 1), (1, 1), in_scale=scale, in_shift=shift, in_relu=True, want_act=True)
+        assert act is not None, "the sliding-window kernel should take this shape"
+        torch.cuda.synchronize()
+        xa, ref = _conv_ref(x, wt, 1, 1, scale, shift)
+        assert _rel(act, xa) < 1e-6
+        assert _rel(y, ref) < TF32_TOL
+
+
+@pytest.mark.parametrize("mode", ["mn", "reg"])
+@pytest.mark.parametrize("shape", [(8, 32, 32, 16, 16, 3, 1), (8, 16, 16, 32, 64, 3, 2), (4, 8, 8, 64, 64, 3, 1),
+                                   (2, 17, 17, 128, 96, 1, 1), (3, 12, 12, 48, 64, 5, 1)])
+def test_wgrad_kernels(mode, shape):
+    """MN-major (copy-only producers) and K-major (register-transposing) weight-gradient kernels vs autograd,
+    with and without the fused input transform."""
+    from distributed_tensorflow_models_b200 import _native as nat
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    torch.backends.cudnn.allow_tf32 = False
+    n, h, w, ci, co, k, st = shape
+    pad = (k - 1) // 2
+    x = _r(n, h, w, ci, seed=1)
+    wt = _r(co, k, k, ci, seed=2, scale=0.1)
+    scale, shift = _r(ci, seed=4).abs() + 0.5, _r(ci, seed=5) * 0.3
+    nat.lib().dtf_debug_set_wgrad_mn(1 if mode == "mn" else 0)
+    try:
+        for aff in (False, True):
+            xa = torch.relu(x * scale + shift) if aff else x
+            wr = wt.clone().requires_grad_(True)
+            yr = _conv_ref(xa, wr, st, pad)[1]
+            dy = _r(*yr.shape, seed=3)
+            yr.backward(dy)
+            kw = dict(in_scale=scale, in_shift=shift, in_relu=True) if aff else {}
+            dw = cn.conv_wgrad(x, dy, wt.shape, (st, st), (pad, pad), **kw)
+            torch.cuda.synchronize()
+            assert _rel(dw, wr.grad) < TF32_TOL
+    finally:
+        nat.lib().dtf_debug_set_wgrad_mn(1)
+
+
+def test_strided_dgrad_zero_insertion_path():
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    torch.backends.cudnn.allow_tf32 = False
+    for (n, h, ci, co) in ((8, 32, 16, 32), (8, 16, 32, 64)):
+        x = _r(n, h, h, ci, seed=1).requires_grad_(True)
+        wt = _r(co, 3, 3, ci, seed=2, scale=0.1)
+        y = _conv_ref(x, wt, 2, 1)[1]
+        dy = _r(*y.shape, seed=3)
+        y.backward(dy)
+        dx = cn.conv_dgrad(dy, cn.weight_transpose(wt), (h, h), (2, 2), (1, 1))
+        torch.cuda.synchronize()
+        assert _rel(dx, x.grad) < TF32_TOL
+
+
+def test_weight_transpose_batched():
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    ws = [_r(16, 3, 3, 16, seed=1), _r(64, 1, 1, 32, seed=2), _r(10, 1, 1, 64, seed=3), _r(48, 5, 5, 20, seed=4)]
+    batch = cn.WeightTransposeBatch()
+    for w in ws:
+        batch.register(w)
+    outs = [batch.get(w) for w in ws]
+    torch.cuda.synchronize()
+    for w, o in zip(ws, outs):
+        assert torch.equal(o, w.permute(3, 1, 2, 0).contiguous())
+    ws[0].mul_(2.0)                       # a new forward pass re-registers -> the next get() refreshes everything
+    batch.register(ws[0])
+    assert torch.equal(batch.get(ws[0]), ws[0].permute(3, 1, 2, 0).contiguous())
