@@ -100,7 +100,26 @@ struct BspArgs {
   const float* hyper;
   int kind;
   unsigned int* epoch_ptr;          // local step counter: epoch = *epoch_ptr + 1 (device memory => graph-safe)
+  // NVLS (NVSwitch multicast) addresses of the same symmetric buffers, or nullptr: with them the gradient reduction
+  // happens inside the switch (multimem.ld_reduce) and the updated range is stored to every replica at once
+  // (multimem.st), so the pull phase disappears.
+  const float* mc_grads;
+  float* mc_params;
 };
+
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const float* mc_addr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(float* mc_addr, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
 
 __global__ void __launch_bounds__(512)
 ps_bsp_step_kernel(const BspArgs a) {
@@ -126,10 +145,14 @@ ps_bsp_step_kernel(const BspArgs a) {
   for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4;
        i4 += (long long)gridDim.x * blockDim.x) {
     float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int q = 0; q < W; ++q) {
-      const int src = (me + q) % W;      // stagger peers so ranks do not all hit the same GPU at once
-      const float4 v = *reinterpret_cast<const float4*>(a.peer_grads[src] + lo + (i4 << 2));
-      g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+    if (a.mc_grads != nullptr) {
+      g = multimem_ld_reduce_add_f32x4(a.mc_grads + lo + (i4 << 2));     // sum over all ranks, formed in the switch
+    } else {
+      for (int q = 0; q < W; ++q) {
+        const int src = (me + q) % W;      // stagger peers so ranks do not all hit the same GPU at once
+        const float4 v = *reinterpret_cast<const float4*>(a.peer_grads[src] + lo + (i4 << 2));
+        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+      }
     }
     g.x *= invW; g.y *= invW; g.z *= invW; g.w *= invW;
     float4 wv = *reinterpret_cast<float4*>(wmine + (i4 << 2));
@@ -143,7 +166,8 @@ ps_bsp_step_kernel(const BspArgs a) {
     wv.y = update_elem(a.kind, h, wv.y, g.y, gi + 1 < a.wd_boundary, &m2.y, &mo.y);
     wv.z = update_elem(a.kind, h, wv.z, g.z, gi + 2 < a.wd_boundary, &m2.z, &mo.z);
     wv.w = update_elem(a.kind, h, wv.w, g.w, gi + 3 < a.wd_boundary, &m2.w, &mo.w);
-    *reinterpret_cast<float4*>(wmine + (i4 << 2)) = wv;
+    if (a.mc_params != nullptr && W > 1) multimem_st_f32x4(a.mc_params + lo + (i4 << 2), wv);   // every replica, mine too
+    else *reinterpret_cast<float4*>(wmine + (i4 << 2)) = wv;
     if (a.kind == 1) {
       *reinterpret_cast<float4*>(a.ms + (i4 << 2)) = m2;
       *reinterpret_cast<float4*>(a.mom + (i4 << 2)) = mo;
@@ -173,7 +197,8 @@ ps_bsp_step_kernel(const BspArgs a) {
   __syncthreads();
   if (!s_ok) { if (threadIdx.x == 0) *a.status = 1; return; }
 
-  // ---- pull: refresh the other owners' ranges of my replica --------------------------------------------
+  // ---- pull: refresh the other owners' ranges of my replica (nothing to do when they were multicast) ------
+  if (a.mc_params != nullptr) return;
   float* mine = a.peer_params[me];
   const long long tot4 = n4 * (W - 1);
   for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < tot4;
@@ -299,14 +324,17 @@ extern "C" int dtf_fused_update(float* w, const float* g, float* ms, float* mom,
 extern "C" int dtf_ps_bsp_step(const float* const* peer_grads, float* const* peer_params,
                                unsigned int* const* peer_flags, unsigned int* local_counter, unsigned int* status,
                                int rank, int world, long long shard, long long wd_boundary, float* ms, float* mom,
-                               float* ema, const float* hyper, int kind, unsigned int* epoch_ptr, void* stream_) {
+                               float* ema, const float* hyper, int kind, unsigned int* epoch_ptr,
+                               const float* mc_grads, float* mc_params, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(shard % 4 == 0, "shard length must be a multiple of 4 floats");
+  DTF_REQUIRE((mc_grads == nullptr) == (mc_params == nullptr), "multicast addresses come in pairs");
   DTF_REQUIRE(world <= 32, "flag signalling assumes world <= 32");
   BspArgs a;
   a.peer_grads = peer_grads; a.peer_params = peer_params; a.peer_flags = peer_flags;
   a.local_counter = local_counter; a.status = status; a.rank = rank; a.W = world; a.shard = shard;
   a.wd_boundary = wd_boundary; a.ms = ms; a.mom = mom; a.ema = ema; a.hyper = hyper; a.kind = kind; a.epoch_ptr = epoch_ptr;
+  a.mc_grads = mc_grads; a.mc_params = mc_params;
   // every block must be co-resident (blocks wait on one another through the flags): one block per SM at most
   long long b = ((shard >> 2) + 511) / 512;
   const int grid = (int)(b < num_sms() ? (b > 0 ? b : 1) : num_sms());

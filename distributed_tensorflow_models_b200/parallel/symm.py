@@ -10,7 +10,9 @@ and learns the base address of every peer's copy.  Per-rank device tables of pee
 ``dtf_ps_bsp_step`` / ``dtf_ps_async_step`` / ``dtf_ssp_clock`` (csrc/ps_update.cu):
 
 * BSP  : one kernel per rank per step = wait(grads ready) -> reduce my range over all ranks' gradient
-         buffers + optimiser (+EMA) -> signal/wait(range updated) -> copy the other owners' ranges
+         buffers (in the NVSwitch with multimem.ld_reduce when a multicast address exists, else peer loads)
+         + optimiser (+EMA) -> multimem.st of the updated range into every replica, or signal/wait(range
+         updated) -> copy the other owners' ranges
          (reduce-scatter + fused update + all-gather; replaces SyncReplicasOptimizer's accumulators,
          chief thread and token queue).
 * ASP  : pusher-side one-sided apply (``red.global.add.f32`` on the owner's HBM), global_step is a
@@ -80,6 +82,13 @@ class SymmComm(Comm):
         self.t_flags = table(o_ctrl)
         self.t_clocks = table(o_ctrl + 64)
         self.gs_ptr_rank0 = bases[0] + 4 * (o_ctrl + 128)
+        # NVLS: one multicast address for the whole symmetric buffer when the fabric offers it (NVSwitch)
+        import os
+        mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+        if os.environ.get("DTF_NVLS", "1") == "0":
+            mc = 0
+        self.mc_grads = mc + 4 * o_grads if mc else 0
+        self.mc_params = mc + 4 * o_params if mc else 0
         # bind the model to the symmetric params / grads (values preserved), chief's init wins
         layout.bind(buf[o_params:o_params + total], buf[o_grads:o_grads + total], copy=True)
         self.dist.broadcast(layout.params, src=0, group=self.group)
@@ -120,7 +129,10 @@ class SymmComm(Comm):
                                             _p(self.local_counter), _p(self.status), self.rank, self.world,
                                             C.c_longlong(self.shard), C.c_longlong(self.layout.wd_boundary),
                                             _p(o.slots.get("RMSProp")), _p(o.slots.get("RMSProp_1")), _p(o.ema),
-                                            _p(h), kind, _p(self.epoch), nat.stream_ptr()), "dtf_ps_bsp_step")
+                                            _p(h), kind, _p(self.epoch),
+                                            C.c_void_p(self.mc_grads) if self.mc_grads else None,
+                                            C.c_void_p(self.mc_params) if self.mc_params else None,
+                                            nat.stream_ptr()), "dtf_ps_bsp_step")
         self._gs += 1
         self._step += 1
         return self._gs

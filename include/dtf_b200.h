@@ -198,11 +198,14 @@ int dtf_colsum(const float* x, long long M, int C, int ld, float* out, void* str
 /* ------------------------------------------------------------------------------------ */
 int dtf_fused_update(float* w, const float* g, float* ms, float* mom, float* ema, long long n,
                      long long n_decayed, const float* hyper, int kind, void* stream);
-/* One BSP step over peer-mapped buffers (reduce-scatter + update + all-gather in one kernel per rank). */
+/* One BSP step over peer-mapped buffers (reduce-scatter + update + all-gather in one kernel per rank).
+ * mc_grads / mc_params: NVLS multicast addresses of the gradient / parameter regions of the same symmetric buffer
+ * (both or neither; NULL = unicast peer loads): the reduction then runs in the NVSwitch (multimem.ld_reduce) and
+ * the updated range is written to all replicas with one multimem.st per 16 bytes. */
 int dtf_ps_bsp_step(const float* const* peer_grads, float* const* peer_params, unsigned int* const* peer_flags,
                     unsigned int* local_counter, unsigned int* status, int rank, int world, long long shard,
                     long long wd_boundary, float* ms, float* mom, float* ema, const float* hyper, int kind,
-                    unsigned int* epoch_ptr, void* stream);
+                    unsigned int* epoch_ptr, const float* mc_grads, float* mc_params, void* stream);
 /* One ASP/SSP step: one-sided apply of the local gradient on every owner's range, then refresh the replica. */
 int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms, float* const* peer_mom,
                       float* const* peer_ema, unsigned long long* global_step, int rank, int world, long long shard,
