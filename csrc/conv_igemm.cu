@@ -622,6 +622,8 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
 }
 using namespace dtf;
 
+extern "C" int dtf_conv_gemm_fuses_finalize(const dtf_conv_gemm_params* pp);
+
 extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const dtf_conv_gemm_params& p = *pp;
@@ -632,6 +634,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   DTF_REQUIRE(p.Nout >= 1 && p.R >= 1 && p.S >= 1, "bad shape");
   DTF_REQUIRE((long long)p.N * p.srcH * p.srcW * p.src_ld < (1LL << 31), "source tensor too large for 32-bit offsets");
   if (p.in_scale) DTF_REQUIRE(p.in_shift != nullptr, "in_scale without in_shift");
+  if (p.fin_stats) DTF_REQUIRE(dtf_conv_gemm_fuses_finalize(pp), "deferred batch-norm finalize needs the sliding-window kernel");
   if (p.bnb_x) {
     DTF_REQUIRE(p.stats && p.bnb_scale && p.bnb_shift, "fused BN-backward reduction needs stats/scale/shift");
     DTF_REQUIRE(p.Nout % 4 == 0 && p.bnb_ld % 4 == 0, "fused BN-backward reduction needs C % 4 == 0");
@@ -730,6 +733,13 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, tma ? *tma : *tm, p, cfg);
   DTF_CHECK(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dtf_conv_gemm_fuses_finalize(const dtf_conv_gemm_params* pp) {
+  const dtf_conv_gemm_params& p = *pp;
+  if (p.in_scale == nullptr || p.srcC % 4 != 0 || p.src_ld % 4 != 0 || p.N * p.OH * p.OW == 0) return 0;
+  bool would = false;
+  return (try_conv_wint(p, nullptr, &would, true) == 0 && would) ? 1 : 0;
 }
 
 extern "C" int dtf_conv_gemm_writes_act(const dtf_conv_gemm_params* pp) {

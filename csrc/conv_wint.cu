@@ -91,7 +91,8 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
   uint32_t* a_off = tmem_slot + 4;                                // [T_MAX_K8]
   int* mtab = reinterpret_cast<int*>(a_off + T_MAX_K8);           // [2][256] frame pixel -> output pixel (or -1)
   float* ssum = reinterpret_cast<float*>(mtab + 512);             // [2][128] per-channel sums (kernel end)
-  float* stag = ssum + 256;                                       // [2][patch_floats] pixel-major accumulator patch
+  float* s_aff = ssum + 256;                                      // [2][64] input transform: scale | shift
+  float* stag = s_aff + 128;                                      // [2][patch_floats] pixel-major accumulator patch
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -119,6 +120,34 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
     tmem_relinquish();
   }
   if (tid < 256) ssum[tid] = 0.f;
+  if (p.in_scale != nullptr && tid < p.srcC) {
+    // input transform of this layer: given, or derived here from the producer's batch statistics (deferred
+    // batch-norm finalize; CTA 0 also publishes it for the backward pass and updates the moving averages)
+    float sc, sh;
+    if (p.fin_stats != nullptr) {
+      const float mean = p.fin_stats[tid] * p.fin_inv_count;
+      float var = p.fin_stats[p.srcC + tid] * p.fin_inv_count - mean * mean;
+      var = var < 0.f ? 0.f : var;
+      const float invstd = rsqrtf(var + p.fin_eps);
+      sc = (p.fin_gamma ? p.fin_gamma[tid] : 1.f) * invstd;
+      sh = (p.fin_beta ? p.fin_beta[tid] : 0.f) - mean * sc;
+      if (blockIdx.x == 0) {
+        const_cast<float*>(p.in_scale)[tid] = sc;
+        const_cast<float*>(p.in_shift)[tid] = sh;
+        if (p.fin_mean) p.fin_mean[tid] = mean;
+        if (p.fin_invstd) p.fin_invstd[tid] = invstd;
+        if (p.fin_update_moving) {
+          p.fin_moving_mean[tid] = p.fin_moving_mean[tid] * p.fin_decay + mean * (1.f - p.fin_decay);
+          p.fin_moving_var[tid] = p.fin_moving_var[tid] * p.fin_decay + var * p.fin_unbias * (1.f - p.fin_decay);
+        }
+      }
+    } else {
+      sc = p.in_scale[tid];
+      sh = p.in_shift[tid];
+    }
+    s_aff[tid] = sc;
+    s_aff[64 + tid] = sh;
+  }
   for (int t = tid; t < cfg.n_k8; t += T_THREADS) {
     const int tap = (int)fdiv((uint32_t)t, cfg.d_k8pt);
     const int c8 = t - tap * (cfg.CB >> 3);
@@ -157,8 +186,8 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
         const int cbase = cblk * cfg.CB + j * 4;
         float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
         if (has_aff) {
-          sc = __ldg(reinterpret_cast<const float4*>(p.in_scale + cbase));
-          sh = __ldg(reinterpret_cast<const float4*>(p.in_shift + cbase));
+          sc = *reinterpret_cast<const float4*>(s_aff + cbase);
+          sh = *reinterpret_cast<const float4*>(s_aff + 64 + cbase);
         }
         mbar_wait(&win_empty[wslot], wphase ^ 1u);
         if (pt == 0 && fseq < 256) ttrace(1024 + 2 * fseq);
@@ -514,7 +543,7 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
   cfg.n_kb = ceil_div(cfg.n_k8, 4);
   cfg.rows_b = p.Nout;
   const int b_stage_bytes = 64 * 128;
-  const int fixed = 1024 + (2 * T_MAX_BSTAGES + 2 * T_MAX_WIN + 4) * 8 + 16 + T_MAX_K8 * 4 + 512 * 4 + 256 * 4;
+  const int fixed = 1024 + (2 * T_MAX_BSTAGES + 2 * T_MAX_WIN + 4) * 8 + 16 + T_MAX_K8 * 4 + 512 * 4 + 256 * 4 + 128 * 4;
   cfg.b_resident = (cfg.n_kb <= T_MAX_BSTAGES && cfg.n_kb * b_stage_bytes <= 80 * 1024) ? 1 : 0;
   int tn = round_up(ceil_div((int)Q, num_sms()), 16);
   if (tn > 256) tn = 256;

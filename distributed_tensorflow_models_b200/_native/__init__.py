@@ -36,6 +36,11 @@ class ConvGemmParams(C.Structure):
         ("stats", C.c_void_p),
         ("bnb_x", C.c_void_p), ("bnb_ld", C.c_int), ("bnb_scale", C.c_void_p), ("bnb_shift", C.c_void_p),
         ("act_out", C.c_void_p),
+        ("fin_stats", C.c_void_p), ("fin_gamma", C.c_void_p), ("fin_beta", C.c_void_p),
+        ("fin_moving_mean", C.c_void_p), ("fin_moving_var", C.c_void_p), ("fin_mean", C.c_void_p),
+        ("fin_invstd", C.c_void_p),
+        ("fin_inv_count", C.c_float), ("fin_unbias", C.c_float), ("fin_eps", C.c_float), ("fin_decay", C.c_float),
+        ("fin_update_moving", C.c_int),
     ]
 
 

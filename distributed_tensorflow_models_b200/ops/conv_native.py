@@ -36,7 +36,7 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
                relu: bool = False, in_scale: Optional[torch.Tensor] = None,
                in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
                stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-               out_hw: Optional[Tuple[int, int]] = None, want_act: bool = False):
+               out_hw: Optional[Tuple[int, int]] = None, want_act: bool = False, bn_pending=None):
     """y = epilogue(conv(act(x), w)); see ``dtf_conv_gemm`` in include/dtf_b200.h.
 
     ``pad`` is the padding *before* (top, left); with TensorFlow 'SAME' the padding after may be one
@@ -71,6 +71,20 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
     p.bnb_x = p.bnb_scale = p.bnb_shift = None
     p.bnb_ld = 0
     p.act_out = None
+    if bn_pending is not None and getattr(bn_pending, "pending", None) is not None:
+        # deferred batch-norm finalize: the sliding-window kernel derives scale / shift from the statistics itself
+        # (and publishes them); any other kernel needs them materialised first
+        if nat.lib().dtf_conv_gemm_fuses_finalize(C.byref(p)):
+            st, g_, b_, mm, mv, count, eps, decay, upd, unbiased = bn_pending.pending
+            bn_pending.pending = None
+            p.fin_stats, p.fin_gamma, p.fin_beta = st.data_ptr(), nat.ptr(g_), nat.ptr(b_)
+            p.fin_moving_mean, p.fin_moving_var = nat.ptr(mm), nat.ptr(mv)
+            p.fin_mean, p.fin_invstd = bn_pending.mean.data_ptr(), bn_pending.invstd.data_ptr()
+            p.fin_inv_count = 1.0 / float(count)
+            p.fin_unbias = float(count) / float(count - 1) if (unbiased and count > 1) else 1.0
+            p.fin_eps, p.fin_decay, p.fin_update_moving = float(eps), float(decay), int(upd)
+        else:
+            bn_pending.materialize()
     act = None
     if want_act and in_scale is not None and x.is_contiguous() and nat.lib().dtf_conv_gemm_writes_act(C.byref(p)):
         act = torch.empty_like(x)

@@ -167,15 +167,33 @@ class BnCoef:
 
     def __init__(self, scale, shift, mean, invstd, training):
         self.scale, self.shift, self.mean, self.invstd, self.training = scale, shift, mean, invstd, training
+        self.pending = None      # deferred finalize: (stats, gamma, beta, mm, mv, count, eps, decay, update, unbiased)
+
+    def materialize(self):
+        """Run the stand-alone finalize kernel if the statistics have not been turned into coefficients yet."""
+        if self.pending is not None:
+            stats, gamma, beta, mm, mv, count, eps, decay, update_moving, unbiased = self.pending
+            self.pending = None
+            nat.check(nat.lib().dtf_bn_finalize(_p(stats), _p(gamma), _p(beta), C.c_longlong(count), C.c_float(eps),
+                                                C.c_float(decay), int(update_moving), int(unbiased), _p(mm), _p(mv),
+                                                _p(self.scale), _p(self.shift), _p(self.mean), _p(self.invstd),
+                                                mm.numel(), nat.stream_ptr()), "dtf_bn_finalize")
+        return self
 
 
 @torch.no_grad()
 def bn_prepare(stats: Optional[torch.Tensor], gamma, beta, mm, mv, count: int, eps: float, decay: float,
-               training: bool, update_moving: bool, unbiased: bool) -> BnCoef:
+               training: bool, update_moving: bool, unbiased: bool, lazy: bool = False) -> BnCoef:
+    """``lazy``: leave the finalize to the first consumer — a sliding-window convolution derives the coefficients
+    in its prologue (``bn_relu_conv``); anything else calls ``coef.materialize()`` first."""
     c = mm.numel()
     dev = mm.device
     buf = torch.empty(4 * c, dtype=torch.float32, device=dev)
     scale, shift, mean, invstd = buf[:c], buf[c:2 * c], buf[2 * c:3 * c], buf[3 * c:]
+    if training and lazy:
+        coef = BnCoef(scale, shift, mean, invstd, training)
+        coef.pending = (stats, gamma, beta, mm, mv, count, eps, decay, update_moving, unbiased)
+        return coef
     if training:
         nat.check(nat.lib().dtf_bn_finalize(_p(stats), _p(gamma), _p(beta), C.c_longlong(count), C.c_float(eps),
                                             C.c_float(decay), int(update_moving), int(unbiased), _p(mm), _p(mv),
@@ -326,7 +344,7 @@ class _BnReluConvFn(torch.autograd.Function):
         # re-applying the transform to every im2col element
         y, act = cn.conv_fprop(x, w, stride, pad, residual=residual, in_scale=coef.scale, in_shift=coef.shift,
                                in_relu=True, stats=stats_out, out_hw=out_hw,
-                               want_act=any(ctx.needs_input_grad))
+                               want_act=any(ctx.needs_input_grad), bn_pending=coef)
         if ctx.needs_input_grad[0]:
             cn.wt_register(w)
         ctx.save_for_backward(x, w)
@@ -387,7 +405,9 @@ def resnet_unit(ctx, x_and_stats, convs, project, bn_vars, conv_var, fixed_paddi
     store = ctx.store
     count = x.numel() // x.shape[-1]
     gamma, beta, mm, mv = bn_vars(store, x.shape[-1])
-    coef = bn_prepare(st, gamma, beta, mm, mv, count, eps, decay, True, ctx.update_moving, True)
+    # identity units: the only consumer of this batch-norm is the first convolution, which finalizes it itself
+    coef = bn_prepare(st, gamma, beta, mm, mv, count, eps, decay, True, ctx.update_moving, True,
+                      lazy=project is None)
     shortcut = x
     if project is not None:
         k, f, s = project
@@ -402,7 +422,7 @@ def resnet_unit(ctx, x_and_stats, convs, project, bn_vars, conv_var, fixed_paddi
         if i > 0:
             gamma, beta, mm, mv = bn_vars(store, y.shape[-1])
             coef = bn_prepare(yst, gamma, beta, mm, mv, y.numel() // y.shape[-1], eps, decay, True,
-                              ctx.update_moving, True)
+                              ctx.update_moving, True, lazy=True)
         w = conv_var(store, y.shape[-1], k, f)
         last = i == n - 1
         y, yst = bn_relu_conv(y, gamma, beta, w, coef, s, fixed_padding(k, s),

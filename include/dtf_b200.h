@@ -64,12 +64,22 @@ typedef struct {
    * read every source pixel exactly once (the sliding-window kernels).  The weight-gradient pass can then copy the
    * activated input instead of re-applying the transform.  Check dtf_conv_gemm_writes_act first. */
   float* act_out;
+  /* optional deferred batch-norm finalize (sliding-window kernel only, see dtf_conv_gemm_fuses_finalize): when
+   * fin_stats != NULL the kernel derives the input transform itself from the producer's per-channel sums
+   *   mean = sum / count, var = sumsq / count - mean^2, scale = gamma * rsqrt(var + eps), shift = beta - mean * scale
+   * and its first CTA writes scale / shift / mean / invstd to in_scale / in_shift / fin_mean / fin_invstd (for the
+   * backward pass) and applies the moving-average update — one tiny kernel launch less per batch-norm. */
+  const float* fin_stats; const float* fin_gamma; const float* fin_beta;
+  float* fin_moving_mean; float* fin_moving_var; float* fin_mean; float* fin_invstd;
+  float fin_inv_count, fin_unbias, fin_eps, fin_decay; int fin_update_moving;
 } dtf_conv_gemm_params;
 
 int dtf_conv_gemm(const dtf_conv_gemm_params* p, void* stream);
 
 /* 1 if dtf_conv_gemm would run a kernel that fills act_out for this problem (act_out itself may be NULL), else 0. */
 int dtf_conv_gemm_writes_act(const dtf_conv_gemm_params* p);
+/* 1 if dtf_conv_gemm would run the kernel that honours the fin_* fields for this problem, else 0. */
+int dtf_conv_gemm_fuses_finalize(const dtf_conv_gemm_params* p);
 
 /* Weight gradient: dW[n][k] (+)= sum_m dY[m, n] * A[m, k], A gathered exactly as in fprop
  * (with the same optional fused input activation).  Split over m across CTAs; partial sums

@@ -323,3 +323,27 @@ def test_weight_transpose_batched():
     ws[0].mul_(2.0)                       # a new forward pass re-registers -> the next get() refreshes everything
     batch.register(ws[0])
     assert torch.equal(batch.get(ws[0]), ws[0].permute(3, 1, 2, 0).contiguous())
+
+
+def test_deferred_bn_finalize_in_window_kernel():
+    """A lazy BnCoef is finalized by the sliding-window convolution itself: same output, same published
+    coefficients and moving statistics as the stand-alone finalize kernel."""
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    from distributed_tensorflow_models_b200.ops import native_ops as no
+    n, h, c = 16, 16, 32
+    x = _r(n, h, h, c, seed=1) * 1.7 + 0.3
+    wt = _r(c, 3, 3, c, seed=2, scale=0.1)
+    gamma, beta = _r(c, seed=3).abs() + 0.5, _r(c, seed=4) * 0.2
+    outs = []
+    for lazy in (False, True):
+        mm, mv = torch.zeros(c, device="cuda"), torch.ones(c, device="cuda")
+        st = no.bn_stats(x)
+        coef = no.bn_prepare(st, gamma, beta, mm, mv, n * h * h, 1e-5, 0.9, True, True, True, lazy=lazy)
+        assert (coef.pending is not None) == lazy
+        y = cn.conv_fprop(x, wt, (1, 1), (1, 1), in_scale=coef.scale, in_shift=coef.shift, in_relu=True,
+                          bn_pending=coef)
+        torch.cuda.synchronize()
+        assert coef.pending is None
+        outs.append((y, coef.scale.clone(), coef.shift.clone(), coef.mean.clone(), coef.invstd.clone(), mm, mv))
+    for a, b in zip(outs[0], outs[1]):
+        assert _rel(b, a) < 1e-5
