@@ -118,6 +118,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constan
   const int warp = tid >> 5;
   const int lane = tid & 31;
   if (tid == 0) trace_stamp(3);
+  pdl_launch_dependents();   // persistent grid, all CTAs resident: the successor may take SMs as they free up
 
   if (warp == MMA_WARP) {
     if (lane == 0) {
@@ -145,6 +146,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constan
   }
   if (tid == PRODUCER_T0) tma_prefetch_desc(&tmapB);
   if (tid == TMA_WARP * 32 && cfg.tma_a) tma_prefetch_desc(&tmapA);
+  pdl_wait();     // everything above is independent of the predecessor kernel
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -730,8 +732,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   }
   const int tiles = cfg.m_tiles * cfg.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_gemm_kernel<<<grid, NUM_THREADS, smem, stream>>>(*tm, tma ? *tma : *tm, p, cfg);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(conv_gemm_kernel, dim3(grid), dim3(NUM_THREADS), smem, stream, *tm, tma ? *tma : *tm, p, cfg));
   return 0;
 }
 

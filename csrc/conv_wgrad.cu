@@ -52,6 +52,7 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
+  pdl_launch_dependents();   // persistent grid, all CTAs resident: the successor may take SMs as they free up
 
   if (warp == WG_MMA_WARP) {
     if (lane == 0) {
@@ -69,6 +70,7 @@ conv_wgrad_kernel(const dtf_conv_wgrad_params p, const WgradCfg cfg) {
     tmem_alloc(tmem_slot, (uint32_t)cfg.tmem_cols);
     tmem_relinquish();
   }
+  pdl_wait();     // everything above is independent of the predecessor kernel
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -373,7 +375,6 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   }
   const int units = cfg.m_tiles * cfg.n_tiles * cfg.splits;
   const int grid = units < num_sms() ? units : num_sms();
-  conv_wgrad_kernel<<<grid, WG_THREADS, smem, stream>>>(p, cfg);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(conv_wgrad_kernel, dim3(grid), dim3(WG_THREADS), smem, stream, p, cfg));
   return 0;
 }

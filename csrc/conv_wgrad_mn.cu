@@ -87,6 +87,7 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
+  pdl_launch_dependents();   // persistent grid, all CTAs resident: the successor may take SMs as they free up
 
   if (warp == MN_MMA_WARP) {
     if (lane == 0) {
@@ -106,6 +107,7 @@ conv_wgrad_mn_kernel(const dtf_conv_wgrad_params p, const WgradMnCfg cfg) {
     tmem_alloc(tmem_slot, (uint32_t)cfg.tmem_cols);
     tmem_relinquish();
   }
+  pdl_wait();     // everything above is independent of the predecessor kernel
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -434,8 +436,7 @@ int try_conv_wgrad_mn(const dtf_conv_wgrad_params& p, cudaStream_t stream, bool*
   }
   const int units = base_units * cfg.splits;
   const int grid = units < num_sms() ? units : num_sms();
-  conv_wgrad_mn_kernel<<<grid, MN_THREADS, smem, stream>>>(p, cfg);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(conv_wgrad_mn_kernel, dim3(grid), dim3(MN_THREADS), smem, stream, p, cfg));
   *launched = true;
   return 0;
 }

@@ -103,6 +103,7 @@ conv_win_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_p
   const int warp = tid >> 5;
   const int lane = tid & 31;
   if (tid == 0) wtrace(3);
+  pdl_launch_dependents();   // persistent grid, all CTAs resident: the successor may take SMs as they free up
 
   if (warp == W_MMA_WARP) {
     if (lane == 0) {
@@ -137,6 +138,7 @@ conv_win_kernel(const __grid_constant__ CUtensorMap tmapB, const dtf_conv_gemm_p
     a_off[t] = (uint32_t)(lin + c8 * 2 * cfg.win_pad);
   }
   if (tid == W_TMA_WARP * 32) tma_prefetch_desc(&tmapB);
+  pdl_wait();     // everything above is independent of the predecessor kernel
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -481,8 +483,7 @@ int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launc
   }
   const int tiles = cfg.m_tiles * cfg.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_win_kernel<<<grid, W_THREADS, smem, stream>>>(*tm, p, cfg);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(conv_win_kernel, dim3(grid), dim3(W_THREADS), smem, stream, *tm, p, cfg));
   *launched = true;
   return 0;
 }

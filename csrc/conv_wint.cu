@@ -98,6 +98,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
   const int warp = tid >> 5;
   const int lane = tid & 31;
   if (tid == 0) ttrace(3);
+  pdl_launch_dependents();   // persistent grid, all CTAs resident: the successor may take SMs as they free up
 
   if (warp == T_MMA_WARP) {
     if (lane == 0) {
@@ -120,6 +121,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
     tmem_relinquish();
   }
   if (tid < 256) ssum[tid] = 0.f;
+  pdl_wait();     // everything above is independent of the predecessor kernel
   if (p.in_scale != nullptr && tid < p.srcC) {
     // input transform of this layer: given, or derived here from the producer's batch statistics (deferred
     // batch-norm finalize; CTA 0 also publishes it for the backward pass and updates the moving averages)
@@ -601,8 +603,7 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
     attr_set[dev & 63] = true;
   }
   const int grid = cfg.m_tiles < num_sms() ? cfg.m_tiles : num_sms();
-  conv_wint_kernel<<<grid, T_THREADS, smem, stream>>>(*tm, p, cfg);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(conv_wint_kernel, dim3(grid), dim3(T_THREADS), smem, stream, *tm, p, cfg));
   *launched = true;
   return 0;
 }

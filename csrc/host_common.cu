@@ -6,6 +6,8 @@
 
 namespace dtf {
 
+int g_pdl_enabled = 1;
+
 static thread_local std::string g_last_error;
 static std::string g_last_error_global;
 static std::mutex g_err_mu;
@@ -189,6 +191,11 @@ const CUtensorMap* get_tmap_im2col_f32(const Im2colSpec& spec) {
 }  // namespace dtf
 
 extern "C" int dtf_version(void) { return 100; }
+
+extern "C" int dtf_debug_set_pdl(int enabled) {
+  dtf::g_pdl_enabled = enabled;
+  return 0;
+}
 
 extern "C" const char* dtf_last_error(void) {
   static thread_local std::string copy;

@@ -32,6 +32,15 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // ---------------------------------------------------------------------------------------
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may start
+// (CTA by CTA, as SMs free up) while its predecessor is still running; its prologue — barrier init, TMEM
+// allocation, descriptor prefetch — overlaps the predecessor's tail, and pdl_wait() blocks until the predecessor
+// grid has completed and its memory is visible.  Both are no-ops for a normally launched kernel.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

@@ -85,6 +85,8 @@ def lib() -> C.CDLL:
             build_library(force=os.environ.get("DTF_REBUILD") == "1")
         l = C.CDLL(str(LIB_PATH))
         _declare(l)
+        if os.environ.get("DTF_PDL") == "0":          # plain stream order instead of programmatic dependent launch
+            l.dtf_debug_set_pdl(0)
         _lib = l
     return _lib
 

@@ -25,6 +25,9 @@ extern "C" {
 /* ------------------------------------------------------------------------------------ */
 int dtf_version(void);
 const char* dtf_last_error(void);
+/* Debug aid: 0 launches the convolution kernels in plain stream order; 1 (default) with programmatic dependent
+ * launch, so that a kernel's prologue overlaps the tail of its predecessor. */
+int dtf_debug_set_pdl(int enabled);
 
 /* ------------------------------------------------------------------------------------ */
 /* K1  implicit-GEMM convolution on tcgen05 (kind::tf32, fp32 accumulate in TMEM)         */
