@@ -16,6 +16,7 @@
 // (resnet/resnet_model.py:41-50), plus their gradients.
 #include "../include/dtf_b200.h"
 #include "host_common.h"
+#include "umma.cuh"
 
 namespace dtf {
 
@@ -151,6 +152,7 @@ bn_bwd_apply_kernel(const float* __restrict__ dy, const float* __restrict__ x, c
                     const float* __restrict__ sums /* [2C] */, int relu, float inv_count, long long total4,
                     int chunks, int C, int ld_x, int ld_dy, int ld_dx, const float* __restrict__ add, int ld_add,
                     float* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  pdl_wait();      // launched with programmatic stream serialization: block scheduling overlaps the predecessor's tail
   if (blockIdx.x == 0) {
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       const float sg = sums[c], sgx = sums[C + c];
@@ -402,10 +404,9 @@ extern "C" int dtf_bn_bwd_apply(const float* dy, const float* x, const float* sc
   DTF_REQUIRE(C % 4 == 0, "channel count must be a multiple of 4");
   const long long total4 = M * (C / 4);
   if (total4 == 0) return 0;
-  bn_bwd_apply_kernel<<<ew_grid(total4), 256, 0, stream>>>(dy, x, scale, shift, mean, invstd, sums, relu,
-                                                           1.f / (float)M, total4, C / 4, C, ld_x, ld_dy, ld_dx, add,
-                                                           ld_add, dx, dgamma, dbeta);
-  DTF_CHECK(cudaGetLastError());
+  DTF_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(ew_grid(total4)), dim3(256), 0, stream, dy, x, scale, shift, mean,
+                       invstd, sums, relu, 1.f / (float)M, total4, C / 4, C, ld_x, ld_dy, ld_dx, add, ld_add, dx, dgamma,
+                       dbeta));
   return 0;
 }
 
