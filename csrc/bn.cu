@@ -131,7 +131,8 @@ affine_act_kernel(const float* __restrict__ x, const float* __restrict__ scale, 
                   int relu, long long total4, int chunks, int ld_x, int ld_y, float* __restrict__ y) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / chunks;
+    // 32-bit division when the index allows it (a 64-bit division by a run-time value is ~100 instructions)
+    const long long r = (i >> 31) == 0 ? (long long)((unsigned)i / (unsigned)chunks) : i / chunks;
     const int cc = (int)(i - r * chunks);
     const float4 xv = __ldg(reinterpret_cast<const float4*>(x + r * ld_x) + cc);
     const float4 sc = __ldg(reinterpret_cast<const float4*>(scale) + cc);
@@ -164,7 +165,8 @@ bn_bwd_apply_kernel(const float* __restrict__ dy, const float* __restrict__ x, c
   }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / chunks;
+    // 32-bit division when the index allows it (a 64-bit division by a run-time value is ~100 instructions)
+    const long long r = (i >> 31) == 0 ? (long long)((unsigned)i / (unsigned)chunks) : i / chunks;
     const int cc = (int)(i - r * chunks);
     const float4 xv = __ldg(reinterpret_cast<const float4*>(x + r * ld_x) + cc);
     float4 g = __ldg(reinterpret_cast<const float4*>(dy + r * ld_dy) + cc);
@@ -204,7 +206,8 @@ affine_act_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
                       int ld_dy, int ld_dx, float* __restrict__ dx) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / chunks;
+    // 32-bit division when the index allows it (a 64-bit division by a run-time value is ~100 instructions)
+    const long long r = (i >> 31) == 0 ? (long long)((unsigned)i / (unsigned)chunks) : i / chunks;
     const int cc = (int)(i - r * chunks);
     const float4 xv = __ldg(reinterpret_cast<const float4*>(x + r * ld_x) + cc);
     float4 g = __ldg(reinterpret_cast<const float4*>(dy + r * ld_dy) + cc);

@@ -25,11 +25,14 @@ max_pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, unsigned
   const int chunks = g.C >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const int cc = (int)(i % chunks);
-    long long p = i / chunks;
-    const int ow = (int)(p % g.OW); p /= g.OW;
-    const int oh = (int)(p % g.OH);
-    const int n = (int)(p / g.OH);
+    // 32-bit index arithmetic (the launcher rejects tensors of 2^31 chunks or more): 64-bit divisions by run-time
+    // values cost ~100 instructions each and made these kernels issue-bound
+    const unsigned iu = (unsigned)i;
+    const int cc = (int)(iu % (unsigned)chunks);
+    unsigned p = iu / (unsigned)chunks;
+    const int ow = (int)(p % (unsigned)g.OW); p /= (unsigned)g.OW;
+    const int oh = (int)(p % (unsigned)g.OH);
+    const int n = (int)(p / (unsigned)g.OH);
     float4 m = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
     uchar4 am = make_uchar4(0, 0, 0, 0);
     for (int r = 0; r < g.kh; ++r) {
@@ -58,11 +61,12 @@ max_pool_bwd_kernel(const float* __restrict__ dy, const unsigned char* __restric
   const int chunks = g.C >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const int cc = (int)(i % chunks);
-    long long p = i / chunks;
-    const int iw = (int)(p % g.W); p /= g.W;
-    const int ih = (int)(p % g.H);
-    const int n = (int)(p / g.H);
+    const unsigned iu = (unsigned)i;
+    const int cc = (int)(iu % (unsigned)chunks);
+    unsigned p = iu / (unsigned)chunks;
+    const int iw = (int)(p % (unsigned)g.W); p /= (unsigned)g.W;
+    const int ih = (int)(p % (unsigned)g.H);
+    const int n = (int)(p / (unsigned)g.H);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     // output rows oh with oh*sh - ph <= ih <= oh*sh - ph + kh - 1
     int oh_lo = (ih + g.ph - g.kh + g.sh) / g.sh; if (ih + g.ph - g.kh + 1 <= 0) oh_lo = 0;
@@ -101,11 +105,14 @@ avg_pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, PoolGeom
   const int chunks = g.C >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const int cc = (int)(i % chunks);
-    long long p = i / chunks;
-    const int ow = (int)(p % g.OW); p /= g.OW;
-    const int oh = (int)(p % g.OH);
-    const int n = (int)(p / g.OH);
+    // 32-bit index arithmetic (the launcher rejects tensors of 2^31 chunks or more): 64-bit divisions by run-time
+    // values cost ~100 instructions each and made these kernels issue-bound
+    const unsigned iu = (unsigned)i;
+    const int cc = (int)(iu % (unsigned)chunks);
+    unsigned p = iu / (unsigned)chunks;
+    const int ow = (int)(p % (unsigned)g.OW); p /= (unsigned)g.OW;
+    const int oh = (int)(p % (unsigned)g.OH);
+    const int n = (int)(p / (unsigned)g.OH);
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = 0; r < g.kh; ++r) {
       const int ih = oh * g.sh - g.ph + r;
@@ -131,11 +138,12 @@ avg_pool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, PoolGe
   const int chunks = g.C >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
-    const int cc = (int)(i % chunks);
-    long long p = i / chunks;
-    const int iw = (int)(p % g.W); p /= g.W;
-    const int ih = (int)(p % g.H);
-    const int n = (int)(p / g.H);
+    const unsigned iu = (unsigned)i;
+    const int cc = (int)(iu % (unsigned)chunks);
+    unsigned p = iu / (unsigned)chunks;
+    const int iw = (int)(p % (unsigned)g.W); p /= (unsigned)g.W;
+    const int ih = (int)(p % (unsigned)g.H);
+    const int n = (int)(p / (unsigned)g.H);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     int oh_lo = (ih + g.ph - g.kh + g.sh) / g.sh; if (ih + g.ph - g.kh + 1 <= 0) oh_lo = 0;
     int oh_hi = (ih + g.ph) / g.sh; if (oh_hi >= g.OH) oh_hi = g.OH - 1;
@@ -217,6 +225,7 @@ extern "C" int dtf_max_pool_fwd(const dtf_pool_params* p, const float* x, float*
   DTF_REQUIRE(p->kh * p->kw <= 255, "window too large for the one-byte argmax");
   const long long total4 = (long long)p->N * p->OH * p->OW * (p->C / 4);
   if (total4 == 0) return 0;
+  DTF_REQUIRE(total4 < (1LL << 31), "pooling tensor too large for 32-bit indexing");
   max_pool_fwd_kernel<<<pool_grid(total4), 256, 0, stream>>>(x, y, argmax, make_geom(*p), total4);
   DTF_CHECK(cudaGetLastError());
   return 0;
@@ -227,6 +236,7 @@ extern "C" int dtf_max_pool_bwd(const dtf_pool_params* p, const float* dy, int l
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const long long total4 = (long long)p->N * p->H * p->W * (p->C / 4);
   if (total4 == 0) return 0;
+  DTF_REQUIRE(total4 < (1LL << 31), "pooling tensor too large for 32-bit indexing");
   max_pool_bwd_kernel<<<pool_grid(total4), 256, 0, stream>>>(dy, argmax, dx, make_geom(*p), ld_dy, ld_dx, total4);
   DTF_CHECK(cudaGetLastError());
   return 0;
@@ -243,6 +253,7 @@ extern "C" int dtf_avg_pool_fwd(const dtf_pool_params* p, const float* x, float*
     DTF_CHECK(cudaGetLastError());
     return 0;
   }
+  DTF_REQUIRE(total4 < (1LL << 31), "pooling tensor too large for 32-bit indexing");
   avg_pool_fwd_kernel<<<pool_grid(total4), 256, 0, stream>>>(x, y, make_geom(*p), total4);
   DTF_CHECK(cudaGetLastError());
   return 0;
@@ -253,6 +264,7 @@ extern "C" int dtf_avg_pool_bwd(const dtf_pool_params* p, const float* dy, int l
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const long long total4 = (long long)p->N * p->H * p->W * (p->C / 4);
   if (total4 == 0) return 0;
+  DTF_REQUIRE(total4 < (1LL << 31), "pooling tensor too large for 32-bit indexing");
   avg_pool_bwd_kernel<<<pool_grid(total4), 256, 0, stream>>>(dy, dx, make_geom(*p), ld_dy, ld_dx, total4);
   DTF_CHECK(cudaGetLastError());
   return 0;
