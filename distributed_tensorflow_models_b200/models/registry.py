@@ -14,7 +14,7 @@ import functools
 from dataclasses import dataclass
 from typing import Callable, Dict, Optional
 
-from . import alexnet, cifarnet, inception_v3, plain_cnn, resnet, vgg
+from . import alexnet, cifarnet, inception_v3, plain_cnn, resnet, vgg, zoo_small
 
 
 @dataclass(frozen=True)
@@ -85,14 +85,17 @@ networks_map: Dict[str, Callable] = {
     "resnet_v2_152": _resnet_imagenet(152),
     "resnet_v2_200": _resnet_imagenet(200),
     "inception_v3": _inception,
+    "lenet": zoo_small.lenet,
+    "overfeat": zoo_small.overfeat,
 }
 
 arg_scopes_map: Dict[str, Callable] = {
     "vgg_a": vgg.vgg_arg_scope, "vgg_16": vgg.vgg_arg_scope, "vgg_19": vgg.vgg_arg_scope,
+    "lenet": zoo_small.lenet_arg_scope, "overfeat": zoo_small.overfeat_arg_scope,
 }
 
 default_image_sizes = {"cnn": 24, "cifarnet": 32, "alexnet_v2": 224, "vgg_a": 224, "vgg_16": 224, "vgg_19": 224,
-                       "resnet_cifar": 32, "inception_v3": 299}
+                       "resnet_cifar": 32, "inception_v3": 299, "lenet": 28, "overfeat": 231}
 
 
 def get_network_fn(name: str, num_classes: int, weight_decay: float = 0.0, is_training: bool = False) -> Callable:

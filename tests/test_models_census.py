@@ -157,3 +157,20 @@ def test_model_specs_cover_reference_defaults():
     assert {k: v.batch_size for k, v in s.items()} == {"cnn": 512, "cifarnet": 512, "alexnet": 128, "vgg": 72,
                                                        "resnet": 128, "inception": 32}
     assert s["cnn"].image_size == 24 and s["inception"].num_classes == 1001
+
+
+def test_zoo_lenet_and_overfeat():
+    """Small zoo members reachable through the factory (vgg/nets/nets_factory.py:39-100)."""
+    st, out, eps = _build("lenet", (2, 28, 28, 1), 10)
+    assert tuple(out.shape) == (2, 10)
+    names = [v.name for v in st.all()]
+    assert names == ["LeNet/conv1/weights", "LeNet/conv1/biases", "LeNet/conv2/weights", "LeNet/conv2/biases",
+                     "LeNet/fc3/weights", "LeNet/fc3/biases", "LeNet/fc4/weights", "LeNet/fc4/biases"]
+    # 5*5*1*32+32 + 5*5*32*64+64 + 7*7*64*1024+1024 + 1024*10+10
+    assert _nparams(st) == 832 + 51264 + 3212288 + 10250
+    assert tuple(eps["pool2"].shape) == (2, 7, 7, 64)
+    st, out, eps = _build("overfeat", (1, 231, 231, 3), 1000)
+    assert tuple(out.shape) == (1, 1000)
+    assert tuple(eps["pool5"].shape) == (1, 6, 6, 1024) and tuple(eps["fc7"].shape) == (1, 1, 1, 4096)
+    assert st.get("overfeat/fc6/weights").tf_shape == (6, 6, 1024, 3072)
+    assert get_network_fn("overfeat", 1000).default_image_size == 231
