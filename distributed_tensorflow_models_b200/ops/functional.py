@@ -102,6 +102,19 @@ def conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None
     return y.permute(0, 2, 3, 1)
 
 
+def atrous_conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], rate: int,
+                  padding: str = "SAME") -> torch.Tensor:
+    """Dilated stride-1 convolution (slim.conv2d(rate=...) under ``output_stride``, vgg/nets/resnet_utils.py:123)."""
+    if use_native(x):
+        raise NotImplementedError("native convolution: rate > 1 (output_stride) is not implemented")
+    co, r, s, ci = w.shape
+    er, es = (r - 1) * rate + 1, (s - 1) * rate + 1
+    oh, ow, ph, pw = resolve_padding(x.shape[1], x.shape[2], er, es, (1, 1), padding)
+    xn = F.pad(x.permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))
+    y = F.conv2d(xn, w.permute(0, 3, 1, 2), bias, dilation=rate)
+    return y.permute(0, 2, 3, 1)
+
+
 def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False) -> torch.Tensor:
     """x[N, in] @ w[out, in]^T + b (tf.matmul/xw_plus_b — cnn/cifar10.py:262, slim/ops.py:305)."""
     if use_native(x):
@@ -109,6 +122,58 @@ def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None
         return native_ops.linear(x, w, bias, relu)
     y = F.linear(x, w, bias)
     return F.relu(y) if relu else y
+
+
+def depthwise_conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, stride=1,
+                     padding: Padding = "SAME", rate: int = 1) -> torch.Tensor:
+    """tf.nn.depthwise_conv2d: filter ``[R, S, C, multiplier]`` (TensorFlow's own layout), output channel
+    ``c*multiplier + m`` (vgg/nets/mobilenet_v1.py:260-277 through slim.separable_conv2d)."""
+    stride = _pair(stride)
+    n, h, wd, c = x.shape
+    r, s, c2, mult = w.shape
+    assert c2 == c
+    er, es = (r - 1) * rate + 1, (s - 1) * rate + 1
+    oh, ow, ph, pw = resolve_padding(h, wd, er, es, stride, padding)
+    if use_native(x):
+        if rate != 1:
+            raise NotImplementedError("native depthwise convolution: rate > 1 is not implemented")
+        from . import zoo_native
+        return zoo_native.depthwise_conv2d(x, w, bias, stride, (ph[0], pw[0]), (oh, ow))
+    xn = F.pad(x.permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))
+    wt = w.permute(2, 3, 0, 1).reshape(c * mult, 1, r, s)
+    y = F.conv2d(xn, wt, bias, stride=stride, dilation=rate, groups=c)[:, :, :oh, :ow]
+    return y.permute(0, 2, 3, 1)
+
+
+def conv2d_transpose_output_size(size: int, k: int, stride: int, padding: str) -> int:
+    """tf.contrib.layers.conv2d_transpose output extent: SAME -> size*stride, VALID -> size*stride + max(k-stride, 0)."""
+    return size * stride if padding.upper() == "SAME" else size * stride + max(k - stride, 0)
+
+
+def conv2d_transpose(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, stride=2,
+                     padding: str = "SAME") -> torch.Tensor:
+    """slim.conv2d_transpose (vgg/nets/dcgan.py:169, pix2pix.py:90, cyclegan.py:110): the gradient of a forward
+    convolution with respect to its input.  ``w`` is stored ``[C_out, R, S, C_in]``."""
+    stride = _pair(stride)
+    n, h, wd, c = x.shape
+    co, r, s, ci = w.shape
+    assert ci == c
+    oh = conv2d_transpose_output_size(h, r, stride[0], padding)
+    ow = conv2d_transpose_output_size(wd, s, stride[1], padding)
+    # padding of the forward convolution (oh, ow) -> (h, wd) this op transposes
+    fh, fw, ph, pw = resolve_padding(oh, ow, r, s, stride, padding)
+    assert (fh, fw) == (h, wd), "transposed convolution geometry does not invert"
+    if use_native(x):
+        from . import zoo_native
+        return zoo_native.conv2d_transpose(x, w, bias, stride, (ph[0], pw[0]), (oh, ow))
+    # conv_transpose2d wants [C_in, C_out, R, S]; build the full output then cut the forward padding off
+    y = F.conv_transpose2d(x.permute(0, 3, 1, 2), w.permute(3, 0, 1, 2), None, stride=stride)
+    full_h, full_w = y.shape[2], y.shape[3]
+    y = F.pad(y, (0, max(0, pw[0] + ow - full_w), 0, max(0, ph[0] + oh - full_h)))
+    y = y[:, :, ph[0]:ph[0] + oh, pw[0]:pw[0] + ow]
+    if bias is not None:
+        y = y + bias.view(1, -1, 1, 1)
+    return y.permute(0, 2, 3, 1)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -228,6 +293,112 @@ def dropout(x: torch.Tensor, keep_prob: float, training: bool) -> torch.Tensor:
 
 def relu(x: torch.Tensor) -> torch.Tensor:
     return F.relu(x)
+
+
+def _act(x: torch.Tensor, kind: str, alpha: float = 0.2) -> torch.Tensor:
+    if use_native(x) and x.dtype == torch.float32:
+        from . import zoo_native
+        return zoo_native.activation(x, kind, alpha)
+    if kind == "relu6":
+        return F.relu6(x)
+    if kind == "leaky_relu":
+        return F.leaky_relu(x, alpha)
+    if kind == "tanh":
+        return torch.tanh(x)
+    return torch.sigmoid(x)
+
+
+def relu6(x: torch.Tensor) -> torch.Tensor:
+    """tf.nn.relu6 (vgg/nets/mobilenet_v1.py:430)."""
+    return _act(x, "relu6")
+
+
+def leaky_relu(x: torch.Tensor, alpha: float = 0.2) -> torch.Tensor:
+    """tf.nn.leaky_relu, default slope 0.2 (vgg/nets/dcgan.py:89, pix2pix.py:172)."""
+    return _act(x, "leaky_relu", alpha)
+
+
+def tanh(x: torch.Tensor) -> torch.Tensor:
+    """tf.tanh (vgg/nets/pix2pix.py:220, cyclegan.py:271)."""
+    return _act(x, "tanh")
+
+
+def sigmoid(x: torch.Tensor) -> torch.Tensor:
+    return _act(x, "sigmoid")
+
+
+def instance_norm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
+                  eps: float = 1e-6) -> torch.Tensor:
+    """tf.contrib.layers.instance_norm: per-image, per-channel moments over H, W (vgg/nets/cyclegan.py:47-60)."""
+    if use_native(x):
+        from . import zoo_native
+        return zoo_native.instance_norm(x, gamma, beta, eps)
+    mean = x.mean((1, 2), keepdim=True)
+    var = x.var((1, 2), unbiased=False, keepdim=True)
+    y = (x - mean) * torch.rsqrt(var + eps)
+    if gamma is not None:
+        y = y * gamma
+    if beta is not None:
+        y = y + beta
+    return y
+
+
+def _resize_index(out: int, size: int, align_corners: bool, device):
+    scale = (size - 1) / (out - 1) if (align_corners and out > 1) else size / out
+    return torch.arange(out, dtype=torch.float32, device=device) * scale
+
+
+def resize_nearest(x: torch.Tensor, out_hw, align_corners: bool = False) -> torch.Tensor:
+    """tf.image.resize_nearest_neighbor (TF1: source index floor(dst * in/out)) — vgg/nets/cyclegan.py:96."""
+    oh, ow = int(out_hw[0]), int(out_hw[1])
+    if use_native(x):
+        from . import zoo_native
+        return zoo_native.resize(x, (oh, ow), False, align_corners)
+    sh = _resize_index(oh, x.shape[1], align_corners, x.device)
+    sw = _resize_index(ow, x.shape[2], align_corners, x.device)
+    ih = (torch.round(sh) if align_corners else torch.floor(sh)).long().clamp_(max=x.shape[1] - 1)
+    iw = (torch.round(sw) if align_corners else torch.floor(sw)).long().clamp_(max=x.shape[2] - 1)
+    return x[:, ih][:, :, iw]
+
+
+def resize_bilinear(x: torch.Tensor, out_hw, align_corners: bool = False) -> torch.Tensor:
+    """tf.image.resize_bilinear with TF1's sampling grid (src = dst * in/out, no half-pixel shift) —
+    vgg/nets/cyclegan.py:101."""
+    oh, ow = int(out_hw[0]), int(out_hw[1])
+    if use_native(x):
+        from . import zoo_native
+        return zoo_native.resize(x, (oh, ow), True, align_corners)
+    h, w = x.shape[1], x.shape[2]
+    sh = _resize_index(oh, h, align_corners, x.device)
+    sw = _resize_index(ow, w, align_corners, x.device)
+    h0 = torch.floor(sh).long().clamp_(max=h - 1)
+    w0 = torch.floor(sw).long().clamp_(max=w - 1)
+    h1 = (h0 + 1).clamp_(max=h - 1)
+    w1 = (w0 + 1).clamp_(max=w - 1)
+    fh = (sh - h0).view(1, oh, 1, 1)
+    fw = (sw - w0).view(1, 1, ow, 1)
+    top = x[:, h0][:, :, w0] + (x[:, h0][:, :, w1] - x[:, h0][:, :, w0]) * fw
+    bot = x[:, h1][:, :, w0] + (x[:, h1][:, :, w1] - x[:, h1][:, :, w0]) * fw
+    return top + (bot - top) * fh
+
+
+def pad_spatial(x: torch.Tensor, pads, mode: str = "constant") -> torch.Tensor:
+    """tf.pad on the two spatial axes of NHWC; ``pads = (top, bottom, left, right)``, mode 'constant' (zeros)
+    or 'reflect' (vgg/nets/cyclegan.py:201, resnet fixed padding)."""
+    pt, pb, pl, pr = (int(v) for v in pads)
+    if use_native(x):
+        from . import zoo_native
+        return zoo_native.pad(x, (pt, pb, pl, pr), mode)
+    return F.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb), mode=mode).permute(0, 2, 3, 1)
+
+
+def drop_path(x: torch.Tensor, keep_prob: float, training: bool, generator=None) -> torch.Tensor:
+    """NASNet's drop-path: zero a whole example's branch with probability 1-keep_prob and rescale the rest
+    (vgg/nets/nasnet/nasnet_utils.py:153-163)."""
+    if not training or keep_prob >= 1.0:
+        return x
+    mask = torch.floor(keep_prob + torch.rand((x.shape[0], 1, 1, 1), device=x.device, generator=generator))
+    return x * (mask / keep_prob)
 
 
 def flatten(x: torch.Tensor) -> torch.Tensor:

@@ -24,7 +24,7 @@ import torch
 from ..ops import functional as Fn
 from . import losses
 from . import variables as V
-from .scopes import add_arg_scope
+from .scopes import add_arg_scope, current_arg_scope
 
 UPDATE_OPS_COLLECTION = V.UPDATE_OPS_COLLECTION
 
@@ -233,16 +233,133 @@ def fully_connected(inputs, num_outputs, activation_fn=relu, weights_initializer
               biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope, trainable=trainable)
 
 
+def _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, trainable=True):
+    """tf.contrib.layers post-processing order: normaliser (which replaces the bias), then activation."""
+    if normalizer_fn is not None:
+        params = dict(normalizer_params or {})
+        if normalizer_fn is batch_norm and _is_relu(activation_fn):
+            return batch_norm(y, activation=activation_fn, trainable=trainable, **params)
+        y = normalizer_fn(y, **params)
+    if activation_fn is not None:
+        y = activation_fn(y)
+    return y
+
+
 @add_arg_scope
 def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", activation_fn=relu,
                   weights_initializer=None, biases_initializer=None, weights_regularizer=None, scope=None,
-                  trainable=True, normalizer_fn=None, normalizer_params=None):
-    """slim.conv2d in its tf.contrib form (cifarnet/cifarnet.py:64, alexnet/alexnet.py:103, vgg.py:190)."""
+                  trainable=True, normalizer_fn=None, normalizer_params=None, rate=1):
+    """slim.conv2d in its tf.contrib form (cifarnet/cifarnet.py:64, alexnet/alexnet.py:103, vgg.py:190; with
+    ``normalizer_fn`` / ``rate`` throughout the zoo, e.g. vgg/nets/resnet_utils.py:123, mobilenet_v1.py:255)."""
     wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
-    return conv2d(inputs, num_outputs, kernel_size, stride=stride, padding=padding, activation=activation_fn,
-                  weight_decay=wd, weights_initializer=weights_initializer or V.xavier_initializer(),
-                  biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope, trainable=trainable,
-                  batch_norm_params=normalizer_params if normalizer_fn is not None else None)
+    w_init = weights_initializer or V.xavier_initializer()
+    if (normalizer_fn is None or normalizer_fn is batch_norm) and rate == 1:
+        bn_params, is_tr = None, True
+        if normalizer_fn is not None:
+            # defaults that an enclosing arg_scope([batch_norm], ...) put in force, then the explicit parameters
+            bn_params = dict(current_arg_scope().get(batch_norm._dtf_arg_scope_key, {}))
+            bn_params.update(normalizer_params or {})
+            is_tr = bn_params.pop("is_training", True)
+            bn_params.pop("activation", None)
+        return conv2d(inputs, num_outputs, kernel_size, stride=stride, padding=padding, activation=activation_fn,
+                      weight_decay=wd, weights_initializer=w_init,
+                      biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope,
+                      trainable=trainable, is_training=is_tr, batch_norm_params=bn_params)
+    store = V.current_store()
+    kh, kw = _two(kernel_size)
+    cin = inputs.shape[-1]
+    with store.scope(scope, "Conv"):
+        reg = losses.l2_regularizer(wd) if wd > 0 else None
+        w = V.variable("weights", (num_outputs, kh, kw, cin), initializer=w_init, regularizer=reg,
+                       trainable=trainable, tf_layout="hwio", tf_shape=(kh, kw, cin, num_outputs),
+                       fan_in=kh * kw * cin, fan_out=kh * kw * num_outputs)
+        b = None
+        if normalizer_fn is None:
+            b = V.variable("biases", (num_outputs,), initializer=biases_initializer or V.zeros_initializer(),
+                           trainable=trainable)
+        if rate != 1:
+            y = Fn.atrous_conv2d(inputs, w, b, rate, padding)
+        else:
+            y = Fn.conv2d(inputs, w, b, _two(stride), padding)
+        return _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, trainable)
+
+
+@add_arg_scope
+def separable_convolution2d(inputs, num_outputs, kernel_size, depth_multiplier=1, stride=1, padding="SAME", rate=1,
+                            activation_fn=relu, normalizer_fn=None, normalizer_params=None,
+                            weights_initializer=None, weights_regularizer=None, biases_initializer=None, scope=None,
+                            trainable=True):
+    """slim.separable_conv2d: a depthwise convolution (``depthwise_weights`` [kh, kw, C, multiplier]) followed,
+    when ``num_outputs`` is not None, by a 1x1 convolution (``pointwise_weights``); the stride belongs to the
+    depthwise stage; bias / normaliser / activation come once, at the end
+    (vgg/nets/mobilenet_v1.py:260-277, mobilenet/conv_blocks.py:120-140, nasnet/nasnet_utils.py:206-240)."""
+    store = V.current_store()
+    kh, kw = _two(kernel_size)
+    cin = inputs.shape[-1]
+    wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
+    reg = losses.l2_regularizer(wd) if wd > 0 else None
+    w_init = weights_initializer or V.xavier_initializer()
+    with store.scope(scope, "SeparableConv2d"):
+        dw = V.variable("depthwise_weights", (kh, kw, cin, depth_multiplier), initializer=w_init, regularizer=reg,
+                        trainable=trainable, fan_in=kh * kw * cin, fan_out=kh * kw * depth_multiplier)
+        cmid = cin * depth_multiplier
+        cout = cmid if num_outputs is None else num_outputs
+        pw = None
+        if num_outputs is not None:
+            pw = V.variable("pointwise_weights", (cout, 1, 1, cmid), initializer=w_init, regularizer=reg,
+                            trainable=trainable, tf_layout="hwio", tf_shape=(1, 1, cmid, cout), fan_in=cmid,
+                            fan_out=cout)
+        b = None
+        if normalizer_fn is None:
+            b = V.variable("biases", (cout,), initializer=biases_initializer or V.zeros_initializer(),
+                           trainable=trainable)
+        y = Fn.depthwise_conv2d(inputs, dw, b if pw is None else None, _two(stride), padding, rate=rate)
+        if pw is not None:
+            y = Fn.conv2d(y, pw, b, (1, 1), "VALID")
+        return _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, trainable)
+
+
+@add_arg_scope
+def convolution2d_transpose(inputs, num_outputs, kernel_size, stride=1, padding="SAME", activation_fn=relu,
+                            normalizer_fn=None, normalizer_params=None, weights_initializer=None,
+                            weights_regularizer=None, biases_initializer=None, scope=None, trainable=True):
+    """slim.conv2d_transpose; ``weights`` is [kh, kw, C_out, C_in] in TensorFlow's layout
+    (vgg/nets/dcgan.py:160-181, pix2pix.py:90, cyclegan.py:110)."""
+    store = V.current_store()
+    kh, kw = _two(kernel_size)
+    cin = inputs.shape[-1]
+    wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
+    with store.scope(scope, "Conv2d_transpose"):
+        w = V.variable("weights", (num_outputs, kh, kw, cin), initializer=weights_initializer or V.xavier_initializer(),
+                       regularizer=losses.l2_regularizer(wd) if wd > 0 else None, trainable=trainable,
+                       tf_layout="hwoi", tf_shape=(kh, kw, num_outputs, cin), fan_in=kh * kw * cin,
+                       fan_out=kh * kw * num_outputs)
+        b = None
+        if normalizer_fn is None:
+            b = V.variable("biases", (num_outputs,), initializer=biases_initializer or V.zeros_initializer(),
+                           trainable=trainable)
+        y = Fn.conv2d_transpose(inputs, w, b, _two(stride), padding)
+        return _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, trainable)
+
+
+@add_arg_scope
+def instance_norm(inputs, center=True, scale=True, epsilon=1e-6, activation_fn=None, trainable=True, scope=None):
+    """tf.contrib.layers.instance_norm: variables ``InstanceNorm/{beta,gamma}`` (vgg/nets/cyclegan.py:47-60)."""
+    store = V.current_store()
+    c = inputs.shape[-1]
+    with store.scope(scope, "InstanceNorm"):
+        beta = V.variable("beta", (c,), initializer=V.zeros_initializer(), trainable=trainable) if center else None
+        gamma = V.variable("gamma", (c,), initializer=V.ones_initializer(), trainable=trainable) if scale else None
+    y = Fn.instance_norm(inputs, gamma, beta, epsilon)
+    return activation_fn(y) if activation_fn is not None else y
+
+
+relu6 = Fn.relu6
+leaky_relu = Fn.leaky_relu
+tanh = Fn.tanh
+sigmoid = Fn.sigmoid
+separable_conv2d = separable_convolution2d
+conv2d_transpose = convolution2d_transpose
 
 
 def softmax(logits: torch.Tensor, scope=None) -> torch.Tensor:

@@ -160,7 +160,8 @@ class Variable:
     device: str = ""                     # TF-style placement string ('' = local)
     weight_decay: float = 0.0            # l2 regulariser weight: loss += wd * sum(w^2)/2
     l1: float = 0.0
-    tf_layout: Optional[str] = None      # 'hwio' (stored OHWI), 'io' (stored [out,in]) or None (as is)
+    tf_layout: Optional[str] = None      # 'hwio' (stored OHWI), 'hwoi' (transposed conv, stored OHWI),
+                                         # 'io' (stored [out,in]) or None (as is)
     tf_shape: Tuple[int, ...] = ()
     restore: bool = True
     partitions: Optional[List[int]] = None   # slice lengths along axis 0 of tf_shape (axis-0 partitioner)
@@ -177,6 +178,8 @@ class Variable:
             return t.permute(1, 2, 3, 0).contiguous()
         if self.tf_layout == "io":
             return t.t().contiguous()
+        if self.tf_layout == "hwoi":          # transposed convolution: stored [C_out, R, S, C_in]
+            return t.permute(1, 2, 0, 3).contiguous()
         return t.clone()
 
     def from_tf(self, value: torch.Tensor) -> None:
@@ -186,6 +189,8 @@ class Variable:
                 v = v.permute(3, 0, 1, 2)
             elif self.tf_layout == "io":
                 v = v.t()
+            elif self.tf_layout == "hwoi":
+                v = v.permute(2, 0, 1, 3)
             self.tensor.copy_(v.reshape(self.tensor.shape))
 
 

@@ -205,6 +205,45 @@ int dtf_dropout(const float* x, float* y, long long n, float keep_prob, const un
 int dtf_colsum(const float* x, long long M, int C, int ld, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------ */
+/* Zoo op kinds: depthwise conv, relu6 / leaky-relu / tanh / sigmoid,        */
+/*     instance norm, resize, spatial padding — dense NHWC fp32 tensors                   */
+/*     (vgg/nets/mobilenet_v1.py:260-277, mobilenet/conv_blocks.py:120-140,               */
+/*      nasnet/nasnet_utils.py:206-240, dcgan.py:89, pix2pix.py:172,220,                  */
+/*      cyclegan.py:47-60,96-103,201-261)                                                 */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dtf_dwconv_params {
+  int N, H, W, C, mult;     /* input [N][H][W][C]; output channel c*mult + m          */
+  int R, S, sh, sw, ph, pw; /* filter [R][S][C][mult], stride, padding before         */
+  int OH, OW;               /* output spatial size (caller-resolved SAME / VALID)     */
+} dtf_dwconv_params;
+int dtf_dwconv_fwd(const dtf_dwconv_params* p, const float* x, const float* w, const float* bias /* or NULL */,
+                   float* y, void* stream);
+int dtf_dwconv_dgrad(const dtf_dwconv_params* p, const float* dy, const float* w, float* dx, void* stream);
+/* dw is ACCUMULATED into (the caller zeroes it) */
+int dtf_dwconv_wgrad(const dtf_dwconv_params* p, const float* x, const float* dy, float* dw, void* stream);
+/* mode: 0 relu6, 1 leaky-relu(alpha), 2 tanh, 3 sigmoid.  Backward takes ref = forward input (modes 0, 1) or
+ * forward output (modes 2, 3). */
+int dtf_act_fwd(const float* x, float* y, long long n, int mode, float alpha, void* stream);
+int dtf_act_bwd(const float* ref, const float* dy, float* dx, long long n, int mode, float alpha, void* stream);
+/* Instance norm over H*W per (image, channel); sums[N][2][C] receives (sum x, sum x^2) and is what the backward
+ * call needs as fwd_sums; bwd_sums[N][2][C] receives (sum dy, sum dy*xhat): dbeta / dgamma are their sums over N.
+ * gamma / beta may be NULL. */
+int dtf_instnorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* sums, int N, int HW,
+                     int C, float eps, void* stream);
+int dtf_instnorm_bwd(const float* x, const float* dy, const float* gamma, const float* fwd_sums, float* bwd_sums,
+                     float* dx, int N, int HW, int C, float eps, void* stream);
+/* TF1 resize (src = dst * in/out, or (in-1)/(out-1) with align_corners); bilinear = 0 -> nearest neighbour */
+int dtf_resize_fwd(const float* x, float* y, int N, int H, int W, int C, int OH, int OW, int bilinear,
+                   int align_corners, void* stream);
+int dtf_resize_bwd(const float* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int bilinear,
+                   int align_corners, void* stream);
+/* spatial padding (top, bottom, left, right); mode 0 zeros, 1 reflect (tf.pad 'REFLECT') */
+int dtf_pad_fwd(const float* x, float* y, int N, int H, int W, int C, int pt, int pb, int pl, int pr, int mode,
+                void* stream);
+int dtf_pad_bwd(const float* dy, float* dx, int N, int H, int W, int C, int pt, int pb, int pl, int pr, int mode,
+                void* stream);
+
+/* ------------------------------------------------------------------------------------ */
 /* K16 + C1..C5  parameter-server update / push / pull / clocks                           */
 /*     hyper[7] (device): lr, grad_scale, weight_decay, rms_decay, momentum, epsilon,    */
 /*     ema_decay (< 0 disables EMA).  kind: 0 SGD, 1 TF1 RMSProp with momentum.          */
