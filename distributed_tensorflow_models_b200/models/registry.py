@@ -14,7 +14,7 @@ import functools
 from dataclasses import dataclass
 from typing import Callable, Dict, Optional
 
-from . import alexnet, cifarnet, inception_v3, plain_cnn, resnet, vgg, zoo_small
+from . import alexnet, cifarnet, inception_v3, inception_zoo, mobilenet, plain_cnn, resnet, resnet_slim, vgg, zoo_small
 
 
 @dataclass(frozen=True)
@@ -87,11 +87,39 @@ networks_map: Dict[str, Callable] = {
     "inception_v3": _inception,
     "lenet": zoo_small.lenet,
     "overfeat": zoo_small.overfeat,
+    # the rest of the vendored zoo (vgg/nets/nets_factory.py:39-68); the slim bottleneck ResNet-v2s are registered
+    # as resnet_v2_*_slim because the plain names above are the reference's own resnet_model.py ImageNet nets
+    "inception_v1": inception_zoo.inception_v1,
+    "inception_v2": inception_zoo.inception_v2,
+    "inception_v3_slim": inception_zoo.inception_v3,
+    "inception_v4": inception_zoo.inception_v4,
+    "inception_resnet_v2": inception_zoo.inception_resnet_v2,
+    "resnet_v1_50": resnet_slim.resnet_v1_50,
+    "resnet_v1_101": resnet_slim.resnet_v1_101,
+    "resnet_v1_152": resnet_slim.resnet_v1_152,
+    "resnet_v1_200": resnet_slim.resnet_v1_200,
+    "resnet_v2_50_slim": resnet_slim.resnet_v2_50,
+    "resnet_v2_101_slim": resnet_slim.resnet_v2_101,
+    "resnet_v2_152_slim": resnet_slim.resnet_v2_152,
+    "resnet_v2_200_slim": resnet_slim.resnet_v2_200,
+    "mobilenet_v1": mobilenet.mobilenet_v1,
+    "mobilenet_v1_075": mobilenet.mobilenet_v1_075,
+    "mobilenet_v1_050": mobilenet.mobilenet_v1_050,
+    "mobilenet_v1_025": mobilenet.mobilenet_v1_025,
+    "mobilenet_v2": mobilenet.mobilenet_v2,
 }
 
 arg_scopes_map: Dict[str, Callable] = {
     "vgg_a": vgg.vgg_arg_scope, "vgg_16": vgg.vgg_arg_scope, "vgg_19": vgg.vgg_arg_scope,
     "lenet": zoo_small.lenet_arg_scope, "overfeat": zoo_small.overfeat_arg_scope,
+    "inception_v1": inception_zoo.inception_v3_arg_scope, "inception_v2": inception_zoo.inception_v3_arg_scope,
+    "inception_v3_slim": inception_zoo.inception_v3_arg_scope, "inception_v4": inception_zoo.inception_v4_arg_scope,
+    "inception_resnet_v2": inception_zoo.inception_resnet_v2_arg_scope,
+    **{f"resnet_v1_{n}": resnet_slim.resnet_arg_scope for n in (50, 101, 152, 200)},
+    **{f"resnet_v2_{n}_slim": resnet_slim.resnet_arg_scope for n in (50, 101, 152, 200)},
+    **{k: mobilenet.mobilenet_v1_arg_scope for k in ("mobilenet_v1", "mobilenet_v1_075", "mobilenet_v1_050",
+                                                      "mobilenet_v1_025")},
+    "mobilenet_v2": mobilenet.mobilenet_v2_training_scope,
 }
 
 default_image_sizes = {"cnn": 24, "cifarnet": 32, "alexnet_v2": 224, "vgg_a": 224, "vgg_16": 224, "vgg_19": 224,

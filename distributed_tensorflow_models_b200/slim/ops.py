@@ -205,7 +205,7 @@ def repeat(inputs, repetitions: int, layer: Callable, *args, **kwargs):
     scope = kwargs.pop("scope", None)
     with store.scope(scope, "Repeat"):
         out = inputs
-        base = scope or "repeat"
+        base = scope or getattr(layer, "__name__", None) or getattr(getattr(layer, "func", None), "__name__", "repeat")
         for i in range(repetitions):
             out = layer(out, *args, scope=f"{base}_{i + 1}", **kwargs)
         return out

@@ -49,6 +49,13 @@ def truncated_normal_initializer(stddev: float = 1.0, mean: float = 0.0) -> Call
     return init
 
 
+def random_normal_initializer(mean: float = 0.0, stddev: float = 1.0) -> Callable:
+    """tf.random_normal_initializer (un-truncated) — the GAN zoo's weight init (vgg/nets/pix2pix.py:59)."""
+    def init(shape, gen, fan_in=None, fan_out=None):
+        return torch.randn(tuple(shape), generator=gen, dtype=torch.float32) * stddev + mean
+    return init
+
+
 def constant_initializer(value: float = 0.0) -> Callable:
     def init(shape, gen, fan_in=None, fan_out=None):
         return torch.full(tuple(shape), float(value), dtype=torch.float32)
