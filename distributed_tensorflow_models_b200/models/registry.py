@@ -14,7 +14,8 @@ import functools
 from dataclasses import dataclass
 from typing import Callable, Dict, Optional
 
-from . import alexnet, cifarnet, inception_v3, inception_zoo, mobilenet, plain_cnn, resnet, resnet_slim, vgg, zoo_small
+from . import (alexnet, cifarnet, inception_v3, inception_zoo, mobilenet, nasnet, plain_cnn, resnet, resnet_slim, vgg,
+               zoo_small)
 
 
 @dataclass(frozen=True)
@@ -107,6 +108,10 @@ networks_map: Dict[str, Callable] = {
     "mobilenet_v1_050": mobilenet.mobilenet_v1_050,
     "mobilenet_v1_025": mobilenet.mobilenet_v1_025,
     "mobilenet_v2": mobilenet.mobilenet_v2,
+    "nasnet_cifar": nasnet.build_nasnet_cifar,
+    "nasnet_mobile": nasnet.build_nasnet_mobile,
+    "nasnet_large": nasnet.build_nasnet_large,
+    "pnasnet_large": nasnet.build_pnasnet_large,
 }
 
 arg_scopes_map: Dict[str, Callable] = {
@@ -120,6 +125,8 @@ arg_scopes_map: Dict[str, Callable] = {
     **{k: mobilenet.mobilenet_v1_arg_scope for k in ("mobilenet_v1", "mobilenet_v1_075", "mobilenet_v1_050",
                                                       "mobilenet_v1_025")},
     "mobilenet_v2": mobilenet.mobilenet_v2_training_scope,
+    "nasnet_cifar": nasnet.nasnet_cifar_arg_scope, "nasnet_mobile": nasnet.nasnet_mobile_arg_scope,
+    "nasnet_large": nasnet.nasnet_large_arg_scope, "pnasnet_large": nasnet.pnasnet_large_arg_scope,
 }
 
 default_image_sizes = {"cnn": 24, "cifarnet": 32, "alexnet_v2": 224, "vgg_a": 224, "vgg_16": 224, "vgg_19": 224,

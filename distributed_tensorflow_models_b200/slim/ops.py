@@ -248,7 +248,7 @@ def _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, 
 @add_arg_scope
 def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", activation_fn=relu,
                   weights_initializer=None, biases_initializer=None, weights_regularizer=None, scope=None,
-                  trainable=True, normalizer_fn=None, normalizer_params=None, rate=1):
+                  trainable=True, normalizer_fn=None, normalizer_params=None, rate=1, use_bias=True):
     """slim.conv2d in its tf.contrib form (cifarnet/cifarnet.py:64, alexnet/alexnet.py:103, vgg.py:190; with
     ``normalizer_fn`` / ``rate`` throughout the zoo, e.g. vgg/nets/resnet_utils.py:123, mobilenet_v1.py:255)."""
     wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
@@ -264,7 +264,7 @@ def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", ac
         return conv2d(inputs, num_outputs, kernel_size, stride=stride, padding=padding, activation=activation_fn,
                       weight_decay=wd, weights_initializer=w_init,
                       biases_initializer=biases_initializer or V.zeros_initializer(), scope=scope,
-                      trainable=trainable, is_training=is_tr, batch_norm_params=bn_params)
+                      trainable=trainable, is_training=is_tr, batch_norm_params=bn_params, use_bias=use_bias)
     store = V.current_store()
     kh, kw = _two(kernel_size)
     cin = inputs.shape[-1]
@@ -274,7 +274,7 @@ def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", ac
                        trainable=trainable, tf_layout="hwio", tf_shape=(kh, kw, cin, num_outputs),
                        fan_in=kh * kw * cin, fan_out=kh * kw * num_outputs)
         b = None
-        if normalizer_fn is None:
+        if normalizer_fn is None and use_bias:
             b = V.variable("biases", (num_outputs,), initializer=biases_initializer or V.zeros_initializer(),
                            trainable=trainable)
         if rate != 1:
@@ -288,7 +288,7 @@ def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", ac
 def separable_convolution2d(inputs, num_outputs, kernel_size, depth_multiplier=1, stride=1, padding="SAME", rate=1,
                             activation_fn=relu, normalizer_fn=None, normalizer_params=None,
                             weights_initializer=None, weights_regularizer=None, biases_initializer=None, scope=None,
-                            trainable=True):
+                            trainable=True, use_bias=True):
     """slim.separable_conv2d: a depthwise convolution (``depthwise_weights`` [kh, kw, C, multiplier]) followed,
     when ``num_outputs`` is not None, by a 1x1 convolution (``pointwise_weights``); the stride belongs to the
     depthwise stage; bias / normaliser / activation come once, at the end
@@ -310,7 +310,7 @@ def separable_convolution2d(inputs, num_outputs, kernel_size, depth_multiplier=1
                             trainable=trainable, tf_layout="hwio", tf_shape=(1, 1, cmid, cout), fan_in=cmid,
                             fan_out=cout)
         b = None
-        if normalizer_fn is None:
+        if normalizer_fn is None and use_bias:
             b = V.variable("biases", (cout,), initializer=biases_initializer or V.zeros_initializer(),
                            trainable=trainable)
         y = Fn.depthwise_conv2d(inputs, dw, b if pw is None else None, _two(stride), padding, rate=rate)

@@ -87,6 +87,16 @@ def variance_scaling_initializer(scale: float = 1.0) -> Callable:
     return init
 
 
+def contrib_variance_scaling_initializer(factor: float = 2.0, mode: str = "fan_in") -> Callable:
+    """tf.contrib.layers.variance_scaling_initializer(factor, mode, uniform=False): truncated normal with
+    stddev = sqrt(1.3 * factor / n), n = fan_in | fan_out | their mean (vgg/nets/nasnet/nasnet.py:117-118)."""
+    def init(shape, gen, fan_in=None, fan_out=None):
+        fi, fo = max(1, fan_in or 1), max(1, fan_out or 1)
+        n = {"fan_in": fi, "fan_out": fo, "fan_avg": (fi + fo) / 2.0}[mode.lower()]
+        return truncated_normal_initializer(math.sqrt(1.3 * factor / n))(shape, gen)
+    return init
+
+
 # ----------------------------------------------------------------------------------------------
 # placement helpers
 # ----------------------------------------------------------------------------------------------

@@ -8,7 +8,7 @@ import functools
 import pytest
 import torch
 
-from distributed_tensorflow_models_b200.models import gan, inception_zoo, mobilenet, registry, resnet_slim
+from distributed_tensorflow_models_b200.models import gan, inception_zoo, mobilenet, nasnet, registry, resnet_slim
 from distributed_tensorflow_models_b200.models.registry import get_network_fn
 from distributed_tensorflow_models_b200.ops import functional as Fn
 from distributed_tensorflow_models_b200.slim import VariableStore, ops
@@ -172,6 +172,54 @@ def test_inception_names_quirks_and_final_endpoints():
     assert "InceptionResnetV2/Repeat_1/block17_20/Branch_1/Conv2d_0c_7x1/weights" in names
 
 
+@pytest.mark.parametrize("fn,scope,size,nc,train,params,endpoints", [
+    # 5,291,035 / 88,757,183 are the published NASNet-A mobile / large sizes (+ the background class of 1001)
+    (nasnet.build_nasnet_mobile, nasnet.nasnet_mobile_arg_scope, 224, 1001, False, 5291035,
+     {"Stem": (28, 28, 88), "Cell_0": (28, 28, 264), "Reduction_Cell_1": (7, 7, 704), "Cell_11": (7, 7, 1056)}),
+    (nasnet.build_nasnet_mobile, nasnet.nasnet_mobile_arg_scope, 224, 1001, True, 7703044, {"AuxLogits": (1001,)}),
+    (nasnet.build_nasnet_cifar, nasnet.nasnet_cifar_arg_scope, 32, 10, True, 4978036,
+     {"Stem": (32, 32, 96), "Cell_17": (8, 8, 768), "AuxLogits": (10,)}),
+    (nasnet.build_nasnet_large, nasnet.nasnet_large_arg_scope, 331, 1001, False, 88757183,
+     {"Cell_0": (42, 42, 1008), "Cell_17": (11, 11, 4032)}),
+    (nasnet.build_pnasnet_large, nasnet.pnasnet_large_arg_scope, 331, 1001, False, 86061989,
+     {"Stem": (42, 42, 540), "Cell_11": (11, 11, 4320)}),
+])
+def test_nasnet_census(fn, scope, size, nc, train, params, endpoints):
+    st, out, ep = _build(fn, scope(), torch.randn(1, size, size, 3), num_classes=nc, is_training=train)
+    assert tuple(out.shape) == (1, nc) and _nparams(st) == params
+    for k, shape in endpoints.items():
+        assert tuple(ep[k].shape[1:]) == shape, k
+    names = {v.name for v in st.all()}
+    assert not any(n.endswith("biases") and "FC" not in n for n in names)      # bare convolutions
+    if fn is not nasnet.build_nasnet_cifar:
+        assert {"conv0/weights", "conv0_bn/gamma", "cell_stem_0/1x1/weights", "cell_stem_1/path1_conv/weights",
+                "cell_stem_1/final_path_bn/beta", "cell_0/path1_conv/weights", "cell_1/prev_1x1/weights",
+                "final_layer/FC/weights"} <= names
+    if fn is nasnet.build_nasnet_mobile:
+        assert {"cell_0/comb_iter_0/left/separable_5x5_1/depthwise_weights",
+                "cell_0/comb_iter_0/left/bn_sep_5x5_2/moving_variance",
+                "reduction_cell_0/comb_iter_1/right/separable_7x7_2/pointwise_weights",
+                "reduction_cell_1/comb_iter_0/left/separable_5x5_1/depthwise_weights"} <= names
+        assert ("aux_7/aux_logits/proj/weights" in names) == train
+
+
+def test_nasnet_genotype_helpers_and_drop_path_schedule():
+    assert nasnet.calc_reduction_layers(18, 2) == [6, 12] and nasnet.calc_reduction_layers(12, 2) == [4, 8]
+    cell = nasnet.Cell(nasnet.NASNET_A_NORMAL, 8, 0.6, 20, 1000, True, current_step=0)
+    x = torch.ones(4, 2, 2, 8)
+    assert torch.equal(cell._drop_path(x, 3), x)                 # ramp starts at keep = 1
+    cell.current_step = 1000
+    torch.manual_seed(0)
+    vals = cell._drop_path(torch.ones(256, 1, 1, 8), 19).unique().tolist()
+    assert len(vals) == 2 and vals[0] == 0.0 and abs(vals[1] - 1 / 0.6) < 1e-5      # last cell, end of training
+    st = VariableStore()
+    with torch.no_grad(), st.as_default(), nasnet.nasnet_cifar_arg_scope():
+        y = nasnet.factorized_reduction(torch.randn(1, 7, 7, 8), 12, 2)
+    assert tuple(y.shape) == (1, 4, 4, 12)
+    assert [v.name for v in st.trainable_variables()] == ["path1_conv/weights", "path2_conv/weights",
+                                                          "final_path_bn/beta", "final_path_bn/gamma"]
+
+
 # ---- the factory over everything it registers ---------------------------------------------------------------
 # the reference's local edits made alexnet_v2 (10 classes), the VGGs and the nets-edition Inception-v3 CIFAR-sized nets
 _SMALL = {"cnn": 24, "cifarnet": 32, "lenet": 28, "resnet_cifar": 32, "inception_v3_slim": 32, "alexnet_v2": 32,
@@ -181,7 +229,8 @@ _SMALL = {"cnn": 24, "cifarnet": 32, "lenet": 28, "resnet_cifar": 32, "inception
 @pytest.mark.parametrize("name", sorted(registry.networks_map))
 def test_nets_factory_builds_every_registered_network(name):
     if name in ("resnet_v2_152", "resnet_v2_200", "resnet_v1_152", "resnet_v1_200", "resnet_v2_152_slim",
-                "resnet_v2_200_slim", "resnet_v2_101", "resnet_v2_101_slim", "resnet_v1_101"):
+                "resnet_v2_200_slim", "resnet_v2_101", "resnet_v2_101_slim", "resnet_v1_101", "nasnet_large",
+                "pnasnet_large"):
         pytest.skip("deeper copies of a tested architecture (CPU time)")
     fn = get_network_fn(name, num_classes=10, is_training=False)
     size = _SMALL.get(name, getattr(fn, "default_image_size", 224))
