@@ -70,10 +70,19 @@ PRESETS: Dict[str, Preset] = {
 }
 
 
+# Any other network of the model zoo trains with the constants of the zoo's own trainer script
+# (vgg/nets/mobilenet_v1_train.py:36-54,133-146): plain SGD, LR 0.045 x0.94 every 2.5 epochs of its (sic) 1,271,167
+# images, batch 64, the per-variable L2 regularisers of the network's arg scope, no EMA, checkpoints every 100 s.
+ZOO_PRESET = Preset("zoo", 64, 1000000, 0.045, False, 0.94, 2.5, 1271167, ema_decay=None, save_secs=100.0,
+                    wipe_train_dir=False, nan_guard=True, log_style="resnet")
+
+
 def preset_for(model: str, mode: str) -> Preset:
     """Mode-specific deviations the reference hard-codes: ASP/SSP do not scale LR by N; ASP-VGG applies a
     per-worker EMA(0.9999) every step (vgg/cifar10.py:384-388); Inception ASP/SSP create but never apply the
     EMA (imagenet_inception_asp.py:120-123)."""
+    if model not in PRESETS:
+        return replace(ZOO_PRESET, model=model)
     p = PRESETS[model]
     if mode in ("asp", "ssp"):
         p = replace(p, lr_times_workers_in_bsp=False)
@@ -93,7 +102,8 @@ def _tf_bool(v) -> bool:
 def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> argparse.ArgumentParser:
     ap = argparse.ArgumentParser(description="B200-native parameter-server CNN trainer", allow_abbrev=False)
     # ---- new switches -----------------------------------------------------------------------------
-    ap.add_argument("--model", choices=MODELS, default=model)
+    ap.add_argument("--model", default=model,
+                    help="one of %s, or any network of the model-zoo registry (models/registry.py)" % (MODELS,))
     ap.add_argument("--mode", choices=MODES, default=mode or "bsp")
     ap.add_argument("--staleness", type=int, default=5, help="SSP bound (reference literal 5, _ssp.py:81)")
     ap.add_argument("--synthetic", type=_tf_bool, nargs="?", const=True, default=None,
@@ -101,6 +111,9 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
     ap.add_argument("--ref_compat", "--ref-compat", type=_tf_bool, nargs="?", const=True, default=False,
                     help="reproduce reference quirks (CifarNet double softmax Q4, ResNet batch-stat eval Q3)")
     ap.add_argument("--resume", type=_tf_bool, nargs="?", const=True, default=False)
+    ap.add_argument("--init_checkpoint", default="",
+                    help="fine-tuning: initialise the variables from this checkpoint (directory or model.ckpt-N prefix), "
+                         "ignoring missing ones, and start at global step 0 (vgg/nets/mobilenet_v1_train.py:165-181)")
     ap.add_argument("--trace", default="", help="write a Chrome-trace JSON of step phases to this path")
     ap.add_argument("--backend", default="auto", choices=("auto", "local", "thread", "gloo", "nccl", "symm"),
                     help="transport: symm = in-kernel NVLink push/pull (product path); nccl = baseline")
@@ -130,7 +143,11 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
     ap.add_argument("--num_epochs_per_decay", type=float, default=None)
     ap.add_argument("--learning_rate_decay_factor", type=float, default=None)
     # ---- reference flags: input pipeline (image_processing.py:47-71) -----------------------------------
-    ap.add_argument("--image_size", type=int, default=299)
+    ap.add_argument("--image_size", type=int, default=None,
+                    help="input resolution (default: the model's own: 299 for inception, default_image_size for zoo nets)")
+    ap.add_argument("--num_classes", type=int, default=None, help="zoo networks only (default 1001)")
+    ap.add_argument("--weight_decay", type=float, default=None,
+                    help="zoo networks only: L2 weight of the network's arg scope (default: the scope's own)")
     ap.add_argument("--num_preprocess_threads", type=int, default=4)
     ap.add_argument("--num_readers", type=int, default=4)
     ap.add_argument("--input_queue_memory_factor", type=int, default=16)
@@ -152,6 +169,10 @@ def parse_args(argv=None, model: Optional[str] = None, mode: Optional[str] = Non
     args = build_parser(model, mode).parse_args(argv)
     if args.model is None:
         raise SystemExit("--model is required")
+    if args.model not in MODELS:
+        from .models import registry
+        if not registry.is_zoo_model(args.model):
+            raise SystemExit("--model: unknown network %r" % args.model)
     p = preset_for(args.model, args.mode)
     if args.batch_size is None:
         args.batch_size = p.batch_size

@@ -23,7 +23,7 @@ import torch
 
 from .. import config as cfg
 from ..ckpt import store as ckpt
-from ..models.registry import MODEL_SPECS
+from ..models.registry import MODEL_SPECS, spec_for
 from ..ops import functional as Fn
 from ..parallel.engine import TrainSetup, Trainer
 from ..utils.logs import format_precision, log
@@ -37,6 +37,11 @@ EVAL_DEFAULTS = {
     "resnet": dict(num_examples=10000, interval=60.0, use_ema=False, batch=128),      # resnet eval :26
     "inception": dict(num_examples=200, interval=300.0, use_ema=True, batch=32),      # inception_eval.py:43,50
 }
+
+
+# any other zoo network: vgg/nets/mobilenet_v1_eval.py:31-39 (one pass over 50,000 validation images, batch 250,
+# raw variables, accuracy + recall@5)
+ZOO_EVAL_DEFAULTS = dict(num_examples=50000, interval=60.0, use_ema=False, batch=250)
 
 
 def _eval_batches(args, spec, batch_size: int):
@@ -78,22 +83,23 @@ def eval_once(trainer: Trainer, args, ckpt_path: str, use_ema: bool, num_example
             t0 = time.time()
     res = {"precision_at_1": top1 / max(total, 1), "global_step": global_step, "examples": total, "time": time.time()}
     log(format_precision(res["precision_at_1"], global_step))
-    if trainer.setup.model == "inception":
+    if trainer.setup.model == "inception" or (trainer.spec.dataset == "imagenet" and logits.shape[1] > 5):
         res["recall_at_5"] = top5 / max(total, 1)
         log("precision @ 1 = %.4f recall @ 5 = %.4f [%d examples]" % (res["precision_at_1"], res["recall_at_5"], total))
     return res
 
 
 def evaluate(args) -> Optional[dict]:
-    d = EVAL_DEFAULTS[args.model]
-    spec = MODEL_SPECS[args.model]
+    d = EVAL_DEFAULTS.get(args.model, ZOO_EVAL_DEFAULTS)
+    spec = spec_for(args.model, args.image_size, args.num_classes)
     num_examples = args.num_examples or d["num_examples"]
     interval = args.eval_interval_secs if args.eval_interval_secs is not None else d["interval"]
     batch_size = min(args.batch_size or d["batch"], d["batch"])
     checkpoint_dir = args.checkpoint_dir or args.train_dir
     device = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # train.sh runs eval on CPU
     trainer = Trainer(TrainSetup(model=args.model, batch_size=batch_size, resnet_size=args.resnet_size,
-                                 ref_compat=args.ref_compat, cuda_graph=False), device=device)
+                                 ref_compat=args.ref_compat, cuda_graph=False, image_size=args.image_size,
+                                 num_classes=args.num_classes, weight_decay=args.weight_decay), device=device)
     batches = _eval_batches(args, spec, batch_size)
     os.makedirs(args.eval_dir, exist_ok=True)
     # ResNet's reference eval builds the network in *training* mode (batch-statistics BN, Q3): only under --ref_compat

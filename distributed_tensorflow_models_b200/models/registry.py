@@ -39,6 +39,24 @@ MODEL_SPECS: Dict[str, ModelSpec] = {
 }
 
 
+def is_zoo_model(name: str) -> bool:
+    """A registry network that is not one of the six trained families (those keep their own trainer presets)."""
+    return name not in MODEL_SPECS and name in networks_map
+
+
+def spec_for(name: str, image_size: Optional[int] = None, num_classes: Optional[int] = None) -> ModelSpec:
+    """``MODEL_SPECS[name]`` for the six trained models; for any other registry network an ImageNet-shaped spec at
+    the network's ``default_image_size`` (``vgg/nets/mobilenet_v1_train.py:36-40``: 1001 classes, batch 64)."""
+    if name in MODEL_SPECS:
+        return MODEL_SPECS[name]
+    if name not in networks_map:
+        raise ValueError("Name of network unknown %s" % name)
+    size = image_size or getattr(networks_map[name], "default_image_size", default_image_sizes.get(name, 224))
+    small = size <= 32
+    return ModelSpec(name, size, size, 3, num_classes or (10 if small else 1001), 64,
+                     "cifar10" if small else "imagenet")
+
+
 @contextlib.contextmanager
 def _null_scope(weight_decay: float = 0.0):
     yield None
@@ -133,7 +151,8 @@ default_image_sizes = {"cnn": 24, "cifarnet": 32, "alexnet_v2": 224, "vgg_a": 22
                        "resnet_cifar": 32, "inception_v3": 299, "lenet": 28, "overfeat": 231}
 
 
-def get_network_fn(name: str, num_classes: int, weight_decay: float = 0.0, is_training: bool = False) -> Callable:
+def get_network_fn(name: str, num_classes: int, weight_decay: Optional[float] = 0.0,
+                   is_training: bool = False) -> Callable:
     """-> ``network_fn(images, **kwargs) -> (logits, end_points)`` with ``default_image_size``."""
     if name not in networks_map:
         raise ValueError("Name of network unknown %s" % name)
@@ -142,7 +161,7 @@ def get_network_fn(name: str, num_classes: int, weight_decay: float = 0.0, is_tr
 
     @functools.wraps(func)
     def network_fn(images, **kwargs):
-        with scope_fn(weight_decay=weight_decay):
+        with (scope_fn() if weight_decay is None else scope_fn(weight_decay=weight_decay)):
             return func(images, num_classes=num_classes, is_training=is_training, **kwargs)
 
     network_fn.default_image_size = getattr(func, "default_image_size", default_image_sizes.get(name, 224))

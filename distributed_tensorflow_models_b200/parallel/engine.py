@@ -51,6 +51,9 @@ class TrainSetup:
     cuda_graph: bool = True
     fuse_bn: bool = True              # native: BN statistics from conv epilogues, BN+ReLU applied on load
     preset: Optional[Preset] = None
+    image_size: Optional[int] = None  # zoo networks: input resolution / classes / arg-scope weight decay
+    num_classes: Optional[int] = None
+    weight_decay: Optional[float] = None
 
     def resolved(self) -> "TrainSetup":
         p = self.preset or preset_for(self.model, self.mode)
@@ -96,6 +99,25 @@ def build_forward(setup: TrainSetup) -> Callable[[torch.Tensor, torch.Tensor, bo
         def fn(x, y, tr):
             logits, aux = inception_v3.inference(x, 1001, for_training=tr)
             return inception_v3.loss((logits, aux), y.long()), logits
+    elif registry.is_zoo_model(m):
+        # any other network of the zoo, built through the factory under its own arg scope; loss as in the zoo's
+        # trainer (softmax cross-entropy on the logits, + 0.4 x the auxiliary head where the network has one,
+        # + the arg scope's L2 regularisers, which the PS update applies as wd * w)
+        spec = registry.spec_for(m, setup.image_size, setup.num_classes)
+        nets = {}
+
+        def fn(x, y, tr):
+            if tr not in nets:
+                # weight_decay=None: the L2 weight of the network's own arg scope
+                nets[tr] = registry.get_network_fn(m, spec.num_classes, weight_decay=setup.weight_decay,
+                                                   is_training=tr)
+            out, end_points = nets[tr](x)
+            logits = out[0] if isinstance(out, tuple) else out
+            loss = Fn.softmax_cross_entropy(logits, y.long())
+            aux = end_points.get("AuxLogits") if isinstance(end_points, dict) else None
+            if aux is not None and tr:
+                loss = loss + Fn.softmax_cross_entropy(aux, y.long(), weight=0.4)
+            return loss, logits
     else:
         raise ValueError(m)
     return fn
@@ -112,7 +134,7 @@ class Trainer:
         if self.device.type == "cuda" and self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
         self.p = self.setup.preset
-        spec = registry.MODEL_SPECS[self.setup.model]
+        spec = registry.spec_for(self.setup.model, self.setup.image_size, self.setup.num_classes)
         self.spec = spec
         self.store = VariableStore(seed=self.setup.seed)
         self.store.fuse_bn = bool(self.setup.fuse_bn)

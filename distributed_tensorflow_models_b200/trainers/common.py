@@ -62,7 +62,8 @@ def make_setup(args, num_workers: int) -> TrainSetup:
                       staleness=args.staleness, resnet_size=args.resnet_size, ref_compat=args.ref_compat,
                       placement=args.placement, seed=args.seed, initial_lr=args.initial_learning_rate,
                       epochs_per_decay=args.num_epochs_per_decay, decay_factor=args.learning_rate_decay_factor,
-                      cuda_graph=bool(args.cuda_graph), preset=args.preset)
+                      cuda_graph=bool(args.cuda_graph), preset=args.preset, image_size=args.image_size,
+                      num_classes=args.num_classes, weight_decay=args.weight_decay)
 
 
 def make_batches(args, spec, rank: int, world: int):
@@ -179,7 +180,7 @@ def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int) -> Optio
     if comm.rank != 0:
         return None
     gs = comm.global_step()
-    tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME[trainer.setup.model])
+    tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME.get(trainer.setup.model, "global_step"))
     return ckpt.save(train_dir, tensors, gs, max_to_keep)
 
 
@@ -208,6 +209,15 @@ def run_worker(args) -> int:
             ckpt.restore(trainer.store, tensors, strict=False)
             comm.set_global_step(ckpt.step_of(latest))
             log("restored %s" % latest)
+    if args.init_checkpoint:
+        src = args.init_checkpoint
+        if os.path.isdir(src):
+            src = ckpt.latest_checkpoint(src)
+        if not src or not os.path.exists(src + ".npz"):
+            raise SystemExit("--init_checkpoint: no checkpoint at %r" % args.init_checkpoint)
+        ckpt.restore(trainer.store, ckpt.load(src), strict=False)
+        comm.set_global_step(0)
+        log("initialised from %s (global step reset to 0)" % src)
     batches = make_batches(args, spec, rank, world)
     metrics = MetricsWriter(args.metrics_jsonl if is_chief else "")
     trace = ChromeTrace(args.trace, pid=rank)
@@ -255,7 +265,7 @@ def run_worker(args) -> int:
             log("saved %s" % path)
     elif p.save_secs is not None and is_chief:
         # dedicated-PS mode: the chief's replica is fresh after its last pull; slots live on the PS processes
-        tensors = ckpt.collect_tensors(trainer.store, None, None, comm.global_step(), GLOBAL_STEP_NAME[args.model])
+        tensors = ckpt.collect_tensors(trainer.store, None, None, comm.global_step(), GLOBAL_STEP_NAME.get(args.model, "global_step"))
         log("saved %s" % ckpt.save(args.train_dir, tensors, comm.global_step(), p.max_to_keep))
     comm.finish()
     trace.save()

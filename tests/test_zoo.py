@@ -350,3 +350,50 @@ def test_instance_norm_resize_pad_activations():
     assert torch.allclose(Fn.leaky_relu(torch.tensor([-2.0, 2.0])), torch.tensor([-0.4, 2.0]))
     d = Fn.drop_path(torch.ones(64, 2, 2, 3), 0.5, True, generator=torch.Generator().manual_seed(0))
     assert set(d.unique().tolist()) <= {0.0, 2.0} and torch.equal(Fn.drop_path(x, 0.5, False), x)
+
+
+# ---- zoo networks through the training engine and the zoo's own train / eval entry points ----------------------
+def test_engine_trains_any_registered_network():
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    t = Trainer(TrainSetup(model="mobilenet_v2", batch_size=8, image_size=32, num_classes=10, initial_lr=0.02,
+                           cuda_graph=False))
+    assert t.spec.image_size == 32 and t.spec.num_classes == 10
+    # the arg scope's L2 (4e-5) sits on the convolution weights only: depthwise filters / BN parameters are not decayed
+    assert t.layout.weight_decay == pytest.approx(4e-5) and 0 < t.layout.wd_boundary < t.layout.params.numel()
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.randn(8, 32, 32, 3, generator=g), torch.randint(0, 10, (8,), generator=g)
+    losses_ = [float(t.train_step(x, y)["loss"]) for _ in range(10)]
+    assert losses_[-1] < 0.5 * losses_[0]            # memorises the batch (dropout + tiny-batch BN make it noisy)
+    # a network with an auxiliary head: its loss joins with weight 0.4 in training, not in evaluation
+    t = Trainer(TrainSetup(model="inception_v3_slim", batch_size=2, image_size=32, num_classes=10, cuda_graph=False))
+    x, y = torch.randn(2, 32, 32, 3, generator=g), torch.randint(0, 10, (2,), generator=g)
+    eval_loss, logits = t.evaluate_batch(x, y, training_bn=True)
+    train_loss = float(t.train_step(x, y, )["loss"])
+    assert tuple(logits.shape) == (2, 10) and torch.isfinite(logits).all()
+    assert train_loss > float(eval_loss)             # same batch statistics, + 0.4 x auxiliary loss (+ dropout)
+
+
+def test_mobilenet_v1_train_eval_and_fine_tune_entry_points(tmp_path):
+    from distributed_tensorflow_models_b200.ckpt import store as ckpt
+    from distributed_tensorflow_models_b200.eval import mobilenet_v1_eval
+    from distributed_tensorflow_models_b200.trainers import mobilenet_v1_train
+    common = ["--depth_multiplier=0.25", "--image_size=64", "--batch_size=2", "--num_classes=7", "--synthetic"]
+    d1, d2 = str(tmp_path / "train"), str(tmp_path / "ft")
+    assert mobilenet_v1_train.main(common + ["--checkpoint_dir=" + d1, "--number_of_steps=2"]) == 0
+    latest = ckpt.latest_checkpoint(d1)
+    assert latest.endswith("model.ckpt-2")
+    tensors = ckpt.load(latest)
+    assert tensors["MobilenetV1/Conv2d_1_depthwise/depthwise_weights"].shape == (3, 3, 8, 1)
+    assert tensors["MobilenetV1/Logits/Conv2d_1c_1x1/weights"].shape == (1, 1, 256, 7)       # HWIO on disk
+    assert int(tensors["global_step"]) == 2
+    assert mobilenet_v1_eval.main(common + ["--checkpoint_dir=" + d1, "--num_examples=4",
+                                            "--eval_dir=" + str(tmp_path / "eval")]) == 0
+    assert (tmp_path / "eval" / "eval.jsonl").read_text().count("recall_at_5") == 1
+    # fine-tuning: variables from the first run, global step back to 0, learning rate 1e-4
+    assert mobilenet_v1_train.main(common + ["--checkpoint_dir=" + d2, "--fine_tune_checkpoint=" + d1,
+                                             "--number_of_steps=1"]) == 0
+    assert ckpt.latest_checkpoint(d2).endswith("model.ckpt-1")
+    with pytest.raises(SystemExit):
+        mobilenet_v1_train.main(common + ["--quantize=True"])
+    with pytest.raises(SystemExit):
+        mobilenet_v1_train.main(["--depth_multiplier=0.3"])
