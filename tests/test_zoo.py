@@ -367,10 +367,11 @@ def test_engine_trains_any_registered_network():
     # a network with an auxiliary head: its loss joins with weight 0.4 in training, not in evaluation
     t = Trainer(TrainSetup(model="inception_v3_slim", batch_size=2, image_size=32, num_classes=10, cuda_graph=False))
     x, y = torch.randn(2, 32, 32, 3, generator=g), torch.randint(0, 10, (2,), generator=g)
-    eval_loss, logits = t.evaluate_batch(x, y, training_bn=True)
-    train_loss = float(t.train_step(x, y, )["loss"])
-    assert tuple(logits.shape) == (2, 10) and torch.isfinite(logits).all()
-    assert train_loss > float(eval_loss)             # same batch statistics, + 0.4 x auxiliary loss (+ dropout)
+    eval_loss, logits = t.evaluate_batch(x, y)
+    assert tuple(logits.shape) == (2, 10) and torch.isfinite(logits).all() and torch.isfinite(eval_loss)
+    out = t.train_step(x, y)
+    main_only = float(Fn.softmax_cross_entropy(out["logits"], y))
+    assert float(out["loss"]) > main_only + 0.3      # + 0.4 x the auxiliary head's cross-entropy (~ln 10 at init)
 
 
 def test_mobilenet_v1_train_eval_and_fine_tune_entry_points(tmp_path):
