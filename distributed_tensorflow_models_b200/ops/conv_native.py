@@ -27,6 +27,18 @@ def _pitch(t: torch.Tensor) -> int:
     return ld
 
 
+def as_pixel_dense(t: torch.Tensor) -> torch.Tensor:
+    """``t`` itself when its pixels are laid out densely (a channel slice of a wider buffer is fine), else a packed
+    copy — spatial slices such as ``x[:, 1:, 1:, :]`` have rows that are not back to back."""
+    n, h, w, c = t.shape
+    if t.stride(3) != 1:
+        return t.contiguous()
+    ld = t.stride(2) if w > 1 else (t.stride(1) if h > 1 else (t.stride(0) if n > 1 else c))
+    if (w > 1 and h > 1 and t.stride(1) != ld * w) or (n > 1 and t.stride(0) != ld * w * h) or ld < c:
+        return t.contiguous()
+    return t
+
+
 def out_size(i: int, k: int, stride: int, pad: int) -> int:
     return (i + 2 * pad - k) // stride + 1
 

@@ -101,7 +101,7 @@ def _pad4(x: torch.Tensor, w: torch.Tensor):
 class _ConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias, stride, pad, out_hw, relu, stats):
-        x = x.contiguous() if x.stride(-1) != 1 else x
+        x = cn.as_pixel_dense(x)
         y = cn.conv_fprop(x, w, stride, pad, bias=bias, relu=relu, stats=stats, out_hw=out_hw)
         if ctx.needs_input_grad[0]:
             cn.wt_register(w)          # its dgrad operand comes from the step's batched transpose

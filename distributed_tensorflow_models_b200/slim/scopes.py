@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import contextlib
 import functools
+import inspect
 import threading
 from typing import Any, Callable, Dict, Iterable, Tuple, Union
 
@@ -70,12 +71,19 @@ def arg_scope(list_ops_or_scope: Union[Iterable[Callable], Scope], **kwargs):
 def add_arg_scope(func: Callable) -> Callable:
     """Decorator: the function picks up defaults from the enclosing ``arg_scope`` frames."""
     key = _key(func)
+    try:
+        positional = [n for n, p in inspect.signature(func).parameters.items()
+                      if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+    except (TypeError, ValueError):
+        positional = []
 
     @functools.wraps(func)
     def with_scoped_args(*args, **kwargs):
         defaults = current_arg_scope().get(key)
         if defaults:
             merged = dict(defaults)
+            for name in positional[:len(args)]:      # an argument given positionally wins over the scope's default
+                merged.pop(name, None)
             merged.update(kwargs)
             kwargs = merged
         return func(*args, **kwargs)
