@@ -155,3 +155,42 @@ class SspManager:
 
     def create_rpc_client(self, server_host: str) -> SspRpcClient:
         return SspRpcClient(server_host, self.port)
+
+
+def main(argv=None) -> int:
+    """Manual probe of a running SSP service — the role of the reference's generated command-line client
+    (``inception/ssp/CheckStaleness-remote``: ``[-h host[:port]] check_staleness <task_index> <local_step>``), or a
+    stand-alone server for experiments:
+
+        python -m distributed_tensorflow_models_b200.parallel.ssp_manager -h 10.0.0.1:8000 check_staleness 2 17
+        python -m distributed_tensorflow_models_b200.parallel.ssp_manager serve --workers 4 --max_stale 5 [--port 8000]
+    """
+    import argparse
+    import sys
+    ap = argparse.ArgumentParser(prog="ssp_manager", add_help=False, description=main.__doc__,
+                                 formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--help", action="help")
+    ap.add_argument("-h", dest="host", default="localhost:%d" % SSP_PORT, help="host[:port] of the service")
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    c = sub.add_parser("check_staleness")
+    c.add_argument("task_index", type=int)
+    c.add_argument("local_step", type=int)
+    s = sub.add_parser("serve")
+    s.add_argument("--workers", type=int, required=True)
+    s.add_argument("--max_stale", type=int, default=5)
+    s.add_argument("--port", type=int, default=SSP_PORT)
+    args = ap.parse_args(sys.argv[1:] if argv is None else argv)
+    if args.cmd == "serve":
+        SspManager(args.workers, args.max_stale, args.port).create_rpc_server("0.0.0.0").serve()
+        return 0
+    host, _, port = args.host.partition(":")
+    client = SspRpcClient("127.0.0.1" if host == "localhost" else host, int(port or SSP_PORT), connect_timeout=5.0)
+    try:
+        print(client.check_staleness(args.task_index, args.local_step))
+    finally:
+        client.close()
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

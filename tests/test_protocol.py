@@ -222,3 +222,17 @@ def test_train_sh_cnn_one_ps_two_workers_localhost(tmp_path, mode):
     for w in ("worker_0.log", "worker_1.log"):
         assert logs[w].count("examples/sec") == 4 and "loss = " in logs[w]
     assert os.path.exists(tmp_path / "train" / "checkpoint")
+
+
+def test_ssp_command_line_probe(capsys):
+    """The manual probe (role of inception/ssp/CheckStaleness-remote) talks to a live service."""
+    from distributed_tensorflow_models_b200.parallel import ssp_manager
+    mgr = ssp_manager.SspManager(2, 3, port=0)
+    server = mgr.create_rpc_server("127.0.0.1")
+    server.serve_in_background()
+    try:
+        assert ssp_manager.main(["-h", "127.0.0.1:%d" % server.port, "check_staleness", "0", "2"]) == 0
+        assert capsys.readouterr().out.strip() == "1"
+        assert mgr.state.local_step_list == [2, 0]
+    finally:
+        server.stop()
