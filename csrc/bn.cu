@@ -48,13 +48,16 @@ col_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dy, con
         sc = __ldg(reinterpret_cast<const float4*>(scale) + cc);
         sh = __ldg(reinterpret_cast<const float4*>(shift) + cc);
       }
-      for (long long r = row0 + rslot; r < row1; r += rpb) {
-        const float4 xv = __ldg(reinterpret_cast<const float4*>(x + r * ld_x) + cc);
+      // four rows per trip, all loads issued before the first use: the kernel is a pure stream over x (and dy), so
+      // what it needs is bytes in flight (one row per trip left it at ~1/6 of the HBM rate)
+      constexpr int U = 4;
+      const long long step = (long long)rpb;
+      long long r = row0 + rslot;
+      auto accumulate = [&](const float4& xv, float4 g) {
         if (MODE == 0) {
           a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
           b.x += xv.x * xv.x; b.y += xv.y * xv.y; b.z += xv.z * xv.z; b.w += xv.w * xv.w;
         } else {
-          float4 g = __ldg(reinterpret_cast<const float4*>(dy + r * ld_dy) + cc);
           if (relu) {
             if (fmaf(xv.x, sc.x, sh.x) <= 0.f) g.x = 0.f;
             if (fmaf(xv.y, sc.y, sh.y) <= 0.f) g.y = 0.f;
@@ -64,6 +67,23 @@ col_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dy, con
           a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
           b.x += g.x * xv.x; b.y += g.y * xv.y; b.z += g.z * xv.z; b.w += g.w * xv.w;
         }
+      };
+      for (; r + (U - 1) * step < row1; r += U * step) {
+        float4 xv[U], gv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          xv[u] = __ldg(reinterpret_cast<const float4*>(x + (r + u * step) * ld_x) + cc);
+          if (MODE == 1) gv[u] = __ldg(reinterpret_cast<const float4*>(dy + (r + u * step) * ld_dy) + cc);
+          else gv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) accumulate(xv[u], gv[u]);
+      }
+      for (; r < row1; r += step) {
+        const float4 xv = __ldg(reinterpret_cast<const float4*>(x + r * ld_x) + cc);
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (MODE == 1) g = __ldg(reinterpret_cast<const float4*>(dy + r * ld_dy) + cc);
+        accumulate(xv, g);
       }
     }
     float* mine = red + t * 8;
@@ -225,10 +245,10 @@ affine_act_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
 }
 
 static int reduce_grid(long long M, int* rows_per_block) {
-  // enough blocks to fill the chip twice, at least 64 rows per block
-  long long blocks = 2LL * num_sms();
+  // 6 blocks per SM (1536 of 2048 threads resident: the reductions are latency-bound streams), >= 32 rows per block
+  long long blocks = 6LL * num_sms();
   long long rpb = (M + blocks - 1) / blocks;
-  if (rpb < 64) rpb = 64;
+  if (rpb < 32) rpb = 32;
   *rows_per_block = (int)rpb;
   return (int)((M + rpb - 1) / rpb);
 }

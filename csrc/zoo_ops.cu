@@ -157,10 +157,11 @@ dwconv_wgrad_kernel(DwP p, const float* __restrict__ x, const float* __restrict_
   long long p1 = p0 + pix_per_block;
   if (p1 > npix) p1 = npix;
   for (long long pix = p0 + warp; pix < p1; pix += 8) {
-    const int ow = (int)(pix % p.OW);
-    const long long t = pix / p.OW;
-    const int oh = (int)(t % p.OH);
-    const int n = (int)(t / p.OH);
+    const unsigned pu = (unsigned)pix;                   // the launcher guarantees < 2^32 pixels
+    const int ow = (int)(pu % (unsigned)p.OW);
+    const unsigned t = pu / (unsigned)p.OW;
+    const int oh = (int)(t % (unsigned)p.OH);
+    const int n = (int)(t / (unsigned)p.OH);
     const int ih = oh * p.sh - p.ph + r;
     if ((unsigned)ih >= (unsigned)p.H) continue;
     const float g = valid ? __ldg(dy + pix * CO + oc) : 0.f;
@@ -183,6 +184,115 @@ dwconv_wgrad_kernel(DwP p, const float* __restrict__ x, const float* __restrict_
       atomicAdd(dw + (size_t)(r * p.S + s0 + s) * CO + oc, a);
     }
   }
+}
+
+// Input gradient for stride 2 (multiplier 1, C % 4 == 0): only the taps whose parity matches (ih + ph, iw + pw)
+// reach an output pixel, so a thread walks r = r0, r0 + 2, ... and s = s0, s0 + 2, ...: ceil(K/2)^2 vector loads of
+// dy instead of K^2 scalar loads with a division and a modulo each.
+template <int K>
+__global__ void __launch_bounds__(256)
+dwconv_dgrad_s2_v4_kernel(DwP p, const float4* __restrict__ dy, const float4* __restrict__ w, float4* __restrict__ dx,
+                          unsigned total) {
+  const unsigned C4 = (unsigned)p.C >> 2;
+  for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
+    const unsigned c4 = i % C4;
+    unsigned t = i / C4;
+    const int iw = (int)(t % (unsigned)p.W); t /= (unsigned)p.W;
+    const int ih = (int)(t % (unsigned)p.H);
+    const int n = (int)(t / (unsigned)p.H);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int th = ih + p.ph, tw = iw + p.pw;
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+      if ((th - r) & 1) continue;
+      const int oh = (th - r) >> 1;
+      if (th - r < 0 || oh >= p.OH) continue;
+      const float4* grow = dy + (size_t)(n * p.OH + oh) * p.OW * C4 + c4;
+#pragma unroll
+      for (int s = 0; s < K; ++s) {
+        if ((tw - s) & 1) continue;
+        const int ow = (tw - s) >> 1;
+        if (tw - s < 0 || ow >= p.OW) continue;
+        fma4(acc, __ldg(grow + (size_t)ow * C4), __ldg(w + (size_t)(r * K + s) * C4 + c4));
+      }
+    }
+    dx[i] = acc;
+  }
+}
+
+// Filter gradient, multiplier 1, square K x K filter, stride SW in both directions: a warp walks whole output rows
+// (lane = channel, so every load is one 128-byte line) and keeps all K*K accumulators in registers; per output pixel
+// it loads dy once and, per filter row, only the SW input columns that entered the window (the other K - SW are
+// shifted along in registers).  Rows are dealt to warps round-robin; partial sums meet in shared memory and leave
+// the block as one atomic per (tap, channel).
+template <int K, int SW>
+__global__ void __launch_bounds__(256)
+dwconv_wgrad_rows_kernel(DwP p, const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
+                         int rows_per_warp) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.y * 32 + lane;
+  const bool valid = c < p.C;
+  const int cc = valid ? c : 0;
+  float acc[K][K];
+#pragma unroll
+  for (int r = 0; r < K; ++r)
+#pragma unroll
+    for (int s = 0; s < K; ++s) acc[r][s] = 0.f;
+  const int nrows = p.N * p.OH;
+  const int row0 = (blockIdx.x * 8 + warp) * rows_per_warp;
+  for (int row = row0; row < row0 + rows_per_warp && row < nrows; ++row) {
+    const int n = row / p.OH, oh = row - n * p.OH;
+    const float* grow = dy + (size_t)row * p.OW * p.C + cc;
+    const float* xrow[K];
+    bool live[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+      const int ih = oh * SW - p.ph + r;
+      live[r] = (unsigned)ih < (unsigned)p.H;
+      xrow[r] = x + (size_t)(n * p.H + (live[r] ? ih : 0)) * p.W * p.C + cc;
+    }
+    float win[K][K];                       // win[r][s] = x[ih(r)][ow*SW - pw + s], carried from pixel to pixel
+#pragma unroll
+    for (int r = 0; r < K; ++r)
+#pragma unroll
+      for (int s = 0; s < K; ++s) {
+        const int iw = -p.pw + s;
+        win[r][s] = (live[r] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[r] + (size_t)iw * p.C) : 0.f;
+      }
+    // unrolled so that the loads of several pixels are in flight together (they do not depend on the arithmetic)
+#pragma unroll 4
+    for (int ow = 0; ow < p.OW; ++ow) {
+      const float g = __ldg(grow + (size_t)ow * p.C);
+#pragma unroll
+      for (int r = 0; r < K; ++r) {
+#pragma unroll
+        for (int s = 0; s < K; ++s) acc[r][s] = fmaf(g, win[r][s], acc[r][s]);
+        // slide to pixel ow + 1: keep K - SW columns, fetch SW new ones (zero beyond the row's end)
+#pragma unroll
+        for (int s = 0; s + SW < K; ++s) win[r][s] = win[r][s + SW];
+#pragma unroll
+        for (int s = K - SW; s < K; ++s) {
+          const int iw = (ow + 1) * SW - p.pw + s;
+          win[r][s] = (live[r] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[r] + (size_t)iw * p.C) : 0.f;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < K; ++r)
+#pragma unroll
+    for (int s = 0; s < K; ++s) {
+      __syncthreads();
+      red[warp][lane] = acc[r][s];
+      __syncthreads();
+      if (warp == 0 && valid) {
+        float a = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a += red[k][lane];
+        atomicAdd(dw + (size_t)(r * K + s) * p.C + c, a);
+      }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -406,7 +516,7 @@ template <int S_, int SW, int TW, bool FLIP>
 static int launch_dw_v4(const DwP& p, const float* x, const float* w, const float* bias, float* y, cudaStream_t st) {
   const unsigned long long total = (unsigned long long)p.N * p.OH * ((p.OW + TW - 1) / TW) * (p.C / 4);
   DTF_REQUIRE(total < 0xffffffffull, "depthwise conv: tensor too large for 32-bit indexing");
-  dwconv_v4_kernel<S_, SW, TW, FLIP><<<grid_for(total), 256, 0, st>>>(
+  dwconv_v4_kernel<S_, SW, TW, FLIP><<<grid_for(total, 256, 1 << 20), 256, 0, st>>>(
       p, reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(w), reinterpret_cast<const float4*>(bias),
       reinterpret_cast<float4*>(y), (unsigned)total);
   DTF_CHECK(cudaGetLastError());
@@ -473,6 +583,17 @@ extern "C" int dtf_dwconv_dgrad(const dtf_dwconv_params* p, const float* dy, con
     const int rc = dispatch_dw_v4<true>(q, dy, w, nullptr, dx, st, &done);
     if (rc || done) return rc;
   }
+  if (p->mult == 1 && p->C % 4 == 0 && p->sh == 2 && p->sw == 2 && p->R == p->S && (p->R == 3 || p->R == 5 || p->R == 7) &&
+      aligned16(dy) && aligned16(w) && aligned16(dx)) {
+    const unsigned total4 = (unsigned)((unsigned long long)p->N * p->H * p->W * (p->C / 4));
+    const float4 *g4 = reinterpret_cast<const float4*>(dy), *w4 = reinterpret_cast<const float4*>(w);
+    float4* d4 = reinterpret_cast<float4*>(dx);
+    if (p->R == 3) dwconv_dgrad_s2_v4_kernel<3><<<grid_for(total4, 256, 64), 256, 0, st>>>(*p, g4, w4, d4, total4);
+    else if (p->R == 5) dwconv_dgrad_s2_v4_kernel<5><<<grid_for(total4, 256, 64), 256, 0, st>>>(*p, g4, w4, d4, total4);
+    else dwconv_dgrad_s2_v4_kernel<7><<<grid_for(total4, 256, 64), 256, 0, st>>>(*p, g4, w4, d4, total4);
+    DTF_CHECK(cudaGetLastError());
+    return 0;
+  }
   const unsigned total = (unsigned)((unsigned long long)p->N * p->H * p->W * p->C);
   dwconv_dgrad_generic_kernel<<<grid_for(total), 256, 0, st>>>(*p, dy, w, dx, total);
   DTF_CHECK(cudaGetLastError());
@@ -483,6 +604,26 @@ extern "C" int dtf_dwconv_wgrad(const dtf_dwconv_params* p, const float* x, cons
                                 void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   if (int rc = dw_check(p)) return rc;
+  if (p->mult == 1 && p->R == p->S && p->sh == p->sw && (p->sh == 1 || p->sh == 2) &&
+      (p->R == 3 || p->R == 5 || p->R == 7)) {
+    const int nrows = p->N * p->OH, cg = ceil_div(p->C, 32);
+    DTF_REQUIRE(cg <= 65535, "depthwise wgrad: grid too large");
+    // ~4 blocks per SM; a warp takes rows_per_warp consecutive output rows
+    long long want_blocks = (4LL * num_sms() + cg - 1) / cg;
+    int rpw = (int)((nrows + want_blocks * 8 - 1) / (want_blocks * 8));
+    if (rpw < 1) rpw = 1;
+    const dim3 grid((unsigned)ceil_div(nrows, 8 * rpw), (unsigned)cg, 1);
+#define DTF_DW_WGRAD(K_, SW_) dwconv_wgrad_rows_kernel<K_, SW_><<<grid, 256, 0, st>>>(*p, x, dy, dw, rpw)
+    if (p->R == 3 && p->sh == 1) DTF_DW_WGRAD(3, 1);
+    else if (p->R == 3) DTF_DW_WGRAD(3, 2);
+    else if (p->R == 5 && p->sh == 1) DTF_DW_WGRAD(5, 1);
+    else if (p->R == 5) DTF_DW_WGRAD(5, 2);
+    else if (p->sh == 1) DTF_DW_WGRAD(7, 1);
+    else DTF_DW_WGRAD(7, 2);
+#undef DTF_DW_WGRAD
+    DTF_CHECK(cudaGetLastError());
+    return 0;
+  }
   const long long npix = (long long)p->N * p->OH * p->OW;
   const int cgroups = ceil_div(p->C * p->mult, 32);
   const bool rowwise = p->S == 3 || p->S == 5 || p->S == 7;

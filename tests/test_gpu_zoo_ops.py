@@ -57,6 +57,9 @@ def _r(*shape, seed=0, scale=1.0):
     (2, 17, 19, 64, 1, 5, 1, "SAME", False),       # odd extents: partial output tiles
     (2, 21, 21, 44, 1, 7, 2, "SAME", False),       # NASNet 7x7 separable, stride 2
     (2, 14, 14, 24, 1, 3, 1, "VALID", True),
+    (2, 23, 17, 40, 1, 5, 2, "SAME", False),       # 5x5 stride 2: parity-walking dgrad, sliding-window wgrad
+    (3, 15, 15, 36, 1, 7, 1, "SAME", True),        # 7x7 stride 1 (49 accumulators per thread in the filter gradient)
+    (2, 16, 16, 72, 1, 3, 2, "VALID", False),      # three channel groups, last one partial
     (2, 12, 12, 6, 2, 3, 1, "SAME", True),         # multiplier 2 -> generic kernels
     (2, 12, 12, 10, 1, 3, 2, "VALID", False),      # C % 4 != 0 -> generic kernels
     (2, 9, 9, 16, 1, (1, 3), 1, "SAME", False),    # single filter row
