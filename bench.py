@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--kernels", default="native", choices=("native", "torch"))
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-fuse-bn", action="store_true")
+    ap.add_argument("--no-branch-streams", action="store_true",
+                    help="run the branches of Inception blocks one after the other instead of on side streams")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -148,7 +150,8 @@ def main():
 
     spec = MODEL_SPECS[args.model]
     setup = TrainSetup(model=args.model, mode=args.mode, num_workers=world, staleness=args.staleness,
-                       cuda_graph=not args.no_graph, fuse_bn=not args.no_fuse_bn, seed=0)
+                       cuda_graph=not args.no_graph, fuse_bn=not args.no_fuse_bn, seed=0,
+                       branch_streams=not args.no_branch_streams)
     if args.batch:
         setup.batch_size = args.batch
     else:

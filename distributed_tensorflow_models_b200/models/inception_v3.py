@@ -21,6 +21,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import torch
 
 from ..ops import functional as Fn
+from ..ops import streams
 from ..slim import losses, ops, scopes
 from ..slim import variables as V
 
@@ -121,10 +122,13 @@ def inception_v3(inputs: torch.Tensor, dropout_keep_prob: float = 0.8, num_class
         with scopes.arg_scope([ops.conv2d, ops.max_pool, ops.avg_pool], stride=1, padding="SAME"):
             for name, branches in BLOCKS:
                 with store.scope(name):
-                    outs = []
-                    for bname, specs in branches:
-                        with store.scope(bname):
-                            outs.append(_run_specs(net, specs))
+                    def _branch(bname, specs, x):
+                        def run():
+                            with store.scope(bname):
+                                return _run_specs(x, specs)
+                        return run
+                    # independent branches: side streams on CUDA (ops/streams.py), plain sequence otherwise
+                    outs = streams.run_branches([_branch(b, sp, net) for b, sp in branches], net)
                     net = end_points[name] = Fn.concat_channels(outs)
                 if name == AUX_AFTER:
                     # auxiliary classifier (inception_model.py:251-263)

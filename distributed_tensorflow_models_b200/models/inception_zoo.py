@@ -23,6 +23,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
+from ..ops import streams
 from ..slim import losses, ops, scopes
 from ..slim import variables as V
 
@@ -60,14 +61,19 @@ def _run_layer(net, spec, depth: Callable[[int], int], padding: str):
 
 def _run_mixed(net, branches, depth, padding: str, scope: str):
     store = V.current_store()
-    outs = []
-    with store.scope(scope):
-        for i, branch in enumerate(branches):
+
+    def _branch(i, branch):
+        def run():
             with store.scope(f"Branch_{i}"):
                 b = net
                 for spec in branch:
                     b = _run_layer(b, spec, depth, padding)
-                outs.append(b)
+                return b
+        return run
+
+    with store.scope(scope):
+        # independent branches: side streams on CUDA (ops/streams.py), plain sequence otherwise
+        outs = streams.run_branches([_branch(i, br) for i, br in enumerate(branches)], net)
     return torch.cat(outs, dim=3)
 
 

@@ -208,11 +208,19 @@ class WeightTransposeBatch:
             return weight_transpose(w)
         if self.dirty:
             self._rebuild()
+        cur = torch.cuda.current_stream()
         if not self.fresh:
             nat.check(nat.lib().dtf_weight_transpose_batched(C.c_void_p(self.table.data_ptr()), len(self.order),
                                                              self.total_blocks, nat.stream_ptr()),
                       "dtf_weight_transpose_batched")
             self.fresh = True
+            # branches of a block run their backward on different streams (ops/streams.py): whoever comes second
+            # must order itself after the launch above
+            self.done = torch.cuda.Event()
+            self.done.record(cur)
+            self.done_stream = cur
+        elif getattr(self, "done", None) is not None and cur != self.done_stream:
+            cur.wait_event(self.done)
         return self.views[key]
 
 

@@ -51,6 +51,7 @@ class TrainSetup:
     cuda_graph: bool = True
     fuse_bn: bool = True              # native: BN statistics from conv epilogues, BN+ReLU applied on load
     preset: Optional[Preset] = None
+    branch_streams: bool = True       # CUDA: independent branches of Inception-style blocks on side streams
     image_size: Optional[int] = None  # zoo networks: input resolution / classes / arg-scope weight decay
     num_classes: Optional[int] = None
     weight_decay: Optional[float] = None
@@ -166,6 +167,8 @@ class Trainer:
 
     # ---- helpers ---------------------------------------------------------------------------------
     def _run_forward(self, x, y, training, build=False):
+        from ..ops import streams
+        streams.set_branch_streams(self.setup.branch_streams and self.device.type == "cuda" and not build)
         with self.store.as_default():
             self.store.begin_forward()
             if self.prefix:
