@@ -96,7 +96,8 @@ def _run_specs(x: torch.Tensor, specs: Sequence[tuple]) -> torch.Tensor:
         elif kind == "max":
             x = ops.max_pool(x, list(sp[1]), stride=sp[2], padding=sp[3])
         elif kind == "fork":
-            x = Fn.concat_channels([_run_specs(x, sp[1]), _run_specs(x, sp[2])])
+            x = Fn.concat_channels(streams.run_branches([lambda a=sp[1], v=x: _run_specs(v, a),
+                                                         lambda b=sp[2], v=x: _run_specs(v, b)], x))
         else:
             raise ValueError(kind)
     return x
@@ -131,14 +132,16 @@ def inception_v3(inputs: torch.Tensor, dropout_keep_prob: float = 0.8, num_class
                     outs = streams.run_branches([_branch(b, sp, net) for b, sp in branches], net)
                     net = end_points[name] = Fn.concat_channels(outs)
                 if name == AUX_AFTER:
-                    # auxiliary classifier (inception_model.py:251-263)
-                    with store.scope("aux_logits"):
-                        aux = ops.avg_pool(net, [5, 5], stride=3, padding="VALID")
-                        aux = ops.conv2d(aux, 128, [1, 1], scope="proj")
-                        aux = ops.conv2d(aux, 768, [aux.shape[1], aux.shape[2]], stddev=0.01, padding="VALID")
-                        aux = ops.flatten(aux)
-                        aux = ops.fc(aux, num_classes, activation=None, stddev=0.001, restore=restore_logits)
-                        end_points["aux_logits"] = aux
+                    # auxiliary classifier (inception_model.py:251-263); its handful of small kernels run beside the
+                    # remaining blocks of the trunk (joined before the function returns)
+                    def _aux(x=net):
+                        with store.scope("aux_logits"):
+                            aux = ops.avg_pool(x, [5, 5], stride=3, padding="VALID")
+                            aux = ops.conv2d(aux, 128, [1, 1], scope="proj")
+                            aux = ops.conv2d(aux, 768, [aux.shape[1], aux.shape[2]], stddev=0.01, padding="VALID")
+                            aux = ops.flatten(aux)
+                            return ops.fc(aux, num_classes, activation=None, stddev=0.001, restore=restore_logits)
+                    aux_head = streams.Detached(_aux, net)
             with store.scope("logits"):
                 net = ops.avg_pool(net, [net.shape[1], net.shape[2]], padding="VALID", scope="pool")
                 net = ops.dropout(net, dropout_keep_prob, scope="dropout")
@@ -146,6 +149,7 @@ def inception_v3(inputs: torch.Tensor, dropout_keep_prob: float = 0.8, num_class
                 logits = ops.fc(net, num_classes, activation=None, scope="logits", restore=restore_logits)
                 end_points["logits"] = logits
                 end_points["predictions"] = torch.softmax(logits.detach(), dim=-1)
+            end_points["aux_logits"] = aux_head.join()
     store.end_points = end_points
     return logits, end_points
 

@@ -17,8 +17,8 @@ from typing import Callable, Dict, List, Sequence
 
 import torch
 
-_STATE = {"enabled": False}
-_POOLS: Dict[int, List["torch.cuda.Stream"]] = {}
+_STATE = {"enabled": False, "depth": 0}
+_POOLS: Dict[tuple, List["torch.cuda.Stream"]] = {}
 
 
 def set_branch_streams(enabled: bool) -> None:
@@ -30,8 +30,10 @@ def branch_streams_enabled() -> bool:
 
 
 def _pool(device: torch.device, n: int) -> List["torch.cuda.Stream"]:
+    """Side streams of the current nesting depth (a fork inside a branch gets its own set, so that it never waits
+    on a sibling of its parent)."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    pool = _POOLS.setdefault(idx, [])
+    pool = _POOLS.setdefault((idx, _STATE["depth"]), [])
     while len(pool) < n:
         pool.append(torch.cuda.Stream(device=idx))
     return pool[:n]
@@ -49,17 +51,59 @@ def run_branches(thunks: Sequence[Callable[[], torch.Tensor]], like: torch.Tenso
     fork.record(main)
     outs: List[torch.Tensor] = [None] * len(thunks)          # type: ignore[list-item]
     joins = []
-    for i in range(1, len(thunks)):
-        s = side[i - 1]
-        s.wait_event(fork)
-        with torch.cuda.stream(s):
-            o = thunks[i]()
-            done = torch.cuda.Event()
-            done.record(s)
-        o.record_stream(main)            # produced on a side stream, consumed (concatenated) on the main one
-        outs[i] = o
-        joins.append(done)
-    outs[0] = thunks[0]()
+    _STATE["depth"] += 1
+    try:
+        # thunks run in their natural order on the host (default variable-scope names are numbered by call order);
+        # the side streams wait on the fork event only, so they do not queue behind thunk 0's kernels
+        outs[0] = thunks[0]()
+        for i in range(1, len(thunks)):
+            s = side[i - 1]
+            s.wait_event(fork)
+            with torch.cuda.stream(s):
+                o = thunks[i]()
+                done = torch.cuda.Event()
+                done.record(s)
+            o.record_stream(main)        # produced on a side stream, consumed (concatenated) on the main one
+            outs[i] = o
+            joins.append(done)
+    finally:
+        _STATE["depth"] -= 1
     for d in joins:
         main.wait_event(d)
     return outs
+
+
+class Detached:
+    """A computation issued on a side stream whose result is needed only later (Inception's auxiliary head runs
+    beside the last blocks of the trunk): ``d = Detached(thunk, like)`` ... ``value = d.join()``."""
+
+    def __init__(self, thunk: Callable[[], torch.Tensor], like: torch.Tensor):
+        self.done = None
+        if not (_STATE["enabled"] and like.is_cuda):
+            self.value = thunk()
+            return
+        self.main = torch.cuda.current_stream(like.device)
+        idx = like.device.index if like.device.index is not None else torch.cuda.current_device()
+        pool = _POOLS.setdefault((idx, "detached"), [])
+        if not pool:
+            pool.append(torch.cuda.Stream(device=idx))
+        s = pool[0]
+        fork = torch.cuda.Event()
+        fork.record(self.main)
+        s.wait_event(fork)
+        _STATE["depth"] += 100           # forks inside the detached computation use their own stream sets
+        try:
+            with torch.cuda.stream(s):
+                self.value = thunk()
+                self.done = torch.cuda.Event()
+                self.done.record(s)
+        finally:
+            _STATE["depth"] -= 100
+
+    def join(self) -> torch.Tensor:
+        if self.done is not None:
+            self.main = torch.cuda.current_stream(self.value.device)
+            self.main.wait_event(self.done)
+            self.value.record_stream(self.main)
+            self.done = None
+        return self.value

@@ -33,6 +33,7 @@ from ..ops import functional as Fn
 from ..parallel.comm import Comm, LocalComm
 from ..parallel.engine import Trainer, TrainSetup
 from ..utils.logs import ChromeTrace, MetricsWriter, format_step, log
+from ..utils.pipeline import DevicePrefetcher, ScalarReadback
 
 GLOBAL_STEP_NAME = {"cnn": "Variable", "cifarnet": "partitioned_space/Variable",
                     "alexnet": "partitioned_space/Variable", "vgg": "root/Variable", "resnet": "Variable",
@@ -218,7 +219,8 @@ def run_worker(args) -> int:
         ckpt.restore(trainer.store, ckpt.load(src), strict=False)
         comm.set_global_step(0)
         log("initialised from %s (global step reset to 0)" % src)
-    batches = make_batches(args, spec, rank, world)
+    batches = DevicePrefetcher(make_batches(args, spec, rank, world), device)
+    losses_rb = ScalarReadback(device)
     metrics = MetricsWriter(args.metrics_jsonl if is_chief else "")
     trace = ChromeTrace(args.trace, pid=rank)
     last_save = time.time()
@@ -227,22 +229,26 @@ def run_worker(args) -> int:
         t0 = time.time()
         images, labels = next(batches)
         t1 = time.time()
-        out = trainer.train_step(images.to(device, non_blocking=True), labels.to(device, non_blocking=True),
-                                 batch_size=args.batch_size)
+        out = trainer.train_step(images, labels, batch_size=args.batch_size)      # already on the device (prefetcher)
         want_log = (step % max(1, args.log_every) == 0) or step == args.max_steps - 1
         if want_log or p.nan_guard:
-            loss_value = float(out["loss"])             # D2H read (also the NaN guard, inception…bsp.py:191)
-            if p.nan_guard:
-                assert not math.isnan(loss_value), "Model diverged with loss = NaN"
+            # the loss is read back one step late (after the next step has been queued) so that the device never
+            # drains; it is still every logged step's own loss, and the NaN guard (inception…bsp.py:191) sees all
+            losses_rb.push(out["loss"], tag=(step, out["global_step"], out["lr"], out["ssp_wait_s"], t0, want_log))
         t2 = time.time()
         trace.add("input", t0 - t_run0, t1 - t0, step=step)
         trace.add("train_step", t1 - t_run0, t2 - t1, step=step)
-        if want_log:
-            duration = max(t2 - t0, 1e-9)
-            log(format_step(p.log_style, step, out["global_step"], loss_value, args.batch_size / duration, duration))
-            metrics.write(step=step, global_step=out["global_step"], loss=loss_value, lr=out["lr"],
-                          examples_per_sec=args.batch_size / duration, sec_per_batch=duration,
-                          ssp_wait_s=out["ssp_wait_s"], time=t2)
+        while len(losses_rb) > (0 if step == args.max_steps - 1 else 1):
+            loss_value, (lstep, lgs, llr, lwait, lt0, llog) = losses_rb.pop()
+            if p.nan_guard:
+                assert not math.isnan(loss_value), "Model diverged with loss = NaN"
+            if llog:
+                t3 = time.time()
+                duration = max((t3 - lt0) / max(1, step - lstep + 1), 1e-9)
+                log(format_step(p.log_style, lstep, lgs, loss_value, args.batch_size / duration, duration))
+                metrics.write(step=lstep, global_step=lgs, loss=loss_value, lr=llr,
+                              examples_per_sec=args.batch_size / duration, sec_per_batch=duration,
+                              ssp_wait_s=lwait, time=t3)
         if p.accuracy_every and step % p.accuracy_every == 0:
             acc = float((out["logits"].argmax(1) == labels.to(device)).float().mean())
             log("step %d, train-batch accuracy = %.4f" % (step, acc))
