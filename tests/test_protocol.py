@@ -236,3 +236,38 @@ def test_ssp_command_line_probe(capsys):
         assert mgr.state.local_step_list == [2, 0]
     finally:
         server.stop()
+
+
+def test_device_prefetcher_and_scalar_readback_cpu_path():
+    """The host pipelining helpers degrade to plain iteration / immediate reads without a GPU."""
+    from distributed_tensorflow_models_b200.utils.pipeline import DevicePrefetcher, ScalarReadback
+    batches = [(torch.full((2, 3), float(i)), torch.tensor([i, i])) for i in range(5)]
+    got = list(DevicePrefetcher(iter(batches), torch.device("cpu")))
+    assert len(got) == 5 and all(float(x[0, 0]) == i and int(y[0]) == i for i, (x, y) in enumerate(got))
+    lazy = DevicePrefetcher(iter(batches), torch.device("cpu"), lazy=True)
+    assert not lazy.started and float(next(lazy)[0][0, 0]) == 0.0 and lazy.started
+    rb = ScalarReadback(torch.device("cpu"), depth=2)
+    rb.push(torch.tensor(1.5), tag="a")
+    rb.push(torch.tensor(2.5), tag="b")
+    with pytest.raises(RuntimeError):
+        rb.push(torch.tensor(3.5))
+    assert rb.pop() == (1.5, "a") and len(rb) == 1 and rb.pop() == (2.5, "b")
+
+
+def test_branch_streams_fall_back_to_call_order_on_cpu():
+    from distributed_tensorflow_models_b200.ops import streams
+    order = []
+
+    def thunk(i):
+        def run():
+            order.append(i)
+            return torch.full((1,), float(i))
+        return run
+
+    streams.set_branch_streams(True)
+    try:
+        outs = streams.run_branches([thunk(0), thunk(1), thunk(2)], torch.zeros(1))
+        aux = streams.Detached(thunk(7), torch.zeros(1))
+        assert [float(o) for o in outs] == [0.0, 1.0, 2.0] and order == [0, 1, 2, 7] and float(aux.join()) == 7.0
+    finally:
+        streams.set_branch_streams(False)
