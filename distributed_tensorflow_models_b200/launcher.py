@@ -9,7 +9,8 @@ Same contract as the reference: hosts come from the ``ps`` / ``workers`` environ
 per worker, ``--job_name/--task_id/--ps_hosts/--worker_hosts`` on the command line (train.sh:49,56); PS
 processes run with ``CUDA_VISIBLE_DEVICES=`` (train.sh:33); stdout+stderr of each process go to
 ``ps_<i>.log`` / ``worker_<j>.log`` and the evaluator started next to worker 0 after 20 s goes to
-``model_eval.log`` (train.sh:57-59).  All 18 model x mode pairs are accepted (the reference ships 9).
+``model_eval.log`` (train.sh:57-59).  All 18 model x mode pairs are accepted (the reference ships 9), and so is any
+network name of the model-zoo registry (``bash train.sh mobilenet_v1 bsp``), which runs the generic trainer.
 
 Differences, on purpose: processes on ``localhost`` are spawned directly instead of through ssh; workers on
 the same host get distinct ports and, on a GPU box, one GPU each (``LOCAL_RANK``) with a shared
@@ -76,11 +77,14 @@ def launch(model: str, mode: str, ps: List[str], workers: List[str], log_dir: st
     os.makedirs(log_dir, exist_ok=True)
     ps_hosts, worker_hosts = host_lists(ps, workers)
     common = [f"--ps_hosts={','.join(ps_hosts)}", f"--worker_hosts={','.join(worker_hosts)}"] + extra
-    mod = f"{PKG}.trainers.{TRAINER[model]}_{mode}"
+    if model in TRAINER:
+        mod_args = [f"{PKG}.trainers.{TRAINER[model]}_{mode}"]
+    else:       # any other network of the model zoo: the generic trainer, selected by registry name
+        mod_args = [f"{PKG}.trainers.train", f"--model={model}", f"--mode={mode}"]
     procs: List[subprocess.Popen] = []
     master_port = str(cfg.WORKER_PORT + 1000)
     for i, h in enumerate(ps):
-        cmd = [python, "-m", mod, "--job_name=ps", f"--task_id={i}"] + common
+        cmd = [python, "-m"] + mod_args + ["--job_name=ps", f"--task_id={i}"] + common
         procs.append(_spawn(h, cmd, {"CUDA_VISIBLE_DEVICES": ""}, os.path.join(log_dir, f"ps_{i}.log")))
     local_slot = 0
     for j, h in enumerate(workers):
@@ -89,7 +93,7 @@ def launch(model: str, mode: str, ps: List[str], workers: List[str], log_dir: st
         if _is_local(h):
             env["LOCAL_RANK"] = str(local_slot)
             local_slot += 1
-        cmd = [python, "-m", mod, "--job_name=worker", f"--task_id={j}"] + common
+        cmd = [python, "-m"] + mod_args + ["--job_name=worker", f"--task_id={j}"] + common
         procs.append(_spawn(h, cmd, env, os.path.join(log_dir, f"worker_{j}.log")))
         if j == 0 and with_eval and model in EVALUATOR:
             ecmd = [python, "-m", f"{PKG}.eval.{EVALUATOR[model]}"] + [a for a in extra if a.startswith(
@@ -143,7 +147,11 @@ def main(argv=None) -> int:
         print("usage: export ps='h1 ...' workers='h2 h3 ...'; bash train.sh <model> <bsp|asp|ssp>   "
               f"(models: {' '.join(cfg.MODELS)})")
         return 1
-    if args.model not in cfg.MODELS or args.mode not in cfg.MODES:
+    known = args.model in cfg.MODELS
+    if not known:
+        from .models import registry
+        known = registry.is_zoo_model(args.model)
+    if not known or args.mode not in cfg.MODES:
         print(f"unknown model/mode {args.model}/{args.mode}")
         return 1
     if not workers:

@@ -201,3 +201,17 @@ def test_launcher_host_lists_usage_and_all_pairs():
             assert hasattr(importlib.import_module(f"distributed_tensorflow_models_b200.trainers.{base}_{mode}"), "main")
     for mod in launcher.EVALUATOR.values():
         importlib.import_module(f"distributed_tensorflow_models_b200.eval.{mod}")
+
+
+def test_launcher_accepts_zoo_networks(tmp_path, monkeypatch):
+    """`train.sh <registry name> <mode>` runs the generic trainer for networks outside the six trained families."""
+    from distributed_tensorflow_models_b200 import launcher
+    spawned = []
+    monkeypatch.setattr(launcher, "_spawn", lambda host, cmd, env, log, delay=0.0: spawned.append(cmd) or
+                        type("P", (), {"pid": 0})())
+    monkeypatch.setenv("workers", "localhost localhost")
+    monkeypatch.setenv("ps", "")
+    assert launcher.main(["mobilenet_v2", "asp", "--log_dir", str(tmp_path), "--no_eval", "--synthetic"]) == 0
+    assert len(spawned) == 2
+    assert spawned[0][2].endswith(".trainers.train") and "--model=mobilenet_v2" in spawned[0] and "--mode=asp" in spawned[0]
+    assert launcher.main(["no_such_net", "bsp", "--log_dir", str(tmp_path)]) == 1
