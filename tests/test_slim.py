@@ -225,3 +225,37 @@ def test_inception_loss_weights():
     total = inception_v3.loss((logits, aux), labels)
     from distributed_tensorflow_models_b200.ops.functional import softmax_cross_entropy as xe
     assert float(total) == pytest.approx(float(xe(logits, labels, 0.1, 1.0) + xe(aux, labels, 0.1, 0.4)), rel=1e-6)
+
+
+def test_contrib_conv_honours_batch_norm_scope_bias_switch_and_separable_variables():
+    """slim.conv2d(normalizer_fn=slim.batch_norm) picks `is_training` / decay / scale up from an enclosing
+    arg_scope([batch_norm], ...) — the way every zoo network switches between training and inference."""
+    import torch
+    from distributed_tensorflow_models_b200.slim import VariableStore, ops, scopes
+    x = torch.randn(4, 6, 6, 3)
+    st = VariableStore()
+    with st.as_default(), scopes.arg_scope([ops.batch_norm], is_training=False, scale=True, decay=0.5):
+        y = ops.convolution2d(x, 5, [3, 3], normalizer_fn=ops.batch_norm, scope="c")
+    names = [v.name for v in st.all()]
+    assert names == ["c/weights", "c/BatchNorm/beta", "c/BatchNorm/gamma", "c/BatchNorm/moving_mean",
+                     "c/BatchNorm/moving_variance"]
+    # inference mode: moving statistics (mean 0, variance 1) were used and left untouched
+    assert float(st.get("c/BatchNorm/moving_mean").tensor.abs().max()) == 0.0
+    ref = torch.relu(torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), st.get("c/weights").tensor.permute(0, 3, 1, 2),
+                                                padding=1) / (1 + 1e-3) ** 0.5).permute(0, 2, 3, 1)
+    assert torch.allclose(y, ref, atol=1e-5)
+    with st.as_default(), scopes.arg_scope([ops.batch_norm], is_training=True, scale=True, decay=0.5):
+        st.begin_forward()
+        ops.convolution2d(x, 5, [3, 3], normalizer_fn=ops.batch_norm, scope="c")
+    assert float(st.get("c/BatchNorm/moving_mean").tensor.abs().max()) > 0.0          # training mode updates them
+    st2 = VariableStore()
+    with st2.as_default():
+        ops.convolution2d(x, 5, [1, 1], use_bias=False, scope="bare")
+        ops.convolution2d(x, 5, [1, 1], scope="biased")
+        ops.separable_convolution2d(x, None, [3, 3], depth_multiplier=2, normalizer_fn=ops.batch_norm, scope="dw")
+        up = ops.convolution2d_transpose(x, 4, [4, 4], stride=2, scope="up")
+        inorm = ops.instance_norm(x, scope="in")
+    assert [v.name for v in st2.all()][:3] == ["bare/weights", "biased/weights", "biased/biases"]
+    assert tuple(st2.get("dw/depthwise_weights").tensor.shape) == (3, 3, 3, 2) and not st2.has("dw/pointwise_weights")
+    assert tuple(up.shape) == (4, 12, 12, 4) and tuple(st2.get("up/weights").to_tf().shape) == (4, 4, 4, 3)
+    assert {"in/beta", "in/gamma"} <= {v.name for v in st2.all()} and tuple(inorm.shape) == tuple(x.shape)
