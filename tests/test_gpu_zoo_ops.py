@@ -130,3 +130,92 @@ def test_conv2d_transpose(cfg):
         _both(lambda x_, w_, b_: Fn.conv2d_transpose(x_, w_, b_, s, pad), [x, w, _r(co, seed=12)], TF32_TOL)
     else:
         _both(lambda x_, w_: Fn.conv2d_transpose(x_, w_, None, s, pad), [x, w], TF32_TOL)
+
+
+# ---- guard-band checks: the pool has no compute-sanitizer, so out-of-bounds accesses are hunted with canaries ----------
+def _guarded(shape, fill, gen=None, guard=4096):
+    """A tensor of ``shape`` carved out of the middle of a larger buffer whose margins hold NaN: an out-of-bounds
+    read of a neighbour poisons the result, an out-of-bounds write destroys a canary."""
+    n = 1
+    for s in shape:
+        n *= s
+    n_al = (n + 3) // 4 * 4
+    buf = torch.full((guard + n_al + guard,), float("nan"), device="cuda")
+    view = buf[guard:guard + n].view(shape)
+    if fill == "randn":
+        view.copy_(torch.randn(shape, generator=gen))
+    elif fill == "zeros":
+        view.zero_()
+    return buf, view, (guard, n)
+
+
+def _canaries_intact(buf, where):
+    guard, n = where
+    return bool(torch.isnan(buf[:guard]).all()) and bool(torch.isnan(buf[guard + (n + 3) // 4 * 4:]).all())
+
+
+@pytest.mark.parametrize("cfg", [(2, 9, 7, 8, 3, 1), (2, 9, 7, 8, 3, 2), (2, 11, 13, 12, 5, 1), (2, 11, 13, 12, 5, 2),
+                                 (1, 9, 9, 36, 7, 1), (1, 10, 9, 36, 7, 2), (3, 8, 8, 4, 3, 1)])
+def test_depthwise_kernels_stay_in_bounds(cfg):
+    import ctypes as C
+
+    from distributed_tensorflow_models_b200.ops import zoo_native as zn
+    n, h, w, c, k, s = cfg
+    g = torch.Generator().manual_seed(3)
+    oh, ow, ph, pw = Fn.resolve_padding(h, w, k, k, (s, s), "SAME")
+    p = zn.DwConvParams(n, h, w, c, 1, k, k, s, s, ph[0], pw[0], oh, ow)
+    bx, x, wx = _guarded((n, h, w, c), "randn", g)
+    bw, wt, ww = _guarded((k, k, c, 1), "randn", g)
+    bdy, dy, wdy = _guarded((n, oh, ow, c), "randn", g)
+    by, y, wy = _guarded((n, oh, ow, c), None)
+    bdx, dx, wdx = _guarded((n, h, w, c), None)
+    bdw, dw, wdw = _guarded((k, k, c, 1), "zeros")
+    vp = lambda t: C.c_void_p(t.data_ptr())
+    lib = nat.lib()
+    nat.check(lib.dtf_dwconv_fwd(C.byref(p), vp(x), vp(wt), None, vp(y), nat.stream_ptr()), "fwd")
+    nat.check(lib.dtf_dwconv_dgrad(C.byref(p), vp(dy), vp(wt), vp(dx), nat.stream_ptr()), "dgrad")
+    nat.check(lib.dtf_dwconv_wgrad(C.byref(p), vp(x), vp(dy), vp(dw), nat.stream_ptr()), "wgrad")
+    torch.cuda.synchronize()
+    for buf, where in ((by, wy), (bdx, wdx), (bdw, wdw), (bx, wx), (bw, ww), (bdy, wdy)):
+        assert _canaries_intact(buf, where), "a kernel wrote outside its tensor"
+    finite = torch.isfinite(y).all() and torch.isfinite(dx).all() and torch.isfinite(dw).all()
+    assert finite, "a kernel read outside its tensor (NaN margin leaked into the result)"
+    Fn.set_backend("torch")
+    try:
+        xr, wr = x.clone().requires_grad_(True), wt.clone().requires_grad_(True)
+        yr = Fn.depthwise_conv2d(xr, wr, None, s, "SAME")
+        yr.backward(dy.clone())
+    finally:
+        Fn.set_backend("auto")
+    assert _rel(y, yr.detach()) < FP32_TOL and _rel(dx, xr.grad) < FP32_TOL and _rel(dw, wr.grad) < FP32_TOL
+
+
+def test_pointwise_zoo_kernels_stay_in_bounds():
+    import ctypes as C
+    g = torch.Generator().manual_seed(4)
+    lib = nat.lib()
+    vp = lambda t: C.c_void_p(t.data_ptr())
+    n, h, w, c = 2, 7, 5, 12
+    bx, x, wx = _guarded((n, h, w, c), "randn", g)
+    # activation (odd element count: scalar tail), instance norm, resize up / down, reflect pad
+    b1, x1, w1 = _guarded((3, 5, 7, 13), "randn", g)
+    by1, y1, wy1 = _guarded((3, 5, 7, 13), None)
+    nat.check(lib.dtf_act_fwd(vp(x1), vp(y1), C.c_longlong(x1.numel()), 2, C.c_float(0.0), nat.stream_ptr()), "act")
+    bs, sums, ws = _guarded((n, 2, c), None)
+    by2, y2, wy2 = _guarded((n, h, w, c), None)
+    nat.check(lib.dtf_instnorm_fwd(vp(x), None, None, vp(y2), vp(sums), n, h * w, c, C.c_float(1e-3), nat.stream_ptr()),
+              "instnorm")
+    by3, y3, wy3 = _guarded((n, 10, 13, c), None)
+    nat.check(lib.dtf_resize_fwd(vp(x), vp(y3), n, h, w, c, 10, 13, 1, 0, nat.stream_ptr()), "resize")
+    bdx, dx, wdx = _guarded((n, h, w, c), None)
+    nat.check(lib.dtf_resize_bwd(vp(y3), vp(dx), n, h, w, c, 10, 13, 1, 0, nat.stream_ptr()), "resize bwd")
+    by4, y4, wy4 = _guarded((n, h + 5, w + 3, c), None)
+    nat.check(lib.dtf_pad_fwd(vp(x), vp(y4), n, h, w, c, 3, 2, 1, 2, 1, nat.stream_ptr()), "pad")
+    bdx2, dx2, wdx2 = _guarded((n, h, w, c), None)
+    nat.check(lib.dtf_pad_bwd(vp(y4), vp(dx2), n, h, w, c, 3, 2, 1, 2, 1, nat.stream_ptr()), "pad bwd")
+    torch.cuda.synchronize()
+    for buf, where in ((by1, wy1), (bs, ws), (by2, wy2), (by3, wy3), (bdx, wdx), (by4, wy4), (bdx2, wdx2), (bx, wx),
+                       (b1, w1)):
+        assert _canaries_intact(buf, where), "a kernel wrote outside its tensor"
+    for t in (y1, sums, y2, y3, dx, y4, dx2):
+        assert torch.isfinite(t).all(), "a kernel read outside its tensor"
