@@ -203,3 +203,38 @@ extern "C" const char* dtf_last_error(void) {
   copy = dtf::g_last_error_global;
   return copy.c_str();
 }
+
+// CRC-32C (Castagnoli), slice-by-8, host only: checkpoint bundles and TFRecord framing checksum every block /
+// record / tensor with it, and the interpreted byte loop manages ~10 MB/s.  crc = dtf_crc32c(data, n, 0) for a
+// fresh checksum; pass a previous result as `crc` to continue over the next chunk.
+namespace {
+struct Crc32cTables {
+  uint32_t t[8][256];
+  Crc32cTables() {
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; ++k) c = (c & 1) ? (c >> 1) ^ 0x82F63B78u : c >> 1;
+      t[0][i] = c;
+    }
+    for (uint32_t i = 0; i < 256; ++i)
+      for (int s = 1; s < 8; ++s) t[s][i] = (t[s - 1][i] >> 8) ^ t[0][t[s - 1][i] & 0xff];
+  }
+};
+}  // namespace
+
+extern "C" uint32_t dtf_crc32c(const void* data, unsigned long long n, uint32_t crc) {
+  static const Crc32cTables T;
+  const unsigned char* p = static_cast<const unsigned char*>(data);
+  uint32_t c = ~crc;
+  while (n && (reinterpret_cast<uintptr_t>(p) & 7)) { c = T.t[0][(c ^ *p++) & 0xff] ^ (c >> 8); --n; }
+  while (n >= 8) {
+    uint64_t w;
+    memcpy(&w, p, 8);
+    w ^= c;                       // little-endian hosts only (x86-64 / aarch64 as deployed)
+    c = T.t[7][w & 0xff] ^ T.t[6][(w >> 8) & 0xff] ^ T.t[5][(w >> 16) & 0xff] ^ T.t[4][(w >> 24) & 0xff] ^
+        T.t[3][(w >> 32) & 0xff] ^ T.t[2][(w >> 40) & 0xff] ^ T.t[1][(w >> 48) & 0xff] ^ T.t[0][(w >> 56) & 0xff];
+    p += 8; n -= 8;
+  }
+  while (n--) c = T.t[0][(c ^ *p++) & 0xff] ^ (c >> 8);
+  return ~c;
+}

@@ -11,9 +11,9 @@ What ``tf.train.Saver`` + ``Supervisor`` do for the reference:
   ``<var>/ExponentialMovingAverage``, and the global step under the trainer's name for it;
 * keep-N policy (``max_to_keep``: 5 by default, 1 for ResNet — resnet/cifar10_resnet_bsp.py:107).
 
-The container is a NumPy ``.npz`` (one array per name).  Writing real TF V2 bundles (``.index`` SSTable +
-``.data``) is out of scope; a TF-side loader only needs ``np.load`` + ``assign`` because names and layouts
-already match.
+Two containers: a NumPy ``.npz`` (one array per name; the default) and TensorFlow's own V2 bundle
+(``model.ckpt-N.index`` + ``model.ckpt-N.data-00000-of-00001``, ``ckpt/tf_bundle.py``; ``--ckpt_format tf``).
+``load`` / ``exists`` / the keep-N policy recognise both, so a run can resume from, evaluate or fine-tune on either.
 """
 from __future__ import annotations
 
@@ -27,6 +27,7 @@ import numpy as np
 import torch
 
 from ..slim.variables import Variable, VariableStore
+from . import tf_bundle
 
 STATE_FILE = "checkpoint"
 PREFIX = "model.ckpt"
@@ -85,6 +86,19 @@ def _file(path: str) -> str:
     return path if path.endswith(".npz") else path + ".npz"
 
 
+def exists(path: str) -> bool:
+    """A checkpoint with this prefix exists in either container."""
+    return bool(path) and (os.path.exists(_file(path)) or tf_bundle.is_bundle(path))
+
+
+def _remove(path: str) -> None:
+    for f in [_file(path)] + tf_bundle.bundle_files(path):
+        try:
+            os.remove(f)
+        except OSError:
+            pass
+
+
 def collect_tensors(store: VariableStore, slot_flats: Optional[Dict[str, torch.Tensor]] = None,
                     layout=None, global_step: int = 0, global_step_name: str = "global_step") -> Dict[str, np.ndarray]:
     """name -> array in TF layout.  ``slot_flats``: full-length flat tensors per slot
@@ -105,26 +119,31 @@ def collect_tensors(store: VariableStore, slot_flats: Optional[Dict[str, torch.T
     return out
 
 
-def save(train_dir: str, tensors: Dict[str, np.ndarray], global_step: int, max_to_keep: int = 5) -> str:
+def save(train_dir: str, tensors: Dict[str, np.ndarray], global_step: int, max_to_keep: int = 5,
+         fmt: str = "npz") -> str:
+    """``fmt``: 'npz' or 'tf' (TensorFlow V2 bundle: ``.index`` + ``.data-00000-of-00001``)."""
     os.makedirs(train_dir, exist_ok=True)
     name = f"{PREFIX}-{int(global_step)}"
-    tmp = os.path.join(train_dir, name + ".tmp.npz")
-    np.savez(tmp, **{k.replace("/", "|"): v for k, v in tensors.items()})
-    os.replace(tmp, os.path.join(train_dir, name + ".npz"))
+    if fmt == "tf":
+        tf_bundle.write_bundle(os.path.join(train_dir, name), tensors)
+    elif fmt == "npz":
+        tmp = os.path.join(train_dir, name + ".tmp.npz")
+        np.savez(tmp, **{k.replace("/", "|"): v for k, v in tensors.items()})
+        os.replace(tmp, os.path.join(train_dir, name + ".npz"))
+    else:
+        raise ValueError("checkpoint format must be 'npz' or 'tf', not %r" % fmt)
     st = get_checkpoint_state(train_dir)
     paths = [os.path.basename(p) for p in (st.all_model_checkpoint_paths if st else [])]
-    paths = [p for p in paths if p != name and os.path.exists(_file(os.path.join(train_dir, p)))] + [name]
+    paths = [p for p in paths if p != name and exists(os.path.join(train_dir, p))] + [name]
     while max_to_keep and len(paths) > max_to_keep:
-        old = paths.pop(0)
-        try:
-            os.remove(_file(os.path.join(train_dir, old)))
-        except OSError:
-            pass
+        _remove(os.path.join(train_dir, paths.pop(0)))
     _write_state(train_dir, paths)
     return os.path.join(train_dir, name)
 
 
 def load(path: str) -> Dict[str, np.ndarray]:
+    if not os.path.exists(_file(path)) and tf_bundle.is_bundle(path):
+        return tf_bundle.read_bundle(path)
     with np.load(_file(path)) as z:
         return {k.replace("|", "/"): z[k] for k in z.files}
 
@@ -163,7 +182,7 @@ def wait_for_checkpoint(checkpoint_dir: str, poll_secs: float = 1.0, timeout: Op
     t0 = time.time()
     while True:
         p = latest_checkpoint(checkpoint_dir)
-        if p and os.path.exists(_file(p)):
+        if p and exists(p):
             return p
         if timeout is not None and time.time() - t0 > timeout:
             return None

@@ -111,6 +111,8 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
     ap.add_argument("--ref_compat", "--ref-compat", type=_tf_bool, nargs="?", const=True, default=False,
                     help="reproduce reference quirks (CifarNet double softmax Q4, ResNet batch-stat eval Q3)")
     ap.add_argument("--resume", type=_tf_bool, nargs="?", const=True, default=False)
+    ap.add_argument("--ckpt_format", default="npz", choices=("npz", "tf"),
+                    help="checkpoint container: NumPy .npz, or TensorFlow's V2 bundle (.index + .data-00000-of-00001)")
     ap.add_argument("--init_checkpoint", default="",
                     help="fine-tuning: initialise the variables from this checkpoint (directory or model.ckpt-N prefix), "
                          "ignoring missing ones, and start at global step 0 (vgg/nets/mobilenet_v1_train.py:165-181)")

@@ -24,11 +24,46 @@ for _i in range(256):
     _TABLE.append(_c)
 
 
-def crc32c(data: bytes) -> int:
-    c = 0xFFFFFFFF
+_NATIVE = [None]
+
+
+def _native_crc():
+    """``dtf_crc32c`` of the native library (host code, slice-by-8) when the library is there; False otherwise."""
+    if _NATIVE[0] is None:
+        try:
+            import ctypes as C
+
+            from .. import _native as nat
+            if not nat.available():
+                raise OSError("native library not built")
+            fn = nat.lib().dtf_crc32c
+            fn.restype = C.c_uint32
+            fn.argtypes = [C.c_char_p, C.c_ulonglong, C.c_uint32]
+            _NATIVE[0] = fn
+        except Exception:
+            _NATIVE[0] = False
+    return _NATIVE[0]
+
+
+def crc32c(data, crc: int = 0) -> int:
+    """CRC-32C of ``data`` (bytes-like), continuing from ``crc``."""
+    data = bytes(data) if not isinstance(data, bytes) else data
+    fn = _native_crc() if len(data) >= 64 else False
+    if fn:
+        return int(fn(data, len(data), crc))
+    c = crc ^ 0xFFFFFFFF
     for b in data:
         c = _TABLE[(c ^ b) & 0xFF] ^ (c >> 8)
     return c ^ 0xFFFFFFFF
+
+
+def mask_crc(c: int) -> int:
+    return (((c >> 15) | (c << 17)) + 0xA282EAD8) & 0xFFFFFFFF
+
+
+def unmask_crc(m: int) -> int:
+    r = (m - 0xA282EAD8) & 0xFFFFFFFF
+    return ((r >> 17) | (r << 15)) & 0xFFFFFFFF
 
 
 def masked_crc(data: bytes) -> int:

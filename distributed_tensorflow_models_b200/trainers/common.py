@@ -174,7 +174,7 @@ def make_comm(args, backend: str, num_workers: int):
     return TorchDistComm("rs_ag"), dev, rank, world
 
 
-def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int) -> Optional[str]:
+def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int, fmt: str = "npz") -> Optional[str]:
     """Chief-side save (all ranks must call: gathering the sharded slots is collective)."""
     comm = trainer.comm
     slots = comm.gather_slot_flats()
@@ -182,7 +182,7 @@ def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int) -> Optio
         return None
     gs = comm.global_step()
     tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME.get(trainer.setup.model, "global_step"))
-    return ckpt.save(train_dir, tensors, gs, max_to_keep)
+    return ckpt.save(train_dir, tensors, gs, max_to_keep, fmt=fmt)
 
 
 def run_worker(args) -> int:
@@ -205,7 +205,7 @@ def run_worker(args) -> int:
     # ---- resume ----
     if (args.resume or not p.wipe_train_dir) and p.save_secs is not None:
         latest = ckpt.latest_checkpoint(args.train_dir)
-        if latest and os.path.exists(latest + ".npz"):
+        if latest and ckpt.exists(latest):
             tensors = ckpt.load(latest)
             ckpt.restore(trainer.store, tensors, strict=False)
             comm.set_global_step(ckpt.step_of(latest))
@@ -214,7 +214,7 @@ def run_worker(args) -> int:
         src = args.init_checkpoint
         if os.path.isdir(src):
             src = ckpt.latest_checkpoint(src)
-        if not src or not os.path.exists(src + ".npz"):
+        if not src or not ckpt.exists(src):
             raise SystemExit("--init_checkpoint: no checkpoint at %r" % args.init_checkpoint)
         ckpt.restore(trainer.store, ckpt.load(src), strict=False)
         comm.set_global_step(0)
@@ -260,19 +260,19 @@ def run_worker(args) -> int:
                 comm.broadcast_state([flag], src=0)
                 due = bool(flag.item() > 0)
             if due:
-                path = save_checkpoint(trainer, args.train_dir, p.max_to_keep)
+                path = save_checkpoint(trainer, args.train_dir, p.max_to_keep, args.ckpt_format)
                 last_save = time.time()
                 if path:
                     log("saved %s" % path)
     # final checkpoint + shutdown
     if p.save_secs is not None and backend != "gloo":
-        path = save_checkpoint(trainer, args.train_dir, p.max_to_keep)
+        path = save_checkpoint(trainer, args.train_dir, p.max_to_keep, args.ckpt_format)
         if path:
             log("saved %s" % path)
     elif p.save_secs is not None and is_chief:
         # dedicated-PS mode: the chief's replica is fresh after its last pull; slots live on the PS processes
         tensors = ckpt.collect_tensors(trainer.store, None, None, comm.global_step(), GLOBAL_STEP_NAME.get(args.model, "global_step"))
-        log("saved %s" % ckpt.save(args.train_dir, tensors, comm.global_step(), p.max_to_keep))
+        log("saved %s" % ckpt.save(args.train_dir, tensors, comm.global_step(), p.max_to_keep, fmt=args.ckpt_format))
     comm.finish()
     trace.save()
     metrics.close()

@@ -28,6 +28,10 @@ const char* dtf_last_error(void);
 /* Debug aid: 0 launches the convolution kernels in plain stream order; 1 (default) with programmatic dependent
  * launch, so that a kernel's prologue overlaps the tail of its predecessor. */
 int dtf_debug_set_pdl(int enabled);
+/* Host-only CRC-32C (Castagnoli) used by the checkpoint-bundle and TFRecord writers: crc of `n` bytes, continuing
+ * from `crc` (0 for a fresh checksum).  No GPU involved; no counterpart in the reference (TensorFlow's C++ runtime
+ * provides it there). */
+uint32_t dtf_crc32c(const void* data, unsigned long long n, uint32_t crc);
 
 /* ------------------------------------------------------------------------------------ */
 /* K1  implicit-GEMM convolution on tcgen05 (kind::tf32, fp32 accumulate in TMEM)         */

@@ -215,3 +215,119 @@ def test_launcher_accepts_zoo_networks(tmp_path, monkeypatch):
     assert len(spawned) == 2
     assert spawned[0][2].endswith(".trainers.train") and "--model=mobilenet_v2" in spawned[0] and "--mode=asp" in spawned[0]
     assert launcher.main(["no_such_net", "bsp", "--log_dir", str(tmp_path)]) == 1
+
+
+# ---- TensorFlow V2 checkpoint bundles (ckpt/tf_bundle.py) -------------------------------------------------------
+def test_tf_bundle_round_trip_multi_block_and_listing(tmp_path):
+    import numpy as np
+    from distributed_tensorflow_models_b200.ckpt import tf_bundle as tb
+    rng = np.random.default_rng(0)
+    tensors = {f"scope_{i // 7}/layer_{i}/weights": rng.standard_normal((3, 3, 4, 5)).astype(np.float32)
+               for i in range(60)}
+    tensors.update({"global_step": np.asarray(1234, dtype=np.int64), "empty": np.zeros((0, 3), np.float32),
+                    "conv1/biases": rng.standard_normal(7).astype(np.float32), "flags": np.array([True, False]),
+                    "scope_0/layer_0/weights/RMSProp": np.ones((2, 2), np.float64),
+                    "ids": np.arange(5, dtype=np.int32)})
+    prefix = str(tmp_path / "model.ckpt-1234")
+    tb.write_bundle(prefix, tensors, block_size=512)          # tiny blocks: many data blocks + a real index block
+    assert sorted(os.listdir(tmp_path)) == ["model.ckpt-1234.data-00000-of-00001", "model.ckpt-1234.index"]
+    back = tb.read_bundle(prefix)
+    assert set(back) == set(tensors)
+    for k, v in tensors.items():
+        assert back[k].dtype == v.dtype and back[k].shape == v.shape and np.array_equal(back[k], v), k
+    listing = tb.list_bundle(prefix)
+    assert listing["global_step"] == (np.dtype("int64"), ()) and listing["empty"] == (np.dtype("float32"), (0, 3))
+    assert tb.read_bundle(prefix, names=["ids"]).keys() == {"ids"}
+    with pytest.raises(KeyError):
+        tb.read_bundle(prefix, names=["nope"])
+    # the table really is sorted, prefix-compressed and split into several blocks
+    raw = open(prefix + ".index", "rb").read()
+    keys = [k for k, _ in tb.read_table(raw)]
+    assert keys[0] == b"" and keys == sorted(keys) and len(keys) == len(tensors) + 1
+    assert raw.count(b"scope_0/layer_0/weights") <= 2        # later keys store only their unshared suffix
+
+
+def test_tf_bundle_byte_layout_matches_the_published_format(tmp_path):
+    """A one-tensor bundle, checked byte by byte against the table / bundle format written out by hand."""
+    import struct
+    import numpy as np
+    from distributed_tensorflow_models_b200.ckpt import tf_bundle as tb
+    from distributed_tensorflow_models_b200.data.tfrecord import crc32c, mask_crc
+    prefix = str(tmp_path / "m")
+    value = np.array([1.0, 2.0], dtype=np.float32)
+    tb.write_bundle(prefix, {"w": value})
+    data = open(prefix + ".data-00000-of-00001", "rb").read()
+    assert data == struct.pack("<2f", 1.0, 2.0)
+    header = bytes([0x08, 0x01, 0x1A, 0x02, 0x08, 0x01])                  # num_shards=1, version{producer=1}
+    entry = (bytes([0x08, 0x01,                                           # dtype = DT_FLOAT
+                    0x12, 0x04, 0x12, 0x02, 0x08, 0x02,                   # shape { dim { size: 2 } }
+                    0x28, 0x08,                                           # size = 8   (offset 0, shard 0 omitted)
+                    0x35]) + struct.pack("<I", mask_crc(crc32c(data))))   # crc32c (fixed32, masked)
+    block = (bytes([0, 0, len(header)]) + header +                        # shared, unshared, value_len, key "", value
+             bytes([0, 1, len(entry)]) + b"w" + entry +
+             struct.pack("<II", 0, 1))                                    # restart[0] = 0, num_restarts = 1
+    trailer = lambda b: b"\x00" + struct.pack("<I", mask_crc(crc32c(b + b"\x00")))
+    meta = struct.pack("<II", 0, 1)
+    meta_off = len(block) + 5
+    index_block = (bytes([0, 1, 2]) + b"w" + bytes([0, len(block)]) + struct.pack("<II", 0, 1))
+    index_off = meta_off + len(meta) + 5
+    footer = bytes([meta_off, len(meta), index_off, len(index_block)])
+    footer += b"\x00" * (40 - len(footer)) + struct.pack("<Q", 0xDB4775248B80FB57)
+    expected = block + trailer(block) + meta + trailer(meta) + index_block + trailer(index_block) + footer
+    assert open(prefix + ".index", "rb").read() == expected
+    assert crc32c(b"123456789") == 0xE3069283                              # the CRC-32C check value
+
+
+def test_tf_bundle_detects_corruption_and_unsupported_input(tmp_path):
+    import numpy as np
+    from distributed_tensorflow_models_b200.ckpt import tf_bundle as tb
+    prefix = str(tmp_path / "c")
+    tb.write_bundle(prefix, {"a/b": np.arange(100, dtype=np.float32), "z": np.ones(3, np.int64)})
+    raw = bytearray(open(prefix + ".data-00000-of-00001", "rb").read())
+    raw[17] ^= 0x40
+    open(prefix + ".data-00000-of-00001", "wb").write(bytes(raw))
+    with pytest.raises(ValueError, match="checksum"):
+        tb.read_bundle(prefix)
+    assert tb.read_bundle(prefix, verify=False)["z"].tolist() == [1, 1, 1]
+    idx = bytearray(open(prefix + ".index", "rb").read())
+    idx[3] ^= 0x01
+    open(prefix + ".index", "wb").write(bytes(idx))
+    with pytest.raises(ValueError, match="checksum"):
+        tb.read_bundle(prefix)
+    open(prefix + ".index", "wb").write(b"not a table at all, but long enough to have a footer ..........")
+    with pytest.raises(ValueError, match="magic"):
+        tb.read_bundle(prefix)
+    with pytest.raises(TypeError):
+        tb.write_bundle(str(tmp_path / "d"), {"c": np.zeros(2, np.complex64)})
+    with pytest.raises(ValueError):
+        w = tb.TableWriter(open(tmp_path / "t", "wb"))
+        w.add(b"b", b"1")
+        w.add(b"a", b"2")
+
+
+def test_trainer_saves_resumes_and_evaluates_tf_bundles(tmp_path):
+    """--ckpt_format tf: the chief writes model.ckpt-N.{index,data-*} + the `checkpoint` state file; eval, resume and
+    the keep-N policy work on them exactly as on the .npz container."""
+    from distributed_tensorflow_models_b200.ckpt import store as ckpt
+    from distributed_tensorflow_models_b200.ckpt import tf_bundle as tb
+    from distributed_tensorflow_models_b200.eval import cifar10_eval
+    from distributed_tensorflow_models_b200.trainers import cifar10_cnn_bsp
+    d = str(tmp_path / "train")
+    base = ["--synthetic", "--batch_size=4", "--train_dir=" + d, "--ckpt_format=tf", "--backend=local"]
+    assert cifar10_cnn_bsp.main(base + ["--max_steps=2"]) == 0
+    latest = ckpt.latest_checkpoint(d)
+    assert latest.endswith("model.ckpt-2") and tb.is_bundle(latest) and not os.path.exists(latest + ".npz")
+    listing = tb.list_bundle(latest)
+    assert listing["conv1/weights"][1] == (5, 5, 3, 64) and listing["local3/weights"][1] == (2304, 384)   # HWIO / [in,out]
+    assert "conv1/weights/ExponentialMovingAverage" in listing and listing["Variable"][1] == ()
+    assert cifar10_eval.main(["--checkpoint_dir=" + d, "--run_once", "--synthetic", "--num_examples=8",
+                              "--batch_size=4", "--eval_dir=" + str(tmp_path / "eval")]) == 0
+    assert cifar10_cnn_bsp.main(base + ["--max_steps=1", "--resume"]) == 0
+    assert ckpt.latest_checkpoint(d).endswith("model.ckpt-3")
+    tensors = ckpt.load(ckpt.latest_checkpoint(d))
+    assert int(tensors["Variable"]) == 3
+    for step in range(4, 11):                                  # keep-N: old bundles (both files) are deleted
+        ckpt.save(d, {"x": tensors["Variable"]}, step, max_to_keep=5, fmt="tf")
+    kept = sorted(f for f in os.listdir(d) if f.endswith(".index"))
+    assert len(kept) == 5 and "model.ckpt-2.index" not in kept
+    assert len([f for f in os.listdir(d) if ".data-" in f]) == 5
