@@ -331,3 +331,23 @@ def test_trainer_saves_resumes_and_evaluates_tf_bundles(tmp_path):
     kept = sorted(f for f in os.listdir(d) if f.endswith(".index"))
     assert len(kept) == 5 and "model.ckpt-2.index" not in kept
     assert len([f for f in os.listdir(d) if ".data-" in f]) == 5
+
+
+def test_checkpoint_inspect_and_convert_cli(tmp_path, capsys):
+    import numpy as np
+    from distributed_tensorflow_models_b200.ckpt import inspect as ck_inspect
+    from distributed_tensorflow_models_b200.ckpt import store as ckpt
+    from distributed_tensorflow_models_b200.ckpt import tf_bundle as tb
+    d = str(tmp_path)
+    ckpt.save(d, {"a/weights": np.arange(6, dtype=np.float32).reshape(2, 3), "global_step": np.asarray(7)}, 7)
+    assert ck_inspect.main([d]) == 0
+    out = capsys.readouterr().out
+    assert "model.ckpt-7" in out and "a/weights" in out and "(2, 3)" in out and "2 tensors, 7 values" in out
+    assert ck_inspect.main([os.path.join(d, "model.ckpt-7.npz"), "--tensor", "a/weights"]) == 0
+    assert "float32 (2, 3)" in capsys.readouterr().out
+    out_prefix = str(tmp_path / "conv" / "model.ckpt-7")
+    assert ck_inspect.main([d, "--convert", "tf", "--out", out_prefix]) == 0
+    assert np.array_equal(tb.read_bundle(out_prefix)["a/weights"], np.arange(6, dtype=np.float32).reshape(2, 3))
+    assert ck_inspect.main([out_prefix + ".index"]) == 0 and "tf bundle" in capsys.readouterr().out
+    with pytest.raises(SystemExit):
+        ck_inspect.main([str(tmp_path / "missing")])
