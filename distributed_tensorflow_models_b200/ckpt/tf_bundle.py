@@ -14,8 +14,14 @@ tooling without TensorFlow being installed here:
   whose value is a ``BundleEntryProto`` (dtype, shape, shard, offset, size, masked CRC-32C of the tensor bytes).
 
 The protocol-buffer messages involved are tiny and are encoded / decoded by hand (varints and length-delimited
-fields), like the ``Example`` protos of ``data/tfrecord.py``.  Partitioned-variable *slice* entries are not produced
-(the framework saves every variable under its full logical name, whole) and are rejected on read.
+fields), like the ``Example`` protos of ``data/tfrecord.py``.
+
+Partitioned variables (the reference's ``fixed_size_partitioner`` trainers: CifarNet, AlexNet, VGG) are stored by
+TensorFlow as one entry under the full name that lists its ``slices`` (start / length per dimension) and carries no
+data, plus one data entry per slice under an *ordered-code* key (a 0 byte, the escaped name, the slice extents in an
+order-preserving integer encoding).  ``read_bundle`` reassembles them into the whole tensor — which is how this
+framework keeps every variable — and ``write_bundle(..., partitions=...)`` can emit them (used by the tests, and for
+handing a checkpoint back to a partitioned TensorFlow graph).
 
 Verified here by round trips, by structural checks of the emitted bytes and by corruption tests
 (``tests/test_ckpt_data_cli.py``); there is no TensorFlow on this box to cross-read the files with.
@@ -212,6 +218,77 @@ def _encode_entry(dtype: int, shape: Tuple[int, ...], shard_id: int, offset: int
     return out + _tag(6, 5) + struct.pack("<I", crc)
 
 
+def _encode_slice_proto(extents: List[Tuple[int, Optional[int]]]) -> bytes:
+    """TensorSliceProto: one Extent {start, length} per dimension; a full dimension has neither set."""
+    out = b""
+    for start, length in extents:
+        ext = b""
+        if length is not None:
+            if start:
+                ext += _tag(1, 0) + _varint(start)
+            ext += _tag(2, 0) + _varint(length)
+        out += _tag(1, 2) + _varint(len(ext)) + ext
+    return out
+
+
+# ---- ordered code (tensorflow/core/lib/strings/ordered_code): the keys of slice data entries -----------------------
+def _oc_num_increasing(v: int) -> bytes:
+    body = v.to_bytes((v.bit_length() + 7) // 8, "big") if v else b""
+    return bytes([len(body)]) + body
+
+
+def _oc_string(s: bytes) -> bytes:
+    esc = b"".join(b"\x00\xff" if c == 0 else (b"\xff\x00" if c == 0xFF else bytes([c])) for c in s)
+    return esc + b"\x00\x01"
+
+
+def _oc_signed_increasing(v: int) -> bytes:
+    """Order-preserving signed encoding: 1 byte holds 6 payload bits, every further byte 7 more; the leading bits
+    count the length in unary, inverted for negative numbers."""
+    x = ~v if v < 0 else v
+    n = 1
+    while x >= (1 << (7 * n - 1)):
+        n += 1
+    raw = (v & ((1 << 80) - 1)).to_bytes(10, "big")[10 - n:] if n <= 10 else None
+    buf = bytearray(raw)
+    header = [(0, 0), (0x80, 0), (0xC0, 0), (0xE0, 0), (0xF0, 0), (0xF8, 0), (0xFC, 0), (0xFE, 0), (0xFF, 0),
+              (0xFF, 0x80), (0xFF, 0xC0)][n]
+    buf[0] ^= header[0]
+    if n > 1:
+        buf[1] ^= header[1]
+    return bytes(buf)
+
+
+def encode_slice_key(name: str, extents: List[Tuple[int, Optional[int]]]) -> bytes:
+    """``checkpoint::EncodeTensorNameSlice``: 0, the name, the rank, then (start, length) per dimension with (-1, -1)
+    standing for "all of it"."""
+    key = _oc_num_increasing(0) + _oc_string(name.encode("utf-8")) + _oc_num_increasing(len(extents))
+    for start, length in extents:
+        if length is None:
+            key += _oc_signed_increasing(-1) + _oc_signed_increasing(-1)
+        else:
+            key += _oc_signed_increasing(start) + _oc_signed_increasing(length)
+    return key
+
+
+def decode_slice_key_name(key: bytes) -> Optional[str]:
+    """The tensor name inside a slice key (None for an ordinary key)."""
+    if not key.startswith(b"\x00") or len(key) < 3:
+        return None
+    out, i = bytearray(), 1
+    while i + 1 < len(key):
+        c, d = key[i], key[i + 1]
+        if c == 0 and d == 1:
+            return out.decode("utf-8")
+        if (c == 0 and d == 0xFF) or (c == 0xFF and d == 0):
+            out.append(c)
+            i += 2
+        else:
+            out.append(c)
+            i += 1
+    return None
+
+
 def _fields(buf: bytes) -> Iterator[Tuple[int, int, object]]:
     pos = 0
     while pos < len(buf):
@@ -235,7 +312,7 @@ def _fields(buf: bytes) -> Iterator[Tuple[int, int, object]]:
 
 
 def _decode_entry(buf: bytes) -> dict:
-    e = {"dtype": 0, "shape": (), "shard_id": 0, "offset": 0, "size": 0, "crc32c": None, "slices": 0}
+    e = {"dtype": 0, "shape": (), "shard_id": 0, "offset": 0, "size": 0, "crc32c": None, "slices": []}
     for field, _, val in _fields(buf):
         if field == 1:
             e["dtype"] = val
@@ -260,7 +337,17 @@ def _decode_entry(buf: bytes) -> dict:
         elif field == 6:
             e["crc32c"] = val
         elif field == 7:
-            e["slices"] += 1
+            extents = []
+            for f2, _, v2 in _fields(val):
+                if f2 == 1:
+                    start, length = 0, None
+                    for f3, _, v3 in _fields(v2):
+                        if f3 == 1:
+                            start = v3
+                        elif f3 == 2:
+                            length = v3
+                    extents.append((start, length))
+            e["slices"].append(extents)
     return e
 
 
@@ -296,12 +383,23 @@ def bundle_files(prefix: str) -> List[str]:
     return out
 
 
-def write_bundle(prefix: str, tensors: Dict[str, np.ndarray], block_size: int = BLOCK_SIZE) -> None:
-    """Write ``tensors`` (name -> array) as one-shard bundle ``prefix``; files appear atomically (index last)."""
+def write_bundle(prefix: str, tensors: Dict[str, np.ndarray], block_size: int = BLOCK_SIZE,
+                 partitions: Optional[Dict[str, List[int]]] = None) -> None:
+    """Write ``tensors`` (name -> array) as one-shard bundle ``prefix``; files appear atomically (index last).
+    ``partitions``: name -> slice lengths along axis 0 for variables to be stored the way TensorFlow stores a
+    partitioned variable (a slice-listing entry + one data entry per slice)."""
     entries = []
     tmp_data = data_path(prefix) + ".tmp"
     offset = 0
+    partitions = partitions or {}
     with open(tmp_data, "wb") as f:
+        def put(key: bytes, a: np.ndarray) -> None:
+            nonlocal offset
+            raw = a.tobytes()
+            f.write(raw)
+            entries.append((key, _encode_entry(DT[a.dtype], a.shape, 0, offset, len(raw), mask_crc(crc32c(raw)))))
+            offset += len(raw)
+
         for name in sorted(tensors, key=lambda s: s.encode("utf-8")):
             if not name:
                 raise ValueError("the empty name is reserved for the bundle header")
@@ -312,11 +410,27 @@ def write_bundle(prefix: str, tensors: Dict[str, np.ndarray], block_size: int = 
                 raise TypeError("dtype %s of %r has no TensorFlow checkpoint encoding here" % (a.dtype, name))
             if a.dtype.byteorder == ">":
                 a = a.astype(a.dtype.newbyteorder("<"))
-            raw = a.tobytes()
-            f.write(raw)
-            entries.append((name.encode("utf-8"), _encode_entry(DT[a.dtype], a.shape, 0, offset, len(raw),
-                                                                mask_crc(crc32c(raw)))))
-            offset += len(raw)
+            parts = partitions.get(name)
+            if not parts or len(parts) < 2:
+                put(name.encode("utf-8"), a)
+                continue
+            if a.ndim == 0 or sum(parts) != a.shape[0]:
+                raise ValueError("partition lengths %s do not add up to dim 0 of %r %s" % (parts, name, a.shape))
+            listing = _tag(1, 0) + _varint(DT[a.dtype])
+            dims = b""
+            for d in a.shape:
+                dim = _tag(1, 0) + _varint(int(d))
+                dims += _tag(2, 2) + _varint(len(dim)) + dim
+            listing += _tag(2, 2) + _varint(len(dims)) + dims
+            start = 0
+            for n in parts:
+                extents = [(start, n)] + [(0, None)] * (a.ndim - 1)
+                sp = _encode_slice_proto(extents)
+                listing += _tag(7, 2) + _varint(len(sp)) + sp
+                put(encode_slice_key(name, extents), np.ascontiguousarray(a[start:start + n]))
+                start += n
+            entries.append((name.encode("utf-8"), listing))
+        entries.sort(key=lambda kv: kv[0])
     tmp_index = index_path(prefix) + ".tmp"
     with open(tmp_index, "wb") as f:
         w = TableWriter(f, block_size)
@@ -333,7 +447,7 @@ def list_bundle(prefix: str) -> Dict[str, Tuple[np.dtype, Tuple[int, ...]]]:
     out = {}
     with open(index_path(prefix), "rb") as f:
         for key, value in read_table(f.read()):
-            if key == HEADER_KEY:
+            if key == HEADER_KEY or decode_slice_key_name(key) is not None:
                 continue
             e = _decode_entry(value)
             out[key.decode("utf-8")] = (DT_INV.get(e["dtype"]), e["shape"])
@@ -352,13 +466,7 @@ def read_bundle(prefix: str, names: Optional[List[str]] = None, verify: bool = T
     shards: Dict[int, np.memmap] = {}
     out: Dict[str, np.ndarray] = {}
     want = set(names) if names is not None else None
-    for key, value in table[1:]:
-        name = key.decode("utf-8")
-        if want is not None and name not in want:
-            continue
-        e = _decode_entry(value)
-        if e["slices"]:
-            raise NotImplementedError("partitioned-variable slice entries (%r) are not supported" % name)
+    def fetch(name: str, e: dict) -> np.ndarray:
         if e["dtype"] not in DT_INV:
             raise TypeError("tensor %r has TensorFlow dtype %d, which is not supported" % (name, e["dtype"]))
         if e["shard_id"] not in shards:
@@ -373,7 +481,44 @@ def read_bundle(prefix: str, names: Optional[List[str]] = None, verify: bool = T
                                                                                   count * dtype.itemsize))
         if verify and e["crc32c"] is not None and unmask_crc(e["crc32c"]) != crc32c(raw):
             raise ValueError("tensor %r: checksum mismatch (corrupt data file)" % name)
-        out[name] = np.frombuffer(raw, dtype=dtype).reshape(e["shape"]).copy()
+        return np.frombuffer(raw, dtype=dtype).reshape(e["shape"]).copy()
+
+    # slice data entries (ordered-code keys sort before every ordinary name), grouped by tensor name in key order
+    slice_data: Dict[str, List[dict]] = {}
+    for key, value in table[1:]:
+        sname = decode_slice_key_name(key)
+        if sname is not None:
+            slice_data.setdefault(sname, []).append(_decode_entry(value))
+    for key, value in table[1:]:
+        if decode_slice_key_name(key) is not None:
+            continue
+        name = key.decode("utf-8")
+        if want is not None and name not in want:
+            continue
+        e = _decode_entry(value)
+        if not e["slices"]:
+            out[name] = fetch(name, e)
+            continue
+        # partitioned variable: paste the slices into the full tensor.  Slice keys encode (start, length) per
+        # dimension with an order-preserving code, so key order == ascending start order of the listed extents.
+        parts = slice_data.get(name, [])
+        specs = sorted(e["slices"], key=lambda ext: [(-1 if ln is None else st) for st, ln in ext])
+        if len(parts) != len(specs):
+            raise ValueError("tensor %r lists %d slices but %d slice entries are stored" % (name, len(specs), len(parts)))
+        full = np.zeros(e["shape"], dtype=DT_INV[e["dtype"]])
+        filled = np.zeros(e["shape"], dtype=bool) if full.size else None
+        for ext, pe in zip(specs, parts):
+            idx = tuple(slice(None) if ln is None else slice(st, st + ln) for st, ln in ext)
+            piece = fetch(name, pe)
+            if full[idx].shape != piece.shape:
+                raise ValueError("tensor %r: slice %s has shape %s, stored piece %s" % (name, ext, full[idx].shape,
+                                                                                         piece.shape))
+            full[idx] = piece
+            if filled is not None:
+                filled[idx] = True
+        if filled is not None and not filled.all():
+            raise ValueError("tensor %r: the stored slices do not cover the whole variable" % name)
+        out[name] = full
     if want is not None and want - set(out):
         raise KeyError("not in the checkpoint: %s" % sorted(want - set(out)))
     return out
