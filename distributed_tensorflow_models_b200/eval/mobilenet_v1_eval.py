@@ -13,11 +13,7 @@ from .evaluator import main as _main
 
 def main(argv=None):
     argv = sys.argv[1:] if argv is None else list(argv)
-    rest, net, _ = translate(argv)
-    # the common flag for the checkpoint location is --checkpoint_dir in eval mode; translate() mapped it to --train_dir
-    rest = [("--checkpoint_dir" if a == "--train_dir" else a) for a in rest]
-    rest = [a for i, a in enumerate(rest) if a not in ("--task_id", "--log_every") and
-            (i == 0 or rest[i - 1] not in ("--task_id", "--log_every"))]
+    rest, net, _ = translate(argv, for_eval=True)
     if "--run_once" not in rest:
         rest.append("--run_once")
     return _main(rest, model=net)

@@ -19,8 +19,8 @@ from .common import main as _main
 _NETS = {1.0: "mobilenet_v1", 0.75: "mobilenet_v1_075", 0.5: "mobilenet_v1_050", 0.25: "mobilenet_v1_025"}
 
 
-def translate(argv):
-    """-> (argv for the common trainer, fine_tune_checkpoint)"""
+def translate(argv, for_eval: bool = False):
+    """-> (argv for the common trainer / evaluator, registry network name, fine_tune_checkpoint)"""
     ap = argparse.ArgumentParser(add_help=False, allow_abbrev=False)
     ap.add_argument("--master", default="")
     ap.add_argument("--task", type=int, default=0)
@@ -37,11 +37,13 @@ def translate(argv):
         raise SystemExit("--quantize: quantisation-aware training is not part of this framework (fp32 / tf32 only)")
     if own.depth_multiplier not in _NETS:
         raise SystemExit("--depth_multiplier must be one of %s" % sorted(_NETS))
-    out = list(rest) + ["--task_id", str(own.task), "--log_every", str(own.log_every_n_steps)]
-    if own.number_of_steps is not None:
-        out += ["--max_steps", str(own.number_of_steps)]
+    out = list(rest)
+    if not for_eval:
+        out += ["--task_id", str(own.task), "--log_every", str(own.log_every_n_steps)]
+        if own.number_of_steps is not None:
+            out += ["--max_steps", str(own.number_of_steps)]
     if own.checkpoint_dir:
-        out += ["--train_dir", own.checkpoint_dir]
+        out += ["--checkpoint_dir" if for_eval else "--train_dir", own.checkpoint_dir]
     if own.dataset_dir:
         out += ["--data_dir", own.dataset_dir]
     if "--image_size" not in " ".join(rest):
