@@ -27,6 +27,7 @@ from ..models.registry import MODEL_SPECS, spec_for
 from ..ops import functional as Fn
 from ..parallel.engine import TrainSetup, Trainer
 from ..utils.logs import format_precision, log
+from ..utils.tfevents import EventFileWriter
 
 # per-model eval defaults (reference flag defaults)
 EVAL_DEFAULTS = {
@@ -102,6 +103,7 @@ def evaluate(args) -> Optional[dict]:
                                  num_classes=args.num_classes, weight_decay=args.weight_decay), device=device)
     batches = _eval_batches(args, spec, batch_size)
     os.makedirs(args.eval_dir, exist_ok=True)
+    summaries = EventFileWriter(args.eval_dir)       # TensorBoard event file, as the reference's FileWriter(eval_dir)
     # ResNet's reference eval builds the network in *training* mode (batch-statistics BN, Q3): only under --ref_compat
     training_bn = bool(args.ref_compat and args.model == "resnet")
     last, res = None, None
@@ -114,6 +116,11 @@ def evaluate(args) -> Optional[dict]:
             res = eval_once(trainer, args, path, d["use_ema"], num_examples, batch_size, batches, training_bn)
             with open(os.path.join(args.eval_dir, "eval.jsonl"), "a") as f:
                 f.write(json.dumps(res) + "\n")
+            scalars = {"Precision @ 1": res["precision_at_1"]}
+            if "recall_at_5" in res:
+                scalars["Recall @ 5"] = res["recall_at_5"]
+            summaries.add_scalars(res["global_step"], scalars)
+            summaries.flush()
             last = path
         if args.run_once:
             return res

@@ -34,6 +34,7 @@ from ..parallel.comm import Comm, LocalComm
 from ..parallel.engine import Trainer, TrainSetup
 from ..utils.logs import ChromeTrace, MetricsWriter, format_step, log
 from ..utils.pipeline import DevicePrefetcher, ScalarReadback
+from ..utils.tfevents import EventFileWriter
 
 GLOBAL_STEP_NAME = {"cnn": "Variable", "cifarnet": "partitioned_space/Variable",
                     "alexnet": "partitioned_space/Variable", "vgg": "root/Variable", "resnet": "Variable",
@@ -222,6 +223,11 @@ def run_worker(args) -> int:
     batches = DevicePrefetcher(make_batches(args, spec, rank, world), device)
     losses_rb = ScalarReadback(device)
     metrics = MetricsWriter(args.metrics_jsonl if is_chief else "")
+    # chief: scalar summaries into train_dir every save_summaries_secs (Supervisor's summary thread; the reference
+    # passes summary_op=None, so its event files hold global_step/sec only — loss and learning rate are extras)
+    events = EventFileWriter(args.train_dir) if (is_chief and p.save_secs is not None and args.save_summaries_secs) \
+        else None
+    last_summary, last_summary_step = time.time(), 0
     trace = ChromeTrace(args.trace, pid=rank)
     last_save = time.time()
     t_run0 = time.time()
@@ -242,6 +248,12 @@ def run_worker(args) -> int:
             loss_value, (lstep, lgs, llr, lwait, lt0, llog) = losses_rb.pop()
             if p.nan_guard:
                 assert not math.isnan(loss_value), "Model diverged with loss = NaN"
+            if events is not None and time.time() - last_summary >= args.save_summaries_secs:
+                now = time.time()
+                events.add_scalars(int(lgs), {"global_step/sec": (lstep - last_summary_step) / max(now - last_summary, 1e-9),
+                                              "total_loss": loss_value, "learning_rate": llr})
+                events.flush()
+                last_summary, last_summary_step = now, lstep
             if llog:
                 t3 = time.time()
                 duration = max((t3 - lt0) / max(1, step - lstep + 1), 1e-9)
@@ -274,6 +286,8 @@ def run_worker(args) -> int:
         tensors = ckpt.collect_tensors(trainer.store, None, None, comm.global_step(), GLOBAL_STEP_NAME.get(args.model, "global_step"))
         log("saved %s" % ckpt.save(args.train_dir, tensors, comm.global_step(), p.max_to_keep, fmt=args.ckpt_format))
     comm.finish()
+    if events is not None:
+        events.close()
     trace.save()
     metrics.close()
     if hasattr(batches, "close"):

@@ -384,3 +384,36 @@ def test_tf_bundle_partitioned_variables_are_reassembled(tmp_path):
     assert tb.decode_slice_key_name(tb.encode_slice_key("a\x00b", [(0, None)])) == "a\x00b"
     with pytest.raises(ValueError):
         tb.write_bundle(str(tmp_path / "bad"), {"w": np.zeros((4, 2), np.float32)}, partitions={"w": [3, 2]})
+
+
+def test_tensorboard_event_files(tmp_path):
+    """Scalar summaries in TensorBoard's event-file format: evaluators write `Precision @ 1` into eval_dir, the chief
+    writes global_step/sec (+ loss, learning rate) into train_dir every --save_summaries_secs."""
+    import glob
+    import struct
+    from distributed_tensorflow_models_b200.eval import cifar10_eval
+    from distributed_tensorflow_models_b200.trainers import cifar10_cnn_bsp
+    from distributed_tensorflow_models_b200.utils import tfevents
+    w = tfevents.EventFileWriter(str(tmp_path / "unit"))
+    w.add_scalars(12, {"Precision @ 1": 0.75, "Recall @ 5": 1.0}, wall_time=1234.5)
+    w.close()
+    evs = tfevents.read_events(w.path)                        # CRC-checked TFRecord framing
+    assert os.path.basename(w.path).startswith("events.out.tfevents.")
+    assert evs[0]["file_version"] == "brain.Event:2" and evs[1]["step"] == 12 and evs[1]["wall_time"] == 1234.5
+    assert evs[1]["scalars"] == {"Precision @ 1": 0.75, "Recall @ 5": 1.0}
+    # Event{wall_time=1(fixed64), step=2, summary=5{value=1{tag=1, simple_value=2(fixed32)}}}
+    raw = tfevents.encode_event(2.0, 3, scalars={"a": 0.5})
+    assert raw == (b"\x09" + struct.pack("<d", 2.0) + b"\x10\x03" + b"\x2a\x0a" + b"\x0a\x08" + b"\x0a\x01a" +
+                   b"\x15" + struct.pack("<f", 0.5))
+    d = str(tmp_path / "train")
+    assert cifar10_cnn_bsp.main(["--synthetic", "--batch_size=4", "--train_dir=" + d, "--max_steps=3",
+                                 "--backend=local", "--save_summaries_secs=0.000001"]) == 0
+    files = glob.glob(os.path.join(d, "events.out.tfevents.*"))
+    assert len(files) == 1
+    evs = tfevents.read_events(files[0])
+    assert len(evs) >= 2 and {"global_step/sec", "total_loss", "learning_rate"} <= set(evs[-1]["scalars"])
+    e = str(tmp_path / "eval")
+    assert cifar10_eval.main(["--checkpoint_dir=" + d, "--run_once", "--synthetic", "--num_examples=8",
+                              "--batch_size=4", "--eval_dir=" + e]) == 0
+    evs = tfevents.read_events(glob.glob(os.path.join(e, "events.out.tfevents.*"))[0])
+    assert evs[-1]["step"] == 3 and "Precision @ 1" in evs[-1]["scalars"]
