@@ -222,15 +222,19 @@ dwconv_dgrad_s2_v4_kernel(DwP p, const float4* __restrict__ dy, const float4* __
   }
 }
 
-// Filter gradient, multiplier 1, square K x K filter, stride SW in both directions: a warp walks whole output rows
-// (lane = channel, so every load is one 128-byte line) and keeps all K*K accumulators in registers; per output pixel
-// it loads dy once and, per filter row, only the SW input columns that entered the window (the other K - SW are
-// shifted along in registers).  Rows are dealt to warps round-robin; partial sums meet in shared memory and leave
-// the block as one atomic per (tap, channel).
-template <int K, int SW>
+// Filter gradient, multiplier 1, square K x K filter, stride SW in both directions.  A warp sweeps RB consecutive
+// output rows of one image at once (lane = channel, so every load is one 128-byte line) and keeps all K*K
+// accumulators in registers.  Per output column it loads dy once per row and only the SW input columns that entered
+// the window of each of the (RB-1)*SW + K input rows involved (the rest is shifted along in registers).  Sweeping RB
+// rows together matters for DRAM traffic, not just instruction count: a row sweep moves far more data through an SM
+// than L1 holds (and, over 148 SMs, than L2 holds), so with RB = 1 every input row was fetched from DRAM once per
+// filter row (ncu: 812 MB read for a 411 MB problem); with RB = 4 a 3x3 filter re-reads 6 input rows per 4 outputs.
+// Partial sums meet in shared memory and leave the block as one atomic per (tap, channel).
+template <int K, int SW, int RB>
 __global__ void __launch_bounds__(256)
 dwconv_wgrad_rows_kernel(DwP p, const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
-                         int rows_per_warp) {
+                         int groups_per_warp) {
+  constexpr int IR = (RB - 1) * SW + K;          // input rows under RB output rows
   __shared__ float red[8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.y * 32 + lane;
@@ -241,42 +245,55 @@ dwconv_wgrad_rows_kernel(DwP p, const float* __restrict__ x, const float* __rest
   for (int r = 0; r < K; ++r)
 #pragma unroll
     for (int s = 0; s < K; ++s) acc[r][s] = 0.f;
-  const int nrows = p.N * p.OH;
-  const int row0 = (blockIdx.x * 8 + warp) * rows_per_warp;
-  for (int row = row0; row < row0 + rows_per_warp && row < nrows; ++row) {
-    const int n = row / p.OH, oh = row - n * p.OH;
-    const float* grow = dy + (size_t)row * p.OW * p.C + cc;
-    const float* xrow[K];
-    bool live[K];
+  const int gpi = (p.OH + RB - 1) / RB;          // row groups per image
+  const int ngroups = p.N * gpi;
+  const int g0 = (blockIdx.x * 8 + warp) * groups_per_warp;
+  for (int g = g0; g < g0 + groups_per_warp && g < ngroups; ++g) {
+    const int n = g / gpi, oh0 = (g - n * gpi) * RB;
+    const float* grow[RB];
+    bool glive[RB];
 #pragma unroll
-    for (int r = 0; r < K; ++r) {
-      const int ih = oh * SW - p.ph + r;
-      live[r] = (unsigned)ih < (unsigned)p.H;
-      xrow[r] = x + (size_t)(n * p.H + (live[r] ? ih : 0)) * p.W * p.C + cc;
+    for (int b = 0; b < RB; ++b) {
+      glive[b] = oh0 + b < p.OH;
+      grow[b] = dy + (size_t)(n * p.OH + (glive[b] ? oh0 + b : oh0)) * p.OW * p.C + cc;
     }
-    float win[K][K];                       // win[r][s] = x[ih(r)][ow*SW - pw + s], carried from pixel to pixel
+    const float* xrow[IR];
+    bool live[IR];
 #pragma unroll
-    for (int r = 0; r < K; ++r)
+    for (int i = 0; i < IR; ++i) {
+      const int ih = oh0 * SW - p.ph + i;
+      live[i] = (unsigned)ih < (unsigned)p.H;
+      xrow[i] = x + (size_t)(n * p.H + (live[i] ? ih : 0)) * p.W * p.C + cc;
+    }
+    float win[IR][K];                      // win[i][s] = x[ih(i)][ow*SW - pw + s], carried from column to column
+#pragma unroll
+    for (int i = 0; i < IR; ++i)
 #pragma unroll
       for (int s = 0; s < K; ++s) {
         const int iw = -p.pw + s;
-        win[r][s] = (live[r] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[r] + (size_t)iw * p.C) : 0.f;
+        win[i][s] = (live[i] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[i] + (size_t)iw * p.C) : 0.f;
       }
-    // unrolled so that the loads of several pixels are in flight together (they do not depend on the arithmetic)
-#pragma unroll 4
+    // unrolled so that the loads of two columns are in flight together (they do not depend on the arithmetic)
+#pragma unroll 2
     for (int ow = 0; ow < p.OW; ++ow) {
-      const float g = __ldg(grow + (size_t)ow * p.C);
+      float gv[RB];
 #pragma unroll
-      for (int r = 0; r < K; ++r) {
+      for (int b = 0; b < RB; ++b) gv[b] = glive[b] ? __ldg(grow[b] + (size_t)ow * p.C) : 0.f;
 #pragma unroll
-        for (int s = 0; s < K; ++s) acc[r][s] = fmaf(g, win[r][s], acc[r][s]);
-        // slide to pixel ow + 1: keep K - SW columns, fetch SW new ones (zero beyond the row's end)
+      for (int b = 0; b < RB; ++b)
 #pragma unroll
-        for (int s = 0; s + SW < K; ++s) win[r][s] = win[r][s + SW];
+        for (int r = 0; r < K; ++r)
+#pragma unroll
+          for (int s = 0; s < K; ++s) acc[r][s] = fmaf(gv[b], win[b * SW + r][s], acc[r][s]);
+      // slide to column ow + 1: keep K - SW columns, fetch SW new ones (zero beyond the row's end)
+#pragma unroll
+      for (int i = 0; i < IR; ++i) {
+#pragma unroll
+        for (int s = 0; s + SW < K; ++s) win[i][s] = win[i][s + SW];
 #pragma unroll
         for (int s = K - SW; s < K; ++s) {
           const int iw = (ow + 1) * SW - p.pw + s;
-          win[r][s] = (live[r] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[r] + (size_t)iw * p.C) : 0.f;
+          win[i][s] = (live[i] && (unsigned)iw < (unsigned)p.W) ? __ldg(xrow[i] + (size_t)iw * p.C) : 0.f;
         }
       }
     }
@@ -608,20 +625,30 @@ extern "C" int dtf_dwconv_wgrad(const dtf_dwconv_params* p, const float* x, cons
   if (int rc = dw_check(p)) return rc;
   if (p->mult == 1 && p->R == p->S && p->sh == p->sw && (p->sh == 1 || p->sh == 2) &&
       (p->R == 3 || p->R == 5 || p->R == 7)) {
-    const int nrows = p->N * p->OH, cg = ceil_div(p->C, 32);
+    const int cg = ceil_div(p->C, 32);
     DTF_REQUIRE(cg <= 65535, "depthwise wgrad: grid too large");
-    // ~4 blocks per SM; a warp takes rows_per_warp consecutive output rows
-    long long want_blocks = (4LL * num_sms() + cg - 1) / cg;
-    int rpw = (int)((nrows + want_blocks * 8 - 1) / (want_blocks * 8));
-    if (rpw < 1) rpw = 1;
-    const dim3 grid((unsigned)ceil_div(nrows, 8 * rpw), (unsigned)cg, 1);
-#define DTF_DW_WGRAD(K_, SW_) dwconv_wgrad_rows_kernel<K_, SW_><<<grid, 256, 0, st>>>(*p, x, dy, dw, rpw)
-    if (p->R == 3 && p->sh == 1) DTF_DW_WGRAD(3, 1);
-    else if (p->R == 3) DTF_DW_WGRAD(3, 2);
-    else if (p->R == 5 && p->sh == 1) DTF_DW_WGRAD(5, 1);
-    else if (p->R == 5) DTF_DW_WGRAD(5, 2);
-    else if (p->sh == 1) DTF_DW_WGRAD(7, 1);
-    else DTF_DW_WGRAD(7, 2);
+    // rows per sweep: 4 (2 for 7x7: registers) while that still leaves ~8 warps per SM, else fewer
+    int rb = p->R == 7 ? 2 : 4;
+    while (rb > 1 && (long long)p->N * ceil_div(p->OH, rb) * cg < 8LL * num_sms()) rb >>= 1;
+    const int ngroups = p->N * ceil_div(p->OH, rb);
+    long long want_blocks = (4LL * num_sms() + cg - 1) / cg;          // ~4 blocks per SM
+    int gpw = (int)((ngroups + want_blocks * 8 - 1) / (want_blocks * 8));
+    if (gpw < 1) gpw = 1;
+    const dim3 grid((unsigned)ceil_div(ngroups, 8 * gpw), (unsigned)cg, 1);
+#define DTF_DW_WGRAD(K_, SW_, RB_) dwconv_wgrad_rows_kernel<K_, SW_, RB_><<<grid, 256, 0, st>>>(*p, x, dy, dw, gpw)
+#define DTF_DW_WGRAD_RB(K_, SW_)                                   \
+  do {                                                             \
+    if (rb == 4) DTF_DW_WGRAD(K_, SW_, 4);                         \
+    else if (rb == 2) DTF_DW_WGRAD(K_, SW_, 2);                    \
+    else DTF_DW_WGRAD(K_, SW_, 1);                                 \
+  } while (0)
+    if (p->R == 3 && p->sh == 1) DTF_DW_WGRAD_RB(3, 1);
+    else if (p->R == 3) DTF_DW_WGRAD_RB(3, 2);
+    else if (p->R == 5 && p->sh == 1) DTF_DW_WGRAD_RB(5, 1);
+    else if (p->R == 5) DTF_DW_WGRAD_RB(5, 2);
+    else if (p->sh == 1) { if (rb == 2) DTF_DW_WGRAD(7, 1, 2); else DTF_DW_WGRAD(7, 1, 1); }
+    else { if (rb == 2) DTF_DW_WGRAD(7, 2, 2); else DTF_DW_WGRAD(7, 2, 1); }
+#undef DTF_DW_WGRAD_RB
 #undef DTF_DW_WGRAD
     DTF_CHECK(cudaGetLastError());
     return 0;

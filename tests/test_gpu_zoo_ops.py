@@ -60,6 +60,13 @@ def _r(*shape, seed=0, scale=1.0):
     (2, 23, 17, 40, 1, 5, 2, "SAME", False),       # 5x5 stride 2: parity-walking dgrad, sliding-window wgrad
     (3, 15, 15, 36, 1, 7, 1, "SAME", True),        # 7x7 stride 1 (49 accumulators per thread in the filter gradient)
     (2, 16, 16, 72, 1, 3, 2, "VALID", False),      # three channel groups, last one partial
+    # enough (image, row-group, channel-group) work that the filter gradient sweeps 4 (7x7: 2) output rows at once;
+    # heights that leave a partial last group
+    (16, 38, 11, 256, 1, 3, 1, "SAME", False),
+    (16, 75, 9, 256, 1, 3, 2, "SAME", False),
+    (16, 38, 9, 256, 1, 5, 1, "SAME", True),
+    (8, 21, 9, 512, 1, 7, 1, "SAME", False),
+    (8, 41, 9, 512, 1, 7, 2, "SAME", False),
     (2, 12, 12, 6, 2, 3, 1, "SAME", True),         # multiplier 2 -> generic kernels
     (2, 12, 12, 10, 1, 3, 2, "VALID", False),      # C % 4 != 0 -> generic kernels
     (2, 9, 9, 16, 1, (1, 3), 1, "SAME", False),    # single filter row
@@ -155,7 +162,8 @@ def _canaries_intact(buf, where):
 
 
 @pytest.mark.parametrize("cfg", [(2, 9, 7, 8, 3, 1), (2, 9, 7, 8, 3, 2), (2, 11, 13, 12, 5, 1), (2, 11, 13, 12, 5, 2),
-                                 (1, 9, 9, 36, 7, 1), (1, 10, 9, 36, 7, 2), (3, 8, 8, 4, 3, 1)])
+                                 (1, 9, 9, 36, 7, 1), (1, 10, 9, 36, 7, 2), (3, 8, 8, 4, 3, 1),
+                                 (16, 38, 9, 256, 3, 1), (16, 39, 9, 256, 5, 2), (8, 21, 9, 512, 7, 1)])
 def test_depthwise_kernels_stay_in_bounds(cfg):
     import ctypes as C
 
