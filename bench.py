@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--no-branch-streams", action="store_true",
                     help="run the branches of Inception blocks one after the other instead of on side streams")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--image-size", type=int, default=None, help="model-zoo networks only (default: the network's own)")
+    ap.add_argument("--num-classes", type=int, default=None, help="model-zoo networks only (default 1001)")
     return ap.parse_args()
 
 
@@ -148,10 +150,15 @@ def main():
     else:
         comm = LocalComm()
 
-    spec = MODEL_SPECS[args.model]
+    if args.model in MODEL_SPECS:
+        spec = MODEL_SPECS[args.model]
+    else:       # any other network of the model-zoo registry (not a BASELINE.json config; for the zoo sweeps)
+        from distributed_tensorflow_models_b200.models.registry import spec_for
+        spec = spec_for(args.model, args.image_size, args.num_classes)
     setup = TrainSetup(model=args.model, mode=args.mode, num_workers=world, staleness=args.staleness,
                        cuda_graph=not args.no_graph, fuse_bn=not args.no_fuse_bn, seed=0,
-                       branch_streams=not args.no_branch_streams)
+                       branch_streams=not args.no_branch_streams, image_size=args.image_size,
+                       num_classes=args.num_classes)
     if args.batch:
         setup.batch_size = args.batch
     else:
