@@ -259,3 +259,15 @@ def test_contrib_conv_honours_batch_norm_scope_bias_switch_and_separable_variabl
     assert tuple(st2.get("dw/depthwise_weights").tensor.shape) == (3, 3, 3, 2) and not st2.has("dw/pointwise_weights")
     assert tuple(up.shape) == (4, 12, 12, 4) and tuple(st2.get("up/weights").to_tf().shape) == (4, 4, 4, 3)
     assert {"in/beta", "in/gamma"} <= {v.name for v in st2.all()} and tuple(inorm.shape) == tuple(x.shape)
+
+
+def test_docs_examples_run():
+    """Every python block of docs/SLIM.md executes, in order, in one namespace."""
+    import os
+    import re
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "docs", "SLIM.md")
+    blocks = re.findall(r"```python\n(.*?)```", open(path).read(), re.S)
+    assert len(blocks) >= 4
+    ns: dict = {}
+    for code in blocks:
+        exec(compile(code, path, "exec"), ns)
