@@ -398,3 +398,28 @@ def test_mobilenet_v1_train_eval_and_fine_tune_entry_points(tmp_path):
         mobilenet_v1_train.main(common + ["--quantize=True"])
     with pytest.raises(SystemExit):
         mobilenet_v1_train.main(["--depth_multiplier=0.3"])
+
+
+def test_zoo_network_under_two_worker_bsp_on_the_thread_cluster():
+    """A zoo network behind the parameter-server protocol: two workers (threads over shared CPU tensors) in BSP take
+    ONE global step per pair of gradients, end with identical replicas, and apply the arg scope's L2 on the owner."""
+    from distributed_tensorflow_models_b200.parallel.comm import ThreadCluster
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    cl = ThreadCluster(2)
+
+    def work(comm):
+        t = Trainer(TrainSetup(model="mobilenet_v1_025", batch_size=2, num_workers=2, image_size=32, num_classes=5,
+                               seed=0, cuda_graph=False), comm)
+        g = torch.Generator().manual_seed(10 + comm.rank)
+        x, y = torch.randn(2, 32, 32, 3, generator=g), torch.randint(0, 5, (2,), generator=g)
+        p0 = t.layout.params.clone()
+        out = t.train_step(x, y)
+        return p0, t.layout.grads.clone(), t.layout.params.clone(), out["global_step"], out["lr"], t.layout
+
+    res = cl.run(work)
+    p0, L, lr = res[0][0], res[0][5], res[0][4]
+    assert all(r[3] == 1 for r in res) and torch.equal(res[0][2], res[1][2])
+    assert lr == pytest.approx(0.045)                       # the zoo trainer's constant, not multiplied by N
+    gmean = (res[0][1] + res[1][1]) / 2
+    gmean[: L.wd_boundary] += L.weight_decay * p0[: L.wd_boundary]
+    assert torch.allclose(res[0][2], p0 - lr * gmean, atol=1e-6)
