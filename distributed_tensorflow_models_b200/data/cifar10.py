@@ -77,8 +77,10 @@ def per_image_standardization(x: torch.Tensor) -> torch.Tensor:
     return ((flat - mean) / std).reshape(x.shape)
 
 
-def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator) -> torch.Tensor:
-    """uint8 [B,32,32,3] -> float32 [B,image_size,image_size,3] with the training distortions."""
+def distort_batch_reference(images_u8: torch.Tensor, image_size: int, gen: torch.Generator) -> torch.Tensor:
+    """The training distortion written out step by step as the reference applies it (cnn/cifar10_input.py:176-190):
+    random crop -> random flip -> random brightness (+-63) -> random contrast (0.2 .. 1.8) -> standardisation.
+    Kept as the oracle of :func:`distort_batch`."""
     b = images_u8.shape[0]
     x = images_u8.to(torch.float32)
     if image_size < 32:
@@ -95,6 +97,41 @@ def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator
     mean = x.mean(dim=(1, 2), keepdim=True)
     x = (x - mean) * factor[:, None, None, None] + mean
     return per_image_standardization(x)
+
+
+def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator) -> torch.Tensor:
+    """uint8 [B,32,32,3] -> float32 [B,image_size,image_size,3] with the training distortions, in three passes.
+
+    Crop and flip are one gather on the uint8 records.  Brightness (x + d) and contrast ((x - m_c) f + m_c, with the
+    per-channel mean m_c) are followed by per-image standardisation, which removes any shift and rescales: with
+    c = x - m_c per channel, the standardised result is (c f + m_c - M) / max(sd(c f + m_c), 1/sqrt(n)), M the
+    mean of the channel means — so the distortions never need to be materialised, only their effect on the
+    statistics.  The same random draws are consumed in the same order as in :func:`distort_batch_reference`, and the
+    outputs agree to rounding (tests/test_ckpt_data_cli.py)."""
+    b = images_u8.shape[0]
+    size = image_size if image_size < 32 else 32
+    if image_size < 32:
+        oy = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+        ox = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+    else:
+        oy = ox = torch.zeros(b, dtype=torch.int64)
+    flip = torch.rand(b, generator=gen) < 0.5
+    _delta = torch.rand(b, generator=gen)          # brightness: drawn (stream parity), cancelled by the standardisation
+    factor = 0.2 + torch.rand(b, generator=gen) * 1.6
+    ar = torch.arange(size)
+    idx_y = oy[:, None] + ar[None, :]
+    cols = torch.where(flip[:, None], (size - 1 - ar)[None, :], ar[None, :])
+    idx_x = ox[:, None] + cols
+    x = images_u8[torch.arange(b)[:, None, None], idx_y[:, :, None], idx_x[:, None, :]].to(torch.float32)
+    n = size * size * 3
+    m_c = x.mean(dim=(1, 2), keepdim=True)                         # per-channel mean (what adjust_contrast uses)
+    c = x - m_c
+    f = factor[:, None, None, None]
+    shift = m_c - m_c.mean(dim=3, keepdim=True)                    # channel mean minus image mean
+    y = c * f + shift                                              # == contrast-adjusted image minus its mean
+    var = (y * y).reshape(b, -1).mean(1)
+    inv = 1.0 / torch.sqrt(var).clamp_min(1.0 / n ** 0.5)
+    return y * inv[:, None, None, None]
 
 
 def center_batch(images_u8: torch.Tensor, image_size: int) -> torch.Tensor:
@@ -120,75 +157,105 @@ def _shutdown_prefetchers():
 atexit.register(_shutdown_prefetchers)
 
 
-class _Prefetcher:
-    def __init__(self, make_batch, depth: int):
-        self.q: "queue.Queue" = queue.Queue(maxsize=depth)
-        self.stop = False
-        self.t = threading.Thread(target=self._run, args=(make_batch,), daemon=True)
-        _LIVE_PREFETCHERS.add(self)
-        self.t.start()
+class _OrderedPrefetcher:
+    """``threads`` producer threads; thread t builds batches t, t + T, t + 2T, ... (``make(k)`` is a pure function of
+    the batch number) into its own queue and the consumer drains the queues round-robin, so the batch sequence is the
+    same for any thread count — the role of the reference's 16 ``tf.train.batch`` threads (cnn/cifar10_input.py:118-135),
+    without their run-to-run reordering."""
 
-    def _run(self, make_batch):
+    def __init__(self, make, threads: int, depth: int):
+        self.T = max(1, threads)
+        self.qs = [queue.Queue(maxsize=max(1, depth)) for _ in range(self.T)]
+        self.stop = False
+        self.next = 0
+        self.ts = [threading.Thread(target=self._run, args=(make, t), daemon=True) for t in range(self.T)]
+        _LIVE_PREFETCHERS.add(self)
+        for t in self.ts:
+            t.start()
+
+    def _run(self, make, t: int):
+        k = t
         while not self.stop:
-            item = make_batch()
+            item = make(k)
             while not self.stop:
                 try:
-                    self.q.put(item, timeout=0.1)
+                    self.qs[t].put(item, timeout=0.1)
                     break
                 except queue.Full:
                     continue
             if item is None:
                 return
+            k += self.T
 
     def get(self):
-        return self.q.get()
+        item = self.qs[self.next % self.T].get()
+        self.next += 1
+        return item
 
     def close(self, join: bool = False):
         self.stop = True
-        if join and self.t.is_alive():
-            try:
-                while True:
-                    self.q.get_nowait()
-            except queue.Empty:
-                pass
-            self.t.join(timeout=2.0)
+        if join:
+            for q_, t in zip(self.qs, self.ts):
+                if t.is_alive():
+                    try:
+                        while True:
+                            q_.get_nowait()
+                    except queue.Empty:
+                        pass
+                    t.join(timeout=2.0)
 
 
 class Cifar10Batches:
-    """Iterator of ``(images float32 NHWC, labels int64)`` host batches."""
+    """Iterator of ``(images float32 NHWC, labels int64)`` host batches.
+
+    Batch ``k`` is a pure function of ``(seed, rank, k)``: its epoch's permutation and its distortion draws come from
+    generators seeded by those numbers, so the stream does not depend on ``num_threads`` and a run can be repeated."""
 
     def __init__(self, data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, train: bool = True,
                  shuffle: bool = True, rank: int = 0, world: int = 1, seed: int = 0, prefetch: int = 4,
-                 repeat: bool = True):
+                 repeat: bool = True, num_threads: Optional[int] = None):
         labels, images = read_records(data_files(data_dir, eval_data=not train))
         if world > 1 and train:
             labels, images = labels[rank::world], images[rank::world]
         self.labels = torch.from_numpy(labels)
         self.images = torch.from_numpy(images)
         self.bs, self.size, self.train, self.shuffle, self.repeat = batch_size, image_size, train, shuffle, repeat
-        self.gen = torch.Generator().manual_seed(seed + 7919 * rank)
-        self.pos = 0
-        self.order = self._new_order()
+        self.seed = seed + 7919 * rank
+        self.n = self.labels.numel()
+        self.bpe = max(1, -(-self.n // batch_size))            # batches per epoch
+        self._orders: dict = {}
+        self._lock = threading.Lock()
         self.pin = torch.cuda.is_available()
-        self.pf = _Prefetcher(self._make, prefetch)
+        if num_threads is None:
+            num_threads = min(4, max(1, (os.cpu_count() or 2) // 2)) if train else 1
+        self.pf = _OrderedPrefetcher(self._make, num_threads, max(1, prefetch // max(1, num_threads)) + 1)
 
-    def _new_order(self):
-        n = self.labels.numel()
-        return torch.randperm(n, generator=self.gen) if (self.shuffle and self.train) else torch.arange(n)
+    def _order(self, epoch: int) -> torch.Tensor:
+        with self._lock:
+            o = self._orders.get(epoch)
+            if o is None:
+                if self.shuffle and self.train:
+                    o = torch.randperm(self.n, generator=torch.Generator().manual_seed(self.seed * 1000003 + epoch))
+                else:
+                    o = torch.arange(self.n)
+                self._orders[epoch] = o
+                for old in [e for e in self._orders if e < epoch - 1]:
+                    del self._orders[old]
+            return o
 
-    def _make(self):
-        n = self.labels.numel()
-        if self.pos >= n:
-            if not self.repeat:
-                return None
-            self.pos = 0
-            self.order = self._new_order()
-        idx = self.order[self.pos:self.pos + self.bs]
+    def _make(self, k: int):
+        epoch, j = divmod(k, self.bpe)
+        if epoch > 0 and not self.repeat:
+            return None
+        order = self._order(epoch)
+        idx = order[j * self.bs:(j + 1) * self.bs]
         if idx.numel() < self.bs and self.repeat:
-            idx = torch.cat([idx, self.order[: self.bs - idx.numel()]])
-        self.pos += self.bs
+            idx = torch.cat([idx, order[: self.bs - idx.numel()]])
         img = self.images[idx]
-        x = distort_batch(img, self.size, self.gen) if self.train else center_batch(img, self.size)
+        if self.train:
+            x = distort_batch(img, self.size, torch.Generator().manual_seed(self.seed * 7368787 + k))
+        else:
+            x = center_batch(img, self.size)
         y = self.labels[idx].clone()
         if self.pin:
             x, y = x.pin_memory(), y.pin_memory()

@@ -417,3 +417,29 @@ def test_tensorboard_event_files(tmp_path):
                               "--batch_size=4", "--eval_dir=" + e]) == 0
     evs = tfevents.read_events(glob.glob(os.path.join(e, "events.out.tfevents.*"))[0])
     assert evs[-1]["step"] == 3 and "Precision @ 1" in evs[-1]["scalars"]
+
+
+def test_cifar_fused_distortion_matches_stepwise_and_stream_is_thread_count_independent(tmp_path):
+    """distort_batch (crop + flip as one uint8 gather, brightness / contrast folded into the standardisation) equals
+    the step-by-step reference distortion; the batch stream is a pure function of (seed, rank, batch number)."""
+    g = torch.Generator().manual_seed(0)
+    raw = torch.randint(0, 256, (16, 32, 32, 3), dtype=torch.uint8, generator=g)
+    for size in (24, 32):
+        a = cifar10.distort_batch_reference(raw, size, torch.Generator().manual_seed(5))
+        b = cifar10.distort_batch(raw, size, torch.Generator().manual_seed(5))
+        assert a.shape == b.shape and float((a - b).abs().max()) < 1e-5
+    flat = torch.full((2, 32, 32, 3), 7, dtype=torch.uint8)              # constant image: the 1/sqrt(n) floor applies
+    assert torch.isfinite(cifar10.distort_batch(flat, 32, torch.Generator().manual_seed(1))).all()
+    synthetic.write_cifar10_binary(str(tmp_path), train_per_file=40, test=8)
+    one = cifar10.distorted_inputs(str(tmp_path), 16, 32, seed=3, num_threads=1)
+    three = cifar10.distorted_inputs(str(tmp_path), 16, 32, seed=3, num_threads=3)
+    try:
+        for _ in range(30):                                               # crosses an epoch boundary (200 / 16)
+            (xa, ya), (xb, yb) = next(one), next(three)
+            assert torch.equal(xa, xb) and torch.equal(ya, yb)
+    finally:
+        one.close()
+        three.close()
+    other = cifar10.distorted_inputs(str(tmp_path), 16, 32, seed=4, num_threads=1)
+    assert not torch.equal(next(other)[1], ya)
+    other.close()
