@@ -17,11 +17,15 @@ cases ``build_imagenet_data.py:264-322`` fixes offline).
 """
 from __future__ import annotations
 
+import atexit
 import io
 import math
+import os
 import queue
 import random
+import sys
 import threading
+import weakref
 from typing import List, Optional, Tuple
 
 import numpy as np
@@ -49,11 +53,15 @@ def parse_example_proto(record: bytes):
     return image, label, bbox, text
 
 
+def decode_jpeg_u8(buf: bytes) -> np.ndarray:
+    """-> uint8 HWC (tf.image.decode_jpeg with channels=3)."""
+    from PIL import Image
+    return np.asarray(Image.open(io.BytesIO(buf)).convert("RGB"), dtype=np.uint8)
+
+
 def decode_jpeg(buf: bytes) -> torch.Tensor:
     """-> float32 HWC in [0, 1] (tf.image.decode_jpeg + convert_image_dtype)."""
-    from PIL import Image
-    img = Image.open(io.BytesIO(buf)).convert("RGB")
-    return torch.from_numpy(np.asarray(img, dtype=np.uint8).copy()).to(torch.float32) / 255.0
+    return torch.from_numpy(decode_jpeg_u8(buf).astype(np.float32) / np.float32(255.0))
 
 
 # ---- geometry ---------------------------------------------------------------------------------------------------
@@ -124,131 +132,281 @@ def hsv_to_rgb(x: torch.Tensor) -> torch.Tensor:
     return torch.stack([r, g, b], -1)
 
 
+def _rgb_to_hsv_np(r: np.ndarray, g: np.ndarray, b: np.ndarray):
+    """Contiguous float32 planes in [0, 1] -> (h in [0, 1), s, v) (same formulas as :func:`rgb_to_hsv`; the modulo
+    operations are written as compare-and-shift because ``np.mod`` costs as much as everything else together)."""
+    f = np.float32
+    mx = np.maximum(np.maximum(r, g), b)
+    mn = np.minimum(np.minimum(r, g), b)
+    d = mx - mn
+    inv = f(1.0) / np.maximum(d, f(1e-12))
+    s = np.where(mx > 0, d / np.maximum(mx, f(1e-12)), f(0.0))
+    hr = (g - b) * inv                       # in [-1, 1]: wrap the negative half by +6
+    hr = np.where(hr < 0, hr + f(6.0), hr)
+    h = np.where(mx == r, hr, np.where(mx == g, (b - r) * inv + f(2.0), (r - g) * inv + f(4.0)))
+    h = np.where(d > 0, h * f(1.0 / 6.0), f(0.0))
+    h = np.where(h >= 1, h - f(1.0), h)
+    return h, s, mx
+
+
+def _hsv_to_rgb_np(h: np.ndarray, s: np.ndarray, v: np.ndarray):
+    """Branch-free form: channel(n) = v - v s max(0, min(k, 4 - k, 1)), k = (n + 6h) mod 6, n = 5, 3, 1."""
+    f = np.float32
+    h6 = h * f(6.0)
+    vs = v * s
+    out = []
+    for n in (5.0, 3.0, 1.0):
+        k = h6 + f(n)
+        k = np.where(k >= 6, k - f(6.0), k)
+        out.append(v - vs * np.clip(np.minimum(k, f(4.0) - k), f(0.0), f(1.0)))
+    return out
+
+
 def distort_color(img: torch.Tensor, thread_id: int, rng: random.Random) -> torch.Tensor:
-    """Two orderings of brightness / saturation / hue / contrast by thread parity (image_processing.py:164-195)."""
-    def brightness(x):
-        return x + rng.uniform(-32.0 / 255.0, 32.0 / 255.0)
+    """Two orderings of brightness / saturation / hue / contrast by thread parity (image_processing.py:164-195).
 
-    def saturation(x):
-        hsv = rgb_to_hsv(x.clamp(0, 1))
-        hsv[..., 1] = (hsv[..., 1] * rng.uniform(0.5, 1.5)).clamp(0, 1)
-        return hsv_to_rgb(hsv)
+    Saturation and hue are neighbours in both orderings and the RGB image between them is already inside [0, 1], so
+    they share one RGB -> HSV -> RGB round trip (the costly part of the whole input pipeline); the arithmetic runs in
+    NumPy float32 on three contiguous colour planes.  The random draws are taken in the reference's order."""
+    f = np.float32
+    x = img.numpy() if isinstance(img, torch.Tensor) else np.asarray(img, dtype=np.float32)
+    planes = [np.ascontiguousarray(x[..., c], dtype=np.float32) for c in range(3)]
 
-    def hue(x):
-        hsv = rgb_to_hsv(x.clamp(0, 1))
-        hsv[..., 0] = (hsv[..., 0] + rng.uniform(-0.2, 0.2)) % 1.0
-        return hsv_to_rgb(hsv)
+    def brightness(p):
+        delta = f(rng.uniform(-32.0 / 255.0, 32.0 / 255.0))
+        return [a + delta for a in p]
 
-    def contrast(x):
-        m = x.mean(dim=(0, 1), keepdim=True)
-        return (x - m) * rng.uniform(0.5, 1.5) + m
+    def saturation_hue(p):
+        sat = f(rng.uniform(0.5, 1.5))
+        hue = f(rng.uniform(-0.2, 0.2))
+        h, s_, v = _rgb_to_hsv_np(*[np.clip(a, f(0.0), f(1.0)) for a in p])
+        s_ = np.clip(s_ * sat, f(0.0), f(1.0))
+        h = h + hue
+        h -= np.floor(h)
+        return _hsv_to_rgb_np(h, s_, v)
 
-    order = (brightness, saturation, hue, contrast) if thread_id % 2 == 0 else (brightness, contrast, saturation, hue)
+    def contrast(p):
+        factor = f(rng.uniform(0.5, 1.5))
+        out = []
+        for a in p:
+            m = a.mean(dtype=np.float32)
+            out.append((a - m) * factor + m)
+        return out
+
+    order = (brightness, saturation_hue, contrast) if thread_id % 2 == 0 else (brightness, contrast, saturation_hue)
     for fn in order:
-        img = fn(img)
-    return img.clamp(0.0, 1.0)
+        planes = fn(planes)
+    out = np.empty(x.shape, dtype=np.float32)
+    for c in range(3):
+        np.clip(planes[c], f(0.0), f(1.0), out=out[..., c])
+    return torch.from_numpy(out)
 
 
-def distort_image(img: torch.Tensor, height: int, width: int, bbox: np.ndarray, thread_id: int,
-                  rng: random.Random) -> torch.Tensor:
+def _to_float(img) -> torch.Tensor:
+    """uint8 HWC (NumPy) -> float32 [0, 1] tensor; float tensors pass through."""
+    if isinstance(img, np.ndarray):
+        return torch.from_numpy(img.astype(np.float32) / np.float32(255.0))
+    return img
+
+
+def distort_image(img, height: int, width: int, bbox: np.ndarray, thread_id: int, rng: random.Random) -> torch.Tensor:
+    """``img``: float HWC tensor in [0, 1], or the decoder's uint8 array (only the crop is then converted)."""
     h, w = img.shape[0], img.shape[1]
     y0, x0, ch, cw = sample_distorted_bounding_box(h, w, bbox, rng)
-    img = img[y0:y0 + ch, x0:x0 + cw]
+    img = _to_float(img[y0:y0 + ch, x0:x0 + cw])
     img = resize(img, height, width, thread_id % 4)
     if rng.random() < 0.5:
         img = img.flip(1)
     return distort_color(img, thread_id, rng)
 
 
-def eval_image(img: torch.Tensor, height: int, width: int) -> torch.Tensor:
+def eval_image(img, height: int, width: int) -> torch.Tensor:
     h, w = img.shape[0], img.shape[1]
     ch, cw = int(h * 0.875), int(w * 0.875)
     y0, x0 = (h - ch) // 2, (w - cw) // 2
-    return resize(img[y0:y0 + ch, x0:x0 + cw], height, width, 0)
+    return resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, 0)
 
 
 def image_preprocessing(image_buffer: bytes, bbox: np.ndarray, train: bool, thread_id: int, rng: random.Random,
                         image_size: int = IMAGE_SIZE) -> torch.Tensor:
-    img = decode_jpeg(image_buffer)
+    img = decode_jpeg_u8(image_buffer)
     img = distort_image(img, image_size, image_size, bbox, thread_id, rng) if train else eval_image(img, image_size,
                                                                                                     image_size)
     return (img - 0.5) * 2.0
 
 
 # ---- batching ---------------------------------------------------------------------------------------------------
+def _worker_loop(tid: int, files: List[str], seed: int, shuffle_buffer: int, train: bool, repeat: bool, size: int,
+                 emit, stopped) -> None:
+    """One reader + preprocessor (the reference runs ``num_readers`` readers and ``num_preprocess_threads``
+    preprocessing graphs around a RandomShuffleQueue, image_processing.py:410-516): reads its share of the shards,
+    keeps a shuffle buffer, emits ``(image, label)`` pairs and finally ``None``."""
+    rng = random.Random(seed)
+    buf: list = []
+
+    def process(rec) -> bool:
+        image, label, bbox, _ = parse_example_proto(rec)
+        return emit((image_preprocessing(image, bbox, train, tid, rng, size), label))
+
+    try:
+        while not stopped():
+            order = list(files)
+            if train:
+                rng.shuffle(order)
+            for path in order:
+                for rec in read_records(path):
+                    if stopped():
+                        return
+                    if train:
+                        buf.append(rec)
+                        if len(buf) < shuffle_buffer:
+                            continue
+                        rec = buf.pop(rng.randrange(len(buf)))
+                    if not process(rec):
+                        return
+            if not repeat:
+                break
+        while buf and not stopped():
+            if not process(buf.pop()):
+                return
+    finally:
+        emit(None)
+
+
+def _process_main(tid, files, seed, shuffle_buffer, train, repeat, size, ring, free_q, ready_q, stop_event) -> None:
+    """Worker process: preprocessed images go into a free slot of the shared-memory ring; only (slot, label) travels
+    through the queue (an mp.Queue moves ~300 MB/s — one 299x299x3 float image is 1 MB)."""
+    torch.set_num_threads(1)          # one core per worker; also keeps the forked child out of the OpenMP pool
+
+    def emit(item) -> bool:
+        if item is None:
+            while not stop_event.is_set():
+                try:
+                    ready_q.put(None, timeout=0.1)
+                    return True
+                except queue.Full:
+                    continue
+            return False
+        x, label = item
+        while not stop_event.is_set():
+            try:
+                slot = free_q.get(timeout=0.1)
+            except queue.Empty:
+                continue
+            ring[slot].copy_(x)
+            ready_q.put((slot, label))           # capacity == number of slots: cannot be full while we hold one
+            return True
+        return False
+
+    _worker_loop(tid, files, seed, shuffle_buffer, train, repeat, size, emit, stop_event.is_set)
+    if stop_event.is_set():           # shut down by the consumer: do not wait for it to read what is still queued
+        ready_q.cancel_join_thread()  # (a normal finish flushes, so that the last images and the end marker arrive)
+    free_q.cancel_join_thread()
+
+
+_LIVE_BATCHERS: "weakref.WeakSet" = weakref.WeakSet()
+
+
+def _close_live_batchers() -> None:
+    for b in list(_LIVE_BATCHERS):
+        b.close()
+
+
+atexit.register(_close_live_batchers)
+
+
 class ImagenetBatches:
+    """Iterator of ``(images float32 NHWC in [-1, 1], labels int64)`` host batches.
+
+    ``workers='process'`` (default for training with more than one worker) runs each reader / preprocessor in its own
+    process and hands images over through a shared-memory ring: JPEG decoding and the colour distortion are
+    Python-level PIL / NumPy work (13.6 ms per image and core) that threads parallelise only up to the interpreter
+    lock (~250 img/s here).  ``workers='thread'`` keeps everything in-process (evaluation, tests, debuggers)."""
+
     def __init__(self, dataset: Dataset, batch_size: int, train: bool, image_size: int = IMAGE_SIZE,
                  num_preprocess_threads: int = NUM_PREPROCESS_THREADS, rank: int = 0, world: int = 1, seed: int = 0,
-                 shuffle_buffer: int = 256, repeat: bool = True):
+                 shuffle_buffer: int = 256, repeat: bool = True, workers: Optional[str] = None):
         files = dataset.data_files()
         if not files:
             raise ValueError(dataset.download_message())
         files = files[rank::world] if len(files) >= world else files
         self.bs, self.size, self.train, self.repeat = batch_size, image_size, train, repeat
-        self.q: "queue.Queue" = queue.Queue(maxsize=max(4 * batch_size, 64))
-        self.stop = False
-        self.n_threads = max(1, min(num_preprocess_threads, len(files)))
-        self.done = 0
-        self.lock = threading.Lock()
-        self.threads = []
-        for t in range(self.n_threads):
-            th = threading.Thread(target=self._worker, args=(t, files[t::self.n_threads], seed + 1000 * rank + t,
-                                                             shuffle_buffer), daemon=True)
-            th.start()
-            self.threads.append(th)
+        self.n_workers = max(1, min(num_preprocess_threads, len(files)))
+        self.mode = workers or ("process" if (train and self.n_workers > 1) else "thread")
+        if self.mode not in ("process", "thread"):
+            raise ValueError("workers must be 'process' or 'thread'")
+        self.finished = 0
+        self._exhausted = False
+        self._closed = False
         self.pin = torch.cuda.is_available()
+        self.workers: list = []
+        if self.mode == "process":
+            import torch.multiprocessing as mp       # pickles the shared ring by handle
+            # "spawn": the trainer process is heavily multi-threaded (CUDA runtime, OpenMP pool, prefetchers) and a
+            # fork() of such a process can leave a child holding a lock nobody will ever release
+            # (a __main__ that cannot be re-imported — a script piped through stdin — leaves only fork)
+            main = sys.modules.get("__main__")
+            mfile = getattr(main, "__file__", None)
+            spawn_ok = getattr(main, "__spec__", None) is not None or mfile is None or os.path.exists(mfile)
+            ctx = mp.get_context("spawn" if spawn_ok else "fork")
+            slots = max(2 * batch_size, 2 * self.n_workers, 16)
+            self.ring = torch.empty((slots, image_size, image_size, 3), dtype=torch.float32).share_memory_()
+            self.free_q = ctx.Queue(maxsize=slots)
+            self.q = ctx.Queue(maxsize=slots + self.n_workers)
+            for i in range(slots):
+                self.free_q.put(i)
+            self.stop_event = ctx.Event()
+            for t in range(self.n_workers):
+                p = ctx.Process(target=_process_main, daemon=True,
+                                args=(t, files[t::self.n_workers], seed + 1000 * rank + t, shuffle_buffer, train, repeat,
+                                      image_size, self.ring, self.free_q, self.q, self.stop_event))
+                p.start()
+                self.workers.append(p)
+        else:
+            self.q = queue.Queue(maxsize=max(4 * batch_size, 64))
+            self.stop_event = threading.Event()
 
-    def _emit(self, item) -> bool:
-        while not self.stop:
-            try:
-                self.q.put(item, timeout=0.1)
-                return True
-            except queue.Full:
-                continue
-        return False
+            def emit(item) -> bool:
+                while not self.stop_event.is_set():
+                    try:
+                        self.q.put(item, timeout=0.1)
+                        return True
+                    except queue.Full:
+                        continue
+                return False
 
-    def _worker(self, tid: int, files: List[str], seed: int, shuffle_buffer: int):
-        rng = random.Random(seed)
-        buf: list = []
-        try:
-            while not self.stop:
-                order = list(files)
-                if self.train:
-                    rng.shuffle(order)
-                for path in order:
-                    for rec in read_records(path):
-                        if self.stop:
-                            return
-                        if self.train:
-                            buf.append(rec)
-                            if len(buf) < shuffle_buffer:
-                                continue
-                            rec = buf.pop(rng.randrange(len(buf)))
-                        image, label, bbox, _ = parse_example_proto(rec)
-                        x = image_preprocessing(image, bbox, self.train, tid, rng, self.size)
-                        if not self._emit((x, label)):
-                            return
-                if not self.repeat:
-                    break
-            while buf and not self.stop:
-                image, label, bbox, _ = parse_example_proto(buf.pop())
-                if not self._emit((image_preprocessing(image, bbox, self.train, tid, rng, self.size), label)):
-                    return
-        finally:
-            with self.lock:
-                self.done += 1
-                if self.done == self.n_threads:
-                    self._emit(None)
+            for t in range(self.n_workers):
+                th = threading.Thread(target=_worker_loop, daemon=True,
+                                      args=(t, files[t::self.n_workers], seed + 1000 * rank + t, shuffle_buffer, train,
+                                            repeat, image_size, emit, self.stop_event.is_set))
+                th.start()
+                self.workers.append(th)
+        _LIVE_BATCHERS.add(self)
 
     def __iter__(self):
         return self
 
+    def _get(self):
+        """Next item, or None when every worker has finished; notices dead worker processes instead of hanging."""
+        while True:
+            try:
+                item = self.q.get(timeout=1.0)
+            except queue.Empty:
+                if self.mode == "process" and not any(p.is_alive() for p in self.workers) and self.q.empty():
+                    return None
+                continue
+            if item is None:
+                self.finished += 1
+                if self.finished < self.n_workers:
+                    continue
+            return item
+
     def __next__(self):
-        if getattr(self, "_exhausted", False):
+        if self._exhausted:
             raise StopIteration
         xs, ys = [], []
         while len(xs) < self.bs:
-            item = self.q.get()
+            item = self._get()
             if item is None:
                 self._exhausted = True
                 if not xs:
@@ -256,14 +414,39 @@ class ImagenetBatches:
                 break
             xs.append(item[0])
             ys.append(item[1])
-        x = torch.stack(xs)
+        if self.mode == "process":
+            x = self.ring[torch.tensor(xs, dtype=torch.int64)]        # gather out of the ring, then free the slots
+            for slot in xs:
+                self.free_q.put(slot)
+        else:
+            x = torch.stack(xs)
         y = torch.tensor(ys, dtype=torch.int64)
         if self.pin:
             x, y = x.pin_memory(), y.pin_memory()
         return x, y
 
     def close(self):
-        self.stop = True
+        if self._closed:
+            return
+        self._closed = True
+        self.stop_event.set()
+        if self.mode == "process":
+            for p in self.workers:
+                p.join(timeout=0.5)
+            for p in self.workers:
+                if p.is_alive():
+                    p.terminate()
+            for q_ in (self.q, self.free_q):
+                q_.cancel_join_thread()
+                q_.close()
+        else:
+            try:                                  # unblock producers waiting on a full queue, then let them finish
+                while True:
+                    self.q.get_nowait()
+            except queue.Empty:
+                pass
+            for th in self.workers:
+                th.join(timeout=1.0)
 
 
 def distorted_inputs(dataset: Dataset, batch_size: int = BATCH_SIZE, image_size: int = IMAGE_SIZE,

@@ -443,3 +443,44 @@ def test_cifar_fused_distortion_matches_stepwise_and_stream_is_thread_count_inde
     other = cifar10.distorted_inputs(str(tmp_path), 16, 32, seed=4, num_threads=1)
     assert not torch.equal(next(other)[1], ya)
     other.close()
+
+
+def test_imagenet_pipeline_process_workers_and_fast_colour_math(tmp_path):
+    """Process workers hand images over through the shared-memory ring: a finite pass delivers every image exactly
+    once, shutting down mid-stream leaves no worker behind; the planar NumPy colour distortion equals the tensor
+    formulas it replaced."""
+    import random
+    from distributed_tensorflow_models_b200.data import imagenet
+    synthetic.write_imagenet_tfrecords(str(tmp_path), "train", num_images=40, num_shards=4, size=48)
+    ds = imagenet.ImagenetData("train", str(tmp_path))
+    it = imagenet.ImagenetBatches(ds, 16, True, 32, 4, repeat=False, workers="process", seed=1)
+    assert it.mode == "process"
+    batches = list(it)
+    it.close()
+    assert sum(b[0].shape[0] for b in batches) == 40 and batches[0][0].shape == (16, 32, 32, 3)
+    assert all(float(b[0].abs().max()) <= 1.0 for b in batches)
+    it = imagenet.distorted_inputs(ds, 8, image_size=32, num_preprocess_threads=4, workers="process")
+    next(it)
+    it.close()
+    assert not any(w.is_alive() for w in it.workers)
+    with pytest.raises(ValueError):
+        imagenet.ImagenetBatches(ds, 8, True, 32, 2, workers="fibers")
+    # colour math: NumPy planes vs the torch HSV formulas, both orderings
+    def stepwise(img, tid, rng):
+        def brightness(x): return x + rng.uniform(-32.0 / 255.0, 32.0 / 255.0)
+        def saturation(x):
+            hsv = imagenet.rgb_to_hsv(x.clamp(0, 1)); hsv[..., 1] = (hsv[..., 1] * rng.uniform(0.5, 1.5)).clamp(0, 1)
+            return imagenet.hsv_to_rgb(hsv)
+        def hue(x):
+            hsv = imagenet.rgb_to_hsv(x.clamp(0, 1)); hsv[..., 0] = (hsv[..., 0] + rng.uniform(-0.2, 0.2)) % 1.0
+            return imagenet.hsv_to_rgb(hsv)
+        def contrast(x):
+            m = x.mean(dim=(0, 1), keepdim=True); return (x - m) * rng.uniform(0.5, 1.5) + m
+        for fn in ((brightness, saturation, hue, contrast) if tid % 2 == 0 else (brightness, contrast, saturation, hue)):
+            img = fn(img)
+        return img.clamp(0.0, 1.0)
+    img = torch.rand(37, 41, 3, generator=torch.Generator().manual_seed(0))
+    for tid in (0, 1):
+        a = stepwise(img.clone(), tid, random.Random(7))
+        b = imagenet.distort_color(img.clone(), tid, random.Random(7))
+        assert float((a - b).abs().max()) < 1e-5
