@@ -434,8 +434,10 @@ class ImagenetBatches:
             for p in self.workers:
                 p.join(timeout=0.5)
             for p in self.workers:
-                if p.is_alive():
+                if p.is_alive():              # e.g. still importing, or blocked on a full pipe: no cooperation needed
                     p.terminate()
+            for p in self.workers:
+                p.join(timeout=2.0)
             for q_ in (self.q, self.free_q):
                 q_.cancel_join_thread()
                 q_.close()
