@@ -68,4 +68,8 @@ def main(argv=None) -> int:
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    try:
+        sys.exit(main())
+    except BrokenPipeError:          # `... | head`
+        sys.stderr.close()
+        sys.exit(0)
