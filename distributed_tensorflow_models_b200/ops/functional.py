@@ -102,14 +102,48 @@ def conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None
     return y.permute(0, 2, 3, 1)
 
 
+def _space_to_batch(x: torch.Tensor, rate: int, ph: Tuple[int, int], pw: Tuple[int, int]):
+    """Zero-pad NHWC ``x`` by (ph, pw) (plus what rounds both extents up to a multiple of ``rate``) and move the
+    ``rate x rate`` sampling phases into the batch: ``[N, H, W, C] -> [rate*rate*N, H'/rate, W'/rate, C]``
+    (tf.space_to_batch, which is how tf.nn.atrous_conv2d / convolution(dilation_rate=) lower a dilated filter)."""
+    n, h, wd, c = x.shape
+    hp, wp = h + ph[0] + ph[1], wd + pw[0] + pw[1]
+    eh, ew = (-hp) % rate, (-wp) % rate
+    x = F.pad(x, (0, 0, pw[0], pw[1] + ew, ph[0], ph[1] + eh))
+    hq, wq = (hp + eh) // rate, (wp + ew) // rate
+    x = x.reshape(n, hq, rate, wq, rate, c).permute(2, 4, 0, 1, 3, 5)
+    return x.reshape(rate * rate * n, hq, wq, c).contiguous()
+
+
+def _batch_to_space(y: torch.Tensor, rate: int, n: int, oh: int, ow: int) -> torch.Tensor:
+    """Inverse of :func:`_space_to_batch` on the convolution's output, cropped to ``oh x ow``."""
+    _, hq, wq, c = y.shape
+    y = y.reshape(rate, rate, n, hq, wq, c).permute(2, 3, 0, 4, 1, 5).reshape(n, hq * rate, wq * rate, c)
+    return y[:, :oh, :ow, :].contiguous()
+
+
+def _by_phases(conv, x, w, bias, rate: int, ph, pw, oh: int, ow: int) -> torch.Tensor:
+    """A stride-1 convolution dilated by ``rate`` as one dense VALID ``conv`` over the stacked sampling phases."""
+    yb = conv(_space_to_batch(x, rate, ph, pw), w, bias, 1, "VALID")
+    return _batch_to_space(yb, rate, x.shape[0], oh, ow)
+
+
 def atrous_conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], rate: int,
                   padding: str = "SAME") -> torch.Tensor:
-    """Dilated stride-1 convolution (slim.conv2d(rate=...) under ``output_stride``, vgg/nets/resnet_utils.py:123)."""
-    if use_native(x):
-        raise NotImplementedError("native convolution: rate > 1 (output_stride) is not implemented")
+    """Dilated stride-1 convolution (slim.conv2d(rate=...) under ``output_stride``, vgg/nets/resnet_utils.py:123).
+
+    Native path: the dilated filter samples every ``rate``-th pixel, so each of the ``rate x rate`` sampling
+    phases of the padded image is an ordinary dense VALID convolution.  The phases are stacked into the batch
+    (:func:`_space_to_batch`), run through the tcgen05 implicit-GEMM kernel as ONE stride-1 convolution with a
+    ``rate^2`` times larger GEMM M, and interleaved back.  The weights are used as they are (no zero-stuffed
+    ``(k-1)*rate+1`` filter), and autograd carries dgrad / wgrad through the same two permutations."""
     co, r, s, ci = w.shape
     er, es = (r - 1) * rate + 1, (s - 1) * rate + 1
     oh, ow, ph, pw = resolve_padding(x.shape[1], x.shape[2], er, es, (1, 1), padding)
+    if use_native(x):
+        if rate == 1:
+            return conv2d(x, w, bias, 1, (ph, pw))
+        return _by_phases(conv2d, x, w, bias, rate, ph, pw, oh, ow)
     xn = F.pad(x.permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))
     y = F.conv2d(xn, w.permute(0, 3, 1, 2), bias, dilation=rate)
     return y.permute(0, 2, 3, 1)
@@ -136,7 +170,10 @@ def depthwise_conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tens
     oh, ow, ph, pw = resolve_padding(h, wd, er, es, stride, padding)
     if use_native(x):
         if rate != 1:
-            raise NotImplementedError("native depthwise convolution: rate > 1 is not implemented")
+            # same lowering as atrous_conv2d: sampling phases into the batch, dense depthwise kernel, back
+            if stride != (1, 1):
+                raise NotImplementedError("depthwise convolution: rate > 1 needs stride 1 (as in TensorFlow)")
+            return _by_phases(depthwise_conv2d, x, w, bias, rate, ph, pw, oh, ow)
         from . import zoo_native
         return zoo_native.depthwise_conv2d(x, w, bias, stride, (ph[0], pw[0]), (oh, ow))
     xn = F.pad(x.permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))

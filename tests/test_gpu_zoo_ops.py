@@ -85,6 +85,21 @@ def test_depthwise_conv2d(cfg):
         _both(lambda x_, w_: Fn.depthwise_conv2d(x_, w_, None, s, pad), [x, wt], FP32_TOL)
 
 
+@pytest.mark.parametrize("cfg", [
+    # n, h, w, c, c_out, k, rate, padding
+    (2, 28, 28, 32, 64, 3, 2, "SAME"),       # ResNet / MobileNet output_stride=16: last stage dilated by 2
+    (2, 17, 19, 16, 32, 3, 4, "SAME"),       # output_stride=8; extents that are not multiples of the rate
+    (2, 21, 23, 16, 16, 3, 3, "VALID"),
+])
+def test_atrous_conv2d_and_depthwise(cfg):
+    """rate > 1: sampling phases stacked into the batch, then the dense tcgen05 / depthwise kernels."""
+    n, h, w, c, co, k, rate, pad = cfg
+    x, wt, b = _r(n, h, w, c, seed=1), _r(co, k, k, c, seed=2, scale=0.1), _r(co, seed=3)
+    _both(lambda x_, w_, b_: Fn.atrous_conv2d(x_, w_, b_, rate, pad), [x, wt, b], TF32_TOL)
+    dw = _r(k, k, c, 1, seed=4, scale=0.3)
+    _both(lambda x_, w_: Fn.depthwise_conv2d(x_, w_, None, 1, pad, rate=rate), [x, dw], FP32_TOL)
+
+
 @pytest.mark.parametrize("kind", ["relu6", "leaky_relu", "tanh", "sigmoid"])
 @pytest.mark.parametrize("shape", [(3, 7, 5, 13), (2, 16, 16, 32)])
 def test_activations(kind, shape):

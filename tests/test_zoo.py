@@ -322,6 +322,33 @@ def test_depthwise_and_separable_conv_against_grouped_convolution():
         ("sep/depthwise_weights", (3, 3, 6, 2)), ("sep/pointwise_weights", (1, 1, 12, 7)), ("sep/biases", (7,))]
 
 
+@pytest.mark.parametrize("cfg", [(2, 17, 19, 8, 12, 3, 2, "SAME"), (1, 16, 16, 4, 4, 3, 4, "SAME"),
+                                 (2, 21, 13, 4, 6, 3, 3, "VALID"), (2, 9, 9, 4, 6, 1, 2, "SAME")])
+def test_dilated_convolution_as_one_dense_convolution_over_sampling_phases(cfg):
+    """The native path of slim.conv2d(rate=) / separable_conv2d(rate=): phases into the batch, dense VALID
+    convolution, phases back — equal to the dilated convolution in value and in both gradients."""
+    n, h, w, c, co, k, rate, pad = cfg
+    torch.manual_seed(3)
+    x = torch.randn(n, h, w, c, requires_grad=True)
+    wt, b, dw = torch.randn(co, k, k, c, requires_grad=True), torch.randn(co), torch.randn(k, k, c, 2)
+    er = (k - 1) * rate + 1
+    oh, ow, ph, pw = Fn.resolve_padding(h, w, er, er, (1, 1), pad)
+    y0 = Fn.atrous_conv2d(x, wt, b, rate, pad)
+    y1 = Fn._by_phases(Fn.conv2d, x, wt, b, rate, ph, pw, oh, ow)
+    assert y0.shape == y1.shape == (n, oh, ow, co)
+    assert torch.allclose(y0, y1, atol=1e-5)
+    g = torch.randn_like(y0)
+    for a, e in zip(torch.autograd.grad(y1, [x, wt], g), torch.autograd.grad(y0, [x, wt], g)):
+        assert torch.allclose(a, e, atol=1e-3, rtol=1e-4)
+    d0 = Fn.depthwise_conv2d(x, dw, None, 1, pad, rate=rate)
+    d1 = Fn._by_phases(Fn.depthwise_conv2d, x, dw, None, rate, ph, pw, oh, ow)
+    assert torch.allclose(d0, d1, atol=1e-5)
+    # round trip of the two permutations alone
+    xb = Fn._space_to_batch(x, rate, (0, 0), (0, 0))
+    assert xb.shape[0] == n * rate * rate
+    assert torch.equal(Fn._batch_to_space(xb, rate, n, h, w), x)
+
+
 @pytest.mark.parametrize("k,s,pad,h", [(4, 2, "SAME", 5), (3, 2, "SAME", 5), (4, 1, "VALID", 1), (3, 2, "VALID", 4)])
 def test_conv2d_transpose_is_the_adjoint_of_conv2d(k, s, pad, h):
     torch.manual_seed(1)
