@@ -365,6 +365,129 @@ act_bwd_kernel(const float* __restrict__ ref, const float* __restrict__ dy, floa
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Fake quantisation (tf.contrib.quantize, used by vgg/nets/mobilenet_v1_train.py:135-139 / mobilenet_v1_eval.py:126):
+// FakeQuantWithMinMaxVars semantics.  The [min, max] range lives in device memory (range[0], range[1]) and is
+// "nudged" so that 0.0 falls on a quantisation step; the forward rounds onto the 2^bits (narrow: 2^bits - 1)
+// steps of the nudged range, the backward passes the gradient where x lies inside it (straight-through).
+// gate[0] == 0 switches the op to the identity (quant_delay not yet reached) without a host decision, so the
+// step stays capturable.  A degenerate range (max <= min) is the identity too.
+//   minmax  : batch min / max of a tensor, atomics on the float bit patterns into mm[0] (init +inf), mm[1] (-inf)
+//   range   : decay < 0  -> range = batch (LastValueQuantize, weights)
+//             otherwise  -> range = range*decay + batch*(1-decay) with the batch range widened to contain 0
+//                           (MovingAvgQuantize, activations); mm is reset to (+inf, -inf) for the next call
+// ---------------------------------------------------------------------------------------------------------
+struct QuantSteps { float nmin, nmax, scale, inv_scale; bool on; };
+
+__device__ __forceinline__ QuantSteps quant_steps(const float* __restrict__ range, const float* __restrict__ gate,
+                                                  int bits, int narrow) {
+  QuantSteps q;
+  const float mn = __ldg(range), mx = __ldg(range + 1);
+  const float qmin = narrow ? 1.f : 0.f, qmax = (float)((1 << bits) - 1);
+  q.on = (gate == nullptr || __ldg(gate) != 0.f) && (mx > mn);
+  q.scale = (mx - mn) / (qmax - qmin);
+  q.on = q.on && (q.scale > 0.f);
+  const float zp_from_min = qmin - mn / q.scale;
+  const float zp = zp_from_min < qmin ? qmin : (zp_from_min > qmax ? qmax : roundf(zp_from_min));
+  q.nmin = (qmin - zp) * q.scale;
+  q.nmax = (qmax - zp) * q.scale;
+  q.inv_scale = 1.f / q.scale;
+  return q;
+}
+__device__ __forceinline__ float fq_f(float v, const QuantSteps& q) {
+  const float c = fminf(fmaxf(v, q.nmin), q.nmax);
+  return floorf((c - q.nmin) * q.inv_scale + 0.5f) * q.scale + q.nmin;
+}
+
+__global__ void __launch_bounds__(256)
+fake_quant_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, const float* __restrict__ range,
+                      const float* __restrict__ gate, int bits, int narrow) {
+  const QuantSteps q = quant_steps(range, gate, bits, narrow);
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < n4; i += stride) {
+    float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    if (q.on) { v.x = fq_f(v.x, q); v.y = fq_f(v.y, q); v.z = fq_f(v.z, q); v.w = fq_f(v.w, q); }
+    reinterpret_cast<float4*>(y)[i] = v;
+  }
+  for (long long i = (n4 << 2) + blockIdx.x * 256LL + threadIdx.x; i < n; i += stride)
+    y[i] = q.on ? fq_f(x[i], q) : x[i];
+}
+
+__global__ void __launch_bounds__(256)
+fake_quant_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx, long long n,
+                      const float* __restrict__ range, const float* __restrict__ gate, int bits, int narrow) {
+  const QuantSteps q = quant_steps(range, gate, bits, narrow);
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < n4; i += stride) {
+    const float4 r = __ldg(reinterpret_cast<const float4*>(x) + i);
+    float4 g = __ldg(reinterpret_cast<const float4*>(dy) + i);
+    if (q.on) {
+      g.x = (r.x >= q.nmin && r.x <= q.nmax) ? g.x : 0.f; g.y = (r.y >= q.nmin && r.y <= q.nmax) ? g.y : 0.f;
+      g.z = (r.z >= q.nmin && r.z <= q.nmax) ? g.z : 0.f; g.w = (r.w >= q.nmin && r.w <= q.nmax) ? g.w : 0.f;
+    }
+    reinterpret_cast<float4*>(dx)[i] = g;
+  }
+  for (long long i = (n4 << 2) + blockIdx.x * 256LL + threadIdx.x; i < n; i += stride)
+    dx[i] = (!q.on || (x[i] >= q.nmin && x[i] <= q.nmax)) ? dy[i] : 0.f;
+}
+
+// float min / max through integer atomics on the bit patterns (any mix of signs; -0.0 is canonicalised first)
+__device__ __forceinline__ void atomic_min_f(float* a, float v) {
+  v += 0.f;
+  if (v >= 0.f) atomicMin(reinterpret_cast<int*>(a), __float_as_int(v));
+  else atomicMax(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float* a, float v) {
+  v += 0.f;
+  if (v >= 0.f) atomicMax(reinterpret_cast<int*>(a), __float_as_int(v));
+  else atomicMin(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
+}
+
+__global__ void __launch_bounds__(256)
+minmax_kernel(const float* __restrict__ x, long long n, float* __restrict__ mm) {
+  float lo = INFINITY, hi = -INFINITY;
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < n4; i += stride) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
+    hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+  }
+  for (long long i = (n4 << 2) + blockIdx.x * 256LL + threadIdx.x; i < n; i += stride) {
+    lo = fminf(lo, x[i]); hi = fmaxf(hi, x[i]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  __shared__ float s_lo[8], s_hi[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { lo = fminf(lo, s_lo[w]); hi = fmaxf(hi, s_hi[w]); }
+    if (lo <= hi) { atomic_min_f(mm, lo); atomic_max_f(mm + 1, hi); }
+  }
+}
+
+__global__ void quant_range_kernel(float* __restrict__ mm, float* __restrict__ range, float decay) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const float lo = mm[0], hi = mm[1];
+    if (lo <= hi) {
+      if (decay < 0.f) { range[0] = lo; range[1] = hi; }
+      else {
+        range[0] = range[0] * decay + fminf(lo, 0.f) * (1.f - decay);
+        range[1] = range[1] * decay + fmaxf(hi, 0.f) * (1.f - decay);
+      }
+    }
+    mm[0] = INFINITY; mm[1] = -INFINITY;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Instance normalisation: per (image, channel) statistics over H*W.
 //   reduce:  sums[n][0][c] += sum_p a ,  sums[n][1][c] += sum_p a*b
 //            forward  : a = x,  b = x           -> sum x, sum x^2
@@ -800,6 +923,42 @@ extern "C" int dtf_pad_bwd(const float* dy, float* dx, int N, int H, int W, int 
   DTF_CHECK(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)N * H * W * C, st));
   const unsigned total = (unsigned)((unsigned long long)N * g.OH * g.OW * C);
   pad_kernel<true><<<grid_for(total), 256, 0, st>>>(g, dy, dx, total);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_fake_quant_fwd(const float* x, float* y, long long n, const float* range, const float* gate,
+                                  int bits, int narrow_range, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(bits >= 2 && bits <= 16, "fake quantisation: 2 to 16 bits");
+  DTF_REQUIRE(aligned16(x) && aligned16(y), "fake-quant kernels need 16-byte aligned tensors");
+  if (n <= 0) return 0;
+  fake_quant_fwd_kernel<<<grid_for((unsigned long long)(n + 3) / 4), 256, 0, st>>>(x, y, n, range, gate, bits,
+                                                                                   narrow_range);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_fake_quant_bwd(const float* x, const float* dy, float* dx, long long n, const float* range,
+                                  const float* gate, int bits, int narrow_range, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(bits >= 2 && bits <= 16, "fake quantisation: 2 to 16 bits");
+  DTF_REQUIRE(aligned16(x) && aligned16(dy) && aligned16(dx), "fake-quant kernels need 16-byte aligned tensors");
+  if (n <= 0) return 0;
+  fake_quant_bwd_kernel<<<grid_for((unsigned long long)(n + 3) / 4), 256, 0, st>>>(x, dy, dx, n, range, gate, bits,
+                                                                                   narrow_range);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_quant_range_update(const float* x, long long n, float* mm, float* range, float decay,
+                                      void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(aligned16(x), "min/max kernel needs a 16-byte aligned tensor");
+  if (n <= 0) return 0;
+  minmax_kernel<<<grid_for((unsigned long long)(n + 3) / 4, 256, 4), 256, 0, st>>>(x, n, mm);
+  DTF_CHECK(cudaGetLastError());
+  quant_range_kernel<<<1, 32, 0, st>>>(mm, range, decay);
   DTF_CHECK(cudaGetLastError());
   return 0;
 }

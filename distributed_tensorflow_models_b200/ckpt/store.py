@@ -107,6 +107,10 @@ def collect_tensors(store: VariableStore, slot_flats: Optional[Dict[str, torch.T
     for v in store.all():
         if v.name == "global_step":
             continue
+        if v.tf_layout == "minmax":          # quantisation range: TensorFlow keeps two scalars, .../min and .../max
+            base, t = v.name.rsplit("/", 1)[0], v.tensor.detach().cpu().numpy()
+            out[base + "/min"], out[base + "/max"] = np.asarray(t[0]), np.asarray(t[1])
+            continue
         out[v.name] = v.to_tf().cpu().numpy()
     if slot_flats and layout is not None:
         for slot, flat in slot_flats.items():
@@ -156,6 +160,15 @@ def restore(store: VariableStore, tensors: Dict[str, np.ndarray], use_ema: bool 
     done = []
     for v in store.get_variables_to_restore():
         if v.name == "global_step":
+            continue
+        if v.tf_layout == "minmax":
+            base = v.name.rsplit("/", 1)[0]
+            if base + "/min" in tensors and base + "/max" in tensors:
+                with torch.no_grad():
+                    v.tensor.copy_(torch.tensor([float(tensors[base + "/min"]), float(tensors[base + "/max"])]))
+                done.append(v.name)
+            elif strict:
+                raise KeyError(f"checkpoint has no tensors named {base}/min, {base}/max")
             continue
         key = v.name
         if use_ema and (v.name + EMA_SUFFIX) in tensors:

@@ -150,6 +150,11 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
     ap.add_argument("--num_classes", type=int, default=None, help="zoo networks only (default 1001)")
     ap.add_argument("--weight_decay", type=float, default=None,
                     help="zoo networks only: L2 weight of the network's arg scope (default: the scope's own)")
+    ap.add_argument("--quantize", type=_tf_bool, nargs="?", const=True, default=False,
+                    help="quantisation-aware training / evaluation: 8-bit fake-quantised weights and activations with "
+                         "folded batch norm (vgg/nets/mobilenet_v1_train.py:40,135-139, mobilenet_v1_eval.py:38,126)")
+    ap.add_argument("--quant_delay", type=int, default=0,
+                    help="global step at which fake quantisation switches on (the ranges are tracked from step 0)")
     ap.add_argument("--num_preprocess_threads", type=int, default=4)
     ap.add_argument("--num_readers", type=int, default=4)
     ap.add_argument("--input_queue_memory_factor", type=int, default=16)

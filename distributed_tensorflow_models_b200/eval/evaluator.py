@@ -100,7 +100,8 @@ def evaluate(args) -> Optional[dict]:
     device = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # train.sh runs eval on CPU
     trainer = Trainer(TrainSetup(model=args.model, batch_size=batch_size, resnet_size=args.resnet_size,
                                  ref_compat=args.ref_compat, cuda_graph=False, image_size=args.image_size,
-                                 num_classes=args.num_classes, weight_decay=args.weight_decay), device=device)
+                                 num_classes=args.num_classes, weight_decay=args.weight_decay,
+                                 quantize=bool(args.quantize)), device=device)
     batches = _eval_batches(args, spec, batch_size)
     os.makedirs(args.eval_dir, exist_ok=True)
     summaries = EventFileWriter(args.eval_dir)       # TensorBoard event file, as the reference's FileWriter(eval_dir)

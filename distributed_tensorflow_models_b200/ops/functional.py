@@ -364,6 +364,69 @@ def sigmoid(x: torch.Tensor) -> torch.Tensor:
     return _act(x, "sigmoid")
 
 
+# ----------------------------------------------------------------------------------------------
+# fake quantisation (tf.contrib.quantize behind --quantize)
+# ----------------------------------------------------------------------------------------------
+def nudged_range(mn: torch.Tensor, mx: torch.Tensor, bits: int, narrow: bool):
+    """TensorFlow's range nudging: move [min, max] so that 0.0 is exactly one of the quantisation steps.
+    -> (nudged_min, nudged_max, step)"""
+    qmin, qmax = (1.0 if narrow else 0.0), float(2 ** bits - 1)
+    scale = (mx - mn) / (qmax - qmin)
+    zp = qmin - mn / scale
+    # std::round: halves away from zero (torch.round is half-to-even)
+    zp_r = torch.sign(zp) * torch.floor(zp.abs() + 0.5)
+    zp_n = torch.where(zp < qmin, torch.full_like(zp, qmin), torch.where(zp > qmax, torch.full_like(zp, qmax), zp_r))
+    return (qmin - zp_n) * scale, (qmax - zp_n) * scale, scale
+
+
+class _FakeQuantRef(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, rng, gate, bits, narrow):
+        mn, mx = rng[0], rng[1]
+        nmin, nmax, scale = nudged_range(mn, mx, bits, narrow)
+        on = (mx > mn) & (scale > 0)
+        if gate is not None:
+            on = on & (gate.reshape(()) != 0)
+        c = torch.minimum(torch.maximum(x, nmin), nmax)
+        q = torch.floor((c - nmin) * (1.0 / scale) + 0.5) * scale + nmin
+        inside = (x >= nmin) & (x <= nmax)
+        ctx.save_for_backward(inside | ~on)
+        return torch.where(on, q, x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        return dy * mask, None, None, None, None
+
+
+def fake_quant(x: torch.Tensor, rng: torch.Tensor, gate: Optional[torch.Tensor] = None, bits: int = 8,
+               narrow_range: bool = False) -> torch.Tensor:
+    """tf.fake_quant_with_min_max_vars: round ``x`` onto the ``2**bits`` (narrow: one fewer) steps of the nudged
+    range ``rng = [min, max]``; the gradient passes where ``x`` lies inside that range.  ``gate`` (a scalar
+    tensor): 0 makes the op the identity — the device-side form of ``quant_delay``
+    (vgg/nets/mobilenet_v1_train.py:66-74,135-139)."""
+    if use_native(x) and x.dtype == torch.float32:
+        from . import zoo_native
+        return zoo_native.fake_quant(x, rng, gate, bits, narrow_range)
+    return _FakeQuantRef.apply(x, rng, gate, bits, narrow_range)
+
+
+@torch.no_grad()
+def quant_range_update(x: torch.Tensor, rng: torch.Tensor, decay: float, scratch: Optional[torch.Tensor] = None):
+    """In place: ``rng <- [min(x), max(x)]`` when ``decay < 0`` (tf.contrib.quantize LastValueQuantize, weights),
+    else ``rng <- rng*decay + [min(min(x), 0), max(max(x), 0)]*(1-decay)`` (MovingAvgQuantize, activations)."""
+    if use_native(x) and x.dtype == torch.float32:
+        from . import zoo_native
+        assert scratch is not None
+        return zoo_native.quant_range_update(x, rng, decay, scratch)
+    lo, hi = torch.aminmax(x.detach())
+    if decay < 0:
+        rng[0], rng[1] = lo, hi
+    else:
+        rng[0] = rng[0] * decay + torch.clamp(lo, max=0.0) * (1 - decay)
+        rng[1] = rng[1] * decay + torch.clamp(hi, min=0.0) * (1 - decay)
+
+
 def instance_norm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor],
                   eps: float = 1e-6) -> torch.Tensor:
     """tf.contrib.layers.instance_norm: per-image, per-channel moments over H, W (vgg/nets/cyclegan.py:47-60)."""

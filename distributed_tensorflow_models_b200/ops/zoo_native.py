@@ -107,6 +107,43 @@ def activation(x, kind: str, alpha: float = 0.2):
 
 
 # ---------------------------------------------------------------------------------------------------
+# fake quantisation (--quantize)
+# ---------------------------------------------------------------------------------------------------
+class _FakeQuantFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, rng, gate, bits, narrow):
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        nat.check(nat.lib().dtf_fake_quant_fwd(_p(x), _p(y), C.c_longlong(x.numel()), _p(rng), _p(gate), int(bits),
+                                               int(bool(narrow)), nat.stream_ptr()), "dtf_fake_quant_fwd")
+        ctx.save_for_backward(x, rng, gate)
+        ctx.cfg = (int(bits), int(bool(narrow)))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, rng, gate = ctx.saved_tensors
+        bits, narrow = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty_like(dy)
+        nat.check(nat.lib().dtf_fake_quant_bwd(_p(x), _p(dy), _p(dx), C.c_longlong(dy.numel()), _p(rng), _p(gate),
+                                               bits, narrow, nat.stream_ptr()), "dtf_fake_quant_bwd")
+        return dx, None, None, None, None
+
+
+def fake_quant(x, rng, gate, bits: int, narrow: bool):
+    return _FakeQuantFn.apply(x, rng, gate, bits, narrow)
+
+
+def quant_range_update(x, rng, decay: float, mm) -> None:
+    """Fold min / max of ``x`` into ``rng`` (two floats) in place; ``decay < 0`` assigns, else moving average.
+    ``mm``: two floats of scratch holding {+inf, -inf}; the call hands it back in that state."""
+    x = x.detach().contiguous()
+    nat.check(nat.lib().dtf_quant_range_update(_p(x), C.c_longlong(x.numel()), _p(mm), _p(rng), C.c_float(decay),
+                                               nat.stream_ptr()), "dtf_quant_range_update")
+
+
+# ---------------------------------------------------------------------------------------------------
 # instance norm
 # ---------------------------------------------------------------------------------------------------
 class _InstNormFn(torch.autograd.Function):

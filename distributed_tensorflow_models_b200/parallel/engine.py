@@ -55,6 +55,8 @@ class TrainSetup:
     image_size: Optional[int] = None  # zoo networks: input resolution / classes / arg-scope weight decay
     num_classes: Optional[int] = None
     weight_decay: Optional[float] = None
+    quantize: bool = False            # fake-quantised weights / activations with folded batch norm (slim/quantize.py)
+    quant_delay: int = 0              # global step at which the fake-quant ops switch on
 
     def resolved(self) -> "TrainSetup":
         p = self.preset or preset_for(self.model, self.mode)
@@ -141,6 +143,9 @@ class Trainer:
         self.store.fuse_bn = bool(self.setup.fuse_bn)
         self.forward = build_forward(self.setup)
         self.prefix = _SCOPE_PREFIX.get(self.setup.model, "")
+        if self.setup.quantize:
+            from ..slim.quantize import QuantState
+            self.store.quant = QuantState(quant_delay=int(self.setup.quant_delay))
         # ---- build pass: create variables (CPU, deterministic from the seed), then move ----
         with torch.no_grad():
             x0 = torch.zeros(2, spec.image_size, spec.image_size, spec.channels)
@@ -148,6 +153,9 @@ class Trainer:
             self._run_forward(x0, y0, True, build=True)
         self.store.freeze()
         self.store.to(self.device)
+        if self.setup.quantize:
+            # the quant_delay switch lives in device memory: flipping it needs no re-capture of the step graph
+            self.store.quant.gate = torch.zeros((), dtype=torch.float32, device=self.device)
         # ---- PS layout + optimiser -------------------------------------------------------------
         wd = self.p.weight_decay if self.p.decay_all_trainables else None
         owners = getattr(self.comm, "owners", self.comm.world)     # PS tasks (== workers in the SPMD transports)
@@ -169,6 +177,8 @@ class Trainer:
     def _run_forward(self, x, y, training, build=False):
         from ..ops import streams
         streams.set_branch_streams(self.setup.branch_streams and self.device.type == "cuda" and not build)
+        if self.setup.quantize:
+            self.store.quant.is_training = bool(training)
         with self.store.as_default():
             self.store.begin_forward()
             if self.prefix:
@@ -259,6 +269,8 @@ class Trainer:
         x = self.prepare_inputs(images)
         gs_before = self.comm.global_step()
         lr = self.learning_rate(gs_before)
+        if s.quantize:
+            self.store.quant.set_step(gs_before)
         scale = 1.0 if batch_size is None else float(batch_size) / float(s.batch_size)
         use_graph = s.cuda_graph and self.device.type == "cuda" and x.shape[0] == s.batch_size
         loss, logits = (self._fwd_bwd_graphed if use_graph else self._fwd_bwd)(x, labels)

@@ -23,6 +23,7 @@ import torch
 
 from ..ops import functional as Fn
 from . import losses
+from . import quantize as Q
 from . import variables as V
 from .scopes import add_arg_scope, current_arg_scope
 
@@ -144,6 +145,12 @@ def fc(inputs: torch.Tensor, num_units_out: int, activation: Optional[Callable] 
                        restore=restore, tf_layout="io", tf_shape=(nin, num_units_out), fan_in=nin,
                        fan_out=num_units_out)
         fuse_relu = _is_relu(activation)
+        quant = Q.current()
+        if quant is not None and batch_norm_params is None:
+            b = V.variable(biases_name, (num_units_out,), initializer=biases_initializer or V.constant_initializer(bias),
+                           trainable=trainable, restore=restore)
+            return Q.folded_layer(quant, lambda wq: Fn.linear(inputs, wq, None), w, b, num_units_out,
+                                  (num_units_out, 1), None, activation, trainable)
         if batch_norm_params is not None:
             y = Fn.linear(inputs, w, None)
             return batch_norm(y, is_training=is_training, trainable=trainable, restore=restore,
@@ -245,6 +252,16 @@ def _normalize_and_activate(y, normalizer_fn, normalizer_params, activation_fn, 
     return y
 
 
+def _merged_bn_params(normalizer_fn, normalizer_params) -> Optional[dict]:
+    """Batch-norm arguments in force for a layer: the enclosing ``arg_scope([batch_norm], ...)`` defaults, then the
+    layer's own ``normalizer_params``; None when the layer has no normaliser."""
+    if normalizer_fn is None:
+        return None
+    params = dict(current_arg_scope().get(batch_norm._dtf_arg_scope_key, {}))
+    params.update(normalizer_params or {})
+    return params
+
+
 @add_arg_scope
 def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", activation_fn=relu,
                   weights_initializer=None, biases_initializer=None, weights_regularizer=None, scope=None,
@@ -253,6 +270,26 @@ def convolution2d(inputs, num_outputs, kernel_size, stride=1, padding="SAME", ac
     ``normalizer_fn`` / ``rate`` throughout the zoo, e.g. vgg/nets/resnet_utils.py:123, mobilenet_v1.py:255)."""
     wd = getattr(weights_regularizer, "l2", 0.0) if weights_regularizer is not None else 0.0
     w_init = weights_initializer or V.xavier_initializer()
+    quant = Q.current()
+    if quant is not None and (normalizer_fn is None or normalizer_fn is batch_norm):
+        store = V.current_store()
+        kh, kw = _two(kernel_size)
+        cin = inputs.shape[-1]
+        with store.scope(scope, "Conv"):
+            w = V.variable("weights", (num_outputs, kh, kw, cin), initializer=w_init,
+                           regularizer=losses.l2_regularizer(wd) if wd > 0 else None, trainable=trainable,
+                           tf_layout="hwio", tf_shape=(kh, kw, cin, num_outputs), fan_in=kh * kw * cin,
+                           fan_out=kh * kw * num_outputs)
+            b = None
+            if normalizer_fn is None and use_bias:
+                b = V.variable("biases", (num_outputs,), initializer=biases_initializer or V.zeros_initializer(),
+                               trainable=trainable)
+            if rate != 1:
+                run = lambda wq: Fn.atrous_conv2d(inputs, wq, None, rate, padding)
+            else:
+                run = lambda wq: Fn.conv2d(inputs, wq, None, _two(stride), padding)
+            return Q.folded_layer(quant, run, w, b, num_outputs, (num_outputs, 1, 1, 1),
+                                  _merged_bn_params(normalizer_fn, normalizer_params), activation_fn, trainable)
     if (normalizer_fn is None or normalizer_fn is batch_norm) and rate == 1:
         bn_params, is_tr = None, True
         if normalizer_fn is not None:
@@ -313,6 +350,19 @@ def separable_convolution2d(inputs, num_outputs, kernel_size, depth_multiplier=1
         if normalizer_fn is None and use_bias:
             b = V.variable("biases", (cout,), initializer=biases_initializer or V.zeros_initializer(),
                            trainable=trainable)
+        quant = Q.current()
+        if quant is not None and (normalizer_fn is None or normalizer_fn is batch_norm):
+            bn = _merged_bn_params(normalizer_fn, normalizer_params)
+            run_dw = lambda wq: Fn.depthwise_conv2d(inputs, wq, None, _two(stride), padding, rate=rate)
+            if pw is None:
+                return Q.folded_layer(quant, run_dw, dw, b, cmid, (1, 1, cin, depth_multiplier), bn, activation_fn,
+                                      trainable)
+            # depthwise stage: weights only (no normaliser / activation of its own), then the quantised 1x1 layer
+            y = run_dw(Q.quantize_weights(quant, dw, quant.is_training if bn is None else bn.get("is_training", True),
+                                          "depthwise_weights_quant"))
+            run_pw = lambda wq: Fn.conv2d(y, wq, None, (1, 1), "VALID")
+            return Q.folded_layer(quant, run_pw, pw, b, cout, (cout, 1, 1, 1), bn, activation_fn, trainable,
+                                  weights_quant_name="pointwise_weights_quant")
         y = Fn.depthwise_conv2d(inputs, dw, b if pw is None else None, _two(stride), padding, rate=rate)
         if pw is not None:
             y = Fn.conv2d(y, pw, b, (1, 1), "VALID")

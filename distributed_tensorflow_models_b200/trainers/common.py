@@ -65,7 +65,8 @@ def make_setup(args, num_workers: int) -> TrainSetup:
                       placement=args.placement, seed=args.seed, initial_lr=args.initial_learning_rate,
                       epochs_per_decay=args.num_epochs_per_decay, decay_factor=args.learning_rate_decay_factor,
                       cuda_graph=bool(args.cuda_graph), preset=args.preset, image_size=args.image_size,
-                      num_classes=args.num_classes, weight_decay=args.weight_decay)
+                      num_classes=args.num_classes, weight_decay=args.weight_decay,
+                      quantize=bool(args.quantize), quant_delay=int(args.quant_delay))
 
 
 def make_batches(args, spec, rank: int, world: int):

@@ -8,8 +8,10 @@ The reference script's flags (``:31-54``) are accepted under their own names and
 ``--task`` -> ``--task_id``, ``--log_every_n_steps`` -> ``--log_every``; ``--depth_multiplier`` picks the registry
 network (1.0 / 0.75 / 0.5 / 0.25); ``--fine_tune_checkpoint`` restores that checkpoint's variables, resets the global
 step and drops the learning rate to 1e-4 (``:59-63,165-181``).  Optimiser, learning-rate schedule and loss are the
-script's own constants (``config.ZOO_PRESET``).  ``--quantize`` (fake-quantised training through
-``tf.contrib.quantize``) has no counterpart here: the framework trains in fp32 storage / tf32 multiplies only.
+script's own constants (``config.ZOO_PRESET``).  ``--quantize`` switches on quantisation-aware training
+(``slim/quantize.py``: 8-bit fake-quantised weights and activations, batch norm folded into the weights) with the
+script's delay: none when fine-tuning, 250000 steps when training from scratch (``:66-74,135-139``);
+``--quant_delay`` overrides it.
 """
 import argparse
 import sys
@@ -27,14 +29,13 @@ def translate(argv, for_eval: bool = False):
     ap.add_argument("--ps_tasks", type=int, default=0)
     ap.add_argument("--number_of_steps", type=int, default=None)
     ap.add_argument("--depth_multiplier", type=float, default=1.0)
-    ap.add_argument("--quantize", default="False")
+    ap.add_argument("--quantize", nargs="?", const="True", default="False")
     ap.add_argument("--fine_tune_checkpoint", default="")
     ap.add_argument("--checkpoint_dir", default="")
     ap.add_argument("--dataset_dir", default="")
     ap.add_argument("--log_every_n_steps", type=int, default=100)
     own, rest = ap.parse_known_args(argv)
-    if str(own.quantize).lower() in ("1", "true", "t", "yes"):
-        raise SystemExit("--quantize: quantisation-aware training is not part of this framework (fp32 / tf32 only)")
+    quantize = str(own.quantize).lower() in ("1", "true", "t", "yes", "")
     if own.depth_multiplier not in _NETS:
         raise SystemExit("--depth_multiplier must be one of %s" % sorted(_NETS))
     out = list(rest)
@@ -48,6 +49,10 @@ def translate(argv, for_eval: bool = False):
         out += ["--data_dir", own.dataset_dir]
     if "--image_size" not in " ".join(rest):
         out += ["--image_size", "224"]
+    if quantize:
+        out += ["--quantize", "True"]
+        if not for_eval and "--quant_delay" not in " ".join(rest):
+            out += ["--quant_delay", "0" if own.fine_tune_checkpoint else "250000"]
     if own.fine_tune_checkpoint and "--initial_learning_rate" not in " ".join(rest):
         out += ["--initial_learning_rate", "1e-4"]
     return out, _NETS[own.depth_multiplier], own.fine_tune_checkpoint

@@ -241,6 +241,17 @@ int dtf_resize_fwd(const float* x, float* y, int N, int H, int W, int C, int OH,
                    int align_corners, void* stream);
 int dtf_resize_bwd(const float* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int bilinear,
                    int align_corners, void* stream);
+/* Fake quantisation with TensorFlow's FakeQuantWithMinMaxVars semantics (tf.contrib.quantize rewrites behind
+ * --quantize, vgg/nets/mobilenet_v1_train.py:135-139, mobilenet_v1_eval.py:126).  range = {min, max} in device memory;
+ * gate (device float, may be NULL): 0 -> identity (quant_delay not reached).  Backward is straight-through inside
+ * the nudged range.  dtf_quant_range_update folds the min / max of x into range: decay < 0 assigns them (weights),
+ * otherwise range = range*decay + batch*(1-decay) with the batch range widened to contain 0 (activations).
+ * mm = two floats of scratch that must hold {+inf, -inf} before the first call; each call leaves them so. */
+int dtf_fake_quant_fwd(const float* x, float* y, long long n, const float* range, const float* gate, int bits,
+                       int narrow_range, void* stream);
+int dtf_fake_quant_bwd(const float* x, const float* dy, float* dx, long long n, const float* range, const float* gate,
+                       int bits, int narrow_range, void* stream);
+int dtf_quant_range_update(const float* x, long long n, float* mm, float* range, float decay, void* stream);
 /* spatial padding (top, bottom, left, right); mode 0 zeros, 1 reflect (tf.pad 'REFLECT') */
 int dtf_pad_fwd(const float* x, float* y, int N, int H, int W, int C, int pt, int pb, int pl, int pr, int mode,
                 void* stream);

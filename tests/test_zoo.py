@@ -422,8 +422,6 @@ def test_mobilenet_v1_train_eval_and_fine_tune_entry_points(tmp_path):
                                              "--number_of_steps=1"]) == 0
     assert ckpt.latest_checkpoint(d2).endswith("model.ckpt-1")
     with pytest.raises(SystemExit):
-        mobilenet_v1_train.main(common + ["--quantize=True"])
-    with pytest.raises(SystemExit):
         mobilenet_v1_train.main(["--depth_multiplier=0.3"])
 
 
