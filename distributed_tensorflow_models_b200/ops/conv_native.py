@@ -7,6 +7,7 @@ Autograd wiring lives in ``ops/functional.py``; this module only validates and l
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 from typing import Optional, Sequence, Tuple
 
@@ -234,8 +235,23 @@ def set_wt_batch(batch: Optional[WeightTransposeBatch]) -> None:
     _current_wt_batch = batch
 
 
+_wt_register_off = [0]
+
+
+@contextlib.contextmanager
+def temporary_weights():
+    """Convolutions run inside do not join the step's batched transpose: their weight operand is a temporary (the
+    fake-quantised weights of ``slim/quantize.py``) whose address is not a property of the model, and the batch
+    is keyed by address.  Their dgrad operand comes from a transpose launch of their own."""
+    _wt_register_off[0] += 1
+    try:
+        yield
+    finally:
+        _wt_register_off[0] -= 1
+
+
 def wt_register(w: torch.Tensor) -> None:
-    if _current_wt_batch is not None:
+    if _current_wt_batch is not None and not _wt_register_off[0]:
         _current_wt_batch.register(w)
 
 

@@ -114,6 +114,14 @@ def _safe(s: torch.Tensor) -> torch.Tensor:
     return torch.where(s.abs() < tiny, torch.full_like(s, tiny), s)
 
 
+def _run_with_temporary_weights(conv: Callable[[torch.Tensor], torch.Tensor], w_q: torch.Tensor) -> torch.Tensor:
+    if w_q.is_cuda:
+        from ..ops import conv_native
+        with conv_native.temporary_weights():
+            return conv(w_q)
+    return conv(w_q)
+
+
 def folded_layer(q: QuantState, conv: Callable[[torch.Tensor], torch.Tensor], w: torch.Tensor,
                  bias: Optional[torch.Tensor], c: int, out_axis_shape, normalizer_params: Optional[dict],
                  activation_fn: Optional[Callable], trainable: bool = True,
@@ -127,7 +135,7 @@ def folded_layer(q: QuantState, conv: Callable[[torch.Tensor], torch.Tensor], w:
     store = V.current_store()
     if normalizer_params is None:
         training = q.is_training
-        y = conv(quantize_weights(q, w, training, weights_quant_name))
+        y = _run_with_temporary_weights(conv, quantize_weights(q, w, training, weights_quant_name))
         if bias is not None:
             y = y + bias
     else:
@@ -149,7 +157,7 @@ def folded_layer(q: QuantState, conv: Callable[[torch.Tensor], torch.Tensor], w:
             s = s * gamma
         s = _safe(s)
         w_q = quantize_weights(q, w * s.reshape(out_axis_shape), training, weights_quant_name)
-        z = conv(w_q)
+        z = _run_with_temporary_weights(conv, w_q)
         u = z / s
         x4 = u if u.dim() == 4 else u.reshape(u.shape[0], 1, 1, c)
         y = Fn.batch_norm(x4, gamma, beta, mm, mv, training=training, decay=bn.get("decay", 0.999), eps=eps,
