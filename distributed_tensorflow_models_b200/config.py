@@ -155,6 +155,9 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
                          "folded batch norm (vgg/nets/mobilenet_v1_train.py:40,135-139, mobilenet_v1_eval.py:38,126)")
     ap.add_argument("--quant_delay", type=int, default=0,
                     help="global step at which fake quantisation switches on (the ranges are tracked from step 0)")
+    ap.add_argument("--input_pipeline", default="host", choices=("host", "device"),
+                    help="CIFAR-10: 'host' distorts on CPU threads (native pass per image) and copies float batches; "
+                         "'device' keeps the uint8 records in HBM and distorts each batch with one kernel")
     ap.add_argument("--num_preprocess_threads", type=int, default=4)
     ap.add_argument("--num_readers", type=int, default=4)
     ap.add_argument("--input_queue_memory_factor", type=int, default=16)

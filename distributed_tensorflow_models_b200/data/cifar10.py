@@ -99,6 +99,57 @@ def distort_batch_reference(images_u8: torch.Tensor, image_size: int, gen: torch
     return per_image_standardization(x)
 
 
+def draw_distortion(b: int, image_size: int, gen: torch.Generator):
+    """The random draws of one training batch, consumed in the order of :func:`distort_batch_reference`:
+    -> (crop rows int64 [b], crop columns int64 [b], flip bool [b], contrast factor float32 [b]).  The brightness
+    delta is drawn too (stream parity) and dropped: the standardisation cancels it."""
+    if image_size < 32:
+        oy = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+        ox = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
+    else:
+        oy = ox = torch.zeros(b, dtype=torch.int64)
+    flip = torch.rand(b, generator=gen) < 0.5
+    _delta = torch.rand(b, generator=gen)
+    factor = 0.2 + torch.rand(b, generator=gen) * 1.6
+    return oy, ox, flip, factor
+
+
+def _native_lib():
+    """The native library when it has been built (``None`` otherwise: the torch formulas then do the work)."""
+    from .. import _native as nat
+    try:
+        return nat.lib() if nat.available() else None
+    except OSError:
+        return None
+
+
+def distort_records_native(images_u8: torch.Tensor, idx: torch.Tensor, oy: torch.Tensor, ox: torch.Tensor,
+                           flip: torch.Tensor, factor: torch.Tensor, size: int, threads: int = 1,
+                           out: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """``csrc/input_pipeline.cu::dtf_cifar_distort_host``: gather records ``idx`` of the resident uint8 set
+    ``[N,32,32,3]``, crop / flip / contrast / standardise in one pass per image on ``threads`` host threads
+    -> float32 ``[b,size,size,3]``; ``None`` when the library is not built."""
+    import ctypes as C
+    lib = _native_lib()
+    if lib is None:
+        return None
+    b = idx.numel()
+    if out is None:
+        out = torch.empty(b, size, size, 3, dtype=torch.float32)
+    idx = idx.to(torch.int64).contiguous()
+    oy32, ox32 = oy.to(torch.int32).contiguous(), ox.to(torch.int32).contiguous()
+    fl, fac = flip.to(torch.uint8).contiguous(), factor.to(torch.float32).contiguous()
+    assert images_u8.dtype == torch.uint8 and images_u8.is_contiguous() and tuple(images_u8.shape[1:]) == (32, 32, 3)
+    rc = lib.dtf_cifar_distort_host(C.c_void_p(images_u8.data_ptr()), C.c_longlong(images_u8.shape[0]),
+                                    C.c_void_p(idx.data_ptr()), C.c_void_p(oy32.data_ptr()),
+                                    C.c_void_p(ox32.data_ptr()), C.c_void_p(fl.data_ptr()), C.c_void_p(fac.data_ptr()),
+                                    int(b), int(size), C.c_void_p(out.data_ptr()), int(threads))
+    if rc != 0:
+        msg = lib.dtf_last_error()
+        raise RuntimeError("dtf_cifar_distort_host failed: %s" % (msg.decode() if msg else rc))
+    return out
+
+
 def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator) -> torch.Tensor:
     """uint8 [B,32,32,3] -> float32 [B,image_size,image_size,3] with the training distortions, in three passes.
 
@@ -110,14 +161,7 @@ def distort_batch(images_u8: torch.Tensor, image_size: int, gen: torch.Generator
     outputs agree to rounding (tests/test_ckpt_data_cli.py)."""
     b = images_u8.shape[0]
     size = image_size if image_size < 32 else 32
-    if image_size < 32:
-        oy = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
-        ox = torch.randint(0, 32 - image_size + 1, (b,), generator=gen)
-    else:
-        oy = ox = torch.zeros(b, dtype=torch.int64)
-    flip = torch.rand(b, generator=gen) < 0.5
-    _delta = torch.rand(b, generator=gen)          # brightness: drawn (stream parity), cancelled by the standardisation
-    factor = 0.2 + torch.rand(b, generator=gen) * 1.6
+    oy, ox, flip, factor = draw_distortion(b, image_size, gen)
     ar = torch.arange(size)
     idx_y = oy[:, None] + ar[None, :]
     cols = torch.where(flip[:, None], (size - 1 - ar)[None, :], ar[None, :])
@@ -213,10 +257,10 @@ class Cifar10Batches:
 
     def __init__(self, data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, train: bool = True,
                  shuffle: bool = True, rank: int = 0, world: int = 1, seed: int = 0, prefetch: int = 4,
-                 repeat: bool = True, num_threads: Optional[int] = None):
+                 repeat: bool = True, num_threads: Optional[int] = None, native: bool = True):
         labels, images = read_records(data_files(data_dir, eval_data=not train))
         if world > 1 and train:
-            labels, images = labels[rank::world], images[rank::world]
+            labels, images = np.ascontiguousarray(labels[rank::world]), np.ascontiguousarray(images[rank::world])
         self.labels = torch.from_numpy(labels)
         self.images = torch.from_numpy(images)
         self.bs, self.size, self.train, self.shuffle, self.repeat = batch_size, image_size, train, shuffle, repeat
@@ -226,6 +270,7 @@ class Cifar10Batches:
         self._orders: dict = {}
         self._lock = threading.Lock()
         self.pin = torch.cuda.is_available()
+        self.native = bool(native) and _native_lib() is not None
         if num_threads is None:
             num_threads = min(4, max(1, (os.cpu_count() or 2) // 2)) if train else 1
         self.pf = _OrderedPrefetcher(self._make, num_threads, max(1, prefetch // max(1, num_threads)) + 1)
@@ -243,23 +288,47 @@ class Cifar10Batches:
                     del self._orders[old]
             return o
 
-    def _make(self, k: int):
-        epoch, j = divmod(k, self.bpe)
-        if epoch > 0 and not self.repeat:
-            return None
+    def _indices(self, epoch: int, j: int) -> torch.Tensor:
         order = self._order(epoch)
         idx = order[j * self.bs:(j + 1) * self.bs]
         if idx.numel() < self.bs and self.repeat:
             idx = torch.cat([idx, order[: self.bs - idx.numel()]])
-        img = self.images[idx]
-        if self.train:
-            x = distort_batch(img, self.size, torch.Generator().manual_seed(self.seed * 7368787 + k))
-        else:
-            x = center_batch(img, self.size)
+        return idx
+
+    def _make(self, k: int):
+        epoch, j = divmod(k, self.bpe)
+        if epoch > 0 and not self.repeat:
+            return None
+        idx = self._indices(epoch, j)
         y = self.labels[idx].clone()
+        x = self._make_native(idx, k) if self.native else None
+        if x is None:
+            img = self.images[idx]
+            if self.train:
+                x = distort_batch(img, self.size, torch.Generator().manual_seed(self.seed * 7368787 + k))
+            else:
+                x = center_batch(img, self.size)
+            if self.pin:
+                x = x.pin_memory()
         if self.pin:
-            x, y = x.pin_memory(), y.pin_memory()
+            y = y.pin_memory()
         return x, y
+
+    def _draws(self, b: int, k: int):
+        """Crop / flip / contrast draws of batch ``k`` (training) or the fixed central crop (evaluation)."""
+        if self.train:
+            return draw_distortion(b, self.size, torch.Generator().manual_seed(self.seed * 7368787 + k))
+        o = torch.full((b,), (32 - self.size) // 2, dtype=torch.int64)
+        return o, o, torch.zeros(b, dtype=torch.bool), torch.ones(b)
+
+    def _make_native(self, idx: torch.Tensor, k: int):
+        """One native pass from the resident records straight into the (pinned) output batch."""
+        if self.size > 32:
+            return None
+        b = idx.numel()
+        oy, ox, flip, factor = self._draws(b, k)
+        out = torch.empty(b, self.size, self.size, 3, dtype=torch.float32, pin_memory=self.pin)
+        return distort_records_native(self.images, idx, oy, ox, flip, factor, self.size, threads=1, out=out)
 
     def __iter__(self):
         return self
@@ -272,6 +341,89 @@ class Cifar10Batches:
 
     def close(self):
         self.pf.close()
+
+
+class RecordBatch:
+    """A batch that does not exist yet: record numbers and distortion draws, packed into one pinned staging buffer
+    (``idx int64[b] | crop row int32[b] | crop column int32[b] | contrast float32[b] | flip uint8[b]``).
+    :meth:`copy_into` produces the float images in a destination buffer on the device that holds the records —
+    one small upload and one kernel (``dtf_cifar_distort``) on the current stream.  ``DevicePrefetcher`` calls it in
+    place of the host-to-device image copy."""
+    dtype = torch.float32
+    BYTES_PER_IMAGE = 8 + 4 + 4 + 4 + 1
+
+    def __init__(self, owner: "DeviceCifar10Batches", idx, oy, ox, flip, factor):
+        b = idx.numel()
+        self.owner, self.b = owner, b
+        self.shape = torch.Size((b, owner.size, owner.size, 3))
+        st = torch.empty(b * self.BYTES_PER_IMAGE, dtype=torch.uint8, pin_memory=owner.pin)
+        st[:8 * b].view(torch.int64).copy_(idx)
+        st[8 * b:12 * b].view(torch.int32).copy_(oy)
+        st[12 * b:16 * b].view(torch.int32).copy_(ox)
+        st[16 * b:20 * b].view(torch.float32).copy_(factor)
+        st[20 * b:].copy_(flip)
+        self.stage = st
+
+    def fields(self, st: torch.Tensor):
+        b = self.b
+        return (st[:8 * b].view(torch.int64), st[8 * b:12 * b].view(torch.int32), st[12 * b:16 * b].view(torch.int32),
+                st[20 * b:], st[16 * b:20 * b].view(torch.float32))
+
+    def copy_into(self, dst: torch.Tensor) -> None:
+        own = self.owner
+        assert dst.shape == self.shape and dst.dtype == torch.float32 and dst.is_contiguous()
+        if dst.is_cuda:
+            import ctypes as C
+            from .. import _native as nat
+            st = self.stage.to(dst.device, non_blocking=True)
+            base, b = st.data_ptr(), self.b
+            vp = C.c_void_p
+            nat.check(nat.lib().dtf_cifar_distort(vp(own.images_dev.data_ptr()), vp(base), vp(base + 8 * b),
+                                                  vp(base + 12 * b), vp(base + 20 * b), vp(base + 16 * b), int(b),
+                                                  int(own.size), vp(dst.data_ptr()), nat.stream_ptr()),
+                      "dtf_cifar_distort")
+        else:
+            idx, oy, ox, flip, factor = self.fields(self.stage)
+            if distort_records_native(own.images, idx, oy, ox, flip, factor, own.size, out=dst) is None:
+                raise RuntimeError("the device-resident CIFAR pipeline needs the native library")
+
+    def to(self, device, non_blocking: bool = False) -> torch.Tensor:
+        """Materialise as a fresh tensor (what a consumer without a destination buffer asks for)."""
+        out = torch.empty(self.shape, dtype=torch.float32, device=device)
+        self.copy_into(out)
+        return out
+
+
+class DeviceCifar10Batches(Cifar10Batches):
+    """CIFAR-10 with the records resident on the training device.
+
+    The uint8 records of this rank (150 MB for the whole training set) are uploaded once; after that a step sends
+    21 bytes per image (record number + draws) instead of 12 KB of float pixels, and crop / flip / contrast /
+    standardisation run in one kernel per batch next to the consumer — the host cores only draw random numbers.
+    Batch ``k`` is the same function of ``(seed, rank, k)`` as in :class:`Cifar10Batches`: same permutation, same
+    draws, same arithmetic (the two pipelines agree to float rounding).  Yields ``(RecordBatch, labels)``;
+    ``utils.pipeline.DevicePrefetcher`` turns them into device tensors."""
+
+    def __init__(self, data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, device="cuda", **kw):
+        if image_size > 32:
+            raise ValueError("the device-resident pipeline crops; image_size must not exceed 32")
+        self.device = torch.device(device)
+        kw["num_threads"] = 1
+        kw["native"] = False
+        self.images_dev = None
+        super().__init__(data_dir, batch_size, image_size, **kw)
+        if self.device.type == "cuda":
+            self.images_dev = self.images.to(self.device)
+
+    def _make(self, k: int):
+        epoch, j = divmod(k, self.bpe)
+        if epoch > 0 and not self.repeat:
+            return None
+        idx = self._indices(epoch, j)
+        y = self.labels[idx].clone()
+        if self.pin:
+            y = y.pin_memory()
+        return RecordBatch(self, idx, *self._draws(idx.numel(), k)), y
 
 
 def distorted_inputs(data_dir: str, batch_size: int, image_size: int = IMAGE_SIZE, **kw) -> Cifar10Batches:

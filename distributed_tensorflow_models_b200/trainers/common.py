@@ -69,13 +69,18 @@ def make_setup(args, num_workers: int) -> TrainSetup:
                       quantize=bool(args.quantize), quant_delay=int(args.quant_delay))
 
 
-def make_batches(args, spec, rank: int, world: int):
+def make_batches(args, spec, rank: int, world: int, device=None):
     """Real data when present (and not ``--synthetic``), synthetic batches of the model's shape otherwise."""
     use_synth = args.synthetic
     if spec.dataset == "cifar10":
         from ..data import cifar10
         if use_synth is None:
             use_synth = not cifar10.maybe_download_and_extract(args.data_dir)
+        if not use_synth and getattr(args, "input_pipeline", "host") == "device" and spec.image_size <= 32:
+            # records resident on the training device, augmentation as one kernel per batch
+            return cifar10.DeviceCifar10Batches(args.data_dir, args.batch_size, spec.image_size,
+                                                device=device if device is not None else "cpu", rank=rank,
+                                                world=world, seed=args.seed)
         if not use_synth:
             return cifar10.distorted_inputs(args.data_dir, args.batch_size, spec.image_size, rank=rank, world=world,
                                             seed=args.seed)
@@ -221,7 +226,7 @@ def run_worker(args) -> int:
         ckpt.restore(trainer.store, ckpt.load(src), strict=False)
         comm.set_global_step(0)
         log("initialised from %s (global step reset to 0)" % src)
-    batches = DevicePrefetcher(make_batches(args, spec, rank, world), device)
+    batches = DevicePrefetcher(make_batches(args, spec, rank, world, device), device)
     losses_rb = ScalarReadback(device)
     metrics = MetricsWriter(args.metrics_jsonl if is_chief else "")
     # chief: scalar summaries into train_dir every save_summaries_secs (Supervisor's summary thread; the reference

@@ -78,7 +78,10 @@ class DevicePrefetcher:
         with torch.cuda.stream(self.stream):
             if self.free[k] is not None:
                 self.stream.wait_event(self.free[k])
-            buf[0].copy_(x, non_blocking=True)
+            if hasattr(x, "copy_into"):       # a batch produced on the device (data/cifar10.py::RecordBatch)
+                x.copy_into(buf[0])
+            else:
+                buf[0].copy_(x, non_blocking=True)
             buf[1].copy_(y, non_blocking=True)
             if self.ready[k] is None:
                 self.ready[k] = torch.cuda.Event()

@@ -259,6 +259,21 @@ int dtf_pad_bwd(const float* dy, float* dx, int N, int H, int W, int C, int pt, 
                 void* stream);
 
 /* ------------------------------------------------------------------------------------ */
+/* CIFAR-10 input: crop + flip + contrast + per-image standardisation from uint8 records   */
+/*     (cnn/cifar10_input.py:176-190 training, :242-247 evaluation; brightness cancels in  */
+/*     the standardisation).  images = [num_records][32][32][3] bytes; per image b: record  */
+/*     idx[b], crop origin (oy[b], ox[b]), flip[b], contrast factor[b]; out = float         */
+/*     [B][S][S][3].  Evaluation = central origin, no flip, factor 1.                      */
+/* ------------------------------------------------------------------------------------ */
+/* device: every pointer is device memory; one thread block per image */
+int dtf_cifar_distort(const unsigned char* images, const long long* idx, const int* oy, const int* ox,
+                      const unsigned char* flip, const float* factor, int B, int S, float* out, void* stream);
+/* host: the same arithmetic on `threads` host threads; indices and crop windows are range-checked */
+int dtf_cifar_distort_host(const unsigned char* images, long long num_records, const long long* idx, const int* oy,
+                           const int* ox, const unsigned char* flip, const float* factor, int B, int S, float* out,
+                           int threads);
+
+/* ------------------------------------------------------------------------------------ */
 /* K16 + C1..C5  parameter-server update / push / pull / clocks                           */
 /*     hyper[7] (device): lr, grad_scale, weight_decay, rms_decay, momentum, epsilon,    */
 /*     ema_decay (< 0 disables EMA).  kind: 0 SGD, 1 TF1 RMSProp with momentum.          */

@@ -1,0 +1,116 @@
+"""The native CIFAR-10 input path (csrc/input_pipeline.cu): one pass from the uint8 records to the distorted float
+batch, on host threads and as a kernel over records resident on the device — against the step-by-step statement of
+the reference's distortion (cnn/cifar10_input.py:176-190, :242-247)."""
+import pytest
+import torch
+
+from distributed_tensorflow_models_b200.data import cifar10, synthetic
+from distributed_tensorflow_models_b200.utils.pipeline import DevicePrefetcher
+
+needs_lib = pytest.mark.skipif(cifar10._native_lib() is None, reason="native library not built")
+
+
+def _records(n=600, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    imgs = torch.randint(0, 256, (n, 32, 32, 3), dtype=torch.uint8, generator=g)
+    imgs[3] = 77                        # a constant image: the standard deviation floor 1/sqrt(n) applies
+    return imgs
+
+
+@needs_lib
+@pytest.mark.parametrize("size", [24, 32, 17])
+def test_native_host_pass_matches_the_step_by_step_distortion(size):
+    imgs = _records()
+    idx = torch.randperm(600, generator=torch.Generator().manual_seed(1))[:64]
+    ref = cifar10.distort_batch_reference(imgs[idx], size, torch.Generator().manual_seed(9))
+    draws = cifar10.draw_distortion(64, size, torch.Generator().manual_seed(9))
+    for threads in (1, 3):
+        out = cifar10.distort_records_native(imgs, idx, *draws, size, threads=threads)
+        assert out.shape == ref.shape and torch.allclose(out, ref, atol=2e-5)
+    # the constant image comes out as exact zeros (the float formulas leave rounding noise there)
+    const = cifar10.distort_records_native(imgs, torch.tensor([3]), *cifar10.draw_distortion(1, size,
+                                           torch.Generator().manual_seed(2)), size)
+    assert torch.equal(const, torch.zeros_like(const))
+    # evaluation preprocessing = the same pass with a central window, no flip, contrast 1
+    o = torch.full((64,), (32 - size) // 2)
+    ev = cifar10.distort_records_native(imgs, idx, o, o, torch.zeros(64, dtype=torch.bool), torch.ones(64), size)
+    keep = idx != 3
+    assert torch.allclose(ev[keep], cifar10.center_batch(imgs[idx], size)[keep], atol=2e-5)
+    # bad arguments are refused, not read
+    with pytest.raises(RuntimeError):
+        cifar10.distort_records_native(imgs, torch.tensor([600]), o[:1], o[:1], torch.zeros(1), torch.ones(1), size)
+    with pytest.raises(RuntimeError):
+        cifar10.distort_records_native(imgs, torch.tensor([0]), torch.tensor([33 - size]), o[:1], torch.zeros(1),
+                                       torch.ones(1), size)
+
+
+@needs_lib
+def test_host_and_device_resident_pipelines_deliver_the_same_batches(tmp_path):
+    synthetic.write_cifar10_binary(str(tmp_path), train_per_file=20, test=12)
+    kw = dict(seed=4, rank=1, world=2)
+    plain = cifar10.Cifar10Batches(str(tmp_path), 8, 24, native=False, **kw)        # torch formulas
+    fast = cifar10.Cifar10Batches(str(tmp_path), 8, 24, native=True, num_threads=3, **kw)
+    resident = cifar10.DeviceCifar10Batches(str(tmp_path), 8, 24, device="cpu", **kw)
+    assert fast.native and not plain.native
+    fed = DevicePrefetcher(resident, torch.device("cpu"))
+    try:
+        for k in range(9):                       # crosses an epoch boundary (50 records per rank, 7 batches)
+            (xa, ya), (xb, yb), (xc, yc) = next(plain), next(fast), next(fed)
+            assert torch.equal(ya, yb) and torch.equal(ya, yc), k
+            assert torch.allclose(xa, xb, atol=2e-5) and torch.equal(xb, xc), k
+            assert isinstance(xc, torch.Tensor) and tuple(xc.shape) == (8, 24, 24, 3)
+    finally:
+        plain.close(), fast.close(), resident.close()
+    # what crosses to the device per image: 21 bytes of record number and draws instead of 6912 bytes of pixels
+    item = resident._make(0)[0]
+    assert item.stage.numel() == 8 * cifar10.RecordBatch.BYTES_PER_IMAGE == 8 * 21
+    idx, oy, ox, flip, factor = item.fields(item.stage)
+    assert idx.dtype == torch.int64 and int(oy.max()) <= 8 and float(factor.min()) >= 0.2
+    # evaluation: every record once, central crop
+    ev_a = cifar10.inputs(True, str(tmp_path), 5, image_size=24, native=False)
+    ev_b = cifar10.DeviceCifar10Batches(str(tmp_path), 5, 24, device="cpu", train=False, shuffle=False, repeat=False)
+    got = [(x.to("cpu"), y) for x, y in ev_b]
+    want = list(ev_a)
+    assert len(got) == len(want) == 3 and sum(x.shape[0] for x, _ in got) == 12
+    for (xa, ya), (xb, yb) in zip(want, got):
+        assert torch.equal(ya, yb) and torch.allclose(xa, xb, atol=2e-5)
+    with pytest.raises(ValueError):
+        cifar10.DeviceCifar10Batches(str(tmp_path), 5, 40, device="cpu")
+
+
+@needs_lib
+def test_trainer_entry_point_with_the_device_resident_pipeline(tmp_path):
+    from distributed_tensorflow_models_b200.trainers import cifar10_cnn_bsp
+    data, train = str(tmp_path / "data"), str(tmp_path / "train")
+    synthetic.write_cifar10_binary(data, train_per_file=16, test=8)
+    assert cifar10_cnn_bsp.main(["--data_dir", data, "--train_dir", train, "--max_steps", "3", "--batch_size", "8",
+                                 "--input_pipeline", "device", "--synthetic", "False"]) == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size", [24, 32])
+def test_device_kernel_matches_the_host_pass(size):
+    """dtf_cifar_distort (one block per image over HBM-resident records) against dtf_cifar_distort_host and the
+    step-by-step PyTorch statement, through the prefetcher's copy stream."""
+    from distributed_tensorflow_models_b200 import _native as nat
+    dev = torch.device("cuda", 0)
+    imgs = _records(2000, seed=3)
+
+    class Source(cifar10.DeviceCifar10Batches):
+        def __init__(self):                                  # records from memory instead of files
+            self.device, self.images, self.size, self.pin = dev, imgs, size, True
+            self.images_dev = imgs.to(dev)
+
+    src = Source()
+    for b, seed in ((128, 1), (7, 2), (512, 3)):
+        idx = torch.randperm(2000, generator=torch.Generator().manual_seed(seed))[:b]
+        draws = cifar10.draw_distortion(b, size, torch.Generator().manual_seed(seed + 10))
+        want = cifar10.distort_records_native(imgs, idx, *draws, size)
+        ref = cifar10.distort_batch_reference(imgs[idx], size, torch.Generator().manual_seed(seed + 10))
+        before = nat.launch_count()
+        got = cifar10.RecordBatch(src, idx, *draws).to(dev)
+        assert nat.launch_count() == before + 1, "the native kernel did not run"
+        torch.cuda.synchronize()
+        assert torch.allclose(got.cpu(), want, atol=1e-6), float((got.cpu() - want).abs().max())
+        keep = idx != 3
+        assert torch.allclose(got.cpu()[keep], ref[keep], atol=2e-5)
