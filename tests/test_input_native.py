@@ -111,6 +111,6 @@ def test_device_kernel_matches_the_host_pass(size):
         got = cifar10.RecordBatch(src, idx, *draws).to(dev)
         assert nat.launch_count() == before + 1, "the native kernel did not run"
         torch.cuda.synchronize()
-        assert torch.allclose(got.cpu(), want, atol=1e-6), float((got.cpu() - want).abs().max())
+        assert torch.allclose(got.cpu(), want, atol=2e-6), float((got.cpu() - want).abs().max())
         keep = idx != 3
         assert torch.allclose(got.cpu()[keep], ref[keep], atol=2e-5)
