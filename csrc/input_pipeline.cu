@@ -15,12 +15,17 @@
 // and, x being bytes, sum(x) and sum(x^2) per channel are exact integers, so
 //     mean(y^2) = (1/n) sum_c [ f^2 (Sxx_c - P m_c^2) + P (m_c - M)^2 ],              P = S*S
 // needs one pass over the bytes; the second pass writes the floats.
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <thread>
 #include <vector>
 
 #include "host_common.h"
+
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 namespace dtf {
 
@@ -182,5 +187,146 @@ extern "C" int dtf_cifar_distort_host(const uint8_t* images, long long num_recor
   for (int t = 1; t < threads; ++t) pool.emplace_back(work, t);
   work(0);
   for (auto& th : pool) th.join();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// ImageNet colour distortion (inception/image_processing.py:164-195) on an HWC float image in [0, 1], in place:
+//   order 0: brightness -> saturation + hue -> contrast        (even preprocessing threads)
+//   order 1: brightness -> contrast -> saturation + hue        (odd threads)
+// then clip to [0, 1].  Saturation and hue share one RGB -> HSV -> RGB round trip on the image clipped to [0, 1];
+// contrast is (x - m_c) * factor + m_c with the per-channel mean of its input, which costs one extra sweep:
+// order 0 sums the channels while it writes the hue stage, order 1 sums the raw image first (the brightness shift
+// moves the mean by delta).  Two sweeps over the image in total instead of a dozen array temporaries.
+// ---------------------------------------------------------------------------------------------------------
+namespace dtf {
+
+static inline float fmin2(float a, float b) { return a < b ? a : b; }     // minss / maxss, not libm calls
+static inline float fmax2(float a, float b) { return a > b ? a : b; }
+static inline float clip01(float v) { return fmin2(fmax2(v, 0.f), 1.f); }
+
+constexpr int kColourBlock = 256;        // pixels handled per inner loop, de-interleaved into planes on the stack
+
+// Saturation + hue on n <= kColourBlock pixels held as three planes.  Selects only: on photographs the comparisons are
+// data dependent and branches would mispredict.  Four pixels per iteration with SSE2 (part of x86-64); the scalar
+// loop does the tail and other hosts.
+static inline void saturation_hue_scalar(float& R, float& G, float& B, float sat, float hue) {
+  const float r = clip01(R), g = clip01(G), b = clip01(B);
+  const float mx = fmax2(fmax2(r, g), b);
+  const float mn = fmin2(fmin2(r, g), b);
+  const float d = mx - mn;
+  const float inv = 1.0f / fmax2(d, 1e-12f);
+  const float s0 = mx > 0.f ? d / fmax2(mx, 1e-12f) : 0.f;
+  float hr = (g - b) * inv;
+  hr = hr < 0.f ? hr + 6.0f : hr;
+  const float hg = (b - r) * inv + 2.0f, hb = (r - g) * inv + 4.0f;
+  float h = mx == r ? hr : (mx == g ? hg : hb);
+  h = d > 0.f ? h * (1.0f / 6.0f) : 0.f;
+  h = h >= 1.f ? h - 1.0f : h;
+  const float s = clip01(s0 * sat);
+  h += hue;                                   // |hue| <= 0.2: h stays within [-1, 2)
+  h = h < 0.f ? h + 1.0f : (h >= 1.f ? h - 1.0f : h);
+  const float h6 = h * 6.0f, vs = mx * s;
+  float k5 = h6 + 5.0f, k3 = h6 + 3.0f, k1 = h6 + 1.0f;
+  k5 = k5 >= 6.f ? k5 - 6.0f : k5;
+  k3 = k3 >= 6.f ? k3 - 6.0f : k3;
+  k1 = k1 >= 6.f ? k1 - 6.0f : k1;
+  R = mx - vs * clip01(fmin2(k5, 4.0f - k5));
+  G = mx - vs * clip01(fmin2(k3, 4.0f - k3));
+  B = mx - vs * clip01(fmin2(k1, 4.0f - k1));
+}
+
+#if defined(__SSE2__)
+static inline __m128 sel(__m128 mask, __m128 a, __m128 b) { return _mm_or_ps(_mm_and_ps(mask, a), _mm_andnot_ps(mask, b)); }
+static inline __m128 clip01v(__m128 v) { return _mm_min_ps(_mm_max_ps(v, _mm_setzero_ps()), _mm_set1_ps(1.0f)); }
+// k -> clip01(min(k', 4 - k')), k' = k wrapped into [0, 6)
+static inline __m128 hue_ramp(__m128 k) {
+  const __m128 six = _mm_set1_ps(6.0f);
+  k = sel(_mm_cmpge_ps(k, six), _mm_sub_ps(k, six), k);
+  return clip01v(_mm_min_ps(k, _mm_sub_ps(_mm_set1_ps(4.0f), k)));
+}
+#endif
+
+static void saturation_hue_block(float* __restrict__ R, float* __restrict__ G, float* __restrict__ B, int n, float sat,
+                                 float hue) {
+  int i = 0;
+#if defined(__SSE2__)
+  const __m128 zero = _mm_setzero_ps(), one = _mm_set1_ps(1.0f), tiny = _mm_set1_ps(1e-12f);
+  for (; i + 4 <= n; i += 4) {
+    const __m128 r = clip01v(_mm_loadu_ps(R + i)), g = clip01v(_mm_loadu_ps(G + i)), b = clip01v(_mm_loadu_ps(B + i));
+    const __m128 mx = _mm_max_ps(_mm_max_ps(r, g), b);
+    const __m128 mn = _mm_min_ps(_mm_min_ps(r, g), b);
+    const __m128 d = _mm_sub_ps(mx, mn);
+    const __m128 inv = _mm_div_ps(one, _mm_max_ps(d, tiny));
+    const __m128 s0 = _mm_and_ps(_mm_cmpgt_ps(mx, zero), _mm_div_ps(d, _mm_max_ps(mx, tiny)));
+    __m128 hr = _mm_mul_ps(_mm_sub_ps(g, b), inv);
+    hr = sel(_mm_cmplt_ps(hr, zero), _mm_add_ps(hr, _mm_set1_ps(6.0f)), hr);
+    const __m128 hg = _mm_add_ps(_mm_mul_ps(_mm_sub_ps(b, r), inv), _mm_set1_ps(2.0f));
+    const __m128 hb = _mm_add_ps(_mm_mul_ps(_mm_sub_ps(r, g), inv), _mm_set1_ps(4.0f));
+    __m128 h = sel(_mm_cmpeq_ps(mx, r), hr, sel(_mm_cmpeq_ps(mx, g), hg, hb));
+    h = _mm_and_ps(_mm_cmpgt_ps(d, zero), _mm_mul_ps(h, _mm_set1_ps(1.0f / 6.0f)));
+    h = sel(_mm_cmpge_ps(h, one), _mm_sub_ps(h, one), h);
+    const __m128 s = clip01v(_mm_mul_ps(s0, _mm_set1_ps(sat)));
+    h = _mm_add_ps(h, _mm_set1_ps(hue));
+    h = sel(_mm_cmplt_ps(h, zero), _mm_add_ps(h, one), sel(_mm_cmpge_ps(h, one), _mm_sub_ps(h, one), h));
+    const __m128 h6 = _mm_mul_ps(h, _mm_set1_ps(6.0f)), vs = _mm_mul_ps(mx, s);
+    _mm_storeu_ps(R + i, _mm_sub_ps(mx, _mm_mul_ps(vs, hue_ramp(_mm_add_ps(h6, _mm_set1_ps(5.0f))))));
+    _mm_storeu_ps(G + i, _mm_sub_ps(mx, _mm_mul_ps(vs, hue_ramp(_mm_add_ps(h6, _mm_set1_ps(3.0f))))));
+    _mm_storeu_ps(B + i, _mm_sub_ps(mx, _mm_mul_ps(vs, hue_ramp(_mm_add_ps(h6, _mm_set1_ps(1.0f))))));
+  }
+#endif
+  for (; i < n; ++i) saturation_hue_scalar(R[i], G[i], B[i], sat, hue);
+}
+
+}  // namespace dtf
+
+extern "C" int dtf_distort_color_host(float* img, long long num_pixels, int order, float delta, float sat, float hue,
+                                      float contrast) {
+  DTF_REQUIRE(order == 0 || order == 1, "colour distortion order: 0 (contrast last) or 1 (contrast second)");
+  DTF_REQUIRE(num_pixels >= 0, "pixel count must not be negative");
+  if (num_pixels == 0) return 0;
+  double sum[3] = {0.0, 0.0, 0.0};
+  float m[3] = {0.f, 0.f, 0.f};
+  float R[kColourBlock], G[kColourBlock], B[kColourBlock];
+  if (order == 1) {                      // contrast acts on the brightness-shifted image: its means are known up front
+    for (long long p = 0; p < num_pixels; ++p) {
+      const float* px = img + 3 * p;
+      sum[0] += px[0]; sum[1] += px[1]; sum[2] += px[2];
+    }
+    for (int c = 0; c < 3; ++c) m[c] = (float)(sum[c] / (double)num_pixels) + delta;
+  }
+  for (long long p0 = 0; p0 < num_pixels; p0 += kColourBlock) {
+    const int n = (int)(num_pixels - p0 < kColourBlock ? num_pixels - p0 : kColourBlock);
+    float* px = img + 3 * p0;
+    if (order == 0) {
+      for (int i = 0; i < n; ++i) { R[i] = px[3 * i] + delta; G[i] = px[3 * i + 1] + delta; B[i] = px[3 * i + 2] + delta; }
+    } else {
+      for (int i = 0; i < n; ++i) {
+        R[i] = (px[3 * i] + delta - m[0]) * contrast + m[0];
+        G[i] = (px[3 * i + 1] + delta - m[1]) * contrast + m[1];
+        B[i] = (px[3 * i + 2] + delta - m[2]) * contrast + m[2];
+      }
+    }
+    saturation_hue_block(R, G, B, n, sat, hue);
+    if (order == 0) {
+      float sr = 0.f, sg = 0.f, sb = 0.f;                 // block sums in float, image sums in double
+      for (int i = 0; i < n; ++i) {
+        sr += R[i]; sg += G[i]; sb += B[i];
+        px[3 * i] = R[i]; px[3 * i + 1] = G[i]; px[3 * i + 2] = B[i];
+      }
+      sum[0] += sr; sum[1] += sg; sum[2] += sb;
+    } else {
+      for (int i = 0; i < n; ++i) { px[3 * i] = clip01(R[i]); px[3 * i + 1] = clip01(G[i]); px[3 * i + 2] = clip01(B[i]); }
+    }
+  }
+  if (order == 0) {
+    for (int c = 0; c < 3; ++c) m[c] = (float)(sum[c] / (double)num_pixels);
+    for (long long p = 0; p < num_pixels; ++p) {
+      float* px = img + 3 * p;
+      px[0] = clip01((px[0] - m[0]) * contrast + m[0]);
+      px[1] = clip01((px[1] - m[1]) * contrast + m[1]);
+      px[2] = clip01((px[2] - m[2]) * contrast + m[2]);
+    }
+  }
   return 0;
 }

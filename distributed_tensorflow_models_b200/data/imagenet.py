@@ -163,7 +163,34 @@ def _hsv_to_rgb_np(h: np.ndarray, s: np.ndarray, v: np.ndarray):
 
 
 def distort_color(img: torch.Tensor, thread_id: int, rng: random.Random) -> torch.Tensor:
-    """Two orderings of brightness / saturation / hue / contrast by thread parity (image_processing.py:164-195).
+    """Two orderings of brightness / saturation / hue / contrast by thread parity (image_processing.py:164-195):
+    two native sweeps over the image (``csrc/input_pipeline.cu::dtf_distort_color_host``) when the library is built,
+    the NumPy planes of :func:`distort_color_numpy` otherwise — same draws in the same order, same result to 1e-5."""
+    from .cifar10 import _native_lib
+    lib = _native_lib()
+    if lib is None:
+        return distort_color_numpy(img, thread_id, rng)
+    import ctypes as C
+    x = img.numpy() if isinstance(img, torch.Tensor) else np.asarray(img)
+    x = np.array(x, dtype=np.float32, order="C", copy=True)
+    assert x.ndim == 3 and x.shape[2] == 3
+    delta = rng.uniform(-32.0 / 255.0, 32.0 / 255.0)
+    if thread_id % 2 == 0:
+        sat, hue = rng.uniform(0.5, 1.5), rng.uniform(-0.2, 0.2)
+        factor = rng.uniform(0.5, 1.5)
+    else:
+        factor = rng.uniform(0.5, 1.5)
+        sat, hue = rng.uniform(0.5, 1.5), rng.uniform(-0.2, 0.2)
+    rc = lib.dtf_distort_color_host(C.c_void_p(x.ctypes.data), C.c_longlong(x.shape[0] * x.shape[1]),
+                                    int(thread_id % 2), C.c_float(delta), C.c_float(sat), C.c_float(hue),
+                                    C.c_float(factor))
+    if rc != 0:
+        raise RuntimeError("dtf_distort_color_host failed (%d)" % rc)
+    return torch.from_numpy(x)
+
+
+def distort_color_numpy(img: torch.Tensor, thread_id: int, rng: random.Random) -> torch.Tensor:
+    """The colour distortion on NumPy planes (the oracle of the native pass, and the fallback without it).
 
     Saturation and hue are neighbours in both orderings and the RGB image between them is already inside [0, 1], so
     they share one RGB -> HSV -> RGB round trip (the costly part of the whole input pipeline); the arithmetic runs in

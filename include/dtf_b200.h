@@ -272,6 +272,10 @@ int dtf_cifar_distort(const unsigned char* images, const long long* idx, const i
 int dtf_cifar_distort_host(const unsigned char* images, long long num_records, const long long* idx, const int* oy,
                            const int* ox, const unsigned char* flip, const float* factor, int B, int S, float* out,
                            int threads);
+/* ImageNet colour distortion (inception/image_processing.py:164-195), host, in place on an HWC float image in [0, 1]:
+ * order 0 = brightness, saturation + hue, contrast; order 1 = brightness, contrast, saturation + hue; then clip. */
+int dtf_distort_color_host(float* img, long long num_pixels, int order, float delta, float saturation, float hue,
+                           float contrast);
 
 /* ------------------------------------------------------------------------------------ */
 /* K16 + C1..C5  parameter-server update / push / pull / clocks                           */

@@ -114,3 +114,31 @@ def test_device_kernel_matches_the_host_pass(size):
         assert torch.allclose(got.cpu(), want, atol=2e-6), float((got.cpu() - want).abs().max())
         keep = idx != 3
         assert torch.allclose(got.cpu()[keep], ref[keep], atol=2e-5)
+
+
+@needs_lib
+@pytest.mark.parametrize("shape", [(299, 299, 3), (37, 41, 3), (1, 3, 3)])
+def test_native_colour_distortion_matches_the_numpy_planes(shape):
+    """dtf_distort_color_host (two sweeps, four pixels per SSE2 iteration + scalar tail) against the NumPy statement
+    of inception/image_processing.py:164-195, for both orderings; greys, blacks, whites and primaries included."""
+    import random
+
+    from distributed_tensorflow_models_b200.data import imagenet
+    img = torch.rand(*shape, generator=torch.Generator().manual_seed(0))
+    if shape[0] > 80:
+        img[:20, :20] = 0.5            # grey: hue undefined (d == 0)
+        img[20:40, :20] = 0.0
+        img[40:60, :20] = 1.0
+        img[60:80, :20, 1:] = 0.0      # pure red: maximum shared by one channel only
+    for thread_id in (0, 1, 2, 3):
+        for seed in range(4):
+            a = imagenet.distort_color(img, thread_id, random.Random(seed))
+            b = imagenet.distort_color_numpy(img, thread_id, random.Random(seed))
+            assert a.shape == b.shape and a.dtype == torch.float32
+            assert float((a - b).abs().max()) < 1e-5, (thread_id, seed)
+            assert float(a.min()) >= 0.0 and float(a.max()) <= 1.0
+    # the input is not modified and both paths leave the generator in the same state
+    before = img.clone()
+    r1, r2 = random.Random(5), random.Random(5)
+    imagenet.distort_color(img, 1, r1), imagenet.distort_color_numpy(img, 1, r2)
+    assert torch.equal(img, before) and r1.random() == r2.random()
