@@ -330,3 +330,130 @@ extern "C" int dtf_distort_color_host(float* img, long long num_pixels, int orde
   }
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Crop + resize (+ left-right flip) of a decoded uint8 HWC image to a float HWC image in [0, 1]
+// (inception/image_processing.py:233-244: the distorted bounding-box crop resized with one of four methods, and
+// :271-274: the central crop resized bilinearly).  Every method is a separable linear filter, so one routine serves
+// them all: per output column / row a short list of (source index, weight) taps, a horizontal pass over the crop's
+// rows into a float strip, a vertical pass out of it.  Tap rules are those of torch.nn.functional.interpolate
+// (the Python fallback): 0 bilinear with half-pixel centres, 1 nearest, 2 bicubic (a = -0.75, edge taps clamped),
+// 3 area = mean over [floor(o in/out), ceil((o+1) in/out)).
+// ---------------------------------------------------------------------------------------------------------
+namespace dtf {
+
+struct Taps {
+  int max_taps = 0;
+  std::vector<int> idx;        // [out][max_taps]
+  std::vector<float> w;        // [out][max_taps]
+  std::vector<int> count;      // [out]
+};
+
+static inline float cubic1(float x, float A) { return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f; }
+static inline float cubic2(float x, float A) { return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A; }
+
+static void make_taps(int in, int out, int method, bool flip, Taps* t) {
+  const int mt = method == 0 ? 2 : method == 1 ? 1 : method == 2 ? 4 : (in + out - 1) / out + 1;
+  t->max_taps = mt;
+  t->idx.assign((size_t)out * mt, 0);
+  t->w.assign((size_t)out * mt, 0.f);
+  t->count.assign(out, 0);
+  const float scale = (float)in / (float)out;
+  for (int o = 0; o < out; ++o) {
+    const int dst = flip ? out - 1 - o : o;          // the flipped image's column o is the plain image's column out-1-o
+    int* ix = &t->idx[(size_t)o * mt];
+    float* w = &t->w[(size_t)o * mt];
+    int n = 0;
+    if (method == 0) {
+      float src = scale * ((float)dst + 0.5f) - 0.5f;
+      if (src < 0.f) src = 0.f;
+      int i0 = (int)src;
+      if (i0 > in - 1) i0 = in - 1;
+      const int i1 = i0 < in - 1 ? i0 + 1 : i0;
+      const float l1 = src - (float)i0;
+      ix[0] = i0; w[0] = 1.f - l1; ix[1] = i1; w[1] = l1; n = 2;
+    } else if (method == 1) {
+      int i0 = (int)floorf((float)dst * scale);
+      if (i0 > in - 1) i0 = in - 1;
+      ix[0] = i0; w[0] = 1.f; n = 1;
+    } else if (method == 2) {
+      const float A = -0.75f;
+      const float src = scale * ((float)dst + 0.5f) - 0.5f;
+      const float fl = floorf(src);
+      const float tt = src - fl;
+      const int i0 = (int)fl;
+      const float c[4] = {cubic2(tt + 1.f, A), cubic1(tt, A), cubic1(1.f - tt, A), cubic2(2.f - tt, A)};
+      for (int k = 0; k < 4; ++k) {
+        int i = i0 - 1 + k;
+        i = i < 0 ? 0 : (i > in - 1 ? in - 1 : i);
+        ix[k] = i; w[k] = c[k];
+      }
+      n = 4;
+    } else {
+      const int s = (int)(((long long)dst * in) / out);
+      const int e = (int)((((long long)dst + 1) * in + out - 1) / out);
+      const float inv = 1.f / (float)(e - s);
+      for (int i = s; i < e && n < mt; ++i) { ix[n] = i; w[n] = inv; ++n; }
+    }
+    t->count[o] = n;
+  }
+}
+
+}  // namespace dtf
+
+extern "C" int dtf_crop_resize_host(const uint8_t* img, int H, int W, int y0, int x0, int ch, int cw, int out_h,
+                                    int out_w, int method, int flip, float* out) {
+  DTF_REQUIRE(H > 0 && W > 0 && ch > 0 && cw > 0 && out_h > 0 && out_w > 0, "image, crop and output sizes must be positive");
+  DTF_REQUIRE(y0 >= 0 && x0 >= 0 && y0 + ch <= H && x0 + cw <= W, "crop window leaves the image");
+  DTF_REQUIRE(method >= 0 && method <= 3, "resize method: 0 bilinear, 1 nearest, 2 bicubic, 3 area");
+  Taps tx, ty;
+  make_taps(cw, out_w, method, flip != 0, &tx);
+  make_taps(ch, out_h, method, false, &ty);
+  const float k255 = 1.0f / 255.0f;
+  if (method == 1) {                     // one source pixel per output pixel: no strip needed
+    for (int oy = 0; oy < out_h; ++oy) {
+      const uint8_t* row = img + ((size_t)(y0 + ty.idx[oy]) * W + x0) * 3;
+      float* orow = out + (size_t)oy * out_w * 3;
+      for (int ox = 0; ox < out_w; ++ox) {
+        const uint8_t* px = row + 3 * tx.idx[ox];
+        orow[3 * ox] = (float)px[0] * k255; orow[3 * ox + 1] = (float)px[1] * k255; orow[3 * ox + 2] = (float)px[2] * k255;
+      }
+    }
+    return 0;
+  }
+  // horizontal pass over the crop's rows: strip[y][ox][c]
+  std::vector<float> strip((size_t)ch * out_w * 3);
+  for (int y = 0; y < ch; ++y) {
+    const uint8_t* row = img + ((size_t)(y0 + y) * W + x0) * 3;
+    float* srow = &strip[(size_t)y * out_w * 3];
+    for (int ox = 0; ox < out_w; ++ox) {
+      const int* ix = &tx.idx[(size_t)ox * tx.max_taps];
+      const float* w = &tx.w[(size_t)ox * tx.max_taps];
+      float r = 0.f, g = 0.f, b = 0.f;
+      for (int k = 0; k < tx.count[ox]; ++k) {
+        const uint8_t* px = row + 3 * ix[k];
+        r += w[k] * (float)px[0]; g += w[k] * (float)px[1]; b += w[k] * (float)px[2];
+      }
+      srow[3 * ox] = r * k255; srow[3 * ox + 1] = g * k255; srow[3 * ox + 2] = b * k255;
+    }
+  }
+  // vertical pass
+  const int row_len = out_w * 3;
+  for (int oy = 0; oy < out_h; ++oy) {
+    const int* iy = &ty.idx[(size_t)oy * ty.max_taps];
+    const float* w = &ty.w[(size_t)oy * ty.max_taps];
+    float* orow = out + (size_t)oy * row_len;
+    const int n = ty.count[oy];
+    {
+      const float* s0 = &strip[(size_t)iy[0] * row_len];
+      const float w0 = w[0];
+      for (int i = 0; i < row_len; ++i) orow[i] = w0 * s0[i];
+    }
+    for (int k = 1; k < n; ++k) {
+      const float* sk = &strip[(size_t)iy[k] * row_len];
+      const float wk = w[k];
+      for (int i = 0; i < row_len; ++i) orow[i] += wk * sk[i];
+    }
+  }
+  return 0;
+}

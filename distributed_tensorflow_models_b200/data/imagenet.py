@@ -236,22 +236,48 @@ def _to_float(img) -> torch.Tensor:
     return img
 
 
+def crop_resize_native(img: np.ndarray, y0: int, x0: int, ch: int, cw: int, height: int, width: int, method: int,
+                       flip: bool) -> Optional[torch.Tensor]:
+    """``csrc/input_pipeline.cu::dtf_crop_resize_host``: window of a decoded uint8 HWC image -> float HWC in [0, 1],
+    resized with ``method`` (0 bilinear, 1 nearest, 2 bicubic, 3 area; the tap rules of :func:`resize`) and
+    optionally mirrored, in one separable pass pair; ``None`` when the library is not built or ``img`` is not uint8."""
+    from .cifar10 import _native_lib
+    lib = _native_lib()
+    if lib is None or not isinstance(img, np.ndarray) or img.dtype != np.uint8 or img.ndim != 3 or img.shape[2] != 3:
+        return None
+    import ctypes as C
+    src = np.ascontiguousarray(img)
+    out = np.empty((height, width, 3), dtype=np.float32)
+    rc = lib.dtf_crop_resize_host(C.c_void_p(src.ctypes.data), int(src.shape[0]), int(src.shape[1]), int(y0), int(x0),
+                                  int(ch), int(cw), int(height), int(width), int(method % 4), int(bool(flip)),
+                                  C.c_void_p(out.ctypes.data))
+    if rc != 0:
+        msg = lib.dtf_last_error()
+        raise RuntimeError("dtf_crop_resize_host failed: %s" % (msg.decode() if msg else rc))
+    return torch.from_numpy(out)
+
+
 def distort_image(img, height: int, width: int, bbox: np.ndarray, thread_id: int, rng: random.Random) -> torch.Tensor:
     """``img``: float HWC tensor in [0, 1], or the decoder's uint8 array (only the crop is then converted)."""
     h, w = img.shape[0], img.shape[1]
     y0, x0, ch, cw = sample_distorted_bounding_box(h, w, bbox, rng)
-    img = _to_float(img[y0:y0 + ch, x0:x0 + cw])
-    img = resize(img, height, width, thread_id % 4)
-    if rng.random() < 0.5:
-        img = img.flip(1)
-    return distort_color(img, thread_id, rng)
+    flip = rng.random() < 0.5
+    out = crop_resize_native(img, y0, x0, ch, cw, height, width, thread_id % 4, flip)
+    if out is None:
+        out = resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, thread_id % 4)
+        if flip:
+            out = out.flip(1)
+    return distort_color(out, thread_id, rng)
 
 
 def eval_image(img, height: int, width: int) -> torch.Tensor:
     h, w = img.shape[0], img.shape[1]
     ch, cw = int(h * 0.875), int(w * 0.875)
     y0, x0 = (h - ch) // 2, (w - cw) // 2
-    return resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, 0)
+    out = crop_resize_native(img, y0, x0, ch, cw, height, width, 0, False)
+    if out is None:
+        out = resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, 0)
+    return out
 
 
 def image_preprocessing(image_buffer: bytes, bbox: np.ndarray, train: bool, thread_id: int, rng: random.Random,
@@ -259,7 +285,7 @@ def image_preprocessing(image_buffer: bytes, bbox: np.ndarray, train: bool, thre
     img = decode_jpeg_u8(image_buffer)
     img = distort_image(img, image_size, image_size, bbox, thread_id, rng) if train else eval_image(img, image_size,
                                                                                                     image_size)
-    return (img - 0.5) * 2.0
+    return img.sub_(0.5).mul_(2.0)              # both branches hand back a fresh tensor
 
 
 # ---- batching ---------------------------------------------------------------------------------------------------

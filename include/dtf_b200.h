@@ -276,6 +276,11 @@ int dtf_cifar_distort_host(const unsigned char* images, long long num_records, c
  * order 0 = brightness, saturation + hue, contrast; order 1 = brightness, contrast, saturation + hue; then clip. */
 int dtf_distort_color_host(float* img, long long num_pixels, int order, float delta, float saturation, float hue,
                            float contrast);
+/* Window (y0, x0, ch, cw) of a decoded uint8 HWC image -> float HWC [out_h][out_w][3] in [0, 1], host
+ * (image_processing.py:233-244, :271-274).  method: 0 bilinear (half-pixel centres), 1 nearest, 2 bicubic (a = -0.75),
+ * 3 area; flip != 0 mirrors left-right. */
+int dtf_crop_resize_host(const unsigned char* img, int H, int W, int y0, int x0, int ch, int cw, int out_h, int out_w,
+                         int method, int flip, float* out);
 
 /* ------------------------------------------------------------------------------------ */
 /* K16 + C1..C5  parameter-server update / push / pull / clocks                           */

@@ -142,3 +142,53 @@ def test_native_colour_distortion_matches_the_numpy_planes(shape):
     r1, r2 = random.Random(5), random.Random(5)
     imagenet.distort_color(img, 1, r1), imagenet.distort_color_numpy(img, 1, r2)
     assert torch.equal(img, before) and r1.random() == r2.random()
+
+
+@needs_lib
+@pytest.mark.parametrize("geom", [(20, 50, 300, 350, 299, 299), (0, 0, 375, 500, 299, 299), (100, 100, 60, 90, 299, 299),
+                                  (3, 7, 301, 299, 224, 160), (0, 0, 10, 10, 8, 8), (5, 5, 1, 1, 4, 4)])
+def test_native_crop_resize_matches_interpolate(geom):
+    """dtf_crop_resize_host (separable taps straight from the uint8 window) against torch.nn.functional.interpolate
+    on the float crop, for the four resize methods the ImageNet distortion cycles through, plain and mirrored."""
+    import numpy as np
+
+    from distributed_tensorflow_models_b200.data import imagenet
+    y0, x0, ch, cw, oh, ow = geom
+    img = np.random.default_rng(1).integers(0, 256, (375, 500, 3), dtype=np.uint8)
+    for method in range(4):
+        for flip in (False, True):
+            ref = imagenet.resize(imagenet._to_float(img[y0:y0 + ch, x0:x0 + cw]), oh, ow, method)
+            ref = ref.flip(1) if flip else ref
+            out = imagenet.crop_resize_native(img, y0, x0, ch, cw, oh, ow, method, flip)
+            assert out.shape == ref.shape and out.dtype == torch.float32
+            assert float((out - ref).abs().max()) < 3e-5, (method, flip)        # a hundredth of one grey level
+    with pytest.raises(RuntimeError):
+        imagenet.crop_resize_native(img, 300, 0, 100, 100, 8, 8, 0, False)      # window leaves the image
+    assert imagenet.crop_resize_native(img.astype(np.float32), 0, 0, 8, 8, 4, 4, 0, False) is None
+
+
+@needs_lib
+def test_imagenet_preprocessing_native_and_fallback_agree(monkeypatch):
+    """Whole per-image path (decode, distorted crop, resize, flip, colour, scale to [-1, 1]) with and without the
+    native passes: same draws, same image."""
+    import io
+    import random
+
+    import numpy as np
+    from PIL import Image
+
+    from distributed_tensorflow_models_b200.data import cifar10 as c10
+    from distributed_tensorflow_models_b200.data import imagenet
+    yy, xx = np.mgrid[0:120, 0:160]
+    arr = np.stack([(np.sin(xx / 20) + 1) * 100 + 30, (np.cos(yy / 15) + 1) * 90 + 40, (xx + yy) % 255], -1)
+    buf = io.BytesIO()
+    Image.fromarray(arr.astype(np.uint8)).save(buf, format="JPEG", quality=90)
+    bbox = np.asarray([[0.1, 0.1, 0.9, 0.9]], dtype=np.float32)
+    for train in (True, False):
+        for tid in range(4):
+            a = imagenet.image_preprocessing(buf.getvalue(), bbox, train, tid, random.Random(tid), image_size=64)
+            monkeypatch.setattr(c10, "_native_lib", lambda: None)
+            b = imagenet.image_preprocessing(buf.getvalue(), bbox, train, tid, random.Random(tid), image_size=64)
+            monkeypatch.undo()
+            assert a.shape == (64, 64, 3) and float(a.min()) >= -1.0 and float(a.max()) <= 1.0
+            assert float((a - b).abs().max()) < 1e-4, (train, tid)
