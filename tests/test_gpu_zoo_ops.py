@@ -85,86 +85,6 @@ def test_depthwise_conv2d(cfg):
         _both(lambda x_, w_: Fn.depthwise_conv2d(x_, w_, None, s, pad), [x, wt], FP32_TOL)
 
 
-@pytest.mark.parametrize("cfg", [
-    # n, h, w, c, c_out, k, rate, padding
-    (2, 28, 28, 32, 64, 3, 2, "SAME"),       # ResNet / MobileNet output_stride=16: last stage dilated by 2
-    (2, 17, 19, 16, 32, 3, 4, "SAME"),       # output_stride=8; extents that are not multiples of the rate
-    (2, 21, 23, 16, 16, 3, 3, "VALID"),
-])
-def test_atrous_conv2d_and_depthwise(cfg):
-    """rate > 1: sampling phases stacked into the batch, then the dense tcgen05 / depthwise kernels."""
-    n, h, w, c, co, k, rate, pad = cfg
-    x, wt, b = _r(n, h, w, c, seed=1), _r(co, k, k, c, seed=2, scale=0.1), _r(co, seed=3)
-    _both(lambda x_, w_, b_: Fn.atrous_conv2d(x_, w_, b_, rate, pad), [x, wt, b], TF32_TOL)
-    dw = _r(k, k, c, 1, seed=4, scale=0.3)
-    _both(lambda x_, w_: Fn.depthwise_conv2d(x_, w_, None, 1, pad, rate=rate), [x, dw], FP32_TOL)
-
-
-@pytest.mark.parametrize("cfg", [
-    # shape, [min, max], bits, narrow, gate
-    ((4, 28, 28, 32), (-6.0, 6.0), 8, False, None),
-    ((3, 7, 5, 13), (-0.37, 2.9), 8, False, 1.0),           # odd element count: scalar tail; range nudged onto zero
-    ((64, 3, 3, 32), (-0.21, 0.17), 8, True, 1.0),          # weights: narrow range
-    ((2, 16, 16, 24), (0.4, 5.0), 4, False, 1.0),           # all-positive range, few levels
-    ((2, 16, 16, 24), (-6.0, 6.0), 8, False, 0.0),          # closed gate: identity
-    ((2, 16, 16, 24), (1.0, 1.0), 8, False, 1.0),           # degenerate range: identity
-])
-def test_fake_quant(cfg):
-    """dtf_fake_quant_fwd / _bwd against the PyTorch statement of FakeQuantWithMinMaxVars (--quantize)."""
-    shape, (mn, mx), bits, narrow, gate = cfg
-    x = _r(*shape, seed=5, scale=3.0)
-    rng = torch.tensor([mn, mx], device="cuda")
-    gate_t = None if gate is None else torch.full((), gate, device="cuda")
-    dy = _r(*shape, seed=6)
-    res = []
-    for backend in ("auto", "torch"):
-        Fn.set_backend(backend)
-        try:
-            xi = x.clone().requires_grad_(True)
-            before = nat.launch_count()
-            y = Fn.fake_quant(xi, rng, gate_t, bits, narrow)
-            y.backward(dy)
-            if backend == "auto":
-                assert nat.launch_count() - before == 2, "the native kernels did not run"
-            res.append((y.detach(), xi.grad))
-        finally:
-            Fn.set_backend("auto")
-    (y_n, g_n), (y_t, g_t) = res
-    identity = gate == 0.0 or mx <= mn
-    if identity:
-        assert torch.equal(y_n, x) and torch.equal(y_t, x) and torch.equal(g_n, dy)
-        return
-    step = float(Fn.nudged_range(rng[0], rng[1], bits, narrow)[2])
-    # a value that sits on a half step may round to the neighbouring level under a different fused-multiply-add choice
-    diff = (y_n - y_t).abs()
-    assert float(diff.max()) <= step * 1.001
-    assert float((diff > 1e-6).float().mean()) < 1e-3
-    assert float((g_n != g_t).float().mean()) < 1e-3
-    assert len(torch.unique(y_n)) <= 2 ** bits
-
-
-@pytest.mark.parametrize("n", [5, 4096, 3 * 224 * 224 + 3])
-def test_quant_range_update(n):
-    """Batch min / max through float-ordered integer atomics, then last-value or moving-average range update."""
-    for sign in (1.0, -1.0, 0.0):                       # all-positive, all-negative and mixed-sign tensors
-        base = _r(n, seed=7, scale=2.0)
-        x = base if sign == 0.0 else sign * (base.abs() + 0.25)
-        mm = torch.tensor([float("inf"), float("-inf")], device="cuda")
-        for decay in (-1.0, 0.9):
-            rng_n = torch.tensor([-6.0, 6.0], device="cuda")
-            rng_t = rng_n.clone()
-            before = nat.launch_count()
-            Fn.quant_range_update(x, rng_n, decay, mm)
-            assert nat.launch_count() - before == 1
-            Fn.set_backend("torch")
-            try:
-                Fn.quant_range_update(x, rng_t, decay)
-            finally:
-                Fn.set_backend("auto")
-            assert torch.allclose(rng_n, rng_t, rtol=1e-6, atol=1e-7), (sign, decay, rng_n, rng_t)
-            assert mm.tolist() == [float("inf"), float("-inf")]      # scratch handed back ready for the next call
-
-
 @pytest.mark.parametrize("kind", ["relu6", "leaky_relu", "tanh", "sigmoid"])
 @pytest.mark.parametrize("shape", [(3, 7, 5, 13), (2, 16, 16, 32)])
 def test_activations(kind, shape):

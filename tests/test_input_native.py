@@ -87,35 +87,6 @@ def test_trainer_entry_point_with_the_device_resident_pipeline(tmp_path):
                                  "--input_pipeline", "device", "--synthetic", "False"]) == 0
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("size", [24, 32])
-def test_device_kernel_matches_the_host_pass(size):
-    """dtf_cifar_distort (one block per image over HBM-resident records) against dtf_cifar_distort_host and the
-    step-by-step PyTorch statement, through the prefetcher's copy stream."""
-    from distributed_tensorflow_models_b200 import _native as nat
-    dev = torch.device("cuda", 0)
-    imgs = _records(2000, seed=3)
-
-    class Source(cifar10.DeviceCifar10Batches):
-        def __init__(self):                                  # records from memory instead of files
-            self.device, self.images, self.size, self.pin = dev, imgs, size, True
-            self.images_dev = imgs.to(dev)
-
-    src = Source()
-    for b, seed in ((128, 1), (7, 2), (512, 3)):
-        idx = torch.randperm(2000, generator=torch.Generator().manual_seed(seed))[:b]
-        draws = cifar10.draw_distortion(b, size, torch.Generator().manual_seed(seed + 10))
-        want = cifar10.distort_records_native(imgs, idx, *draws, size)
-        ref = cifar10.distort_batch_reference(imgs[idx], size, torch.Generator().manual_seed(seed + 10))
-        before = nat.launch_count()
-        got = cifar10.RecordBatch(src, idx, *draws).to(dev)
-        assert nat.launch_count() == before + 1, "the native kernel did not run"
-        torch.cuda.synchronize()
-        assert torch.allclose(got.cpu(), want, atol=2e-6), float((got.cpu() - want).abs().max())
-        keep = idx != 3
-        assert torch.allclose(got.cpu()[keep], ref[keep], atol=2e-5)
-
-
 @needs_lib
 @pytest.mark.parametrize("shape", [(299, 299, 3), (37, 41, 3), (1, 3, 3)])
 def test_native_colour_distortion_matches_the_numpy_planes(shape):
