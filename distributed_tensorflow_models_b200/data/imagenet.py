@@ -162,7 +162,7 @@ def _hsv_to_rgb_np(h: np.ndarray, s: np.ndarray, v: np.ndarray):
     return out
 
 
-def distort_color(img: torch.Tensor, thread_id: int, rng: random.Random) -> torch.Tensor:
+def distort_color(img: torch.Tensor, thread_id: int, rng: random.Random, inplace: bool = False) -> torch.Tensor:
     """Two orderings of brightness / saturation / hue / contrast by thread parity (image_processing.py:164-195):
     two native sweeps over the image (``csrc/input_pipeline.cu::dtf_distort_color_host``) when the library is built,
     the NumPy planes of :func:`distort_color_numpy` otherwise — same draws in the same order, same result to 1e-5."""
@@ -172,7 +172,8 @@ def distort_color(img: torch.Tensor, thread_id: int, rng: random.Random) -> torc
         return distort_color_numpy(img, thread_id, rng)
     import ctypes as C
     x = img.numpy() if isinstance(img, torch.Tensor) else np.asarray(img)
-    x = np.array(x, dtype=np.float32, order="C", copy=True)
+    if not (inplace and x.dtype == np.float32 and x.flags.c_contiguous and x.flags.writeable):
+        x = np.array(x, dtype=np.float32, order="C", copy=True)      # ``inplace``: the caller owns a fresh image
     assert x.ndim == 3 and x.shape[2] == 3
     delta = rng.uniform(-32.0 / 255.0, 32.0 / 255.0)
     if thread_id % 2 == 0:
@@ -263,10 +264,11 @@ def distort_image(img, height: int, width: int, bbox: np.ndarray, thread_id: int
     y0, x0, ch, cw = sample_distorted_bounding_box(h, w, bbox, rng)
     flip = rng.random() < 0.5
     out = crop_resize_native(img, y0, x0, ch, cw, height, width, thread_id % 4, flip)
-    if out is None:
-        out = resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, thread_id % 4)
-        if flip:
-            out = out.flip(1)
+    if out is not None:
+        return distort_color(out, thread_id, rng, inplace=True)
+    out = resize(_to_float(img[y0:y0 + ch, x0:x0 + cw]), height, width, thread_id % 4)
+    if flip:
+        out = out.flip(1)
     return distort_color(out, thread_id, rng)
 
 
