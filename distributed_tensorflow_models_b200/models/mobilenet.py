@@ -18,7 +18,7 @@ import contextlib
 import functools
 from typing import Dict, Optional
 
-from ..slim import losses, ops, scopes
+from ..slim import losses, ops, quantize, scopes
 from ..slim import variables as V
 
 # (kind, kernel, stride, depth): the v1 layer table
@@ -170,7 +170,7 @@ def expanded_conv(net, num_outputs: int, stride: int = 1, expansion: int = 6, ke
             end_points["depthwise_output"] = net
         net = ops.convolution2d(net, num_outputs, [1, 1], activation_fn=None, scope="project")
         if residual and stride == 1 and net.shape[-1] == inp.shape[-1]:
-            net = net + inp
+            net = quantize.after_add(net + inp)
         return net
 
 

@@ -25,7 +25,7 @@ import contextlib
 from typing import Dict, List, NamedTuple, Optional
 
 from ..ops import functional as Fn
-from ..slim import losses, ops, scopes
+from ..slim import losses, ops, quantize, scopes
 from ..slim import variables as V
 
 
@@ -74,7 +74,7 @@ def bottleneck_v1(inputs, depth: int, depth_bottleneck: int, stride: int, rate: 
         residual = ops.convolution2d(inputs, depth_bottleneck, [1, 1], stride=1, scope="conv1")
         residual = conv2d_same(residual, depth_bottleneck, 3, stride, rate=rate, scope="conv2")
         residual = ops.convolution2d(residual, depth, [1, 1], stride=1, activation_fn=None, scope="conv3")
-        return Fn.relu(shortcut + residual)
+        return quantize.after_add(Fn.relu(shortcut + residual))
 
 
 def bottleneck_v2(inputs, depth: int, depth_bottleneck: int, stride: int, rate: int = 1, scope: Optional[str] = None):
@@ -90,7 +90,7 @@ def bottleneck_v2(inputs, depth: int, depth_bottleneck: int, stride: int, rate: 
         residual = conv2d_same(residual, depth_bottleneck, 3, stride, rate=rate, scope="conv2")
         residual = ops.convolution2d(residual, depth, [1, 1], stride=1, normalizer_fn=None, activation_fn=None,
                                      scope="conv3")
-        return shortcut + residual
+        return quantize.after_add(shortcut + residual)
 
 
 def stack_blocks_dense(net, blocks: List[Block], output_stride: Optional[int], end_points: dict, prefix: str):

@@ -25,7 +25,8 @@ convolution and fully connected layer becomes
 * ``quant_delay``: until the global step reaches it the fake-quant ops are the identity while the ranges already
   track the data.  The switch is a float in device memory (``QuantState.gate``) that the trainer sets before each
   step, so a captured CUDA graph stays valid when the delay runs out.
-* Not quantised: the network input (the converter's job in TensorFlow too) and the outputs of residual additions.
+* Residual additions (MobileNet-v2 blocks, the slim ResNet units) quantise their output too (:func:`after_add`,
+  range ``<unit>/add_quant``).  Not quantised: the network input (the converter's job in TensorFlow as well).
 
 Variables: one non-trainable 2-vector ``<layer>/weights_quant/min_max`` and ``<layer>/act_quant/min_max`` per
 layer (``depthwise_weights_quant`` / ``pointwise_weights_quant`` for a separable convolution that has both).
@@ -106,6 +107,15 @@ def quantize_activation(q: QuantState, y: torch.Tensor, training: bool, name: st
         full = V.current_store().full_name(name)
         Fn.quant_range_update(y, rng, q.ema_decay, q.scratch(full, y.device))
     return Fn.fake_quant(y, rng, q.gate if training else None, q.activation_bits, narrow_range=False)
+
+
+def after_add(y: torch.Tensor, name: str = "add_quant") -> torch.Tensor:
+    """Output of a residual addition (after its activation, where it has one): quantised like a layer output when
+    quantisation is on, returned as it is otherwise.  Models call it where TensorFlow's rewriter finds a bypass."""
+    q = current()
+    if q is None:
+        return y
+    return quantize_activation(q, y, q.is_training, name)
 
 
 def _safe(s: torch.Tensor) -> torch.Tensor:

@@ -203,3 +203,24 @@ def test_trainer_quant_delay_checkpoint_names_and_entry_points(tmp_path):
     assert mobilenet_v1_eval.main(common + ["--checkpoint_dir=" + d, "--num_examples=4",
                                             "--eval_dir=" + str(tmp_path / "eval")]) == 0
     assert (tmp_path / "eval" / "eval.jsonl").read_text().count("precision_at_1") == 1
+
+
+@pytest.mark.parametrize("model,adds", [("mobilenet_v2", 10), ("resnet_v1_50", 16), ("resnet_v2_50_slim", 16)])
+def test_residual_additions_get_a_range_of_their_own(model, adds):
+    """TensorFlow's rewriter quantises the output of every bypass addition; here the models ask for it themselves."""
+    from distributed_tensorflow_models_b200.models import registry
+    net = registry.get_network_fn(model, 7, is_training=True)
+    size = 64
+    plain, quant = VariableStore(seed=1), VariableStore(seed=1)
+    quant.quant = Q.QuantState()
+    x = torch.randn(2, size, size, 3, generator=torch.Generator().manual_seed(0))
+    outs = []
+    for st in (plain, quant):
+        with st.as_default():
+            st.begin_forward()
+            out = net(x)[0]
+            outs.append(out[0] if isinstance(out, tuple) else out)
+    assert outs[0].shape == outs[1].shape and torch.isfinite(outs[1]).all()
+    names = [v.name for v in quant.all()]
+    assert sum(n.endswith("add_quant/min_max") for n in names) == adds
+    assert [n for n in names if "_quant" not in n] == [v.name for v in plain.all()]
