@@ -102,13 +102,13 @@ cifar_distort_kernel(const uint8_t* __restrict__ images, const long long* __rest
     s_coef = cifar_stats(tx, txx, S, factor[b]);
   }
   __syncthreads();
-  const CifarCoef k = s_coef;
+  const float mul = s_coef.mul;          // mean / add stay in shared memory: they are indexed by the channel
   float* dst = out + (size_t)b * P * 3;
   for (int e = threadIdx.x; e < P * 3; e += 128) {
     const int p = e / 3, c = e - p * 3;
     const int yy = p / S, xx = p - yy * S;
     const uint8_t v = rec[((y0 + yy) * kSrc + x0 + (fl ? S - 1 - xx : xx)) * 3 + c];
-    dst[e] = ((float)v - k.mean[c]) * k.mul + k.add[c];
+    dst[e] = ((float)v - s_coef.mean[c]) * mul + s_coef.add[c];
   }
 }
 
