@@ -57,17 +57,40 @@ _TV_DECODE = []          # [callable or None], resolved on first use (the import
 
 
 def _torchvision_decoder():
+    """torchvision's libjpeg-turbo binding, reached through its operator library alone: importing the torchvision
+    package costs ~8 s per (worker) process, loading ``image.so`` costs nothing."""
     if not _TV_DECODE:
+        dec = None
         try:
-            from torchvision.io import ImageReadMode, decode_jpeg as tv_decode
+            import importlib.util
+            spec = importlib.util.find_spec("torchvision")
+            lib = os.path.join(os.path.dirname(spec.origin), "image.so") if spec and spec.origin else ""
+            if os.path.exists(lib):
+                torch.ops.load_library(lib)
+                op = torch.ops.image.decode_jpeg
+                RGB = 3                                           # torchvision.io.ImageReadMode.RGB
 
-            def dec(buf: bytes) -> np.ndarray:
-                chw = tv_decode(torch.frombuffer(bytearray(buf), dtype=torch.uint8), mode=ImageReadMode.RGB)
-                return chw.permute(1, 2, 0).contiguous().numpy()
-            _TV_DECODE.append(dec)
+                def dec(buf: bytes) -> np.ndarray:
+                    chw = op(torch.frombuffer(bytearray(buf), dtype=torch.uint8), RGB, False)
+                    return chw.permute(1, 2, 0).contiguous().numpy()
+                probe = dec(_PROBE_JPEG)                          # an operator with another signature fails here
+                if probe.shape != (1, 1, 3):
+                    dec = None
         except Exception:
-            _TV_DECODE.append(None)
+            dec = None
+        _TV_DECODE.append(dec)
     return _TV_DECODE[0]
+
+
+# 1x1 white baseline JPEG: checks the operator's calling convention once per process
+_PROBE_JPEG = bytes.fromhex(
+    "ffd8ffe000104a46494600010100000100010000ffdb004300080606070605080707070909080a0c140d0c0b0b0c1912130f141d1a1f"
+    "1e1d1a1c1c20242e2720222c231c1c2837292c30313434341f27393d38323c2e333432ffc0000b080001000101011100ffc4001f0000"
+    "010501010101010100000000000000000102030405060708090a0bffc400b5100002010303020403050504040000017d010203000411"
+    "05122131410613516107227114328191a1082342b1c11552d1f02433627282090a161718191a25262728292a3435363738393a434445"
+    "464748494a535455565758595a636465666768696a737475767778797a838485868788898a92939495969798999aa2a3a4a5a6a7a8a9"
+    "aab2b3b4b5b6b7b8b9bac2c3c4c5c6c7c8c9cad2d3d4d5d6d7d8d9dae1e2e3e4e5e6e7e8e9eaf1f2f3f4f5f6f7f8f9faffda00080101"
+    "00003f00f7faffd9")
 
 
 def decode_jpeg_u8(buf: bytes) -> np.ndarray:
