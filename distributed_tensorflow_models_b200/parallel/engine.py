@@ -153,6 +153,10 @@ class Trainer:
             self._run_forward(x0, y0, True, build=True)
         self.store.freeze()
         self.store.to(self.device)
+        if self.setup.quantize and not any(v.tf_layout == "minmax" for v in self.store.all()):
+            raise ValueError("--quantize: %r builds its layers without the slim layer functions that carry the "
+                             "fake-quantisation hooks (plain CNN and the tf.layers ResNet); nothing would be "
+                             "quantised" % self.setup.model)
         if self.setup.quantize:
             # the quant_delay switch lives in device memory: flipping it needs no re-capture of the step graph
             self.store.quant.gate = torch.zeros((), dtype=torch.float32, device=self.device)

@@ -94,6 +94,17 @@ def conv2d(inputs: torch.Tensor, num_filters_out: int, kernel_size, stride=1, pa
                        tf_shape=(kh, kw, cin, num_filters_out), fan_in=kh * kw * cin,
                        fan_out=kh * kw * num_filters_out)
         fuse_relu = _is_relu(activation)
+        quant = Q.current()
+        if quant is not None:                  # --quantize: folded batch norm + fake-quantised weights / output
+            bn, b = None, None
+            if batch_norm_params is not None:
+                bn = dict(batch_norm_params, is_training=is_training)
+            elif use_bias:
+                b = V.variable(biases_name, (num_filters_out,),
+                               initializer=biases_initializer or V.constant_initializer(bias), trainable=trainable,
+                               restore=restore)
+            return Q.folded_layer(quant, lambda wq: Fn.conv2d(inputs, wq, None, (sh, sw), padding), w, b,
+                                  num_filters_out, (num_filters_out, 1, 1, 1), bn, activation, trainable)
         if batch_norm_params is not None:
             if getattr(store, "fuse_bn", False) and inputs.is_cuda and Fn.use_native(inputs) and is_training:
                 from ..ops import native_ops

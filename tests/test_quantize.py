@@ -224,3 +224,17 @@ def test_residual_additions_get_a_range_of_their_own(model, adds):
     names = [v.name for v in quant.all()]
     assert sum(n.endswith("add_quant/min_max") for n in names) == adds
     assert [n for n in names if "_quant" not in n] == [v.name for v in plain.all()]
+
+
+def test_first_class_models_quantise_through_the_old_slim_layers_or_say_that_they_cannot():
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.randn(4, 32, 32, 3, generator=g), torch.randint(0, 10, (4,), generator=g)
+    t = Trainer(TrainSetup(model="alexnet", batch_size=4, cuda_graph=False, quantize=True))
+    names = [v.name for v in t.store.all() if "_quant" in v.name]
+    assert len(names) == 16 and names[0] == "partitioned_space/alexnet_v2/conv1/weights_quant/min_max"
+    losses_ = [float(t.train_step(x, y)["loss"]) for _ in range(4)]
+    assert all(np.isfinite(losses_)) and losses_[-1] < losses_[0]
+    for model in ("cnn", "resnet"):
+        with pytest.raises(ValueError, match="--quantize"):
+            Trainer(TrainSetup(model=model, batch_size=4, cuda_graph=False, quantize=True))
