@@ -71,7 +71,18 @@ def main(argv=None) -> int:
     ap.add_argument("--imagenet_metadata_file", default="imagenet_metadata.txt")
     ap.add_argument("--bounding_box_file", default="./imagenet_2012_bounding_boxes.csv")
     a = ap.parse_args(argv)
-    synsets = [l.strip() for l in open(a.labels_file) if l.strip()]
+    if os.path.exists(a.labels_file):
+        synsets = [l.strip() for l in open(a.labels_file) if l.strip()]
+    else:
+        # the ILSVRC synsets file is the sorted list of the 1000 class directories: without it, read them off the
+        # training directory (labels then come out the same, 1..1000 in that order)
+        synsets = sorted(d for d in os.listdir(a.train_directory)
+                         if os.path.isdir(os.path.join(a.train_directory, d)))
+        if not synsets:
+            raise SystemExit("--labels_file %r not found and %r has no class directories" %
+                             (a.labels_file, a.train_directory))
+        print("labels file %r not found: %d classes taken from the directories of %s" %
+              (a.labels_file, len(synsets), a.train_directory))
     humans = build_synset_lookup(a.imagenet_metadata_file)
     boxes = build_bounding_box_lookup(a.bounding_box_file)
     for name, d, shards in (("validation", a.validation_directory, a.validation_shards),

@@ -484,3 +484,34 @@ def test_imagenet_pipeline_process_workers_and_fast_colour_math(tmp_path):
         a = stepwise(img.clone(), tid, random.Random(7))
         b = imagenet.distort_color(img.clone(), tid, random.Random(7))
         assert float((a - b).abs().max()) < 1e-5
+
+
+def test_build_imagenet_data_without_a_synsets_file(tmp_path, capsys):
+    """The ILSVRC synsets file is the sorted list of the class directories: the builder reads the classes off the
+    training tree when the file is not there, and labels come out 1..N in that order (0 = background)."""
+    from PIL import Image
+    from distributed_tensorflow_models_b200.data import build_imagenet_data as bimd
+    rs = np.random.RandomState(0)
+    for split, per in (("train", 3), ("val", 1)):
+        for syn in ("n02000000", "n01000000"):
+            os.makedirs(tmp_path / split / syn)
+            for i in range(per):
+                Image.fromarray(rs.randint(0, 255, (20, 24, 3), dtype=np.uint8)).save(
+                    tmp_path / split / syn / f"{syn}_{i}.JPEG")
+    out = tmp_path / "records"
+    os.makedirs(out)
+    assert bimd.main(["--train_directory", str(tmp_path / "train"), "--validation_directory", str(tmp_path / "val"),
+                      "--output_directory", str(out), "--train_shards", "2", "--validation_shards", "1",
+                      "--num_threads", "1", "--labels_file", str(tmp_path / "missing.txt"),
+                      "--imagenet_metadata_file", str(tmp_path / "missing_too.txt"),
+                      "--bounding_box_file", str(tmp_path / "none.csv")]) == 0
+    assert "2 classes taken from the directories" in capsys.readouterr().out
+    got = {}
+    for p in sorted(os.listdir(out)):
+        for rec in tfrecord.read_records(str(out / p)):
+            image, label, bbox, text = imagenet.parse_example_proto(rec)
+            got.setdefault(p.split("-")[0], []).append((int(label), text))
+    assert sorted(got["train"]) == [(1, b"n01000000")] * 3 + [(2, b"n02000000")] * 3
+    assert sorted(got["validation"]) == [(1, b"n01000000"), (2, b"n02000000")]
+    with pytest.raises(SystemExit):
+        bimd.main(["--train_directory", str(out), "--labels_file", str(tmp_path / "missing.txt")])
