@@ -203,6 +203,19 @@ def test_launcher_host_lists_usage_and_all_pairs():
         importlib.import_module(f"distributed_tensorflow_models_b200.eval.{mod}")
 
 
+def test_launcher_divides_the_cores_of_a_host_among_its_local_processes(monkeypatch):
+    from distributed_tensorflow_models_b200 import launcher
+    monkeypatch.delenv("OMP_NUM_THREADS", raising=False)
+    ps_env, w_env = launcher.local_thread_shares(["localhost"], ["localhost", "localhost"], cores=8)
+    assert ps_env["OMP_NUM_THREADS"] == "1" and w_env == {"OMP_NUM_THREADS": "3", "MKL_NUM_THREADS": "3"}
+    assert launcher.local_thread_shares([], ["localhost"] * 8, cores=192)[1]["OMP_NUM_THREADS"] == "24"
+    assert launcher.local_thread_shares(["localhost"], ["localhost"] * 16, cores=4)[1]["OMP_NUM_THREADS"] == "1"
+    # remote hosts do not count, a single local process keeps the machine, and the user's own setting wins
+    assert launcher.local_thread_shares(["far-away"], ["localhost"], cores=8) == ({}, {})
+    monkeypatch.setenv("OMP_NUM_THREADS", "5")
+    assert launcher.local_thread_shares(["localhost"], ["localhost", "localhost"], cores=8) == ({}, {})
+
+
 def test_launcher_accepts_zoo_networks(tmp_path, monkeypatch):
     """`train.sh <registry name> <mode>` runs the generic trainer for networks outside the six trained families."""
     from distributed_tensorflow_models_b200 import launcher
