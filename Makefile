@@ -1,7 +1,7 @@
 # Convenience targets; everything here is a one-liner you can also type yourself (README.md "Use").
 PY ?= python
 
-.PHONY: build test gpu-test bench bench8 sass clean
+.PHONY: build test gpu-test bench bench8 bench-input sass clean
 
 build:            ## nvcc -gencode arch=compute_100a,code=sm_100a for every csrc/*.cu, in-tree .so
 	$(PY) -c "import __graft_entry__ as g; g.build()"
@@ -18,6 +18,9 @@ bench: build      ## headline: ResNet-32 b128 BSP on one GPU, one JSON line
 bench8: build     ## weak scaling on 8 GPUs
 	$(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 \
 	    bench.py --gpus 8 --steps 50 --warmup 10
+
+bench-input: build  ## host input pipelines (no GPU): CIFAR-10 and ImageNet, native passes vs torch / NumPy
+	$(PY) scripts/bench_input_pipeline.py
 
 sass: build       ## SASS of the built library (compare with profiles/sass/)
 	cuobjdump -sass distributed_tensorflow_models_b200/_native/libdtfb200.so | less
