@@ -171,6 +171,26 @@ def test_device_kernel_matches_the_host_pass(size):
 
 
 
+def test_device_resident_pipeline_feeds_the_same_batches_as_the_host_pipeline(tmp_path):
+    """DeviceCifar10Batches behind the prefetcher (upload of 21 bytes per image + kernel on the copy stream, event
+    ordered against the consumer) next to the host pipeline behind the same prefetcher."""
+    from distributed_tensorflow_models_b200.data import synthetic
+    from distributed_tensorflow_models_b200.utils.pipeline import DevicePrefetcher
+    dev = torch.device("cuda", 0)
+    synthetic.write_cifar10_binary(str(tmp_path), train_per_file=40, test=8)
+    host = cifar10.Cifar10Batches(str(tmp_path), 16, 24, seed=3)
+    resident = cifar10.DeviceCifar10Batches(str(tmp_path), 16, 24, device=dev, seed=3)
+    a, b = DevicePrefetcher(host, dev), DevicePrefetcher(resident, dev)
+    try:
+        for k in range(30):                                  # several passes over the three device buffers
+            (xa, ya), (xb, yb) = next(a), next(b)
+            assert xb.is_cuda and xb.shape == (16, 24, 24, 3) and torch.equal(ya, yb), k
+            assert torch.allclose(xa, xb, atol=2e-6), (k, float((xa - xb).abs().max()))
+            xb.add_(1.0)                                     # a consumer may scribble over its batch
+    finally:
+        host.close(), resident.close()
+
+
 def test_quantised_trainer_on_the_native_kernels_under_a_cuda_graph():
     """The whole quantised step (range kernels, fake-quant forward / backward, folded batch norm) inside the captured
     CUDA graph: the delay switch flips between replays without a re-capture, the ranges keep moving, training learns."""
