@@ -375,6 +375,9 @@ class RecordBatch:
         if dst.is_cuda:
             import ctypes as C
             from .. import _native as nat
+            if own.images_dev is None or own.images_dev.device != dst.device:
+                raise RuntimeError("the records live on %s but the batch is wanted on %s: build DeviceCifar10Batches "
+                                   "with device=<the training device>" % (own.device, dst.device))
             st = self.stage.to(dst.device, non_blocking=True)
             base, b = st.data_ptr(), self.b
             vp = C.c_void_p
