@@ -58,7 +58,7 @@ def _r(*shape, seed=0, scale=1.0):
 @pytest.mark.parametrize("cfg", [
     # n, h, w, c, c_out, k, rate, padding
     (2, 28, 28, 32, 64, 3, 2, "SAME"),       # ResNet / MobileNet output_stride=16: last stage dilated by 2
-    (2, 17, 19, 16, 32, 3, 4, "SAME"),       # output_stride=8; extents that are not multiples of the rate
+    (2, 33, 35, 16, 32, 3, 4, "SAME"),       # output_stride=8; extents that are not multiples of the rate
     (2, 21, 23, 16, 16, 3, 3, "VALID"),
 ])
 def test_atrous_conv2d_and_depthwise(cfg):
