@@ -371,7 +371,10 @@ def nudged_range(mn: torch.Tensor, mx: torch.Tensor, bits: int, narrow: bool):
     """TensorFlow's range nudging: move [min, max] so that 0.0 is exactly one of the quantisation steps.
     -> (nudged_min, nudged_max, step)"""
     qmin, qmax = (1.0 if narrow else 0.0), float(2 ** bits - 1)
-    scale = (mx - mn) / (qmax - qmin)
+    # tensor / tensor: a correctly rounded fp32 division like TensorFlow's and the kernel's.  tensor / python-scalar
+    # is evaluated by the CUDA backend as a multiplication by fl(1/255), which lands on the other side of the
+    # 127.5 rounding tie of the default (-6, 6) range and moves every clamped value by one step.
+    scale = (mx - mn) / torch.full_like(mx, qmax - qmin)
     zp = qmin - mn / scale
     # std::round: halves away from zero (torch.round is half-to-even)
     zp_r = torch.sign(zp) * torch.floor(zp.abs() + 0.5)
