@@ -21,6 +21,7 @@
 #include "../include/dtf_b200.h"
 #include "host_common.h"
 #include "umma.cuh"
+#include "ps_gate.cuh"
 #include "conv_epilogue.cuh"
 
 namespace dtf {
@@ -239,6 +240,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constan
       const bool has_aff = p.in_scale != nullptr;
       int stage = 0; uint32_t phase = 0;
       int gseq = 0;
+      weight_gate_warp(p);     // PS pull: the owners' updates of this layer's bucket must have landed (ps_gate.cuh)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;
         const int m0 = mt * BM, n0 = nt * BN;
@@ -302,6 +304,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constan
     const bool div1 = (p.div_h == 1) && (p.div_w == 1);
     int2* rtab = row_table + grp * BM;
     int q = 0, q_grp = 0, stage = 0; uint32_t phase = 0;
+    if (gt == 0) weight_gate_thread(p);   // this thread issues the group's weight-tile loads (PS pull gate)
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int mt = tile / cfg.n_tiles, nt = tile - mt * cfg.n_tiles;

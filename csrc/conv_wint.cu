@@ -25,6 +25,7 @@
 #include "../include/dtf_b200.h"
 #include "host_common.h"
 #include "umma.cuh"
+#include "ps_gate.cuh"
 
 namespace dtf {
 
@@ -276,6 +277,7 @@ conv_wint_kernel(const __grid_constant__ CUtensorMap tmapW, const dtf_conv_gemm_
   } else if (warp == T_TMA_WARP) {
     // =========================== weight loads ==================================================
     const int per32 = cfg.CB >= 32 ? (cfg.CB >> 5) : 1;
+    weight_gate_warp(p);       // PS pull: the owners' updates of this layer's bucket must have landed (ps_gate.cuh)
     if (cfg.b_resident) {
       if (elect_one()) {
         for (int kb = 0; kb < cfg.n_kb; ++kb) {

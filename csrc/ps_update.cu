@@ -1,16 +1,23 @@
 // K16 + C1/C2/C3/C4: parameter-server update kernels.
 //
 //  dtf_fused_update   one rank: w/slots/EMA update of a flat range from a local gradient (also the N=1 path)
-//  dtf_ps_bsp_step    BSP step over peer-mapped HBM in ONE kernel per rank:
-//                       wait "gradients ready" from all ranks            (flag words in peer memory)
-//                       push : owner reads its range of every rank's gradient buffer over NVLink (P2P
-//                              ld.global), averages, applies SGD / TF1-RMSProp(+momentum) / weight decay /
-//                              EMA in registers, writes the fp32 master range              [reduce-scatter + K16]
-//                       signal "range updated" to all ranks, wait for all owners
-//                       pull : copy every other owner's range from its HBM into the local replica  [all-gather]
+//  dtf_ps_bucket_step BSP push of ONE bucket (a contiguous range of the flat buffer = a group of layers), launched
+//                     on a side stream as soon as the backward pass has produced the bucket's gradients:
+//                       signal "my gradients of bucket b are complete" to all ranks, wait for everybody's
+//                       push : the owner of each 1/W of the bucket forms the mean of the W gradient copies
+//                              (multimem.ld_reduce in the NVSwitch, or P2P ld.global), applies SGD /
+//                              TF1-RMSProp(+momentum) / weight decay / EMA in registers  [reduce-scatter + K16]
+//                       pull : and stores the new values into EVERY rank's replica (multimem.st, or P2P st) [all-gather]
+//                       signal "my part of bucket b is updated" to all ranks — and exit; nobody waits here
+//  dtf_ps_gate        the other half of the pull: wait until every owner's part of buckets [b0, b1) carries this
+//                     step's epoch.  The convolution kernels run the same wait in their weight-load warp
+//                     (dtf_conv_gemm_params.gate_*), so the next forward pass starts while later buckets of the
+//                     previous step are still arriving.
 //  dtf_ps_async_step  ASP/SSP step: the *pusher* applies its own gradient to every owner's master range
-//                       (red.global.add.f32 for SGD — Hogwild, the reference runs use_locking=False), bumps the
-//                       global step on rank 0 with a system-scope atomic, then refreshes its replica; no barrier
+//                       (red.global.add.v4.f32 for SGD — Hogwild, the reference runs use_locking=False), bumps
+//                       the global step on rank 0 with a system-scope atomic, then refreshes its replica with
+//                       128-bit loads; no barrier.  RMSProp: the scaled gradient is handed to the owner's inbox
+//                       (one-way red.add) and the owner applies it to its slots locally.
 //  dtf_ssp_clock      publish clock[rank] = step in every peer's clock table, spin (bounded) while
 //                       step > min(clock) + bound                          [replaces the Thrift RPC loop]
 //
@@ -60,13 +67,13 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   return v;
 }
 
-// Wait until flags[q] >= epoch for every q < W.  Returns false on timeout (~2 s).
-__device__ bool wait_all(const unsigned int* flags, int W, unsigned int epoch) {
+// Spin (one thread) until flags[q] >= epoch for every q < n.  Bounded: false after timeout_cycles SM clocks.
+__device__ bool wait_all(const unsigned int* flags, int n, unsigned int epoch, long long timeout_cycles) {
   const long long t0 = clock64();
-  for (int q = 0; q < W; ++q) {
+  for (int q = 0; q < n; ++q) {
     while ((int)(ld_acquire_sys(flags + q) - epoch) < 0) {
       __nanosleep(64);
-      if (clock64() - t0 > 4000000000LL) return false;
+      if (clock64() - t0 > timeout_cycles) return false;
     }
   }
   return true;
@@ -87,24 +94,35 @@ fused_update_kernel(float* __restrict__ w, const float* __restrict__ g, float* _
   }
 }
 
-struct BspArgs {
+// ---------------------------------------------------------------------------------------------------------
+// BSP, one bucket.  Flag block of a rank (uint32 words in its symmetric buffer, written by its peers):
+//   ready  [b*W + q]            rank q's gradients of bucket b are complete for epoch e
+//   updated[(B + b)*W + q]      owner q has written its part of bucket b into THIS rank's replica for epoch e
+// Epochs count completed steps (device word *epoch_ptr, bumped by the step's last bucket), so a captured graph
+// replays without host-side arguments changing.  Within the bucket [lo, lo+len) rank r owns
+// [lo + r*chunk, min(lo + (r+1)*chunk, lo+len)); chunk % 4 == 0.
+// ---------------------------------------------------------------------------------------------------------
+struct BucketArgs {
   const float* const* peer_grads;   // [W] gradient buffers of every rank (device pointers valid on this GPU)
   float* const* peer_params;        // [W] parameter replicas of every rank
-  unsigned int* const* peer_flags;  // [W] flag blocks of every rank: [0,W) grads-ready, [W,2W) range-updated
-  unsigned int* local_counter;      // block-completion counter (local, zeroed by the kernel's last block)
+  unsigned int* const* peer_flags;  // [W] flag blocks of every rank
+  unsigned int* local_counter;      // block-completion counter of this bucket (local, reset by the last block)
   unsigned int* status;             // 0 = ok, 1 = timeout
   int rank, W;
-  long long shard;                  // elements per rank (flat placement: range of rank r = [r*shard,(r+1)*shard))
+  int ready_off, updated_off;       // word offsets of this bucket's rows inside a flag block
+  long long lo, len, chunk;
   long long wd_boundary;
-  float* ms; float* mom; float* ema;   // slots of the local range (length shard)
+  float* ms; float* mom; float* ema;   // slots of this rank's part of the bucket (length <= chunk)
   const float* hyper;
   int kind;
-  unsigned int* epoch_ptr;          // local step counter: epoch = *epoch_ptr + 1 (device memory => graph-safe)
+  const unsigned int* epoch_ptr;    // completed steps; this launch works for epoch *epoch_ptr + 1
+  unsigned int* epoch_out;          // non-null on the step's last bucket: receives the new epoch at the end
   // NVLS (NVSwitch multicast) addresses of the same symmetric buffers, or nullptr: with them the gradient reduction
   // happens inside the switch (multimem.ld_reduce) and the updated range is stored to every replica at once
-  // (multimem.st), so the pull phase disappears.
+  // (multimem.st).
   const float* mc_grads;
   float* mc_params;
+  long long timeout_cycles;
 };
 
 __device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const float* mc_addr) {
@@ -120,95 +138,133 @@ __device__ __forceinline__ void multimem_st_f32x4(float* mc_addr, const float4 v
                "f"(v.z), "f"(v.w)
                : "memory");
 }
+__device__ __forceinline__ float4 ld_peer_f32x4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_f32x4(float* p, const float4 v) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+constexpr int PUSH_UNROLL = 4;      // 16-byte reductions in flight per thread
 
 __global__ void __launch_bounds__(512)
-ps_bsp_step_kernel(const BspArgs a) {
+ps_bucket_kernel(const BucketArgs a) {
   __shared__ int s_ok;
   const int W = a.W, me = a.rank;
-  unsigned int* myflags = a.peer_flags[me];
-  const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(a.epoch_ptr) + 1u;
-  // ---- B1: announce "my gradients are complete", then wait for everybody's -----------------------------
-  if (blockIdx.x == 0 && threadIdx.x < W) {
-    __threadfence_system();
-    st_release_sys(a.peer_flags[threadIdx.x] + me, epoch);
+  const unsigned int epoch = *reinterpret_cast<const volatile unsigned int*>(a.epoch_ptr) + 1u;
+  // ---- "my gradients of this bucket are complete" -> every rank; then wait for everybody's -----------------
+  if (W > 1) {
+    if (blockIdx.x == 0 && threadIdx.x < W) {
+      __threadfence_system();
+      st_release_sys(a.peer_flags[threadIdx.x] + a.ready_off + me, epoch);
+    }
+    if (threadIdx.x == 0) s_ok = wait_all(a.peer_flags[me] + a.ready_off, W, epoch, a.timeout_cycles) ? 1 : 0;
+    __syncthreads();
+    if (!s_ok) { if (threadIdx.x == 0) atomicExch(a.status, 1u); return; }
   }
-  if (threadIdx.x == 0) s_ok = wait_all(myflags, W, epoch) ? 1 : 0;
-  __syncthreads();
-  if (!s_ok) { if (threadIdx.x == 0) *a.status = 1; return; }
 
-  // ---- push: reduce my range over all ranks' gradients + optimiser -------------------------------------
+  // ---- push: reduce my part over all ranks' gradients + optimiser; pull: store into every replica -----------
   const Hyper h = load_hyper(a.hyper);
-  const long long lo = (long long)me * a.shard;
+  const long long lo = a.lo + (long long)me * a.chunk;
+  long long n = a.len - (long long)me * a.chunk;
+  n = n < 0 ? 0 : (n > a.chunk ? a.chunk : n);
   const float invW = 1.f / (float)W;
   float* wmine = a.peer_params[me] + lo;
-  const long long n4 = a.shard >> 2;
-  for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4;
-       i4 += (long long)gridDim.x * blockDim.x) {
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.mc_grads != nullptr) {
-      g = multimem_ld_reduce_add_f32x4(a.mc_grads + lo + (i4 << 2));     // sum over all ranks, formed in the switch
-    } else {
-      for (int q = 0; q < W; ++q) {
-        const int src = (me + q) % W;      // stagger peers so ranks do not all hit the same GPU at once
-        const float4 v = *reinterpret_cast<const float4*>(a.peer_grads[src] + lo + (i4 << 2));
-        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const bool use_mc = a.mc_grads != nullptr && W > 1;
+  for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < n4; base += stride * PUSH_UNROLL) {
+    float4 g[PUSH_UNROLL];
+    // issue all the remote reductions of this round before touching any of them
+#pragma unroll
+    for (int u = 0; u < PUSH_UNROLL; ++u) {
+      const long long i4 = base + u * stride;
+      g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i4 < n4) {
+        if (use_mc) {
+          g[u] = multimem_ld_reduce_add_f32x4(a.mc_grads + lo + (i4 << 2));   // sum over all ranks, formed in the switch
+        } else {
+          for (int q = 0; q < W; ++q) {
+            const int src = (me + q) % W;      // stagger peers so ranks do not all hit the same GPU at once
+            const float4 v = ld_peer_f32x4(a.peer_grads[src] + lo + (i4 << 2));
+            g[u].x += v.x; g[u].y += v.y; g[u].z += v.z; g[u].w += v.w;
+          }
+        }
       }
     }
-    g.x *= invW; g.y *= invW; g.z *= invW; g.w *= invW;
-    float4 wv = *reinterpret_cast<float4*>(wmine + (i4 << 2));
-    float4 m2 = make_float4(0.f, 0.f, 0.f, 0.f), mo = m2;
-    if (a.kind == 1) {
-      m2 = *reinterpret_cast<float4*>(a.ms + (i4 << 2));
-      mo = *reinterpret_cast<float4*>(a.mom + (i4 << 2));
-    }
-    const long long gi = lo + (i4 << 2);
-    wv.x = update_elem(a.kind, h, wv.x, g.x, gi + 0 < a.wd_boundary, &m2.x, &mo.x);
-    wv.y = update_elem(a.kind, h, wv.y, g.y, gi + 1 < a.wd_boundary, &m2.y, &mo.y);
-    wv.z = update_elem(a.kind, h, wv.z, g.z, gi + 2 < a.wd_boundary, &m2.z, &mo.z);
-    wv.w = update_elem(a.kind, h, wv.w, g.w, gi + 3 < a.wd_boundary, &m2.w, &mo.w);
-    if (a.mc_params != nullptr && W > 1) multimem_st_f32x4(a.mc_params + lo + (i4 << 2), wv);   // every replica, mine too
-    else *reinterpret_cast<float4*>(wmine + (i4 << 2)) = wv;
-    if (a.kind == 1) {
-      *reinterpret_cast<float4*>(a.ms + (i4 << 2)) = m2;
-      *reinterpret_cast<float4*>(a.mom + (i4 << 2)) = mo;
-    }
-    if (a.ema && h.ema_decay >= 0.f) {
-      float4 e = *reinterpret_cast<float4*>(a.ema + (i4 << 2));
-      const float k = 1.f - h.ema_decay;
-      e.x -= k * (e.x - wv.x); e.y -= k * (e.y - wv.y); e.z -= k * (e.z - wv.z); e.w -= k * (e.w - wv.w);
-      *reinterpret_cast<float4*>(a.ema + (i4 << 2)) = e;
+#pragma unroll
+    for (int u = 0; u < PUSH_UNROLL; ++u) {
+      const long long i4 = base + u * stride;
+      if (i4 >= n4) break;
+      float4 gv = g[u];
+      gv.x *= invW; gv.y *= invW; gv.z *= invW; gv.w *= invW;
+      float4 wv = *reinterpret_cast<float4*>(wmine + (i4 << 2));
+      float4 m2 = make_float4(0.f, 0.f, 0.f, 0.f), mo = m2;
+      if (a.kind == 1) {
+        m2 = *reinterpret_cast<float4*>(a.ms + (i4 << 2));
+        mo = *reinterpret_cast<float4*>(a.mom + (i4 << 2));
+      }
+      const long long gi = lo + (i4 << 2);
+      wv.x = update_elem(a.kind, h, wv.x, gv.x, gi + 0 < a.wd_boundary, &m2.x, &mo.x);
+      wv.y = update_elem(a.kind, h, wv.y, gv.y, gi + 1 < a.wd_boundary, &m2.y, &mo.y);
+      wv.z = update_elem(a.kind, h, wv.z, gv.z, gi + 2 < a.wd_boundary, &m2.z, &mo.z);
+      wv.w = update_elem(a.kind, h, wv.w, gv.w, gi + 3 < a.wd_boundary, &m2.w, &mo.w);
+      if (use_mc) {
+        multimem_st_f32x4(a.mc_params + gi, wv);                 // every replica, mine too
+      } else {
+        *reinterpret_cast<float4*>(wmine + (i4 << 2)) = wv;
+        for (int q = 1; q < W; ++q)                               // P2P stores into the other replicas
+          *reinterpret_cast<float4*>(a.peer_params[(me + q) % W] + gi) = wv;
+      }
+      if (a.kind == 1) {
+        *reinterpret_cast<float4*>(a.ms + (i4 << 2)) = m2;
+        *reinterpret_cast<float4*>(a.mom + (i4 << 2)) = mo;
+      }
+      if (a.ema && h.ema_decay >= 0.f) {
+        float4 e = *reinterpret_cast<float4*>(a.ema + (i4 << 2));
+        const float k = 1.f - h.ema_decay;
+        e.x -= k * (e.x - wv.x); e.y -= k * (e.y - wv.y); e.z -= k * (e.z - wv.z); e.w -= k * (e.w - wv.w);
+        *reinterpret_cast<float4*>(a.ema + (i4 << 2)) = e;
+      }
     }
   }
-  if (W == 1) return;
 
-  // ---- B2: last block of this rank announces "my range is updated" -------------------------------------
+  // ---- the last block to finish announces "my part of the bucket is in your replica" to every rank ---------
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int done = atomicAdd(a.local_counter, 1u);
     if (done == gridDim.x - 1) {
       *a.local_counter = 0;
-      *a.epoch_ptr = epoch;
       __threadfence_system();
-      for (int q = 0; q < W; ++q) st_release_sys(a.peer_flags[q] + W + me, epoch);
+      if (W > 1)
+        for (int q = 0; q < W; ++q) st_release_sys(a.peer_flags[(me + q) % W] + a.updated_off + me, epoch);
+      if (a.epoch_out != nullptr) { *a.epoch_out = epoch; __threadfence(); }
     }
-    s_ok = wait_all(myflags + W, W, epoch) ? 1 : 0;
   }
-  __syncthreads();
-  if (!s_ok) { if (threadIdx.x == 0) *a.status = 1; return; }
+}
 
-  // ---- pull: refresh the other owners' ranges of my replica (nothing to do when they were multicast) ------
-  if (a.mc_params != nullptr) return;
-  float* mine = a.peer_params[me];
-  const long long tot4 = n4 * (W - 1);
-  for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < tot4;
-       j += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(j / n4);
-    const long long i4 = j - (long long)k * n4;
-    const int owner = (me + 1 + k) % W;
-    const long long off = (long long)owner * a.shard + (i4 << 2);
-    *reinterpret_cast<float4*>(mine + off) = *reinterpret_cast<const float4*>(a.peer_params[owner] + off);
+// Wait until flags[0 .. n) all carry at least *epoch_ptr (the number of completed steps): "every owner's part of
+// these buckets has reached my replica".  One warp; lane q polls the words q, q+32, ...
+__global__ void ps_gate_kernel(const unsigned int* flags, int n, const unsigned int* epoch_ptr, unsigned int* status,
+                               long long timeout_cycles) {
+  const unsigned int epoch = *reinterpret_cast<const volatile unsigned int*>(epoch_ptr);
+  const long long t0 = clock64();
+  bool ok = true;
+  for (int q = threadIdx.x; q < n && ok; q += 32) {
+    while ((int)(ld_acquire_sys(flags + q) - epoch) < 0) {
+      __nanosleep(32);
+      if (clock64() - t0 > timeout_cycles) { ok = false; break; }
+    }
   }
+  if (!ok) atomicExch(status, 1u);
 }
 
 struct AsyncArgs {
@@ -224,44 +280,81 @@ struct AsyncArgs {
   int kind;
 };
 
+constexpr int ASYNC_UNROLL = 4;
+
+// ASP / SSP step of one worker, 16 bytes per access and ASYNC_UNROLL accesses in flight per thread.  Per element
+// the traffic that crosses NVLink is: SGD — one red.add out, one load back; RMSProp — the owner's two slots in
+// (one round trip, both loads issued together), their new values and the red.add of the step out.  The refresh of
+// the replica rides in the same loop as the push (opposite link directions), so the two phases overlap.
 __global__ void __launch_bounds__(512)
 ps_async_step_kernel(const AsyncArgs a) {
   const Hyper h = load_hyper(a.hyper);
   const int W = a.W, me = a.rank;
-  const long long total = a.shard * W;
+  const long long shard4 = a.shard >> 2;
+  const long long total4 = shard4 * W;
   float* mine = a.peer_params[me];
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd_system(a.global_step, 1ull);
-  // ---- push: apply my gradient to every owner's master range (owner order staggered by rank).
-  // Only one-way traffic crosses NVLink for SGD: the weight-decay term uses this worker's replica of w (what
-  // the gradient was computed from), so the update is a single red.global.add.f32 per element on the owner.
-  for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total;
-       j += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(j / a.shard);
-    const long long i = j - (long long)k * a.shard;
-    const int owner = (me + k) % W;
-    const long long gi = (long long)owner * a.shard + i;
-    float g = a.grads[gi] * h.gscale;
-    if (gi < a.wd_boundary) g = fmaf(h.wd, mine[gi], g);
-    float* wp = a.peer_params[owner] + gi;
-    if (a.kind == 0) {
-      atomicAdd(wp, -h.lr * g);                       // one-sided red.add on the owner's HBM (Hogwild)
-    } else {
-      float* msp = a.peer_ms[owner] + i;              // slots live with the owner; racy RMW is the semantics
-      float* mop = a.peer_mom[owner] + i;             // of use_locking=False
-      const float m2 = h.rms_decay * (*msp) + (1.f - h.rms_decay) * g * g;
-      const float mo = h.momentum * (*mop) + h.lr * g * rsqrtf(m2 + h.eps);
-      *msp = m2;
-      *mop = mo;
-      atomicAdd(wp, -mo);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < total4; base += stride * ASYNC_UNROLL) {
+    float4 g[ASYNC_UNROLL], m2[ASYNC_UNROLL], mo[ASYNC_UNROLL];
+    long long gi[ASYNC_UNROLL];
+    int own[ASYNC_UNROLL];
+#pragma unroll
+    for (int u = 0; u < ASYNC_UNROLL; ++u) {
+      const long long j4 = base + u * stride;
+      own[u] = -1;
+      if (j4 < total4) {
+        const int k = (int)(j4 / shard4);
+        const long long i4 = j4 - (long long)k * shard4;
+        own[u] = (me + k) % W;                 // owner order staggered by rank
+        gi[u] = (long long)own[u] * a.shard + (i4 << 2);
+        float4 gv = *reinterpret_cast<const float4*>(a.grads + gi[u]);
+        gv.x *= h.gscale; gv.y *= h.gscale; gv.z *= h.gscale; gv.w *= h.gscale;
+        // the weight-decay term uses this worker's replica of w (what the gradient was computed from)
+        const float4 wl = *reinterpret_cast<const float4*>(mine + gi[u]);
+        if (gi[u] + 0 < a.wd_boundary) gv.x = fmaf(h.wd, wl.x, gv.x);
+        if (gi[u] + 1 < a.wd_boundary) gv.y = fmaf(h.wd, wl.y, gv.y);
+        if (gi[u] + 2 < a.wd_boundary) gv.z = fmaf(h.wd, wl.z, gv.z);
+        if (gi[u] + 3 < a.wd_boundary) gv.w = fmaf(h.wd, wl.w, gv.w);
+        g[u] = gv;
+        if (a.kind == 1) {                      // slots live with the owner; racy RMW is the semantics of
+          m2[u] = ld_peer_f32x4(a.peer_ms[own[u]] + (i4 << 2));      // use_locking=False
+          mo[u] = ld_peer_f32x4(a.peer_mom[own[u]] + (i4 << 2));
+        }
+      }
     }
-  }
-  // ---- pull: refresh my replica from the masters (no barrier: stale reads are the semantics) ------------
-  __threadfence_system();
-  for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total;
-       j += (long long)gridDim.x * blockDim.x) {
-    const int owner = (int)(j / a.shard);
-    if (owner == me) continue;
-    mine[j] = *reinterpret_cast<volatile const float*>(a.peer_params[owner] + j);
+#pragma unroll
+    for (int u = 0; u < ASYNC_UNROLL; ++u) {
+      if (own[u] < 0) break;
+      float* wp = a.peer_params[own[u]] + gi[u];
+      float4 d;
+      if (a.kind == 0) {
+        d = make_float4(-h.lr * g[u].x, -h.lr * g[u].y, -h.lr * g[u].z, -h.lr * g[u].w);
+      } else {
+        const long long i = gi[u] - (long long)own[u] * a.shard;
+        float4 n2, nm;
+        n2.x = h.rms_decay * m2[u].x + (1.f - h.rms_decay) * g[u].x * g[u].x;
+        n2.y = h.rms_decay * m2[u].y + (1.f - h.rms_decay) * g[u].y * g[u].y;
+        n2.z = h.rms_decay * m2[u].z + (1.f - h.rms_decay) * g[u].z * g[u].z;
+        n2.w = h.rms_decay * m2[u].w + (1.f - h.rms_decay) * g[u].w * g[u].w;
+        nm.x = h.momentum * mo[u].x + h.lr * g[u].x * rsqrtf(n2.x + h.eps);
+        nm.y = h.momentum * mo[u].y + h.lr * g[u].y * rsqrtf(n2.y + h.eps);
+        nm.z = h.momentum * mo[u].z + h.lr * g[u].z * rsqrtf(n2.z + h.eps);
+        nm.w = h.momentum * mo[u].w + h.lr * g[u].w * rsqrtf(n2.w + h.eps);
+        *reinterpret_cast<float4*>(a.peer_ms[own[u]] + i) = n2;
+        *reinterpret_cast<float4*>(a.peer_mom[own[u]] + i) = nm;
+        d = make_float4(-nm.x, -nm.y, -nm.z, -nm.w);
+      }
+      red_add_f32x4(wp, d);                     // one-sided red.add on the owner's HBM (Hogwild)
+    }
+    // refresh my replica of the ranges I just pushed to (no barrier: stale reads are the semantics)
+    float4 fresh[ASYNC_UNROLL];
+#pragma unroll
+    for (int u = 0; u < ASYNC_UNROLL; ++u)
+      if (own[u] >= 0 && own[u] != me) fresh[u] = ld_peer_f32x4(a.peer_params[own[u]] + gi[u]);
+#pragma unroll
+    for (int u = 0; u < ASYNC_UNROLL; ++u)
+      if (own[u] >= 0 && own[u] != me) *reinterpret_cast<float4*>(mine + gi[u]) = fresh[u];
   }
   // ---- EMA of my own range, owner side (local traffic only).  The reference applies the average after
   // every worker's step; the owner sees W such steps per step of its own, so the host passes decay^W.
@@ -269,9 +362,12 @@ ps_async_step_kernel(const AsyncArgs a) {
     float* ema = a.peer_ema[me];
     const float* wm = mine + (long long)me * a.shard;
     const float k = 1.f - h.ema_decay;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.shard;
-         i += (long long)gridDim.x * blockDim.x)
-      ema[i] -= k * (ema[i] - wm[i]);
+    for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < shard4; i4 += stride) {
+      float4 e = *reinterpret_cast<float4*>(ema + (i4 << 2));
+      const float4 wv = ld_peer_f32x4(wm + (i4 << 2));
+      e.x -= k * (e.x - wv.x); e.y -= k * (e.y - wv.y); e.z -= k * (e.z - wv.z); e.w -= k * (e.w - wv.w);
+      *reinterpret_cast<float4*>(ema + (i4 << 2)) = e;
+    }
   }
 }
 
@@ -321,24 +417,48 @@ extern "C" int dtf_fused_update(float* w, const float* g, float* ms, float* mom,
   return 0;
 }
 
-extern "C" int dtf_ps_bsp_step(const float* const* peer_grads, float* const* peer_params,
-                               unsigned int* const* peer_flags, unsigned int* local_counter, unsigned int* status,
-                               int rank, int world, long long shard, long long wd_boundary, float* ms, float* mom,
-                               float* ema, const float* hyper, int kind, unsigned int* epoch_ptr,
-                               const float* mc_grads, float* mc_params, void* stream_) {
+static long long timeout_cycles_of(double timeout_s) {
+  if (!(timeout_s > 0.0)) timeout_s = 300.0;
+  return (long long)(timeout_s * 1.9e9);
+}
+
+extern "C" int dtf_ps_bucket_step(const float* const* peer_grads, float* const* peer_params,
+                                  unsigned int* const* peer_flags, unsigned int* local_counter, unsigned int* status,
+                                  int rank, int world, int ready_off, int updated_off, long long lo, long long len,
+                                  long long chunk, long long wd_boundary, float* ms, float* mom, float* ema,
+                                  const float* hyper, int kind, const unsigned int* epoch_ptr, unsigned int* epoch_out,
+                                  const float* mc_grads, float* mc_params, double timeout_s, int max_blocks,
+                                  void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-  DTF_REQUIRE(shard % 4 == 0, "shard length must be a multiple of 4 floats");
+  DTF_REQUIRE(len % 4 == 0 && chunk % 4 == 0 && lo % 4 == 0, "bucket bounds must be multiples of 4 floats");
+  DTF_REQUIRE(chunk * world >= len, "the owners' parts must cover the bucket");
   DTF_REQUIRE((mc_grads == nullptr) == (mc_params == nullptr), "multicast addresses come in pairs");
   DTF_REQUIRE(world <= 32, "flag signalling assumes world <= 32");
-  BspArgs a;
+  DTF_REQUIRE(kind == 0 || (ms && mom), "RMSProp needs its slots");
+  BucketArgs a;
   a.peer_grads = peer_grads; a.peer_params = peer_params; a.peer_flags = peer_flags;
-  a.local_counter = local_counter; a.status = status; a.rank = rank; a.W = world; a.shard = shard;
-  a.wd_boundary = wd_boundary; a.ms = ms; a.mom = mom; a.ema = ema; a.hyper = hyper; a.kind = kind; a.epoch_ptr = epoch_ptr;
-  a.mc_grads = mc_grads; a.mc_params = mc_params;
-  // every block must be co-resident (blocks wait on one another through the flags): one block per SM at most
-  long long b = ((shard >> 2) + 511) / 512;
-  const int grid = (int)(b < num_sms() ? (b > 0 ? b : 1) : num_sms());
-  ps_bsp_step_kernel<<<grid, 512, 0, stream>>>(a);
+  a.local_counter = local_counter; a.status = status; a.rank = rank; a.W = world;
+  a.ready_off = ready_off; a.updated_off = updated_off; a.lo = lo; a.len = len; a.chunk = chunk;
+  a.wd_boundary = wd_boundary; a.ms = ms; a.mom = mom; a.ema = ema; a.hyper = hyper; a.kind = kind;
+  a.epoch_ptr = epoch_ptr; a.epoch_out = epoch_out; a.mc_grads = mc_grads; a.mc_params = mc_params;
+  a.timeout_cycles = timeout_cycles_of(timeout_s);
+  // blocks do not wait on one another (each one polls the flags itself), so the grid need not be co-resident;
+  // it is sized so that a thread runs about one unrolled round, capped to leave SMs to the backward pass
+  long long n = len - (long long)rank * chunk;
+  n = n < 0 ? 0 : (n > chunk ? chunk : n);
+  long long b = ((n >> 2) + 512LL * PUSH_UNROLL - 1) / (512LL * PUSH_UNROLL);
+  const int cap = max_blocks > 0 ? max_blocks : num_sms();
+  const int grid = (int)(b < cap ? (b > 0 ? b : 1) : cap);
+  ps_bucket_kernel<<<grid, 512, 0, stream>>>(a);
+  DTF_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int* epoch_ptr, unsigned int* status,
+                           double timeout_s, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (n <= 0) return 0;
+  ps_gate_kernel<<<1, 32, 0, stream>>>(flags, n, epoch_ptr, status, timeout_cycles_of(timeout_s));
   DTF_CHECK(cudaGetLastError());
   return 0;
 }
@@ -348,11 +468,15 @@ extern "C" int dtf_ps_async_step(const float* grads, float* const* peer_params, 
                                  int rank, int world, long long shard, long long wd_boundary, const float* hyper,
                                  int kind, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(shard % 4 == 0, "shard length must be a multiple of 4 floats");
+  DTF_REQUIRE(kind == 0 || (peer_ms && peer_mom), "RMSProp needs its slots");
   AsyncArgs a;
   a.grads = grads; a.peer_params = peer_params; a.peer_ms = peer_ms; a.peer_mom = peer_mom; a.peer_ema = peer_ema;
   a.global_step = global_step; a.rank = rank; a.W = world; a.shard = shard; a.wd_boundary = wd_boundary;
   a.hyper = hyper; a.kind = kind;
-  ps_async_step_kernel<<<update_grid(shard * world), 512, 0, stream>>>(a);
+  long long b = ((shard * world >> 2) + 512LL * ASYNC_UNROLL - 1) / (512LL * ASYNC_UNROLL);
+  const long long cap = 2LL * num_sms();
+  ps_async_step_kernel<<<(int)(b < cap ? (b > 0 ? b : 1) : cap), 512, 0, stream>>>(a);
   DTF_CHECK(cudaGetLastError());
   return 0;
 }
@@ -362,8 +486,8 @@ extern "C" int dtf_ssp_clock(unsigned int* const* peer_clocks, int rank, int wor
                              void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(world <= 32, "clock table assumes world <= 32");
-  const long long cycles = (long long)(timeout_s * 1.9e9);
-  ssp_clock_kernel<<<1, 32, 0, stream>>>(peer_clocks, rank, world, step, bound, cycles, status, waited_polls);
+  ssp_clock_kernel<<<1, 32, 0, stream>>>(peer_clocks, rank, world, step, bound, timeout_cycles_of(timeout_s), status,
+                                         waited_polls);
   DTF_CHECK(cudaGetLastError());
   return 0;
 }

@@ -41,6 +41,8 @@ class ConvGemmParams(C.Structure):
         ("fin_invstd", C.c_void_p),
         ("fin_inv_count", C.c_float), ("fin_unbias", C.c_float), ("fin_eps", C.c_float), ("fin_decay", C.c_float),
         ("fin_update_moving", C.c_int),
+        ("gate_flags", C.c_void_p), ("gate_n", C.c_int), ("gate_epoch", C.c_void_p), ("gate_status", C.c_void_p),
+        ("gate_timeout_cycles", C.c_longlong),
     ]
 
 
@@ -114,9 +116,36 @@ def check(rc: int, what: str) -> None:
         raise NativeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")
 
 
-def stream_ptr() -> C.c_void_p:
-    """Current torch CUDA stream as a ``void*`` for the C ABI."""
+_pre_launch = [None]
+
+
+def set_pre_launch(fn) -> None:
+    """Install (or clear, with ``None``) a callable that runs in front of every native launch.  The symmetric-memory
+    transport uses it to put parameter-server pull gates that no convolution has taken over ahead of whatever kernel
+    comes next (parallel/symm.py)."""
+    _pre_launch[0] = fn
+
+
+def run_pre_launch() -> None:
+    """What a native launch would trigger, for code that is about to read parameters with a PyTorch kernel."""
+    if _pre_launch[0] is not None:
+        fn, _pre_launch[0] = _pre_launch[0], None
+        try:
+            fn()
+        finally:
+            _pre_launch[0] = fn
+
+
+def stream_ptr(hook: bool = True) -> C.c_void_p:
+    """Current torch CUDA stream as a ``void*`` for the C ABI (every launch wrapper fetches it right before its
+    call, which makes this the one place that sees all native launches)."""
     import torch
+    if hook and _pre_launch[0] is not None:
+        fn, _pre_launch[0] = _pre_launch[0], None        # the hook launches kernels itself: no re-entry
+        try:
+            fn()
+        finally:
+            _pre_launch[0] = fn
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

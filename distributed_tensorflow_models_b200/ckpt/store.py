@@ -182,6 +182,44 @@ def restore(store: VariableStore, tensors: Dict[str, np.ndarray], use_ema: bool 
     return done
 
 
+SLOT_NAMES = ("RMSProp", "RMSProp_1", "ExponentialMovingAverage")
+
+
+def slot_flats_from(store: VariableStore, tensors: Dict[str, np.ndarray], layout) -> Dict[str, torch.Tensor]:
+    """Inverse of the slot part of :func:`collect_tensors`: full-length flat tensors (parameter order of
+    ``layout``) for every optimiser slot / EMA shadow the checkpoint holds for *all* trainable variables —
+    ``Supervisor`` / ``Saver`` restore these together with the variables (inception/imagenet_inception_bsp.py:156-167).
+    A slot that is missing for some variable is left out altogether."""
+    out: Dict[str, torch.Tensor] = {}
+    for slot in SLOT_NAMES:
+        if not all(f"{e.name}/{slot}" in tensors for e in layout.entries):
+            continue
+        flat = torch.zeros(layout.total, dtype=torch.float32)
+        if slot == "RMSProp":
+            flat.fill_(1.0)                       # padding between tensors keeps the slot's initial value
+        for e in layout.entries:
+            v = store.get(e.name)
+            dst = flat[e.offset:e.offset + e.numel].view(e.shape)
+            tmp = Variable(e.name, dst, True, tf_layout=v.tf_layout)
+            tmp.from_tf(torch.from_numpy(np.asarray(tensors[f"{e.name}/{slot}"])))
+        out[slot] = flat
+    return out
+
+
+def restore_training_state(trainer, tensors: Dict[str, np.ndarray]) -> List[str]:
+    """Variables, optimiser slots and EMA shadows of a checkpoint into a live trainer (resume).  Without shadows in
+    the checkpoint the EMA restarts from the restored weights rather than from the random initial values."""
+    done = restore(trainer.store, tensors, strict=False)
+    comm = trainer.comm
+    flats = slot_flats_from(trainer.store, tensors, trainer.layout)
+    if flats:
+        comm.load_slot_flats(flats)
+        done += sorted(flats)
+    if "ExponentialMovingAverage" not in flats:
+        comm.reset_ema_to_params()
+    return done
+
+
 def wipe(train_dir: str) -> None:
     """CIFAR chiefs delete and recreate train_dir at start (cifarnet/cifar10_cifarnet_bsp.py:45-48)."""
     if os.path.isdir(train_dir):

@@ -40,6 +40,16 @@ def as_pixel_dense(t: torch.Tensor) -> torch.Tensor:
     return t
 
 
+_gate_provider = [None]
+
+
+def set_gate_provider(fn) -> None:
+    """``fn(w) -> (flags, n, epoch, status, timeout_cycles) | None``: the parameter-server pull gate of the bucket
+    that holds the weight tensor ``w`` (parallel/symm.py).  The forward convolution hands it to the kernel, whose
+    weight-load warp waits on the flags before its first weight TMA (csrc/ps_gate.cuh)."""
+    _gate_provider[0] = fn
+
+
 def out_size(i: int, k: int, stride: int, pad: int) -> int:
     return (i + 2 * pad - k) // stride + 1
 
@@ -84,6 +94,10 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
     p.bnb_x = p.bnb_scale = p.bnb_shift = None
     p.bnb_ld = 0
     p.act_out = None
+    if _gate_provider[0] is not None:
+        gate = _gate_provider[0](w)
+        if gate is not None:
+            p.gate_flags, p.gate_n, p.gate_epoch, p.gate_status, p.gate_timeout_cycles = gate
     if bn_pending is not None and getattr(bn_pending, "pending", None) is not None:
         # deferred batch-norm finalize: the sliding-window kernel derives scale / shift from the statistics itself
         # (and publishes them); any other kernel needs them materialised first

@@ -119,6 +119,7 @@ class _ConvFn(torch.autograd.Function):
             dy = torch.ops.aten.threshold_backward(dy, y, 0.0)
         dx = dw = db = None
         wparam, bparam = ctx.params
+        wrote = []
         if has_bias and ctx.needs_input_grad[2]:
             co = dy.shape[-1]
             slot = _grad_slot(bparam)
@@ -127,20 +128,24 @@ class _ConvFn(torch.autograd.Function):
                       "dtf_colsum")
             if slot is not None:
                 db = None
+                wrote.append(bparam)
         if ctx.needs_input_grad[0]:
             dx = cn.conv_dgrad(dy, cn.wt_get(w), (x.shape[1], x.shape[2]), stride, pad)
         if ctx.needs_input_grad[1]:
             slot = _grad_slot(wparam)
             if slot is not None:
                 cn.conv_wgrad(x, dy, w.shape, stride, pad, out=slot)      # red.add straight into the flat buffer
+                wrote.append(wparam)
             else:
                 dw = cn.conv_wgrad(x, dy, w.shape, stride, pad)
+        _grad_written(*wrote)
         return dx, dw, db, None, None, None, None, None
 
 
 def conv2d(x, w, bias, stride, pad_before, out_hw, relu, stats=None):
     cin = x.shape[-1]
     if cin % 4 != 0:
+        nat.run_pre_launch()      # the pad below reads w with a PyTorch kernel: a pull gate still owed goes first
         x, w = _pad4(x, w)        # differentiable pads: the weight gradient is sliced back by autograd
     return _ConvFn.apply(x, w, bias, tuple(stride), tuple(pad_before), tuple(out_hw), bool(relu), stats)
 
@@ -213,6 +218,24 @@ def bn_stats(x: torch.Tensor) -> torch.Tensor:
     return st
 
 
+_grad_listener = [None]
+
+
+def set_grad_listener(fn) -> None:
+    """``fn(param)`` is called right after a kernel that wrote ``param``'s gradient straight into the flat PS
+    gradient buffer has been launched (gradients that travel through autograd are reported by the engine's
+    post-accumulate hooks instead).  The bucketed push starts a bucket when all its tensors have reported."""
+    _grad_listener[0] = fn
+
+
+def _grad_written(*params) -> None:
+    fn = _grad_listener[0]
+    if fn is not None:
+        for p in params:
+            if p is not None:
+                fn(p)
+
+
 def _grad_slot(p):
     """The parameter's pre-allocated .grad (a view of the flat PS gradient buffer) when it can be accumulated
     into directly — saves one elementwise add kernel per parameter per step."""
@@ -262,6 +285,7 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
             # d/dgamma of gamma*invstd*(x-mean): invstd * (sum g*x - mean * sum g), with moving statistics
             dg.copy_(coef.invstd_eval * (sums[c:] - coef.mean_eval * sums[:c]))
     if direct:
+        _grad_written(gamma if has_gamma else None, beta if has_beta else None)
         return dx, None, None
     return dx, dg, db
 
@@ -384,6 +408,8 @@ class _BnReluConvFn(torch.autograd.Function):
             if ctx.link_first:
                 add = ctx.res_link.pop("g", None)
         dx, dg, db = _bn_backward(da, x, coef, True, True, True, add=add, gamma=gamma, beta=beta, sums=sums)
+        if slot is not None:
+            _grad_written(wparam)
         return dx, dg, db, dw, d_res, None, None, None, None, None, None, None, None
 
 
@@ -607,11 +633,18 @@ def softmax_xent(logits, labels, smoothing, weight):
 # ---------------------------------------------------------------------------------------------------
 # fused optimiser update
 # ---------------------------------------------------------------------------------------------------
+_HYPER_RING = 4
+
+
 def hyper_tensor(opt, device) -> torch.Tensor:
     h = getattr(opt, "_hyper", None)
     if h is None:
         h = opt._hyper = torch.zeros(8, dtype=torch.float32, device=device)
-        opt._hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory()
+        # a ring of pinned staging buffers: the host runs a step ahead of the device, so the buffer a pending
+        # copy reads from must not be rewritten by the next step's values
+        opt._hyper_ring = [(torch.zeros(8, dtype=torch.float32).pin_memory(), torch.cuda.Event())
+                           for _ in range(_HYPER_RING)]
+        opt._hyper_i = 0
     return h
 
 
@@ -622,8 +655,12 @@ def set_hyper(opt, lr: float, grad_scale: float, ema_decay: float) -> torch.Tens
             float(cfg.epsilon), float(ema_decay), 0.0)
     if getattr(opt, "_hyper_vals", None) != vals:
         opt._hyper_vals = vals
-        opt._hyper_host.copy_(torch.tensor(vals, dtype=torch.float32))
-        h.copy_(opt._hyper_host, non_blocking=True)
+        host, ev = opt._hyper_ring[opt._hyper_i % _HYPER_RING]
+        opt._hyper_i += 1
+        ev.synchronize()                   # the copy that last read this slot (4 changes ago) has long finished
+        host.copy_(torch.tensor(vals, dtype=torch.float32))
+        h.copy_(host, non_blocking=True)
+        ev.record()
     return h
 
 

@@ -54,6 +54,24 @@ class Comm:
     def ssp_wait(self, step: int, bound: int, timeout: float = 600.0) -> float:
         raise NotImplementedError
 
+    # -- step hooks (transports that work from inside the step; defaults: whole-step protocol) ---------
+    push_enabled = True
+
+    def prepare_step(self, lr: float, grad_scale: float = 1.0) -> None:
+        pass
+
+    def begin_step(self) -> None:
+        self.layout.zero_grads()
+
+    def before_backward(self) -> None:
+        pass
+
+    def end_step(self) -> None:
+        pass
+
+    def sync_replica(self) -> None:
+        """Make the current stream wait until the local parameter replica holds every owner's last update."""
+
     # -- plumbing -------------------------------------------------------------------------------
     def barrier(self) -> None:
         pass
@@ -83,6 +101,20 @@ class Comm:
                 flat = out.setdefault(name, torch.zeros(L.total, dtype=torch.float32, device=t.device))
                 flat[o.lo:o.hi].copy_(t)
         return out
+
+    def load_slot_flats(self, flats: dict) -> None:
+        """Inverse of :meth:`gather_slot_flats`: take this rank's part of full-length slot / shadow tensors
+        (resume from a checkpoint)."""
+        for o in self.owned_optimizers():
+            for name, t in o.state_tensors().items():
+                if name in flats:
+                    t.copy_(flats[name][o.lo:o.hi].to(t.device))
+
+    def reset_ema_to_params(self) -> None:
+        """EMA shadows := current parameters (a checkpoint without shadows was restored)."""
+        for o in self.owned_optimizers():
+            if o.ema is not None:
+                o.ema.copy_(o.w)
 
     def finish(self) -> None:
         pass

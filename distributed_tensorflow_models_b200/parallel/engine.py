@@ -167,7 +167,16 @@ class Trainer:
                                  default_weight_decay=wd)
         ema = EmaConfig(self.p.ema_decay) if self.p.ema_decay else None
         self.opt_cfg = OptimizerConfig(kind=self.p.optimizer, weight_decay=self.layout.weight_decay, ema=ema)
+        self.comm.mode = self.setup.mode          # transports that shard differently per consistency mode
         self.comm.setup(self.layout, self.opt_cfg)
+        if hasattr(self.comm, "on_fetch"):
+            # parameter-server pull gates: the transport learns where each variable is first used (parallel/symm.py)
+            self.store.fetch_hook = self.comm.on_fetch
+            if self.setup.quantize:
+                self.comm.no_fused_gate = True    # folded / fake-quantised weights are read by other kernels first
+        if hasattr(self.comm, "grad_ready"):
+            for v in self.store.trainable_variables():
+                v.tensor.register_post_accumulate_grad_hook(self.comm.grad_ready)
         # non-trainable state (BN moving statistics): replicated per rank, chief's values at start (C6/C7)
         self.comm.broadcast_state([v.tensor for v in self.store.all() if not v.trainable], src=0)
         self.local_step = 0
@@ -227,16 +236,21 @@ class Trainer:
             if self._wt_batch is None:
                 self._wt_batch = conv_native.WeightTransposeBatch()
             conv_native.set_wt_batch(self._wt_batch)      # dgrad operands of all layers: one launch per step
+            if hasattr(self.comm, "grad_ready"):
+                native_ops.set_grad_listener(self.comm.grad_ready)
         try:
-            self.layout.zero_grads()
+            self.comm.begin_step()                 # zero the gradients (bucketed push: behind the previous step's flags)
             loss, logits = self._run_forward(x, y, True)
             total = loss
             if not self.setup.fused_l2:
                 total = loss + self.l2_term()
+            self.comm.before_backward()
             total.backward()
+            self.comm.end_step()                   # bucketed push: join the push stream
         finally:
             if native:
                 conv_native.set_wt_batch(None)
+                native_ops.set_grad_listener(None)
         return loss.detach(), logits.detach()
 
     def _fwd_bwd_graphed(self, x, y):
@@ -246,11 +260,14 @@ class Trainer:
             self._static[1].copy_(y)
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
+            snap = self._snapshot_side_state()
+            self.comm.push_enabled = False               # warm-up passes must not update the parameters
             with torch.cuda.stream(s):
                 for _ in range(2):                       # warm-up outside capture (allocator, tensor maps)
                     self._fwd_bwd(*self._static)
+                self._undo_warmup_side_effects(snap)
+            self.comm.push_enabled = True
             torch.cuda.current_stream().wait_stream(s)
-            self._undo_warmup_side_effects()
             from .. import _native as nat
             before = nat.launch_count()
             g = torch.cuda.CUDAGraph()
@@ -263,8 +280,22 @@ class Trainer:
         self._graph.replay()
         return self._out
 
-    def _undo_warmup_side_effects(self):
-        pass
+    def _snapshot_side_state(self):
+        """Everything a forward/backward pass changes besides the gradients: batch-norm moving statistics,
+        quantisation ranges (non-trainable variables) and the dropout seed."""
+        snap = [(v.tensor, v.tensor.detach().clone()) for v in self.store.all() if not v.trainable]
+        if self.device.type == "cuda" and Fn.get_backend() != "torch":
+            from ..ops import native_ops
+            seed = native_ops.dropout_seed(self.device)
+            snap.append((seed, seed.clone()))
+        return snap
+
+    @torch.no_grad()
+    def _undo_warmup_side_effects(self, snap):
+        """The warm-up passes before the graph capture ran the real step body: put back what they moved, so the
+        first captured step starts from the same state as an eager first step would."""
+        for t, saved in snap:
+            t.copy_(saved)
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor, batch_size: Optional[int] = None) -> Dict:
         """One worker step.  ``batch_size``: this step's actual batch (gradient re-weighting hook,
@@ -276,6 +307,8 @@ class Trainer:
         if s.quantize:
             self.store.quant.set_step(gs_before)
         scale = 1.0 if batch_size is None else float(batch_size) / float(s.batch_size)
+        if s.mode == "bsp":
+            self.comm.prepare_step(lr, scale)      # transports that push from inside the backward pass
         use_graph = s.cuda_graph and self.device.type == "cuda" and x.shape[0] == s.batch_size
         loss, logits = (self._fwd_bwd_graphed if use_graph else self._fwd_bwd)(x, labels)
         if s.mode == "bsp":
@@ -291,5 +324,6 @@ class Trainer:
     @torch.no_grad()
     def evaluate_batch(self, images: torch.Tensor, labels: torch.Tensor, training_bn: bool = False):
         x = self.prepare_inputs(images)
+        self.comm.sync_replica()
         loss, logits = self._run_forward(x, labels, training_bn)
         return loss, logits

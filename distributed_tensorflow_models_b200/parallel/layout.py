@@ -42,6 +42,57 @@ def _round_up(a: int, b: int) -> int:
     return (a + b - 1) // b * b
 
 
+@dataclass
+class Bucket:
+    """A contiguous range ``[lo, lo+length)`` of the flat buffer that is pushed as one unit (a group of layers whose
+    gradients become complete at about the same time in the backward pass).  Inside a bucket rank ``r`` owns
+    ``[lo + r*chunk, min(lo + (r+1)*chunk, lo+length))``; its optimiser slots for that part start at ``slot_off``
+    of the rank's slot arrays."""
+    index: int
+    lo: int
+    length: int
+    chunk: int
+    slot_off: int
+    names: Tuple[str, ...]
+
+    @property
+    def hi(self) -> int:
+        return self.lo + self.length
+
+    def part(self, rank: int) -> Tuple[int, int]:
+        lo = min(self.lo + rank * self.chunk, self.hi)
+        return lo, min(lo + self.chunk, self.hi)
+
+
+def plan_buckets(entries: Sequence["Entry"], total: int, world: int, target_floats: int,
+                 max_buckets: int = 64) -> List[Bucket]:
+    """Cut ``[0, total)`` at tensor starts into buckets of at least ``target_floats`` elements (a tensor is never
+    split: its gradient is produced by one kernel, so its halves would become ready together anyway)."""
+    ents = sorted(entries, key=lambda e: e.offset)
+    target = max(int(target_floats), (total + max_buckets - 1) // max_buckets, 4 * world)
+    cuts: List[Tuple[int, List[str]]] = []          # (start offset, names)
+    cur_lo, cur_names = 0, []
+    for e in ents:
+        if cur_names and e.offset - cur_lo >= target:
+            cuts.append((cur_lo, cur_names))
+            cur_lo, cur_names = e.offset, []
+        cur_names.append(e.name)
+    cuts.append((cur_lo, cur_names))
+    if len(cuts) > 1 and total - cuts[-1][0] < target // 4:       # a small tail joins its predecessor
+        lo, names = cuts.pop()
+        cuts[-1] = (cuts[-1][0], cuts[-1][1] + names)
+    out: List[Bucket] = []
+    slot_off = 0
+    for i, (lo, names) in enumerate(cuts):
+        hi = cuts[i + 1][0] if i + 1 < len(cuts) else total
+        length = hi - lo
+        assert length % 4 == 0 and lo % 4 == 0, (lo, hi)
+        chunk = _round_up((length + world - 1) // world, 4)
+        out.append(Bucket(i, lo, length, chunk, slot_off, tuple(names)))
+        slot_off += chunk
+    return out
+
+
 class FlatLayout:
     def __init__(self, store: VariableStore, world_size: int = 1, placement: str = "flat",
                  device: Optional[torch.device] = None, default_weight_decay: Optional[float] = None,

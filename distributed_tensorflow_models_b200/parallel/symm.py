@@ -4,48 +4,85 @@ our own sm_100a kernels over NVLink / NVSwitch (no NCCL on the step path).
 Every rank allocates ONE symmetric buffer (``torch.distributed._symmetric_memory`` does the
 cuMem/fabric-handle exchange — SURVEY §5.8 allows torch to bootstrap; the kernels are ours) laid out as
 
-    [ params (total) | grads (total) | ms (shard) | mom (shard) | ema (shard) | control words ]
+    [ params (total) | grads (total) | ms (S) | mom (S) | ema (S) | control words ]
 
-and learns the base address of every peer's copy.  Per-rank device tables of peer pointers are handed to
-``dtf_ps_bsp_step`` / ``dtf_ps_async_step`` / ``dtf_ssp_clock`` (csrc/ps_update.cu):
+and learns the base address of every peer's copy (plus the NVLS multicast address of the whole buffer when the
+fabric has one).
 
-* BSP  : one kernel per rank per step = wait(grads ready) -> reduce my range over all ranks' gradient
-         buffers (in the NVSwitch with multimem.ld_reduce when a multicast address exists, else peer loads)
-         + optimiser (+EMA) -> multimem.st of the updated range into every replica, or signal/wait(range
-         updated) -> copy the other owners' ranges
-         (reduce-scatter + fused update + all-gather; replaces SyncReplicasOptimizer's accumulators,
-         chief thread and token queue).
-* ASP  : pusher-side one-sided apply (``red.global.add.f32`` on the owner's HBM), global_step is a
-         system-scope atomic on rank 0, replica refresh without a barrier.
+BSP (``mode='bsp'``) — bucketed push overlapped with the backward pass, pull gated in the consumer
+--------------------------------------------------------------------------------------------------
+The flat buffer is cut at tensor starts into *buckets* (``layout.plan_buckets``); inside a bucket every rank
+owns 1/W.  The reference keeps one accumulator per variable, so its gradients leave the worker variable by
+variable while the backward pass is still running (resnet/cifar10_resnet_bsp.py:91-99); here
+
+* the engine tells the transport when a parameter's gradient has been written (``grad_ready``); as soon as the
+  last tensor of a bucket has reported, ``dtf_ps_bucket_step`` is launched for it on a high-priority side stream
+  behind an event — the reduction (in the NVSwitch with ``multimem.ld_reduce``, else peer loads), the optimiser
+  and the store of the new values into every replica (``multimem.st``, else peer stores) then run while the
+  remaining weight-gradient kernels of the step are still computing.  All ranks issue the buckets in one agreed
+  order (learned in the first pass), so the per-bucket flag waits cannot cross;
+* nobody waits for the *other* owners inside the push.  The next forward pass waits per bucket where the values
+  are consumed: convolutions get the bucket's ``updated`` flag words and their weight-load warp spins on them
+  before its first weight TMA (``csrc/ps_gate.cuh``); every other parameter (biases, batch-norm scales) is
+  covered by a one-warp ``dtf_ps_gate`` launch in front of its first consumer on that stream;
+* before this step's gradients may overwrite the buffers that peers were reading, a side stream waits for *all*
+  flags of the previous step and only then zeroes the gradient buffer (``begin_step`` / ``before_backward``).
+
+ASP / SSP — flat shards (rank r owns ``[r*shard, (r+1)*shard)``)
+-----------------------------------------------------------------
+* ASP  : pusher-side one-sided apply (``red.global.add.v4.f32`` on the owner's HBM), global_step is a
+         system-scope atomic on rank 0, replica refresh in the same loop without a barrier.
 * SSP  : ASP + ``clock[rank] = step`` written into every peer's clock table, bounded spin while
          ``step > min(clock) + bound`` (replaces ssp_manager.py's Thrift RPC).
 
-NCCL is used only to bootstrap (process group, initial broadcast) and for ``max_over_ranks``.
+NCCL is used only to bootstrap (process group, initial broadcast), for checkpoint gathers and ``max_over_ranks``.
 """
 from __future__ import annotations
 
+import bisect
 import ctypes as C
-from typing import List, Optional
+import os
+from typing import Dict, List, Optional
 
 import torch
 
 from .. import _native as nat
 from ..optim.schedule import ema_decay as _ema_decay
-from ..optim.updates import OptimizerConfig, ShardOptimizer
+from ..optim.updates import OptimizerConfig
 from .comm import Comm, StalenessTimeout
-from .layout import FlatLayout
-
-CTRL_WORDS = 256      # uint32 control region per rank: [0,2W) bsp flags, [64,64+W) ssp clocks, [128,130) global step
+from .layout import Bucket, FlatLayout, plan_buckets
 
 
 def _p(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
 
 
+def _round_up(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+class _OwnedState:
+    """What this rank holds as a parameter server: optimiser slots and EMA shadows of the ranges it owns."""
+
+    def __init__(self, cfg: OptimizerConfig, params: torch.Tensor):
+        self.cfg = cfg
+        self.w = params                    # (the whole replica: only its device is used through this handle)
+        self.slots: Dict[str, torch.Tensor] = {}
+        self.ema: Optional[torch.Tensor] = None
+
+    def state_tensors(self) -> Dict[str, torch.Tensor]:
+        out = dict(self.slots)
+        if self.ema is not None:
+            out["ExponentialMovingAverage"] = self.ema
+        return out
+
+
 class SymmComm(Comm):
     supports_async = True
+    mode = "bsp"                           # set by the engine before setup(): decides the ownership map
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, overlap: Optional[bool] = None, bucket_mb: Optional[float] = None,
+                 timeout_s: Optional[float] = None, ssp_timeout_s: Optional[float] = None):
         import torch.distributed as dist
         self.dist = dist
         self.group = group if group is not None else dist.group.WORLD
@@ -53,26 +90,60 @@ class SymmComm(Comm):
         self.world = dist.get_world_size(self.group)
         self._gs = 0
         self._step = 0
+        env = os.environ
+        self.overlap = bool(int(env.get("DTF_PUSH_OVERLAP", "1"))) if overlap is None else bool(overlap)
+        self.bucket_mb = float(env["DTF_BUCKET_MB"]) if (bucket_mb is None and "DTF_BUCKET_MB" in env) else bucket_mb
+        # a peer that stays away this long is dead: the waits give up, the status word goes to 1 and the host aborts
+        self.timeout_s = float(env.get("DTF_PS_TIMEOUT_S", "300")) if timeout_s is None else float(timeout_s)
+        self.ssp_timeout_s = float(env.get("DTF_SSP_TIMEOUT_S", "30")) if ssp_timeout_s is None else float(ssp_timeout_s)
+        self.gate_mode = env.get("DTF_PULL_GATE", "fused")          # fused | fetch (every gate as its own launch)
+        self.push_blocks = int(env.get("DTF_PUSH_BLOCKS", "0"))     # 0 = one block per SM
+        self.push_enabled = True           # the engine switches the pushes off for its warm-up passes
+        self._in_step = False
+        self._engine_driven = False        # True once an engine runs the step hooks (the pushes are then its)
 
     # ------------------------------------------------------------------------------------------
     def setup(self, layout: FlatLayout, opt_cfg: OptimizerConfig) -> None:
         import torch.distributed._symmetric_memory as symm_mem
-        assert layout.placement == "flat", "the in-kernel push/pull uses equal flat shards"
+        if layout.placement != "flat":
+            raise ValueError(
+                "--backend symm keeps the parameter-server shards as equal ranges of each bucket of the flat buffer; "
+                f"--placement {layout.placement} (the reference's whole-tensor / axis-0 placement) is available "
+                "with --backend nccl, gloo or the thread cluster")
         dev = layout.params.device
         W = self.world
         total = layout.total
-        shard = total // W
-        assert shard % 4 == 0
-        self.layout, self.shard, self.cfg = layout, shard, opt_cfg
-        n = 2 * total + 3 * shard + CTRL_WORDS
+        self.layout, self.cfg = layout, opt_cfg
+        self.bucketed = self.mode == "bsp"
+        if self.bucketed:
+            if self.bucket_mb is None:
+                target = min(max(total // 12, 1 << 18), 8 << 20)         # floats: 1 MB .. 32 MB, ~12 buckets
+            else:
+                target = int(self.bucket_mb * (1 << 20) / 4)
+            self.buckets: List[Bucket] = plan_buckets(layout.entries, total, W, target)
+            S = sum(b.chunk for b in self.buckets)
+            self.shard = None
+        else:
+            self.buckets = []
+            assert (total // W) % 4 == 0
+            self.shard = total // W
+            S = self.shard
+        B = max(1, len(self.buckets))
+        self.n_slot = S
+        # control words (uint32): ready[B][W] | updated[B][W] | clocks[W] (64-aligned) | global step (2 words)
+        self.o_ready, self.o_updated = 0, B * W
+        self.o_clocks = _round_up(2 * B * W, 64)
+        self.o_gs = self.o_clocks + _round_up(W, 64)
+        ctrl_words = self.o_gs + 64
+        n = 2 * total + 3 * S + ctrl_words
         buf = symm_mem.empty(n, dtype=torch.float32, device=dev)
         buf.zero_()
         self.hdl = symm_mem.rendezvous(buf, self.group)
         self.buf = buf
         bases = [int(p) for p in self.hdl.buffer_ptrs]
         o_params, o_grads = 0, total
-        o_ms, o_mom, o_ema = 2 * total, 2 * total + shard, 2 * total + 2 * shard
-        o_ctrl = 2 * total + 3 * shard
+        o_ms, o_mom, o_ema = 2 * total, 2 * total + S, 2 * total + 2 * S
+        self.o_ctrl = o_ctrl = 2 * total + 3 * S
 
         def table(off_floats: int) -> torch.Tensor:
             return torch.tensor([b + 4 * off_floats for b in bases], dtype=torch.int64, device=dev)
@@ -80,10 +151,10 @@ class SymmComm(Comm):
         self.t_params, self.t_grads = table(o_params), table(o_grads)
         self.t_ms, self.t_mom, self.t_ema = table(o_ms), table(o_mom), table(o_ema)
         self.t_flags = table(o_ctrl)
-        self.t_clocks = table(o_ctrl + 64)
-        self.gs_ptr_rank0 = bases[0] + 4 * (o_ctrl + 128)
+        self.t_clocks = table(o_ctrl + self.o_clocks)
+        self.flags_local = bases[self.rank] + 4 * o_ctrl
+        self.gs_ptr_rank0 = bases[0] + 4 * (o_ctrl + self.o_gs)
         # NVLS: one multicast address for the whole symmetric buffer when the fabric offers it (NVSwitch)
-        import os
         mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
         if os.environ.get("DTF_NVLS", "1") == "0":
             mc = 0
@@ -92,28 +163,67 @@ class SymmComm(Comm):
         # bind the model to the symmetric params / grads (values preserved), chief's init wins
         layout.bind(buf[o_params:o_params + total], buf[o_grads:o_grads + total], copy=True)
         self.dist.broadcast(layout.params, src=0, group=self.group)
-        lo = self.rank * shard
-        opt = ShardOptimizer(opt_cfg, layout.params, lo, lo + shard, layout.wd_boundary)
+        opt = _OwnedState(opt_cfg, layout.params)
         if opt_cfg.kind == "rmsprop":
-            ms, mom = buf[o_ms:o_ms + shard], buf[o_mom:o_mom + shard]
+            ms, mom = buf[o_ms:o_ms + S], buf[o_mom:o_mom + S]
             ms.fill_(1.0)
             mom.zero_()
             opt.slots = {"RMSProp": ms, "RMSProp_1": mom}
-        if opt.ema is not None:
-            ema = buf[o_ema:o_ema + shard]
-            ema.copy_(opt.w)
-            opt.ema = ema
+        if opt_cfg.ema is not None:
+            opt.ema = buf[o_ema:o_ema + S]
         self.opt = opt
-        self.local_counter = torch.zeros(1, dtype=torch.int32, device=dev)
+        if opt.ema is not None:
+            self._owned_copy(layout.params, opt.ema)           # shadows start at the initial values
+        self.counters = torch.zeros(B, dtype=torch.int32, device=dev)
         self.epoch = torch.zeros(1, dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.status_event = None
         self.polls = torch.zeros(1, dtype=torch.int32, device=dev)
         self.gs_host = torch.zeros(1, dtype=torch.int64).pin_memory()
-        self.gs_view = buf[o_ctrl + 128:o_ctrl + 130].view(torch.int64)
+        self.gs_view = buf[o_ctrl + self.o_gs:o_ctrl + self.o_gs + 2].view(torch.int64)
+        self.clocks_view = buf[o_ctrl + self.o_clocks:o_ctrl + self.o_clocks + W].view(torch.int32)
+        # bucket bookkeeping
+        self._bucket_lo = [b.lo for b in self.buckets]
+        self._bucket_of_name = {name: b.index for b in self.buckets for name in b.names}
+        self._need: List[Dict[int, int]] = []          # per bucket: id(param) -> notifications expected per step
+        self._need_total: List[int] = []
+        self._order: Optional[List[int]] = None        # agreed issue order of the buckets
+        self._learned = False
+        self._h = None
+        self._reset_step_state()
+        self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.aux_stream = torch.cuda.Stream(device=dev)
         torch.cuda.synchronize(dev)
         self.dist.barrier(group=self.group)
 
-    # ------------------------------------------------------------------------------------------
+    # ---- ownership maps ----------------------------------------------------------------------------
+    def _owned_copy(self, flat: torch.Tensor, dst: torch.Tensor) -> None:
+        """dst (length S) <- the elements of the full-length ``flat`` that this rank owns."""
+        if not self.bucketed:
+            dst.copy_(flat[self.rank * self.shard:(self.rank + 1) * self.shard])
+            return
+        for b in self.buckets:
+            lo, hi = b.part(self.rank)
+            if hi > lo:
+                dst[b.slot_off:b.slot_off + hi - lo].copy_(flat[lo:hi])
+
+    def _unshard(self, gathered: torch.Tensor) -> torch.Tensor:
+        """[W, S] (every rank's slot array) -> full-length flat tensor in parameter order."""
+        if not self.bucketed:
+            return gathered.reshape(-1)[: self.layout.total]
+        flat = torch.zeros(self.layout.total, dtype=gathered.dtype, device=gathered.device)
+        for b in self.buckets:
+            for r in range(self.world):
+                lo, hi = b.part(r)
+                if hi > lo:
+                    flat[lo:hi].copy_(gathered[r, b.slot_off:b.slot_off + hi - lo])
+        return flat
+
+    def bucket_of(self, offset: int) -> int:
+        return bisect.bisect_right(self._bucket_lo, offset) - 1
+
+    # ---- hyper-parameters --------------------------------------------------------------------------
     def _hyper(self, lr, grad_scale, num_updates, ema_power: int = 1):
         from ..ops import native_ops
         d = -1.0
@@ -121,20 +231,252 @@ class SymmComm(Comm):
             d = _ema_decay(self.cfg.ema.decay, num_updates if self.cfg.ema.use_num_updates else None) ** ema_power
         return native_ops.set_hyper(self.opt, lr, grad_scale, d)
 
-    def bsp_step(self, lr, grad_scale=1.0):
-        h = self._hyper(lr, grad_scale, self._gs)
+    # ---- BSP: step protocol driven by the engine ---------------------------------------------------
+    def _reset_step_state(self) -> None:
+        self._got: List[int] = [0] * len(self.buckets)      # notifications received per bucket this step
+        self._seen: Dict[int, int] = {}
+        self._events: List[Dict[int, torch.cuda.Event]] = [{} for _ in self.buckets]   # per bucket: stream -> last event
+        self._complete: List[bool] = [False] * len(self.buckets)
+        self._completion_order: List[int] = []
+        self._next = 0                                      # position in the agreed order
+        self._issued = 0
+        self._gated = set()                                 # (bucket, stream) pairs that have waited this step
+        self._deferred: Dict[int, tuple] = {}               # weight address -> (bucket, stream): gate owed
+        self._zeroed = None
+        if not self._learned:
+            self._need_learning: Dict[int, Dict[int, int]] = {}
+            self._last_seen_bucket_order: List[int] = []
+
+    def prepare_step(self, lr: float, grad_scale: float = 1.0) -> None:
+        """Hyper-parameters of the coming step into device memory (the push kernels run inside the step)."""
+        if self.bucketed:
+            self._h = self._hyper(lr, grad_scale, self._gs)
+
+    def begin_step(self) -> None:
+        """Start of forward: on a side stream wait until every owner has finished the previous step (then nobody
+        reads my old gradients any more) and zero the gradient buffer; the forward pass runs meanwhile."""
+        if not self.bucketed:
+            self.layout.zero_grads()
+            return
+        self._reset_step_state()
+        self._in_step = True
+        self._engine_driven = True
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.aux_stream.wait_event(ev)
+        with torch.cuda.stream(self.aux_stream):
+            if self.world > 1:
+                self._gate_launch(0, len(self.buckets))
+            self.layout.zero_grads()
+            self._zeroed = torch.cuda.Event()
+            self._zeroed.record(self.aux_stream)
+        nat.set_pre_launch(self._flush_deferred)
+        from ..ops import conv_native
+        conv_native.set_gate_provider(self._gate_for_weight if self.world > 1 else None)
+
+    def before_backward(self) -> None:
+        if self.bucketed and self._zeroed is not None:
+            self._flush_deferred()
+            torch.cuda.current_stream().wait_event(self._zeroed)
+
+    def end_step(self) -> None:
+        """After backward: issue whatever has not been pushed yet and join the side streams."""
+        if not self.bucketed or not self._in_step:
+            return
+        self._in_step = False
+        nat.set_pre_launch(None)
+        from ..ops import conv_native
+        conv_native.set_gate_provider(None)
+        if not self._learned:
+            self._finish_learning()
+        if self.push_enabled:
+            cur = torch.cuda.current_stream()
+            if self._issued < len(self.buckets):
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                self.comm_stream.wait_event(ev)
+                for b in self._order[self._next:]:
+                    self._launch_bucket(b)
+                self._next = len(self._order)
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            cur.wait_event(done)
+
+    # -- gradient notifications (called from the backward pass, possibly on branch streams) -----------
+    def grad_ready(self, param: torch.Tensor) -> None:
+        if not self.bucketed or not self._in_step:
+            return
+        g = param.grad
+        if g is None:
+            return
+        off = (g.data_ptr() - self.layout.grads.data_ptr()) // 4
+        if off < 0 or off >= self.layout.total:
+            return
+        b = self.bucket_of(off)
+        key = id(param)
+        if not self._learned:
+            need = self._need_learning.setdefault(b, {})
+            need[key] = need.get(key, 0) + 1
+            self._last_seen_bucket_order.append(b)
+            return
+        need = self._need[b]
+        if key not in need:
+            return
+        self._seen[key] = self._seen.get(key, 0) + 1
+        if self._seen[key] > need[key]:
+            return
+        self._got[b] += 1
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._events[b][cur.cuda_stream] = ev         # a later event on the same stream covers the earlier ones
+        if self._got[b] == self._need_total[b]:
+            self._complete[b] = True
+            self._issue_ready()
+
+    def _issue_ready(self) -> None:
+        if not (self.push_enabled and self.overlap):
+            return
+        while self._next < len(self._order) and self._complete[self._order[self._next]]:
+            b = self._order[self._next]
+            for ev in self._events[b].values():
+                self.comm_stream.wait_event(ev)
+            self._launch_bucket(b)
+            self._next += 1
+
+    def _finish_learning(self) -> None:
+        """First pass over the model: which parameters report how often, and in which order the buckets complete.
+        Rank 0's order is adopted by everybody (the per-bucket flag waits must be issued in one global order)."""
+        nb = len(self.buckets)
+        need = [dict(self._need_learning.get(b, {})) for b in range(nb)]
+        order: List[int] = []
+        remaining = [sum(n.values()) for n in need]
+        for b in self._last_seen_bucket_order:
+            remaining[b] -= 1
+            if remaining[b] == 0:
+                order.append(b)
+        order += [b for b in range(nb - 1, -1, -1) if b not in order]        # buckets nobody reported for: last
+        t = torch.tensor(order, dtype=torch.int64, device=self.layout.params.device)
+        if self.world > 1:
+            self.dist.broadcast(t, src=0, group=self.group)
+        agreed = [int(v) for v in t.tolist()]
+        if agreed != order:
+            # this rank's backward pass completes the buckets in another order: it still issues in the agreed one
+            order = agreed
+        self._need = need
+        self._need_total = [sum(n.values()) for n in need]
+        self._order = order
+        self._learned = True
+        self._next = 0
+
+    def _launch_bucket(self, b: int) -> None:
+        bk = self.buckets[b]
         o = self.opt
         kind = 0 if self.cfg.kind == "sgd" else 1
-        nat.check(nat.lib().dtf_ps_bsp_step(_p(self.t_grads), _p(self.t_params), _p(self.t_flags),
-                                            _p(self.local_counter), _p(self.status), self.rank, self.world,
-                                            C.c_longlong(self.shard), C.c_longlong(self.layout.wd_boundary),
-                                            _p(o.slots.get("RMSProp")), _p(o.slots.get("RMSProp_1")), _p(o.ema),
-                                            _p(h), kind, _p(self.epoch),
-                                            C.c_void_p(self.mc_grads) if self.mc_grads else None,
-                                            C.c_void_p(self.mc_params) if self.mc_params else None,
-                                            nat.stream_ptr()), "dtf_ps_bsp_step")
+        W = self.world
+
+        def slot(t):
+            return C.c_void_p(t.data_ptr() + 4 * bk.slot_off) if t is not None else None
+
+        last = self._issued == len(self.buckets) - 1
+        with torch.cuda.stream(self.comm_stream):
+            nat.check(nat.lib().dtf_ps_bucket_step(
+                _p(self.t_grads), _p(self.t_params), _p(self.t_flags),
+                C.c_void_p(self.counters.data_ptr() + 4 * b), _p(self.status), self.rank, W,
+                self.o_ready + b * W, self.o_updated + b * W,
+                C.c_longlong(bk.lo), C.c_longlong(bk.length), C.c_longlong(bk.chunk),
+                C.c_longlong(self.layout.wd_boundary),
+                slot(o.slots.get("RMSProp")), slot(o.slots.get("RMSProp_1")), slot(o.ema), _p(self._h), kind,
+                _p(self.epoch), _p(self.epoch) if last else None,
+                C.c_void_p(self.mc_grads) if self.mc_grads else None,
+                C.c_void_p(self.mc_params) if self.mc_params else None,
+                C.c_double(self.timeout_s), self.push_blocks, nat.stream_ptr(hook=False)), "dtf_ps_bucket_step")
+        self._issued += 1
+
+    # -- pull gates ------------------------------------------------------------------------------------
+    def _gate_launch(self, b0: int, b1: int) -> None:
+        W = self.world
+        nat.check(nat.lib().dtf_ps_gate(C.c_void_p(self.flags_local + 4 * (self.o_updated + b0 * W)), (b1 - b0) * W,
+                                        _p(self.epoch), _p(self.status), C.c_double(self.timeout_s),
+                                        nat.stream_ptr(hook=False)), "dtf_ps_gate")
+
+    def on_fetch(self, var) -> None:
+        """A model function has just looked a variable up (``VariableStore.variable``): make sure the stream it is
+        about to be used on waits for the owners' updates of its bucket."""
+        if not (self.bucketed and self._in_step and self.world > 1 and var.trainable):
+            return
+        b = self._bucket_of_name.get(var.name)
+        if b is None:
+            return
+        sid = torch.cuda.current_stream().cuda_stream
+        if (b, sid) in self._gated:
+            return
+        t = var.tensor
+        if self.gate_mode == "fused" and t.dim() in (2, 4) and self._fused_gate_ok:
+            self._deferred[t.data_ptr()] = (b, sid)       # a convolution is expected to take it (conv_native)
+            return
+        self._gated.add((b, sid))
+        self._gate_launch(b, b + 1)
+
+    def _flush_deferred(self) -> None:
+        """Some other kernel is about to be launched: gates still owed are launched as kernels of their own."""
+        if not self._deferred:
+            return
+        owed, self._deferred = self._deferred, {}
+        cur = torch.cuda.current_stream().cuda_stream
+        for (b, sid) in owed.values():
+            if (b, sid) in self._gated:
+                continue
+            self._gated.add((b, sid))
+            if sid == cur:
+                self._gate_launch(b, b + 1)
+            else:
+                with torch.cuda.stream(torch.cuda.ExternalStream(sid)):
+                    self._gate_launch(b, b + 1)
+
+    def _gate_for_weight(self, w: torch.Tensor):
+        """-> (flags, n, epoch, status, timeout cycles) for the convolution that is about to load ``w``, or None."""
+        owed = self._deferred.pop(w.data_ptr(), None)
+        if owed is None:
+            return None
+        b, sid = owed
+        if (b, sid) in self._gated or sid != torch.cuda.current_stream().cuda_stream:
+            if (b, sid) not in self._gated:
+                self._deferred[w.data_ptr()] = owed
+            return None
+        self._gated.add((b, sid))
+        W = self.world
+        return (self.flags_local + 4 * (self.o_updated + b * W), W, self.epoch.data_ptr(), self.status.data_ptr(),
+                int(self.timeout_s * 1.9e9))
+
+    @property
+    def _fused_gate_ok(self) -> bool:
+        from ..ops import functional as Fn
+        return Fn.get_backend() != "torch" and not getattr(self, "no_fused_gate", False)
+
+    # ---- BSP: the call the engine (or a script) makes after backward -----------------------------------
+    def bsp_step(self, lr, grad_scale=1.0):
+        if not self._engine_driven:
+            # stand-alone use (scripts that fill the gradient buffer themselves): the whole push happens here
+            self._h = self._hyper(lr, grad_scale, self._gs)
+            if self._order is None:
+                self._order = list(range(len(self.buckets) - 1, -1, -1))
+            cur = torch.cuda.current_stream()
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self.comm_stream.wait_event(ev)
+            for b in self._order:
+                self._launch_bucket(b)
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            cur.wait_event(done)
+            if self.world > 1:
+                self._gate_launch(0, len(self.buckets))      # stand-alone callers read the replica right away
+            self._issued = 0
         self._gs += 1
         self._step += 1
+        self._poll_status()
         return self._gs
 
     def async_step(self, lr, grad_scale=1.0):
@@ -154,20 +496,42 @@ class SymmComm(Comm):
         if self.rank == 0:
             self.gs_host.copy_(self.gs_view, non_blocking=True)
             self._gs = max(self._gs + 1, int(self.gs_host.item()))
+        self._poll_status()
         return self._gs
 
-    def ssp_wait(self, step, bound, timeout=600.0):
+    def ssp_wait(self, step, bound, timeout=None):
+        timeout = self.ssp_timeout_s if timeout is None else timeout
         nat.check(nat.lib().dtf_ssp_clock(_p(self.t_clocks), self.rank, self.world, C.c_uint(step), C.c_uint(bound),
                                           C.c_double(timeout), _p(self.status), _p(self.polls), nat.stream_ptr()),
                   "dtf_ssp_clock")
         return 0.0
 
-    def check_status(self) -> None:
-        s = int(self.status.item())
+    # ---- failure detection -----------------------------------------------------------------------------
+    def _poll_status(self) -> None:
+        """A flag wait that timed out means a peer is gone and this rank's replica is no longer trustworthy: abort.
+        The status word is copied to pinned memory every 16 steps and looked at once that copy has landed — no
+        synchronisation on the step path."""
+        if self.status_event is not None and self.status_event.query():
+            self.status_event = None
+            self._raise_on(int(self.status_host.item()))
+        if self.status_event is None and self._step % 16 == 0 and not torch.cuda.is_current_stream_capturing():
+            self.status_host.copy_(self.status, non_blocking=True)
+            self.status_event = torch.cuda.Event()
+            self.status_event.record()
+
+    def _raise_on(self, s: int) -> None:
         if s == 1:
-            raise RuntimeError("ps_bsp_step timed out waiting for a peer (a rank died or fell > 2 s behind)")
+            raise RuntimeError("a parameter-server flag wait timed out after %.0f s: a peer rank died or stalled "
+                               "(DTF_PS_TIMEOUT_S)" % self.timeout_s)
         if s == 2:
-            raise StalenessTimeout("SSP clock wait timed out")
+            raise StalenessTimeout("SSP clock wait timed out after %.0f s (DTF_SSP_TIMEOUT_S)" % self.ssp_timeout_s)
+
+    def check_status(self) -> None:
+        self._raise_on(int(self.status.item()))
+
+    def sync_replica(self) -> None:
+        if self.bucketed and self.world > 1:
+            self._gate_launch(0, len(self.buckets))
 
     # ------------------------------------------------------------------------------------------
     def barrier(self):
@@ -188,16 +552,25 @@ class SymmComm(Comm):
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
         return float(t.item())
 
-    def owned_optimizers(self) -> List[ShardOptimizer]:
+    def owned_optimizers(self):
         return [self.opt]
 
     def gather_slot_flats(self):
         out = {}
         for name, t in self.opt.state_tensors().items():
-            flat = torch.empty(self.layout.total, dtype=torch.float32, device=t.device)
-            self.dist.all_gather_into_tensor(flat, t.contiguous().clone(), group=self.group)
-            out[name] = flat
+            g = torch.empty(self.world * self.n_slot, dtype=torch.float32, device=t.device)
+            self.dist.all_gather_into_tensor(g, t.contiguous().clone(), group=self.group)
+            out[name] = self._unshard(g.view(self.world, self.n_slot))
         return out
+
+    def load_slot_flats(self, flats) -> None:
+        for name, t in self.opt.state_tensors().items():
+            if name in flats:
+                self._owned_copy(flats[name].to(t.device), t)
+
+    def reset_ema_to_params(self) -> None:
+        if self.opt.ema is not None:
+            self._owned_copy(self.layout.params, self.opt.ema)
 
     def finish(self):
         torch.cuda.synchronize()

@@ -241,6 +241,7 @@ class VariableStore(nn.Module):
         self.end_points: Dict[str, torch.Tensor] = {}
         self._params = nn.ParameterDict()
         self._n_buffers = 0
+        self.fetch_hook: Optional[Callable[["Variable"], None]] = None   # called on every look-up of an existing variable
 
     # ---- activation -------------------------------------------------------------------------
     @contextlib.contextmanager
@@ -323,6 +324,8 @@ class VariableStore(nn.Module):
         if v is not None:
             if tuple(v.tensor.shape) != tuple(shape):
                 raise ValueError(f"variable {full} exists with shape {tuple(v.tensor.shape)}, asked {tuple(shape)}")
+            if self.fetch_hook is not None:
+                self.fetch_hook(v)
             return v.tensor
         if self.frozen:
             raise RuntimeError(f"variable {full} requested after the store was frozen")

@@ -184,12 +184,17 @@ def make_comm(args, backend: str, num_workers: int):
 def save_checkpoint(trainer: Trainer, train_dir: str, max_to_keep: int, fmt: str = "npz") -> Optional[str]:
     """Chief-side save (all ranks must call: gathering the sharded slots is collective)."""
     comm = trainer.comm
+    comm.sync_replica()                    # the chief's replica must hold every owner's last update
     slots = comm.gather_slot_flats()
-    if comm.rank != 0:
-        return None
-    gs = comm.global_step()
-    tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME.get(trainer.setup.model, "global_step"))
-    return ckpt.save(train_dir, tensors, gs, max_to_keep, fmt=fmt)
+    path = None
+    if comm.rank == 0:
+        gs = comm.global_step()
+        tensors = ckpt.collect_tensors(trainer.store, slots, trainer.layout, gs, GLOBAL_STEP_NAME.get(trainer.setup.model, "global_step"))
+        path = ckpt.save(train_dir, tensors, gs, max_to_keep, fmt=fmt)
+    # nobody runs ahead into the next step's flag waits while the chief is still writing (seconds for a large
+    # model): a peer's wait would otherwise count the save against its timeout
+    comm.barrier()
+    return path
 
 
 def run_worker(args) -> int:
@@ -214,7 +219,7 @@ def run_worker(args) -> int:
         latest = ckpt.latest_checkpoint(args.train_dir)
         if latest and ckpt.exists(latest):
             tensors = ckpt.load(latest)
-            ckpt.restore(trainer.store, tensors, strict=False)
+            ckpt.restore_training_state(trainer, tensors)      # variables + RMSProp slots + EMA shadows
             comm.set_global_step(ckpt.step_of(latest))
             log("restored %s" % latest)
     if args.init_checkpoint:
@@ -224,6 +229,7 @@ def run_worker(args) -> int:
         if not src or not ckpt.exists(src):
             raise SystemExit("--init_checkpoint: no checkpoint at %r" % args.init_checkpoint)
         ckpt.restore(trainer.store, ckpt.load(src), strict=False)
+        comm.reset_ema_to_params()                             # fine-tuning: shadows start at the loaded weights
         comm.set_global_step(0)
         log("initialised from %s (global step reset to 0)" % src)
     batches = DevicePrefetcher(make_batches(args, spec, rank, world, device), device)

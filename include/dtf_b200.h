@@ -79,6 +79,12 @@ typedef struct {
   const float* fin_stats; const float* fin_gamma; const float* fin_beta;
   float* fin_moving_mean; float* fin_moving_var; float* fin_mean; float* fin_invstd;
   float fin_inv_count, fin_unbias, fin_eps, fin_decay; int fin_update_moving;
+  /* optional pull gate (BSP push / pull over symmetric memory, see dtf_ps_bucket_step): when gate_flags != NULL the
+   * weight-load warp waits until gate_flags[0 .. gate_n) >= *gate_epoch before its first weight load — "every
+   * owner's part of the bucket that holds wt has reached this replica".  The wait gives up after
+   * gate_timeout_cycles SM clocks and sets *gate_status = 1. */
+  const unsigned int* gate_flags; int gate_n; const unsigned int* gate_epoch; unsigned int* gate_status;
+  long long gate_timeout_cycles;
 } dtf_conv_gemm_params;
 
 int dtf_conv_gemm(const dtf_conv_gemm_params* p, void* stream);
@@ -289,14 +295,26 @@ int dtf_crop_resize_host(const unsigned char* img, int H, int W, int y0, int x0,
 /* ------------------------------------------------------------------------------------ */
 int dtf_fused_update(float* w, const float* g, float* ms, float* mom, float* ema, long long n,
                      long long n_decayed, const float* hyper, int kind, void* stream);
-/* One BSP step over peer-mapped buffers (reduce-scatter + update + all-gather in one kernel per rank).
+/* BSP push of one bucket [lo, lo+len) of the flat buffer over peer-mapped memory: rank r owns
+ * [lo + r*chunk, min(lo + (r+1)*chunk, lo+len)).  The kernel signals ready[rank] to every peer, waits for all W
+ * ready words, reduces its part over the W gradient buffers, applies the optimiser (slots ms / mom / ema: this
+ * rank's part only), stores the result into every replica and raises updated[rank] in every peer's flag block; it
+ * does not wait for the other owners (dtf_ps_gate / the convolution gate do, where the values are consumed).
+ * Flag block of a rank: uint32 words; ready_off / updated_off are the word offsets of this bucket's W-word rows.
+ * *epoch_ptr = completed steps; epoch_out (NULL except on the step's last bucket) receives *epoch_ptr + 1.
  * mc_grads / mc_params: NVLS multicast addresses of the gradient / parameter regions of the same symmetric buffer
- * (both or neither; NULL = unicast peer loads): the reduction then runs in the NVSwitch (multimem.ld_reduce) and
- * the updated range is written to all replicas with one multimem.st per 16 bytes. */
-int dtf_ps_bsp_step(const float* const* peer_grads, float* const* peer_params, unsigned int* const* peer_flags,
-                    unsigned int* local_counter, unsigned int* status, int rank, int world, long long shard,
-                    long long wd_boundary, float* ms, float* mom, float* ema, const float* hyper, int kind,
-                    unsigned int* epoch_ptr, const float* mc_grads, float* mc_params, void* stream);
+ * (both or neither; NULL = unicast peer loads and stores): the reduction then runs in the NVSwitch
+ * (multimem.ld_reduce) and the updated range is written to all replicas with one multimem.st per 16 bytes.
+ * timeout_s <= 0: 300 s.  max_blocks <= 0: one block per SM. */
+int dtf_ps_bucket_step(const float* const* peer_grads, float* const* peer_params, unsigned int* const* peer_flags,
+                       unsigned int* local_counter, unsigned int* status, int rank, int world, int ready_off,
+                       int updated_off, long long lo, long long len, long long chunk, long long wd_boundary,
+                       float* ms, float* mom, float* ema, const float* hyper, int kind,
+                       const unsigned int* epoch_ptr, unsigned int* epoch_out, const float* mc_grads,
+                       float* mc_params, double timeout_s, int max_blocks, void* stream);
+/* Wait (one warp, bounded) until flags[0 .. n) >= *epoch_ptr; status = 1 on timeout. */
+int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int* epoch_ptr, unsigned int* status,
+                double timeout_s, void* stream);
 /* One ASP/SSP step: one-sided apply of the local gradient on every owner's range, then refresh the replica. */
 int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms, float* const* peer_mom,
                       float* const* peer_ema, unsigned long long* global_step, int rank, int world, long long shard,
