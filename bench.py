@@ -7,9 +7,13 @@ ResNet-32 (CIFAR-10 shapes, resnet_model.py) BSP, batch 128 per worker — on N 
         bench.py --gpus N --steps K --warmup W
 
 One JSON line is printed by rank 0 (contract in the task statement).  ``value`` is the device-timed
-whole-job images/sec over exactly K steps with inputs resident on the GPU; ``e2e`` repeats the measurement
+whole-job images/sec with inputs resident on the GPU: the K-step region is timed ``repeats`` times back to back
+inside one pair of CUDA events so that at least ``--min-seconds`` (1 s) of device time is covered
+(``steps_timed = repeats * K``; nvidia-smi is sampled every 20 ms meanwhile).  ``e2e`` repeats the measurement
 through the public ``Trainer.train_step`` API with a pinned-host -> device copy of every batch and a
-device -> host read of every loss inside the timed region.  Other models/modes: ``--model inception --mode ssp``.
+device -> host read of every loss inside the timed region.  ``secondary`` carries the other configs of
+BASELINE.json's metric at the same N, each measured exactly like the headline: Inception-v3 SSP (bound 3),
+Inception-v3 BSP and ResNet-32 SSP.  Other models/modes as the headline: ``--model inception --mode ssp``.
 
 ``--impl reference`` would run the unmodified reference; it is Python-2 / TensorFlow-1.x code that cannot
 be installed here, so that arm reports ``unavailable``.
@@ -47,6 +51,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--image-size", type=int, default=None, help="model-zoo networks only (default: the network's own)")
     ap.add_argument("--num-classes", type=int, default=None, help="model-zoo networks only (default 1001)")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="headline only: skip the other BASELINE.json configs (Inception-v3 SSP / BSP, ResNet SSP)")
+    ap.add_argument("--min-seconds", type=float, default=1.0,
+                    help="the K-step region is repeated back to back until this much device time has been timed")
     return ap.parse_args()
 
 
@@ -64,7 +72,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
@@ -110,38 +118,17 @@ def _protect_stdout():
     return emit
 
 
-def main():
-    args = parse()
-    emit = _protect_stdout()
-    if args.impl == "reference":
-        emit(json.dumps({"impl": "reference", "unavailable":
-                         "reference is Python-2/TensorFlow-1.x (tf.contrib.slim, Supervisor, SyncReplicasOptimizer, "
-                         "thrift) with no setup.py; it cannot be installed or run offline on this image (DESIGN.md)"}))
-        return 0
-
+def measure(args, model, mode, world, rank, local_rank, device, want_e2e=True):
+    """One config, measured like the headline: warm-up, device-timed region (>= min-seconds), end-to-end region."""
     import torch
     import torch.distributed as dist
 
     from distributed_tensorflow_models_b200 import _native as nat
     from distributed_tensorflow_models_b200.models.registry import MODEL_SPECS
-    from distributed_tensorflow_models_b200.ops import functional as Fn
     from distributed_tensorflow_models_b200.parallel.comm import LocalComm, TorchDistComm
     from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and world > 1:
-        args.gpus = world
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    Fn.set_backend("auto" if args.kernels == "native" else "torch")
-    torch.backends.cudnn.allow_tf32 = True
-    torch.backends.cuda.matmul.allow_tf32 = True
-
     if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
         if args.backend == "symm":
             from distributed_tensorflow_models_b200.parallel.symm import SymmComm
             comm = SymmComm()
@@ -150,19 +137,16 @@ def main():
     else:
         comm = LocalComm()
 
-    if args.model in MODEL_SPECS:
-        spec = MODEL_SPECS[args.model]
+    if model in MODEL_SPECS:
+        spec = MODEL_SPECS[model]
     else:       # any other network of the model-zoo registry (not a BASELINE.json config; for the zoo sweeps)
         from distributed_tensorflow_models_b200.models.registry import spec_for
-        spec = spec_for(args.model, args.image_size, args.num_classes)
-    setup = TrainSetup(model=args.model, mode=args.mode, num_workers=world, staleness=args.staleness,
+        spec = spec_for(model, args.image_size, args.num_classes)
+    setup = TrainSetup(model=model, mode=mode, num_workers=world, staleness=args.staleness,
                        cuda_graph=not args.no_graph, fuse_bn=not args.no_fuse_bn, seed=0,
                        branch_streams=not args.no_branch_streams, image_size=args.image_size,
                        num_classes=args.num_classes)
-    if args.batch:
-        setup.batch_size = args.batch
-    else:
-        setup.batch_size = spec.batch_size
+    setup.batch_size = args.batch if args.batch else spec.batch_size
     trainer = Trainer(setup, comm, device)
     bs = setup.batch_size
 
@@ -180,11 +164,22 @@ def main():
             torch.cuda.synchronize(device)
 
     # ---- warm-up (also captures the CUDA graph) -----------------------------------------------------
-    for i in range(max(3, args.warmup)):
+    warm = max(3, args.warmup)
+    for i in range(warm):
         trainer.train_step(dev_x[i % 2], dev_y[i % 2])
     sync_all()
+    # a short probe decides how often the K-step region is repeated to cover --min-seconds of device time
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    for i in range(3):
+        trainer.train_step(dev_x[i % 2], dev_y[i % 2])
+    p1.record()
+    sync_all()
+    probe_ms = comm.max_over_ranks(p0.elapsed_time(p1) / 3.0)
+    repeats = max(1, int(-(-args.min_seconds * 1e3 // max(probe_ms * args.steps, 1e-3))))
+    steps_timed = repeats * args.steps
 
-    # ---- device-timed region: exactly K steps -------------------------------------------------------
+    # ---- device-timed region -----------------------------------------------------------------------
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -192,26 +187,26 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     e0.record()
-    for i in range(args.steps):
+    for i in range(steps_timed):
         out = trainer.train_step(dev_x[i % 2], dev_y[i % 2])
     e1.record()
     sync_all()
     ms = e0.elapsed_time(e1)
-    launches = nat.launch_count() + trainer.graph_kernel_launches * args.steps
+    launches = nat.launch_count() + trainer.graph_kernel_launches * steps_timed
     clocks = sampler.stop() if rank == 0 else None
     ms = comm.max_over_ranks(ms)
     last_loss = float(out["loss"])
 
     # ---- end-to-end region: pinned host -> device copy + loss read-back every step -------------------
     e2e = None
-    if not args.no_e2e:
+    if want_e2e and not args.no_e2e:
         sync_all()
         t0 = torch.cuda.Event(enable_timing=True)
         t1 = torch.cuda.Event(enable_timing=True)
         from distributed_tensorflow_models_b200.utils.pipeline import DevicePrefetcher, ScalarReadback
         # one-time set-up (a copy stream, four pinned 4-byte slots) happens before the clock starts, as it does at
         # the start of a training run; no copy is issued until the first next() inside the timed region
-        feed = DevicePrefetcher(((host_x[i % n_host_batches], host_y[i % n_host_batches]) for i in range(args.steps)),
+        feed = DevicePrefetcher(((host_x[i % n_host_batches], host_y[i % n_host_batches]) for i in range(steps_timed)),
                                 device, lazy=True)
         reader = ScalarReadback(device)
         sync_all()
@@ -220,7 +215,7 @@ def main():
         # every step's loss is read back, both inside the timed region; the copy of step i+1 is issued while step i
         # computes and the loss of step i is read after step i+1 has been launched
         read = []
-        for i in range(args.steps):
+        for i in range(steps_timed):
             x, y = next(feed)
             o = trainer.train_step(x, y)
             reader.push(o["loss"])
@@ -228,37 +223,88 @@ def main():
                 read.append(reader.pop()[0])
         while len(reader):
             read.append(reader.pop()[0])              # D2H read of every step's result
-        assert len(read) == args.steps and all(v == v for v in read)
+        assert len(read) == steps_timed and all(v == v for v in read)
         t1.record()
         sync_all()
         ems = comm.max_over_ranks(t0.elapsed_time(t1))
-        e2e = {"value": world * bs * args.steps / (ems / 1e3), "unit": "images/sec",
+        e2e = {"value": world * bs * steps_timed / (ems / 1e3), "unit": "images/sec",
                "h2d_bytes_per_step": host_x[0].numel() * 4 + host_y[0].numel() * 8, "d2h_bytes_per_step": 4,
-               "ms_per_step": ems / args.steps,
+               "ms_per_step": ems / steps_timed,
                "pipeline": "every step's batch is copied from pinned host memory (copy of step i+1 overlaps step i) "
                            "and every step's loss is read back (after step i+1 has been queued)"}
     if hasattr(comm, "check_status"):
         comm.check_status()
-
-    if rank == 0:
-        value = world * bs * args.steps / (ms / 1e3)
-        line = {
-            "metric": f"images/sec, {args.model} ({'CIFAR-10' if spec.dataset == 'cifar10' else 'ImageNet'} shapes) {args.mode.upper()} training",
-            "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "fp32 storage/accumulate, tf32 tensor-core multiply (reference is fp32; no bf16/fp8)",
-            "data": "synthetic (random images of the dataset's shape, random-init weights)",
-            "config": {"model": f"resnet{setup.resnet_size}" if args.model == "resnet" else args.model,
-                       "global_batch": world * bs, "per_gpu_batch": bs, "image": spec.image_size,
-                       "parallelism": f"ps-dp{world} ({args.backend if world > 1 else 'single rank'})",
-                       "mode": args.mode, "kernels": args.kernels, "cuda_graph": not args.no_graph,
-                       "l2": "no explicit flush: each step streams > 126 MB of activations/gradients through HBM"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": last_loss,
-            "impl": "ours",
-        }
-        emit(json.dumps(line))
     if world > 1:
         comm.finish()
+    res = {
+        "metric": f"images/sec, {model} ({'CIFAR-10' if spec.dataset == 'cifar10' else 'ImageNet'} shapes) {mode.upper()} training",
+        "value": world * bs * steps_timed / (ms / 1e3), "unit": "images/sec", "n_gpus": world, "steps": args.steps,
+        "repeats": repeats, "steps_timed": steps_timed, "warmup": warm, "ms_per_step": ms / steps_timed,
+        "timed_region_ms": ms,
+        "config": {"model": f"resnet{setup.resnet_size}" if model == "resnet" else model,
+                   "global_batch": world * bs, "per_gpu_batch": bs, "image": spec.image_size,
+                   "parallelism": f"ps-dp{world} ({args.backend if world > 1 else 'single rank'})",
+                   "mode": mode, "kernels": args.kernels, "cuda_graph": not args.no_graph,
+                   "l2": "no explicit flush: each step streams > 126 MB of activations/gradients through HBM"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": last_loss,
+    }
+    if mode == "ssp":
+        res["config"]["staleness"] = args.staleness
+    if world > 1 and args.backend == "symm" and getattr(comm, "bucketed", False):
+        res["config"]["push"] = {"buckets": len(comm.buckets), "overlap_with_backward": bool(comm.overlap),
+                                 "nvls": bool(comm.mc_params), "pull_gate": comm.gate_mode}
+    del trainer, comm
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+def main():
+    args = parse()
+    emit = _protect_stdout()
+    if args.impl == "reference":
+        emit(json.dumps({"impl": "reference", "unavailable":
+                         "reference is Python-2/TensorFlow-1.x (tf.contrib.slim, Supervisor, SyncReplicasOptimizer, "
+                         "thrift) with no setup.py; it cannot be installed or run offline on this image (DESIGN.md)"}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    from distributed_tensorflow_models_b200.ops import functional as Fn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    Fn.set_backend("auto" if args.kernels == "native" else "torch")
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    line = measure(args, args.model, args.mode, world, rank, local_rank, device)
+    line.update({"higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                 "dtype": "fp32 storage/accumulate, tf32 tensor-core multiply (reference is fp32; no bf16/fp8)",
+                 "data": "synthetic (random images of the dataset's shape, random-init weights)", "impl": "ours"})
+    secondary = []
+    if not args.no_secondary and args.model == "resnet" and args.mode == "bsp":
+        # the other half of BASELINE.json's metric ("ResNet CIFAR-10 & Inception-v3 in BSP/SSP modes") at the same N
+        for model, mode in (("inception", "ssp"), ("inception", "bsp"), ("resnet", "ssp")):
+            try:
+                secondary.append(measure(args, model, mode, world, rank, local_rank, device))
+            except Exception as e:  # noqa: BLE001 — the headline must still be printed
+                secondary.append({"metric": f"{model} {mode}", "error": repr(e)[:300]})
+                break
+    line["secondary"] = secondary
+    if rank == 0:
+        emit(json.dumps(line))
+    if world > 1:
         dist.destroy_process_group()
     return 0
 

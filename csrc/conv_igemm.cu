@@ -664,7 +664,7 @@ extern "C" int dtf_conv_gemm(const dtf_conv_gemm_params* pp, void* stream_) {
   cfg.tmem_cols = next_pow2_cols(2 * cfg.BN);
   const int stage_bytes = A_STAGE_BYTES + cfg.BN * BK * 4;
   const int fixed_smem = 1024 + 16 * 3 * 8 + 4 * 8 + 16 + 2 * 256 * 4 + PRODUCER_GROUPS * BM * (int)sizeof(int2);
-  int stages = (227 * 1024 - fixed_smem) / stage_bytes;
+  int stages = (SMEM_BUDGET - fixed_smem) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages > cfg.num_kb + 1) stages = cfg.num_kb + 1;
   if (stages < 2) stages = 2;

@@ -354,7 +354,7 @@ extern "C" int dtf_conv_wgrad(const dtf_conv_wgrad_params* pp, void* stream_) {
   while (tc < 2 * cfg.BN) tc <<= 1;
   cfg.tmem_cols = tc;
   const int stage_bytes = WG_A_STAGE_BYTES + cfg.BN * WG_BK * 4;
-  int stages = (224 * 1024) / stage_bytes;
+  int stages = (SMEM_BUDGET - 3 * 1024) / stage_bytes;
   if (stages > 6) stages = 6;
   if (stages < 2) stages = 2;
   cfg.stages = stages;

@@ -414,7 +414,7 @@ int try_conv_wgrad_mn(const dtf_conv_wgrad_params& p, cudaStream_t stream, bool*
   cfg.tmem_cols = tc;
   const int stage_bytes = MN_A_STAGE_BYTES + cfg.n_atoms * MN_ATOM_BYTES;
   const int fixed = 1024 + (3 * 8 + 4) * 8 + 32 + 4 * MN_BKP * 16;
-  int stages = (227 * 1024 - fixed) / stage_bytes;
+  int stages = (SMEM_BUDGET - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return 0;
   cfg.stages = stages;

@@ -443,7 +443,7 @@ int try_conv_win(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* launc
   const int b_stage_bytes = cfg.BN * 128;
   const int win_bytes = cfg.win_pad * CB * 4;
   const int fixed = 1024 + (2 * W_MAX_BSTAGES + 2 * W_MAX_WIN + 4) * 8 + 16 + 2 * 256 * 4 + W_MAX_K8 * 4;
-  const int avail = 227 * 1024 - fixed;
+  const int avail = SMEM_BUDGET - fixed;
   cfg.b_resident = (cfg.cblocks == 1 && cfg.n_tiles == 1 && cfg.n_kb <= W_MAX_BSTAGES &&
                     cfg.n_kb * b_stage_bytes <= 80 * 1024) ? 1 : 0;
   if (cfg.b_resident) {

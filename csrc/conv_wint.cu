@@ -560,7 +560,7 @@ int try_conv_wint(const dtf_conv_gemm_params& p, cudaStream_t stream, bool* laun
     cfg.win = tn + lin_max - cfg.lin_min;
     cfg.win_pad = ceil_div(cfg.win - 2, 8) * 8 + 2;
     win_bytes = cfg.win_pad * CB * 4;
-    const int avail = 227 * 1024 - fixed - 2 * tn * p.Nout * 4;
+    const int avail = SMEM_BUDGET - fixed - 2 * tn * p.Nout * 4;
     if (cfg.b_resident) {
       cfg.b_stages = cfg.n_kb;
       const int nw = (avail - cfg.b_stages * b_stage_bytes) / win_bytes;

@@ -18,7 +18,7 @@ void set_last_error(const std::string& s) {
   g_last_error_global = s;
 }
 
-int num_sms() {
+int hw_num_sms() {
   static int cached[64] = {0};
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
@@ -29,6 +29,24 @@ int num_sms() {
   }
   return cached[dev];
 }
+
+// SMs the compute kernels size their grids for.  While a parameter-server push runs beside the backward pass it owns
+// a few SMs outright (its blocks take a whole register file, see ps_update.cu), and the persistent convolution
+// kernels are launched with correspondingly fewer CTAs instead of queueing a second wave behind the push.
+static int g_sm_reserved = 0;      // process-wide: the backward pass launches from the autograd thread
+int num_sms() {
+  const int n = hw_num_sms() - g_sm_reserved;
+  return n > 8 ? n : 8;
+}
+}  // namespace dtf
+
+extern "C" int dtf_reserve_sms(int n) {
+  const int prev = dtf::g_sm_reserved;
+  dtf::g_sm_reserved = n > 0 ? n : 0;
+  return prev;
+}
+
+namespace dtf {
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

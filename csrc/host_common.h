@@ -33,7 +33,8 @@ void set_last_error(const std::string& s);
     }                                                                                       \
   } while (0)
 
-int num_sms();
+int num_sms();      // SMs available to compute kernels (hardware count minus dtf_reserve_sms)
+int hw_num_sms();
 
 // [rows][cols] fp32 row-major matrix, box = {32 cols (128 B), box_rows}, 128-byte swizzle.
 // Returns nullptr (and sets last error) on failure.  Cached per (ptr, rows, cols, box_rows).
@@ -72,6 +73,9 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   cfg.numAttrs = g_pdl_enabled ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+
+// Shared-memory budget of the persistent tensor-core kernels (the most a CTA may take).
+constexpr int SMEM_BUDGET = 227 * 1024;
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int round_up(int a, int b) { return ceil_div(a, b) * b; }

@@ -153,10 +153,16 @@ __device__ __forceinline__ void red_add_f32x4(float* p, const float4 v) {
 }
 
 constexpr int PUSH_UNROLL = 4;      // 16-byte reductions in flight per thread
+// Block shape.  A push block cannot share an SM with a persistent convolution CTA (13-14 warps x 120-128 registers
+// fill the 16 K registers of the busiest SM sub-partition; measured: every convolution of VGG's backward pass waited
+// for the push's last block, profiles/trace_vgg_bsp_n2_before_carveout.txt).  So the push does not try to squeeze
+// in: it runs 1024-thread blocks that take a whole register file each, on as many SMs as the host reserves for it
+// (dtf_reserve_sms keeps the compute grids off that many), with 64 KB of reductions in flight per SM.
+constexpr int PUSH_THREADS = 1024;
 
-__global__ void __launch_bounds__(512)
+template <int KIND, bool USE_MC>
+__global__ void __launch_bounds__(PUSH_THREADS, 1)
 ps_bucket_kernel(const BucketArgs a) {
-  __shared__ int s_ok;
   const int W = a.W, me = a.rank;
   const unsigned int epoch = *reinterpret_cast<const volatile unsigned int*>(a.epoch_ptr) + 1u;
   // ---- "my gradients of this bucket are complete" -> every rank; then wait for everybody's -----------------
@@ -165,9 +171,9 @@ ps_bucket_kernel(const BucketArgs a) {
       __threadfence_system();
       st_release_sys(a.peer_flags[threadIdx.x] + a.ready_off + me, epoch);
     }
-    if (threadIdx.x == 0) s_ok = wait_all(a.peer_flags[me] + a.ready_off, W, epoch, a.timeout_cycles) ? 1 : 0;
-    __syncthreads();
-    if (!s_ok) { if (threadIdx.x == 0) atomicExch(a.status, 1u); return; }
+    int timed_out = 0;
+    if (threadIdx.x == 0) timed_out = wait_all(a.peer_flags[me] + a.ready_off, W, epoch, a.timeout_cycles) ? 0 : 1;
+    if (__syncthreads_or(timed_out)) { if (threadIdx.x == 0) atomicExch(a.status, 1u); return; }   // (no static smem)
   }
 
   // ---- push: reduce my part over all ranks' gradients + optimiser; pull: store into every replica -----------
@@ -179,7 +185,6 @@ ps_bucket_kernel(const BucketArgs a) {
   float* wmine = a.peer_params[me] + lo;
   const long long n4 = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  const bool use_mc = a.mc_grads != nullptr && W > 1;
   for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < n4; base += stride * PUSH_UNROLL) {
     float4 g[PUSH_UNROLL];
     // issue all the remote reductions of this round before touching any of them
@@ -188,7 +193,7 @@ ps_bucket_kernel(const BucketArgs a) {
       const long long i4 = base + u * stride;
       g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (i4 < n4) {
-        if (use_mc) {
+        if (USE_MC) {
           g[u] = multimem_ld_reduce_add_f32x4(a.mc_grads + lo + (i4 << 2));   // sum over all ranks, formed in the switch
         } else {
           for (int q = 0; q < W; ++q) {
@@ -202,28 +207,28 @@ ps_bucket_kernel(const BucketArgs a) {
 #pragma unroll
     for (int u = 0; u < PUSH_UNROLL; ++u) {
       const long long i4 = base + u * stride;
-      if (i4 >= n4) break;
+      if (i4 >= n4) continue;
       float4 gv = g[u];
       gv.x *= invW; gv.y *= invW; gv.z *= invW; gv.w *= invW;
       float4 wv = *reinterpret_cast<float4*>(wmine + (i4 << 2));
       float4 m2 = make_float4(0.f, 0.f, 0.f, 0.f), mo = m2;
-      if (a.kind == 1) {
+      if (KIND == 1) {
         m2 = *reinterpret_cast<float4*>(a.ms + (i4 << 2));
         mo = *reinterpret_cast<float4*>(a.mom + (i4 << 2));
       }
       const long long gi = lo + (i4 << 2);
-      wv.x = update_elem(a.kind, h, wv.x, gv.x, gi + 0 < a.wd_boundary, &m2.x, &mo.x);
-      wv.y = update_elem(a.kind, h, wv.y, gv.y, gi + 1 < a.wd_boundary, &m2.y, &mo.y);
-      wv.z = update_elem(a.kind, h, wv.z, gv.z, gi + 2 < a.wd_boundary, &m2.z, &mo.z);
-      wv.w = update_elem(a.kind, h, wv.w, gv.w, gi + 3 < a.wd_boundary, &m2.w, &mo.w);
-      if (use_mc) {
+      wv.x = update_elem(KIND, h, wv.x, gv.x, gi + 0 < a.wd_boundary, &m2.x, &mo.x);
+      wv.y = update_elem(KIND, h, wv.y, gv.y, gi + 1 < a.wd_boundary, &m2.y, &mo.y);
+      wv.z = update_elem(KIND, h, wv.z, gv.z, gi + 2 < a.wd_boundary, &m2.z, &mo.z);
+      wv.w = update_elem(KIND, h, wv.w, gv.w, gi + 3 < a.wd_boundary, &m2.w, &mo.w);
+      if (USE_MC) {
         multimem_st_f32x4(a.mc_params + gi, wv);                 // every replica, mine too
       } else {
         *reinterpret_cast<float4*>(wmine + (i4 << 2)) = wv;
         for (int q = 1; q < W; ++q)                               // P2P stores into the other replicas
           *reinterpret_cast<float4*>(a.peer_params[(me + q) % W] + gi) = wv;
       }
-      if (a.kind == 1) {
+      if (KIND == 1) {
         *reinterpret_cast<float4*>(a.ms + (i4 << 2)) = m2;
         *reinterpret_cast<float4*>(a.mom + (i4 << 2)) = mo;
       }
@@ -278,6 +283,8 @@ struct AsyncArgs {
   long long shard, wd_boundary;
   const float* hyper;
   int kind;
+  long long lo, len;                // the part of the flat buffer this launch pushes (a bucket; multiples of 4)
+  int bump_step;                    // 1 on the step's first launch: global_step += 1
 };
 
 constexpr int ASYNC_UNROLL = 4;
@@ -286,14 +293,16 @@ constexpr int ASYNC_UNROLL = 4;
 // the traffic that crosses NVLink is: SGD — one red.add out, one load back; RMSProp — the owner's two slots in
 // (one round trip, both loads issued together), their new values and the red.add of the step out.  The refresh of
 // the replica rides in the same loop as the push (opposite link directions), so the two phases overlap.
-__global__ void __launch_bounds__(512)
+template <int KIND, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1)
 ps_async_step_kernel(const AsyncArgs a) {
   const Hyper h = load_hyper(a.hyper);
   const int W = a.W, me = a.rank;
-  const long long shard4 = a.shard >> 2;
-  const long long total4 = shard4 * W;
+  const long long total4 = a.len >> 2;
+  // workers start at different places of the range, so that they do not all hit the same owner at once
+  const long long rot4 = (total4 / W) * me;
   float* mine = a.peer_params[me];
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd_system(a.global_step, 1ull);
+  if (a.bump_step && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd_system(a.global_step, 1ull);
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < total4; base += stride * ASYNC_UNROLL) {
     float4 g[ASYNC_UNROLL], m2[ASYNC_UNROLL], mo[ASYNC_UNROLL];
@@ -304,10 +313,11 @@ ps_async_step_kernel(const AsyncArgs a) {
       const long long j4 = base + u * stride;
       own[u] = -1;
       if (j4 < total4) {
-        const int k = (int)(j4 / shard4);
-        const long long i4 = j4 - (long long)k * shard4;
-        own[u] = (me + k) % W;                 // owner order staggered by rank
-        gi[u] = (long long)own[u] * a.shard + (i4 << 2);
+        long long r4 = j4 + rot4;
+        if (r4 >= total4) r4 -= total4;
+        gi[u] = a.lo + (r4 << 2);
+        own[u] = (int)(gi[u] / a.shard);       // flat shards: rank r owns [r*shard, (r+1)*shard)
+        const long long i4 = (gi[u] - (long long)own[u] * a.shard) >> 2;
         float4 gv = *reinterpret_cast<const float4*>(a.grads + gi[u]);
         gv.x *= h.gscale; gv.y *= h.gscale; gv.z *= h.gscale; gv.w *= h.gscale;
         // the weight-decay term uses this worker's replica of w (what the gradient was computed from)
@@ -317,7 +327,7 @@ ps_async_step_kernel(const AsyncArgs a) {
         if (gi[u] + 2 < a.wd_boundary) gv.z = fmaf(h.wd, wl.z, gv.z);
         if (gi[u] + 3 < a.wd_boundary) gv.w = fmaf(h.wd, wl.w, gv.w);
         g[u] = gv;
-        if (a.kind == 1) {                      // slots live with the owner; racy RMW is the semantics of
+        if (KIND == 1) {                      // slots live with the owner; racy RMW is the semantics of
           m2[u] = ld_peer_f32x4(a.peer_ms[own[u]] + (i4 << 2));      // use_locking=False
           mo[u] = ld_peer_f32x4(a.peer_mom[own[u]] + (i4 << 2));
         }
@@ -328,7 +338,7 @@ ps_async_step_kernel(const AsyncArgs a) {
       if (own[u] < 0) break;
       float* wp = a.peer_params[own[u]] + gi[u];
       float4 d;
-      if (a.kind == 0) {
+      if (KIND == 0) {
         d = make_float4(-h.lr * g[u].x, -h.lr * g[u].y, -h.lr * g[u].z, -h.lr * g[u].w);
       } else {
         const long long i = gi[u] - (long long)own[u] * a.shard;
@@ -362,7 +372,11 @@ ps_async_step_kernel(const AsyncArgs a) {
     float* ema = a.peer_ema[me];
     const float* wm = mine + (long long)me * a.shard;
     const float k = 1.f - h.ema_decay;
-    for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < shard4; i4 += stride) {
+    // the part of my own shard that lies inside this launch's range
+    long long e_lo = a.lo - (long long)me * a.shard, e_hi = a.lo + a.len - (long long)me * a.shard;
+    e_lo = e_lo < 0 ? 0 : e_lo;
+    e_hi = e_hi > a.shard ? a.shard : e_hi;
+    for (long long i4 = (e_lo >> 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < (e_hi >> 2); i4 += stride) {
       float4 e = *reinterpret_cast<float4*>(ema + (i4 << 2));
       const float4 wv = ld_peer_f32x4(wm + (i4 << 2));
       e.x -= k * (e.x - wv.x); e.y -= k * (e.y - wv.y); e.z -= k * (e.z - wv.z); e.w -= k * (e.w - wv.w);
@@ -417,6 +431,18 @@ extern "C" int dtf_fused_update(float* w, const float* g, float* ms, float* mom,
   return 0;
 }
 
+// The persistent convolution kernels need the SM's largest shared-memory carve-out (> 220 KB).  An SM cannot change
+// its carve-out while blocks are resident, so a kernel that runs beside them must ask for the same split: with the
+// default (L1-heavy) preference the 1 ms push of VGG's fc6 bucket kept every convolution of the backward pass
+// waiting until its last block had left (profiles/trace_vgg_bsp_n2_before_carveout.txt).
+template <typename K>
+static void prefer_max_shared_once(K kernel, bool* done_for_device) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done_for_device[dev]) return;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  done_for_device[dev] = true;
+}
+
 static long long timeout_cycles_of(double timeout_s) {
   if (!(timeout_s > 0.0)) timeout_s = 300.0;
   return (long long)(timeout_s * 1.9e9);
@@ -446,10 +472,21 @@ extern "C" int dtf_ps_bucket_step(const float* const* peer_grads, float* const* 
   // it is sized so that a thread runs about one unrolled round, capped to leave SMs to the backward pass
   long long n = len - (long long)rank * chunk;
   n = n < 0 ? 0 : (n > chunk ? chunk : n);
-  long long b = ((n >> 2) + 512LL * PUSH_UNROLL - 1) / (512LL * PUSH_UNROLL);
-  const int cap = max_blocks > 0 ? max_blocks : num_sms();
+  long long b = ((n >> 2) + (long long)PUSH_THREADS * PUSH_UNROLL - 1) / ((long long)PUSH_THREADS * PUSH_UNROLL);
+  const int cap = max_blocks > 0 ? max_blocks : hw_num_sms();
   const int grid = (int)(b < cap ? (b > 0 ? b : 1) : cap);
-  ps_bucket_kernel<<<grid, 512, 0, stream>>>(a);
+  const bool mc = mc_grads != nullptr && world > 1;
+  static bool carveout_set[4][64];
+#define DTF_LAUNCH_BUCKET(K, M, slot)                                        \
+  do {                                                                       \
+    prefer_max_shared_once(ps_bucket_kernel<K, M>, carveout_set[slot]);      \
+    ps_bucket_kernel<K, M><<<grid, PUSH_THREADS, 0, stream>>>(a);            \
+  } while (0)
+  if (kind == 0 && mc) DTF_LAUNCH_BUCKET(0, true, 0);
+  else if (kind == 0) DTF_LAUNCH_BUCKET(0, false, 1);
+  else if (mc) DTF_LAUNCH_BUCKET(1, true, 2);
+  else DTF_LAUNCH_BUCKET(1, false, 3);
+#undef DTF_LAUNCH_BUCKET
   DTF_CHECK(cudaGetLastError());
   return 0;
 }
@@ -458,6 +495,8 @@ extern "C" int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int*
                            double timeout_s, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (n <= 0) return 0;
+  static bool carveout_set[64];
+  prefer_max_shared_once(ps_gate_kernel, carveout_set);
   ps_gate_kernel<<<1, 32, 0, stream>>>(flags, n, epoch_ptr, status, timeout_cycles_of(timeout_s));
   DTF_CHECK(cudaGetLastError());
   return 0;
@@ -466,17 +505,30 @@ extern "C" int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int*
 extern "C" int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms,
                                  float* const* peer_mom, float* const* peer_ema, unsigned long long* global_step,
                                  int rank, int world, long long shard, long long wd_boundary, const float* hyper,
-                                 int kind, void* stream_) {
+                                 int kind, long long lo, long long len, int bump_step, int max_blocks, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(shard % 4 == 0, "shard length must be a multiple of 4 floats");
+  DTF_REQUIRE(lo % 4 == 0 && len % 4 == 0 && lo >= 0 && lo + len <= shard * world, "range must be 4-aligned and inside the buffer");
   DTF_REQUIRE(kind == 0 || (peer_ms && peer_mom), "RMSProp needs its slots");
   AsyncArgs a;
   a.grads = grads; a.peer_params = peer_params; a.peer_ms = peer_ms; a.peer_mom = peer_mom; a.peer_ema = peer_ema;
   a.global_step = global_step; a.rank = rank; a.W = world; a.shard = shard; a.wd_boundary = wd_boundary;
-  a.hyper = hyper; a.kind = kind;
-  long long b = ((shard * world >> 2) + 512LL * ASYNC_UNROLL - 1) / (512LL * ASYNC_UNROLL);
-  const long long cap = 2LL * num_sms();
-  ps_async_step_kernel<<<(int)(b < cap ? (b > 0 ? b : 1) : cap), 512, 0, stream>>>(a);
+  a.hyper = hyper; a.kind = kind; a.lo = lo; a.len = len; a.bump_step = bump_step;
+  if (len == 0 && !bump_step) return 0;
+  // SGD keeps 16 registers of gradient per thread: 1024 threads per SM at 64 registers; RMSProp also carries the
+  // owner's two slots: 512 threads at 128
+  const long long threads = kind == 0 ? 1024 : 512;
+  long long b = ((len >> 2) + threads * ASYNC_UNROLL - 1) / (threads * ASYNC_UNROLL);
+  const long long cap = max_blocks > 0 ? max_blocks : hw_num_sms();
+  const int grid = (int)(b < cap ? (b > 0 ? b : 1) : cap);
+  static bool carveout_set[2][64];
+  if (kind == 0) {
+    prefer_max_shared_once(ps_async_step_kernel<0, 1024>, carveout_set[0]);
+    ps_async_step_kernel<0, 1024><<<grid, 1024, 0, stream>>>(a);
+  } else {
+    prefer_max_shared_once(ps_async_step_kernel<1, 512>, carveout_set[1]);
+    ps_async_step_kernel<1, 512><<<grid, 512, 0, stream>>>(a);
+  }
   DTF_CHECK(cudaGetLastError());
   return 0;
 }

@@ -98,6 +98,9 @@ def _pad4(x: torch.Tensor, w: torch.Tensor):
     return torch.nn.functional.pad(x, (0, padc)), torch.nn.functional.pad(w, (0, padc)).contiguous()
 
 
+one_tap_enabled = [True]      # tests switch the single-live-tap shortcut off to compare against the full sweep
+
+
 class _ConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias, stride, pad, out_hw, relu, stats):
@@ -142,8 +145,66 @@ class _ConvFn(torch.autograd.Function):
         return dx, dw, db, None, None, None, None, None
 
 
+class _OneTapFn(torch.autograd.Function):
+    """A k x k convolution whose input AND output are 1 x 1 maps: exactly one filter tap ever meets data, all the
+    others multiply padding (AlexNet's fc6 = 5x5 SAME and VGG's fc6 = 7x7 'same' on the 1x1 map that CIFAR images
+    leave, alexnet/alexnet.py:119, vgg/nets/vgg.py:202-203 — 24/25 and 48/49 of those tensors).  The full tensor stays
+    a variable (it is pushed, pulled, decayed and checkpointed like any other: SURVEY §7.4 item 10), but the compute
+    runs as the [C_out, C_in] GEMM of the live tap: forward, input gradient and weight gradient touch 1/(R*S) of the
+    weights instead of sweeping 400 MB three times per step; the dead taps' gradient is the zero the buffer holds."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, tap, relu):
+        co, r, s, ci = w.shape
+        nat.run_pre_launch()                      # the slice below reads w with a PyTorch kernel: pull gate first
+        wc = w.detach()[:, tap[0], tap[1], :].contiguous().view(co, 1, 1, ci)
+        x = cn.as_pixel_dense(x)
+        y = cn.conv_fprop(x, wc, (1, 1), (0, 0), bias=bias, relu=relu, out_hw=(1, 1))
+        ctx.save_for_backward(x, wc, y if relu else None)
+        ctx.cfg = (tap, relu, bias is not None)
+        ctx.params = (w, bias)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, wc, y = ctx.saved_tensors
+        tap, relu, has_bias = ctx.cfg
+        wparam, bparam = ctx.params
+        dy = dy.contiguous()
+        if relu:
+            dy = torch.ops.aten.threshold_backward(dy, y, 0.0)
+        dx = dw = db = None
+        wrote = []
+        if has_bias and ctx.needs_input_grad[2]:
+            co = dy.shape[-1]
+            slot = _grad_slot(bparam)
+            db = slot if slot is not None else _zeros(co, dy.device)
+            nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db), nat.stream_ptr()),
+                      "dtf_colsum")
+            if slot is not None:
+                db = None
+                wrote.append(bparam)
+        if ctx.needs_input_grad[0]:
+            dx = cn.conv_dgrad(dy, cn.weight_transpose(wc), (1, 1), (1, 1), (0, 0))
+        if ctx.needs_input_grad[1]:
+            dwc = cn.conv_wgrad(x, dy, wc.shape, (1, 1), (0, 0)).view(wc.shape[0], wc.shape[3])
+            slot = _grad_slot(wparam)
+            if slot is not None:
+                slot[:, tap[0], tap[1], :].add_(dwc)
+                wrote.append(wparam)
+            else:
+                dw = torch.zeros_like(wparam)
+                dw[:, tap[0], tap[1], :] = dwc
+        _grad_written(*wrote)
+        return dx, dw, db, None, None
+
+
 def conv2d(x, w, bias, stride, pad_before, out_hw, relu, stats=None):
     cin = x.shape[-1]
+    co, r, s, _ = w.shape
+    if (r * s > 1 and x.shape[1] == 1 and x.shape[2] == 1 and tuple(out_hw) == (1, 1) and stats is None
+            and cin % 4 == 0 and 0 <= pad_before[0] < r and 0 <= pad_before[1] < s and one_tap_enabled[0]):
+        return _OneTapFn.apply(x, w, bias, (int(pad_before[0]), int(pad_before[1])), bool(relu))
     if cin % 4 != 0:
         nat.run_pre_launch()      # the pad below reads w with a PyTorch kernel: a pull gate still owed goes first
         x, w = _pad4(x, w)        # differentiable pads: the weight gradient is sliced back by autograd

@@ -251,6 +251,7 @@ class Trainer:
             if native:
                 conv_native.set_wt_batch(None)
                 native_ops.set_grad_listener(None)
+                native_ops.nat.lib().dtf_reserve_sms(0)      # (a push transport may have kept SMs out of the backward grids)
         return loss.detach(), logits.detach()
 
     def _fwd_bwd_graphed(self, x, y):
@@ -307,8 +308,7 @@ class Trainer:
         if s.quantize:
             self.store.quant.set_step(gs_before)
         scale = 1.0 if batch_size is None else float(batch_size) / float(s.batch_size)
-        if s.mode == "bsp":
-            self.comm.prepare_step(lr, scale)      # transports that push from inside the backward pass
+        self.comm.prepare_step(lr, scale)          # transports that push from inside the backward pass
         use_graph = s.cuda_graph and self.device.type == "cuda" and x.shape[0] == s.batch_size
         loss, logits = (self._fwd_bwd_graphed if use_graph else self._fwd_bwd)(x, labels)
         if s.mode == "bsp":

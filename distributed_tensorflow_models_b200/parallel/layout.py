@@ -65,15 +65,20 @@ class Bucket:
 
 
 def plan_buckets(entries: Sequence["Entry"], total: int, world: int, target_floats: int,
-                 max_buckets: int = 64) -> List[Bucket]:
+                 max_buckets: int = 64, head_floats: int = 0) -> List[Bucket]:
     """Cut ``[0, total)`` at tensor starts into buckets of at least ``target_floats`` elements (a tensor is never
-    split: its gradient is produced by one kernel, so its halves would become ready together anyway)."""
+    split: its gradient is produced by one kernel, so its halves would become ready together anyway).
+
+    ``head_floats`` > 0: the bucket at offset 0 closes after that many elements already.  The buffer starts with the
+    first layers of the network, whose gradients are the last to be produced and whose new values are the first the
+    next forward pass needs — that bucket's push cannot hide behind anything, so it should be pure latency."""
     ents = sorted(entries, key=lambda e: e.offset)
     target = max(int(target_floats), (total + max_buckets - 1) // max_buckets, 4 * world)
+    head = max(int(head_floats), 4 * world) if head_floats else target
     cuts: List[Tuple[int, List[str]]] = []          # (start offset, names)
     cur_lo, cur_names = 0, []
     for e in ents:
-        if cur_names and e.offset - cur_lo >= target:
+        if cur_names and e.offset - cur_lo >= (head if not cuts else target):
             cuts.append((cur_lo, cur_names))
             cur_lo, cur_names = e.offset, []
         cur_names.append(e.name)

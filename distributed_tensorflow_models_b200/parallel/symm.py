@@ -97,7 +97,10 @@ class SymmComm(Comm):
         self.timeout_s = float(env.get("DTF_PS_TIMEOUT_S", "300")) if timeout_s is None else float(timeout_s)
         self.ssp_timeout_s = float(env.get("DTF_SSP_TIMEOUT_S", "30")) if ssp_timeout_s is None else float(ssp_timeout_s)
         self.gate_mode = env.get("DTF_PULL_GATE", "fused")          # fused | fetch (every gate as its own launch)
-        self.push_blocks = int(env.get("DTF_PUSH_BLOCKS", "0"))     # 0 = one block per SM
+        # SMs that belong to the push while it runs beside the backward pass (the compute kernels are launched
+        # with that many CTAs fewer); None = 16 for models of >= 16 MB, 0 (and a single bucket) for smaller ones,
+        # whose push is pure latency and simply follows the last weight-gradient kernel
+        self.push_sms = int(env["DTF_PUSH_SMS"]) if "DTF_PUSH_SMS" in env else None
         self.push_enabled = True           # the engine switches the pushes off for its warm-up passes
         self._in_step = False
         self._engine_driven = False        # True once an engine runs the step hooks (the pushes are then its)
@@ -114,17 +117,24 @@ class SymmComm(Comm):
         W = self.world
         total = layout.total
         self.layout, self.cfg = layout, opt_cfg
-        self.bucketed = self.mode == "bsp"
+        self.bucketed = self.mode == "bsp"          # ownership: 1/W of every bucket (BSP) or flat shards (ASP / SSP)
+        small = total * 4 < (16 << 20)
+        if self.push_sms is None:
+            # BSP: the NVSwitch reduction saturates from 16 SMs; the one-sided ASP push keeps its in-flight data in
+            # registers (64 KB per SM) and needs about twice as many to cover the NVLink latency
+            self.push_sms = 0 if (small or W == 1) else (16 if self.bucketed else 32)
+        # small models: one bucket, pushed behind the last weight-gradient kernel on the compute stream itself
+        self.inline = self.push_sms == 0
+        if self.bucket_mb is None:
+            target = total if small else min(max(total // 12, 1 << 18), 8 << 20)   # floats: ~12 buckets of <= 32 MB
+        else:
+            target = int(self.bucket_mb * (1 << 20) / 4)
+        head = 0 if (small and self.bucket_mb is None) else int(float(os.environ.get("DTF_BUCKET_HEAD_KB", "64")) * 256)
+        self.buckets: List[Bucket] = plan_buckets(layout.entries, total, W, target, head_floats=min(head, target))
         if self.bucketed:
-            if self.bucket_mb is None:
-                target = min(max(total // 12, 1 << 18), 8 << 20)         # floats: 1 MB .. 32 MB, ~12 buckets
-            else:
-                target = int(self.bucket_mb * (1 << 20) / 4)
-            self.buckets: List[Bucket] = plan_buckets(layout.entries, total, W, target)
             S = sum(b.chunk for b in self.buckets)
             self.shard = None
         else:
-            self.buckets = []
             assert (total // W) % 4 == 0
             self.shard = total // W
             S = self.shard
@@ -243,69 +253,85 @@ class SymmComm(Comm):
         self._gated = set()                                 # (bucket, stream) pairs that have waited this step
         self._deferred: Dict[int, tuple] = {}               # weight address -> (bucket, stream): gate owed
         self._zeroed = None
+        self._all_gated = True
         if not self._learned:
             self._need_learning: Dict[int, Dict[int, int]] = {}
             self._last_seen_bucket_order: List[int] = []
 
     def prepare_step(self, lr: float, grad_scale: float = 1.0) -> None:
         """Hyper-parameters of the coming step into device memory (the push kernels run inside the step)."""
-        if self.bucketed:
-            self._h = self._hyper(lr, grad_scale, self._gs)
+        self._h = self._hyper(lr, grad_scale, self._gs, ema_power=1 if self.bucketed else self.world)
 
     def begin_step(self) -> None:
-        """Start of forward: on a side stream wait until every owner has finished the previous step (then nobody
-        reads my old gradients any more) and zero the gradient buffer; the forward pass runs meanwhile."""
-        if not self.bucketed:
-            self.layout.zero_grads()
-            return
+        """Start of forward.  BSP: wait until every owner has finished the previous step (then nobody reads my old
+        gradients any more) and zero the gradient buffer — on a side stream while the forward pass runs, or in line
+        for small models.  ASP / SSP: nothing to wait for."""
         self._reset_step_state()
         self._in_step = True
         self._engine_driven = True
+        sync = self.bucketed and self.world > 1
+        if self.inline or not sync:
+            if sync:
+                self._gate_launch(0, len(self.buckets))
+            self.layout.zero_grads()
+            self._all_gated = True                 # the wait above covers every bucket on every stream that forks later
+            return
+        self._all_gated = False
         cur = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(cur)
         self.aux_stream.wait_event(ev)
         with torch.cuda.stream(self.aux_stream):
-            if self.world > 1:
-                self._gate_launch(0, len(self.buckets))
+            self._gate_launch(0, len(self.buckets))
             self.layout.zero_grads()
             self._zeroed = torch.cuda.Event()
             self._zeroed.record(self.aux_stream)
         nat.set_pre_launch(self._flush_deferred)
         from ..ops import conv_native
-        conv_native.set_gate_provider(self._gate_for_weight if self.world > 1 else None)
+        conv_native.set_gate_provider(self._gate_for_weight)
 
     def before_backward(self) -> None:
-        if self.bucketed and self._zeroed is not None:
+        if not self._in_step:
+            return
+        if self._zeroed is not None:
             self._flush_deferred()
             torch.cuda.current_stream().wait_event(self._zeroed)
+        if self.push_sms and self.push_enabled and self.overlap and self.world > 1:
+            nat.lib().dtf_reserve_sms(int(self.push_sms))      # the backward kernels leave these SMs to the push
 
     def end_step(self) -> None:
         """After backward: issue whatever has not been pushed yet and join the side streams."""
-        if not self.bucketed or not self._in_step:
+        if not self._in_step:
             return
         self._in_step = False
+        nat.lib().dtf_reserve_sms(0)
         nat.set_pre_launch(None)
         from ..ops import conv_native
         conv_native.set_gate_provider(None)
         if not self._learned:
             self._finish_learning()
-        if self.push_enabled:
-            cur = torch.cuda.current_stream()
-            if self._issued < len(self.buckets):
-                ev = torch.cuda.Event()
-                ev.record(cur)
-                self.comm_stream.wait_event(ev)
-                for b in self._order[self._next:]:
-                    self._launch_bucket(b)
-                self._next = len(self._order)
-            done = torch.cuda.Event()
-            done.record(self.comm_stream)
-            cur.wait_event(done)
+        if not self.push_enabled:
+            return
+        cur = torch.cuda.current_stream()
+        if self.inline:
+            for b in self._order[self._next:]:
+                self._launch_bucket(b, cur)
+            self._next = len(self._order)
+            return
+        if self._issued < len(self.buckets):
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self.comm_stream.wait_event(ev)
+            for b in self._order[self._next:]:
+                self._launch_bucket(b)
+            self._next = len(self._order)
+        done = torch.cuda.Event()
+        done.record(self.comm_stream)
+        cur.wait_event(done)
 
     # -- gradient notifications (called from the backward pass, possibly on branch streams) -----------
     def grad_ready(self, param: torch.Tensor) -> None:
-        if not self.bucketed or not self._in_step:
+        if not self._in_step:
             return
         g = param.grad
         if g is None:
@@ -336,7 +362,7 @@ class SymmComm(Comm):
             self._issue_ready()
 
     def _issue_ready(self) -> None:
-        if not (self.push_enabled and self.overlap):
+        if not (self.push_enabled and self.overlap) or self.inline:
             return
         while self._next < len(self._order) and self._complete[self._order[self._next]]:
             b = self._order[self._next]
@@ -370,28 +396,39 @@ class SymmComm(Comm):
         self._learned = True
         self._next = 0
 
-    def _launch_bucket(self, b: int) -> None:
+    def _launch_bucket(self, b: int, stream=None) -> None:
         bk = self.buckets[b]
         o = self.opt
         kind = 0 if self.cfg.kind == "sgd" else 1
         W = self.world
+        blocks = int(self.push_sms or 8)
 
         def slot(t):
             return C.c_void_p(t.data_ptr() + 4 * bk.slot_off) if t is not None else None
 
-        last = self._issued == len(self.buckets) - 1
-        with torch.cuda.stream(self.comm_stream):
-            nat.check(nat.lib().dtf_ps_bucket_step(
-                _p(self.t_grads), _p(self.t_params), _p(self.t_flags),
-                C.c_void_p(self.counters.data_ptr() + 4 * b), _p(self.status), self.rank, W,
-                self.o_ready + b * W, self.o_updated + b * W,
-                C.c_longlong(bk.lo), C.c_longlong(bk.length), C.c_longlong(bk.chunk),
-                C.c_longlong(self.layout.wd_boundary),
-                slot(o.slots.get("RMSProp")), slot(o.slots.get("RMSProp_1")), slot(o.ema), _p(self._h), kind,
-                _p(self.epoch), _p(self.epoch) if last else None,
-                C.c_void_p(self.mc_grads) if self.mc_grads else None,
-                C.c_void_p(self.mc_params) if self.mc_params else None,
-                C.c_double(self.timeout_s), self.push_blocks, nat.stream_ptr(hook=False)), "dtf_ps_bucket_step")
+        first, last = self._issued == 0, self._issued == len(self.buckets) - 1
+        with torch.cuda.stream(stream if stream is not None else self.comm_stream):
+            if self.bucketed:
+                nat.check(nat.lib().dtf_ps_bucket_step(
+                    _p(self.t_grads), _p(self.t_params), _p(self.t_flags),
+                    C.c_void_p(self.counters.data_ptr() + 4 * b), _p(self.status), self.rank, W,
+                    self.o_ready + b * W, self.o_updated + b * W,
+                    C.c_longlong(bk.lo), C.c_longlong(bk.length), C.c_longlong(bk.chunk),
+                    C.c_longlong(self.layout.wd_boundary),
+                    slot(o.slots.get("RMSProp")), slot(o.slots.get("RMSProp_1")), slot(o.ema), _p(self._h), kind,
+                    _p(self.epoch), _p(self.epoch) if last else None,
+                    C.c_void_p(self.mc_grads) if self.mc_grads else None,
+                    C.c_void_p(self.mc_params) if self.mc_params else None,
+                    C.c_double(self.timeout_s), blocks, nat.stream_ptr(hook=False)), "dtf_ps_bucket_step")
+            else:
+                has_ema = o.ema is not None
+                nat.check(nat.lib().dtf_ps_async_step(
+                    _p(self.layout.grads), _p(self.t_params), _p(self.t_ms) if kind == 1 else None,
+                    _p(self.t_mom) if kind == 1 else None, _p(self.t_ema) if has_ema else None,
+                    C.c_void_p(self.gs_ptr_rank0), self.rank, W, C.c_longlong(self.shard),
+                    C.c_longlong(self.layout.wd_boundary), _p(self._h), kind, C.c_longlong(bk.lo),
+                    C.c_longlong(bk.length), 1 if first else 0, blocks if not self.inline else 0,
+                    nat.stream_ptr(hook=False)), "dtf_ps_async_step")
         self._issued += 1
 
     # -- pull gates ------------------------------------------------------------------------------------
@@ -404,7 +441,7 @@ class SymmComm(Comm):
     def on_fetch(self, var) -> None:
         """A model function has just looked a variable up (``VariableStore.variable``): make sure the stream it is
         about to be used on waits for the owners' updates of its bucket."""
-        if not (self.bucketed and self._in_step and self.world > 1 and var.trainable):
+        if not (self._in_step and var.trainable) or self._all_gated:
             return
         b = self._bucket_of_name.get(var.name)
         if b is None:
@@ -480,16 +517,13 @@ class SymmComm(Comm):
         return self._gs
 
     def async_step(self, lr, grad_scale=1.0):
-        h = self._hyper(lr, grad_scale, self._gs, ema_power=self.world)
-        kind = 0 if self.cfg.kind == "sgd" else 1
-        has_ema = self.opt.ema is not None
-        nat.check(nat.lib().dtf_ps_async_step(_p(self.layout.grads), _p(self.t_params),
-                                              _p(self.t_ms) if kind == 1 else None,
-                                              _p(self.t_mom) if kind == 1 else None,
-                                              _p(self.t_ema) if has_ema else None,
-                                              C.c_void_p(self.gs_ptr_rank0), self.rank, self.world,
-                                              C.c_longlong(self.shard), C.c_longlong(self.layout.wd_boundary), _p(h),
-                                              kind, nat.stream_ptr()), "dtf_ps_async_step")
+        if not self._engine_driven:
+            # stand-alone use: the whole buffer in one launch on the caller's stream
+            self._h = self._hyper(lr, grad_scale, self._gs, ema_power=self.world)
+            self._issued = 0
+            for b in range(len(self.buckets)):
+                self._launch_bucket(b, torch.cuda.current_stream())
+            self._issued = 0
         self._step += 1
         # global_step lives on rank 0; refresh the host mirror lazily (one step stale is fine for the LR schedule)
         self._gs += self.world if self.rank != 0 else 0

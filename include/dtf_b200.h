@@ -28,6 +28,10 @@ const char* dtf_last_error(void);
 /* Debug aid: 0 launches the convolution kernels in plain stream order; 1 (default) with programmatic dependent
  * launch, so that a kernel's prologue overlaps the tail of its predecessor. */
 int dtf_debug_set_pdl(int enabled);
+/* Keep n SMs out of the grids of every kernel launched afterwards by this process (0 = none): the engine calls
+ * it around the backward pass when the parameter-server push runs beside it on SMs of its own.  Returns the previous
+ * value.  No counterpart in the reference. */
+int dtf_reserve_sms(int n);
 /* Host-only CRC-32C (Castagnoli) used by the checkpoint-bundle and TFRecord writers: crc of `n` bytes, continuing
  * from `crc` (0 for a fresh checksum).  No GPU involved; no counterpart in the reference (TensorFlow's C++ runtime
  * provides it there). */
@@ -305,7 +309,7 @@ int dtf_fused_update(float* w, const float* g, float* ms, float* mom, float* ema
  * mc_grads / mc_params: NVLS multicast addresses of the gradient / parameter regions of the same symmetric buffer
  * (both or neither; NULL = unicast peer loads and stores): the reduction then runs in the NVSwitch
  * (multimem.ld_reduce) and the updated range is written to all replicas with one multimem.st per 16 bytes.
- * timeout_s <= 0: 300 s.  max_blocks <= 0: one block per SM. */
+ * timeout_s <= 0: 300 s.  max_blocks <= 0: one 1024-thread block per SM. */
 int dtf_ps_bucket_step(const float* const* peer_grads, float* const* peer_params, unsigned int* const* peer_flags,
                        unsigned int* local_counter, unsigned int* status, int rank, int world, int ready_off,
                        int updated_off, long long lo, long long len, long long chunk, long long wd_boundary,
@@ -315,10 +319,14 @@ int dtf_ps_bucket_step(const float* const* peer_grads, float* const* peer_params
 /* Wait (one warp, bounded) until flags[0 .. n) >= *epoch_ptr; status = 1 on timeout. */
 int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int* epoch_ptr, unsigned int* status,
                 double timeout_s, void* stream);
-/* One ASP/SSP step: one-sided apply of the local gradient on every owner's range, then refresh the replica. */
+/* ASP/SSP push of the range [lo, lo+len) of the flat buffer (the whole buffer, or one bucket while the backward pass
+ * is still running): one-sided apply of the local gradient on the owners' master copies (flat shards: rank r owns
+ * [r*shard, (r+1)*shard)), then refresh of the replica from them; no flags, no barrier.  bump_step: global_step += 1
+ * (the step's first launch).  max_blocks <= 0: one block per SM. */
 int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms, float* const* peer_mom,
                       float* const* peer_ema, unsigned long long* global_step, int rank, int world, long long shard,
-                      long long wd_boundary, const float* hyper, int kind, void* stream);
+                      long long wd_boundary, const float* hyper, int kind, long long lo, long long len, int bump_step,
+                      int max_blocks, void* stream);
 /* SSP: publish clock[rank] = step to every peer, wait while step > min(clock) + bound (status 2 on timeout). */
 int dtf_ssp_clock(unsigned int* const* peer_clocks, int rank, int world, unsigned int step, unsigned int bound,
                   double timeout_s, unsigned int* status, unsigned int* waited_polls, void* stream);

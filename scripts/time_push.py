@@ -1,5 +1,6 @@
-"""Time the fused BSP push/update/pull kernel alone (torchrun, N GPUs): ms per call (max over ranks) and the
-fraction of the NVLink roofline it reaches.  Roofline bytes per GPU and direction: every rank ships (N-1)/N of its
+"""Time the BSP push alone (torchrun, N GPUs): every bucket's dtf_ps_bucket_step back to back on the push stream plus
+the gate on all `updated` flags — ms per whole-model push (max over ranks) and the fraction of the NVLink roofline it
+reaches.  Environment: DTF_BUCKET_MB, DTF_PUSH_SMS (SMs the push runs on), DTF_NVLS=0.  Roofline bytes per GPU and direction: every rank ships (N-1)/N of its
 gradient buffer to the owners (push) and, without NVLS, receives (N-1)/N of the parameters back (pull); with NVLS
 the pull is one multicast store of the rank's own 1/N.  NVLink 5: 900 GB/s per direction per GPU."""
 import json
@@ -38,11 +39,12 @@ for model in sys.argv[1:] or ["vgg", "alexnet", "inception", "resnet"]:
     out_bytes = P * (world - 1) / world + (P / world if nvls else 0)          # egress per GPU
     in_bytes = (P / world if nvls else P * (world - 1) / world) + (P * (world - 1) / world)   # ingress per GPU
     roof_ms = max(out_bytes, in_bytes) / 900e9 * 1e3
-    out[model] = {"param_MB": round(P / 1e6, 1), "ms": round(ms, 4), "nvls": nvls, "roofline_ms": round(roof_ms, 4),
+    out[model] = {"param_MB": round(P / 1e6, 1), "buckets": len(comm.buckets), "ms": round(ms, 4), "nvls": nvls,
+                  "roofline_ms": round(roof_ms, 4),
                   "fraction_of_nvlink_roofline": round(roof_ms / ms, 3)}
     comm.finish()
     del t, comm
     torch.cuda.empty_cache()
 if rank == 0:
-    print(json.dumps({"world": world, "push_update_pull_kernel": out}))
+    print(json.dumps({"world": world, "push_sms": os.environ.get("DTF_PUSH_SMS", "default"), "bsp_push": out}))
 dist.destroy_process_group()

@@ -347,3 +347,35 @@ def test_deferred_bn_finalize_in_window_kernel():
         outs.append((y, coef.scale.clone(), coef.shift.clone(), coef.mean.clone(), coef.invstd.clone(), mm, mv))
     for a, b in zip(outs[0], outs[1]):
         assert _rel(b, a) < 1e-5
+
+
+@pytest.mark.parametrize("k,pad", [(5, "SAME"), (7, "SAME"), (3, ((1, 1), (1, 1)))])
+def test_one_live_tap_convolution_on_1x1_maps(k, pad):
+    """AlexNet / VGG fc6: a k x k convolution on a 1 x 1 map runs as the GEMM of its single live tap
+    (native_ops._OneTapFn); values and all gradients equal the full convolution's, dead taps get exact zeros."""
+    from distributed_tensorflow_models_b200.ops import native_ops
+    n, ci, co = 24, 64, 96
+    x = _r(n, 1, 1, ci, seed=1)
+    wt = _r(co, k, k, ci, seed=2, scale=ci ** -0.5)
+    b = _r(co, seed=3)
+    _both(lambda x, wt, b: Fn.conv2d(x, wt, b, 1, pad, relu=True), [x, wt, b], TF32_TOL)
+    # into a pre-allocated .grad slot (the flat PS gradient buffer): accumulates, dead taps untouched
+    w = torch.nn.Parameter(wt.clone())
+    w.grad = torch.full_like(w, 0.5)
+    xi = x.clone().requires_grad_(True)
+    y = Fn.conv2d(xi, w, None, 1, pad)
+    dy = _r(*y.shape, seed=4)
+    y.backward(dy)
+    native_ops.one_tap_enabled[0] = False
+    try:
+        w2 = torch.nn.Parameter(wt.clone())
+        w2.grad = torch.full_like(w2, 0.5)
+        x2 = x.clone().requires_grad_(True)
+        Fn.conv2d(x2, w2, None, 1, pad).backward(dy)
+    finally:
+        native_ops.one_tap_enabled[0] = True
+    assert _rel(w.grad, w2.grad) < TF32_TOL and _rel(xi.grad, x2.grad) < TF32_TOL
+    c = k // 2
+    dead = w.grad.clone()
+    dead[:, c, c, :] = 0.5
+    assert torch.equal(dead, torch.full_like(dead, 0.5))
