@@ -32,6 +32,7 @@
 // SspHandler.check_staleness (inception/ssp_manager.py:21-29).
 #include "../include/dtf_b200.h"
 #include "host_common.h"
+#include "umma.cuh"
 
 namespace dtf {
 
@@ -385,6 +386,206 @@ ps_async_step_kernel(const AsyncArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// ASP / SSP push for SGD on the bulk-copy engine (TMA): no atomics, no registers in flight.
+//
+// What limits the register version above is not NVLink but the SM: a red.add retires about one fp32 element per
+// clock per SM (measured: 6.3 GB/s per SM for REDG.128 from threads and, identically, for cp.reduce.async.bulk.add
+// from the copy engine; VGG-16 on 2 GPUs 6.9 / 4.6 / 4.0 ms per step with 16 / 32 / 48 SMs).  The reference does not
+// use atomics either: apply_gradients with use_locking=False is a plain racy read-modify-write of the variable on the
+// parameter server (vgg/cifar10.py:368-372) — Hogwild.  So the pusher does exactly that, through shared memory:
+//   loaders  cp.async.bulk  owner's HBM -> smem : 16 KB of the owner's master copy (up to ~100 KB per SM in flight,
+//            one issuing thread);  cp.async.bulk local -> smem : the same chunk of my gradient
+//   math     w <- w - lr * (gscale * g + wd * w), in place in shared memory (4 groups of 2 warps, a chunk each)
+//   mover    cp.async.bulk  smem -> owner's HBM (the push) and smem -> my replica (the pull, same bytes)
+// Two workers that update the same chunk at the same moment can lose one of the two updates, as in the reference.
+// Peer memory is only ever the source of a plain (non-multicast) bulk load / the target of a bulk store.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int BULK_CHUNK = 4096;                 // floats per chunk (16 KB)
+constexpr int BULK_NG = 4;                       // gradient slots (local loads: short latency)
+constexpr int BULK_NP = 9;                       // parameter slots (remote loads: this is what covers the link latency)
+constexpr int BULK_K = 2;                        // rounds a store may stay pending before its slot is reused
+// The math stage has a fixed cost per chunk (two barrier waits, a proxy fence, two arrivals: ~1 us) that a single
+// group of warps pays serially — 8 KB chunks through one group ran at 7 GB/s per SM whatever the copy engine did.
+// Four groups of two warps work on four consecutive chunks at once.
+constexpr int BULK_GROUPS = 4;
+constexpr int BULK_GROUP_THREADS = 64;
+constexpr int BULK_MATH_THREADS = BULK_GROUPS * BULK_GROUP_THREADS;
+constexpr int BULK_THREADS = 64 + BULK_MATH_THREADS + 32;
+constexpr int BULK_SMEM = (BULK_NG + BULK_NP) * BULK_CHUNK * 4 + 1024;
+
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_dst), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_reduce_add_f32(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+               ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// The range [lo, lo+len) cut at owner boundaries and then into chunks; chunk c -> (first element, length, owner).
+struct BulkChunks {
+  long long lo, hi, shard;
+  int first_owner, n_owners;
+  long long total;
+  __device__ void init(long long lo_, long long len, long long shard_) {
+    lo = lo_; hi = lo_ + len; shard = shard_;
+    first_owner = (int)(lo / shard);
+    n_owners = len > 0 ? (int)((hi - 1) / shard) - first_owner + 1 : 0;
+    total = 0;
+    for (int k = 0; k < n_owners; ++k) total += count(k);
+  }
+  __device__ long long seg_lo(int k) const { const long long a = (long long)(first_owner + k) * shard; return a > lo ? a : lo; }
+  __device__ long long seg_hi(int k) const { const long long b = (long long)(first_owner + k + 1) * shard; return b < hi ? b : hi; }
+  __device__ long long count(int k) const { return (seg_hi(k) - seg_lo(k) + BULK_CHUNK - 1) / BULK_CHUNK; }
+  __device__ void get(long long c, long long* gi, int* n, int* owner) const {
+    int k = 0;
+    for (; k < n_owners - 1; ++k) {
+      const long long m = count(k);
+      if (c < m) break;
+      c -= m;
+    }
+    const long long a = seg_lo(k) + c * BULK_CHUNK, b = seg_hi(k);
+    *gi = a;
+    *n = (int)((b - a) < BULK_CHUNK ? (b - a) : BULK_CHUNK);
+    *owner = first_owner + k;
+  }
+};
+
+__global__ void __launch_bounds__(BULK_THREADS, 1)
+ps_async_bulk_kernel(const AsyncArgs a) {
+  extern __shared__ uint8_t bulk_smem_raw[];
+  const uint32_t raw = smem_u32(bulk_smem_raw);
+  uint8_t* smem = bulk_smem_raw + ((128u - (raw & 127u)) & 127u);
+  float* sG = reinterpret_cast<float*>(smem);
+  float* sP = sG + BULK_NG * BULK_CHUNK;
+  uint64_t* fullG = reinterpret_cast<uint64_t*>(sP + BULK_NP * BULK_CHUNK);
+  uint64_t* emptyG = fullG + BULK_NG;
+  uint64_t* fullP = emptyG + BULK_NG;
+  uint64_t* doneP = fullP + BULK_NP;       // math finished: the slot holds the new values
+  uint64_t* emptyP = doneP + BULK_NP;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int me = a.rank, W = a.W;
+  if (tid == 0) {
+    for (int i = 0; i < BULK_NG; ++i) { mbar_init(&fullG[i], 1); mbar_init(&emptyG[i], BULK_GROUP_THREADS); }
+    for (int i = 0; i < BULK_NP; ++i) { mbar_init(&fullP[i], 1); mbar_init(&doneP[i], BULK_GROUP_THREADS); mbar_init(&emptyP[i], 1); }
+    fence_mbar_init();
+    if (a.bump_step && blockIdx.x == 0) atomicAdd_system(a.global_step, 1ull);
+  }
+  __syncthreads();
+
+  BulkChunks ch;
+  ch.init(a.lo, a.len, a.shard);
+  // this CTA's chunks: c = blockIdx.x + i * gridDim.x, rotated by rank so that the workers start on different owners
+  const long long rot = (ch.total / W) * me;
+  const long long n_my = ch.total > blockIdx.x ? (ch.total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  float* mine = a.peer_params[me];
+  const Hyper h = load_hyper(a.hyper);
+#define BULK_CHUNK_OF(i, gi, n, own)                          \
+  long long gi; int n, own;                                   \
+  {                                                           \
+    long long c_ = blockIdx.x + (i) * gridDim.x + rot;        \
+    if (c_ >= ch.total) c_ -= ch.total;                       \
+    ch.get(c_, &gi, &n, &own);                                \
+  }
+
+  if (warp == 0) {
+    // ================= parameter loader: the owner's master copy, far ahead =================
+    if (lane == 0) {
+      for (long long i = 0; i < n_my; ++i) {
+        const int sp = (int)(i % BULK_NP);
+        mbar_wait(&emptyP[sp], (uint32_t)(((i / BULK_NP) & 1) ^ 1));
+        BULK_CHUNK_OF(i, gi, n, own);
+        mbar_arrive_expect_tx(&fullP[sp], (uint32_t)n * 4u);
+        bulk_load(smem_u32(sP + sp * BULK_CHUNK), a.peer_params[own] + gi, (uint32_t)n * 4u, &fullP[sp]);
+      }
+    }
+  } else if (warp == 1) {
+    // ================= gradient loader (local) =================
+    if (lane == 0) {
+      for (long long i = 0; i < n_my; ++i) {
+        const int sg = (int)(i % BULK_NG);
+        mbar_wait(&emptyG[sg], (uint32_t)(((i / BULK_NG) & 1) ^ 1));
+        BULK_CHUNK_OF(i, gi, n, own);
+        (void)own;
+        mbar_arrive_expect_tx(&fullG[sg], (uint32_t)n * 4u);
+        bulk_load(smem_u32(sG + sg * BULK_CHUNK), a.grads + gi, (uint32_t)n * 4u, &fullG[sg]);
+      }
+    }
+  } else if (warp < 2 + BULK_MATH_THREADS / 32) {
+    // ================= math: w <- w - lr * (gscale * g + wd * w), in place =================
+    const int grp = (tid - 64) / BULK_GROUP_THREADS, mt = (tid - 64) % BULK_GROUP_THREADS;
+    for (long long i = grp; i < n_my; i += BULK_GROUPS) {
+      const int sg = (int)(i % BULK_NG), sp = (int)(i % BULK_NP);
+      BULK_CHUNK_OF(i, gi, n, own);
+      (void)own;
+      mbar_wait(&fullG[sg], (uint32_t)((i / BULK_NG) & 1));
+      mbar_wait(&fullP[sp], (uint32_t)((i / BULK_NP) & 1));
+      const float4* g4 = reinterpret_cast<const float4*>(sG + sg * BULK_CHUNK);
+      float4* w4 = reinterpret_cast<float4*>(sP + sp * BULK_CHUNK);
+      for (int t = mt; t < (n >> 2); t += BULK_GROUP_THREADS) {
+        float4 g = g4[t];
+        float4 w = w4[t];
+        const long long e = gi + ((long long)t << 2);
+        g.x *= h.gscale; g.y *= h.gscale; g.z *= h.gscale; g.w *= h.gscale;
+        if (e + 0 < a.wd_boundary) g.x = fmaf(h.wd, w.x, g.x);
+        if (e + 1 < a.wd_boundary) g.y = fmaf(h.wd, w.y, g.y);
+        if (e + 2 < a.wd_boundary) g.z = fmaf(h.wd, w.z, g.z);
+        if (e + 3 < a.wd_boundary) g.w = fmaf(h.wd, w.w, g.w);
+        w.x = fmaf(-h.lr, g.x, w.x); w.y = fmaf(-h.lr, g.y, w.y);
+        w.z = fmaf(-h.lr, g.z, w.z); w.w = fmaf(-h.lr, g.w, w.w);
+        w4[t] = w;
+      }
+      fence_proxy_async_smem();            // my writes -> visible to the copy engine
+      mbar_arrive(&doneP[sp]);             // -> mover
+      mbar_arrive(&emptyG[sg]);            // -> gradient loader
+    }
+  } else if (lane == 0) {
+    // ================= mover: new values -> the owner's master copy and my replica =================
+    for (long long i = 0; i < n_my + BULK_K; ++i) {
+      if (i < n_my) {
+        const int sp = (int)(i % BULK_NP);
+        BULK_CHUNK_OF(i, gi, n, own);
+        mbar_wait(&doneP[sp], (uint32_t)((i / BULK_NP) & 1));
+        bulk_store(a.peer_params[own] + gi, smem_u32(sP + sp * BULK_CHUNK), (uint32_t)n * 4u);      // the push
+        if (own != me) bulk_store(mine + gi, smem_u32(sP + sp * BULK_CHUNK), (uint32_t)n * 4u);     // the pull
+      }
+      bulk_commit();
+      bulk_wait_read<BULK_K>();            // the stores of round i-K have read their slot: back to the loader
+      const long long jp = i - BULK_K;
+      if (jp >= 0 && jp < n_my) mbar_arrive(&emptyP[(int)(jp % BULK_NP)]);
+    }
+    bulk_wait_all();                       // the stores have landed before the CTA goes away
+  }
+#undef BULK_CHUNK_OF
+  __syncthreads();
+  // ---- EMA of my own shard inside this range, owner side (local traffic only; see the register kernel) --------
+  if (a.peer_ema && h.ema_decay >= 0.f) {
+    float* ema = a.peer_ema[me];
+    const float* wm = mine + (long long)me * a.shard;
+    const float k = 1.f - h.ema_decay;
+    long long e_lo = a.lo - (long long)me * a.shard, e_hi = a.lo + a.len - (long long)me * a.shard;
+    e_lo = e_lo < 0 ? 0 : e_lo;
+    e_hi = e_hi > a.shard ? a.shard : e_hi;
+    for (long long i4 = (e_lo >> 2) + (long long)blockIdx.x * blockDim.x + tid; i4 < (e_hi >> 2);
+         i4 += (long long)gridDim.x * blockDim.x) {
+      float4 e = *reinterpret_cast<float4*>(ema + (i4 << 2));
+      const float4 wv = ld_peer_f32x4(wm + (i4 << 2));
+      e.x -= k * (e.x - wv.x); e.y -= k * (e.y - wv.y); e.z -= k * (e.z - wv.z); e.w -= k * (e.w - wv.w);
+      *reinterpret_cast<float4*>(ema + (i4 << 2)) = e;
+    }
+  }
+}
+
 __global__ void ssp_clock_kernel(unsigned int* const* peer_clocks, int rank, int W, unsigned int step,
                                  unsigned int bound, long long timeout_cycles, unsigned int* status,
                                  unsigned int* waited_polls) {
@@ -502,6 +703,13 @@ extern "C" int dtf_ps_gate(const unsigned int* flags, int n, const unsigned int*
   return 0;
 }
 
+static int g_async_bulk = 1;
+extern "C" int dtf_debug_set_async_bulk(int enabled) {
+  const int prev = g_async_bulk;
+  g_async_bulk = enabled;
+  return prev;
+}
+
 extern "C" int dtf_ps_async_step(const float* grads, float* const* peer_params, float* const* peer_ms,
                                  float* const* peer_mom, float* const* peer_ema, unsigned long long* global_step,
                                  int rank, int world, long long shard, long long wd_boundary, const float* hyper,
@@ -522,6 +730,21 @@ extern "C" int dtf_ps_async_step(const float* grads, float* const* peer_params, 
   const long long cap = max_blocks > 0 ? max_blocks : hw_num_sms();
   const int grid = (int)(b < cap ? (b > 0 ? b : 1) : cap);
   static bool carveout_set[2][64];
+  if (kind == 0 && g_async_bulk) {
+    static bool attr_set[64];
+    int dev = 0;
+    DTF_CHECK(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      DTF_CHECK(cudaFuncSetAttribute(ps_async_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BULK_SMEM));
+      attr_set[dev] = true;
+    }
+    const long long chunks = (len + BULK_CHUNK - 1) / BULK_CHUNK + world;
+    const long long bcap = max_blocks > 0 ? max_blocks : 16;
+    const int bgrid = (int)(chunks < bcap ? (chunks > 0 ? chunks : 1) : bcap);
+    ps_async_bulk_kernel<<<bgrid, BULK_THREADS, BULK_SMEM, stream>>>(a);
+    DTF_CHECK(cudaGetLastError());
+    return 0;
+  }
   if (kind == 0) {
     prefer_max_shared_once(ps_async_step_kernel<0, 1024>, carveout_set[0]);
     ps_async_step_kernel<0, 1024><<<grid, 1024, 0, stream>>>(a);

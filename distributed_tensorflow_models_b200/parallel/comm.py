@@ -16,7 +16,8 @@ Back-ends
 ``ThreadCluster``  fake cluster: N ranks are threads of this process sharing CPU tensors — peers' buffers are
                    directly addressable, which makes it the CPU twin of the GPU symmetric-memory path (same
                    one-sided protocol, testable without hardware; SURVEY §4 "what we must add").
-``TorchDistComm``  torch.distributed collectives (gloo on CPU, NCCL on GPU): BSP only.  This is the *baseline*
+``TorchDistComm``  torch.distributed collectives (gloo on CPU, NCCL on GPU): BSP, and a lock-step emulation of
+                   ASP / SSP.  This is the *baseline*
                    arm (BASELINE.md B1 all-reduce, B2 reduce-scatter + all-gather), never the product path.
 ``SymmComm``       (parallel/symm.py) peer-mapped HBM + our sm_100a push/pull kernels over NVLink.
 """
@@ -317,7 +318,7 @@ class ThreadComm(Comm):
 
 # =================================================================================================
 class TorchDistComm(Comm):
-    """BSP over torch.distributed collectives — the NCCL / gloo baseline arm.
+    """BSP (and emulated ASP / SSP) over torch.distributed collectives — the NCCL / gloo baseline arm.
 
     ``algo='rs_ag'``: reduce-scatter -> unfused shard update -> all-gather ("NCCL-PS", BASELINE.md B2);
     ``algo='allreduce'``: all-reduce -> every rank updates the whole buffer (DDP-style, B1).
@@ -363,8 +364,37 @@ class TorchDistComm(Comm):
         self._gs += 1
         return self._gs
 
+    supports_async = True
+
+    def async_step(self, lr, grad_scale=1.0):
+        """ASP / SSP on collectives — the baseline arm of the one-sided push.  A collective
+        cannot be one-sided, so this is the lock-step emulation of what the reference's parameter servers end up
+        doing in one round of W worker steps (vgg/cifar10.py:366-372, inception/imagenet_inception_asp.py:131-143):
+        every worker ships slice r of its *own* gradient to owner r (all-to-all), the owner applies the W gradients
+        one after the other (W optimiser steps, learning rate not scaled by W, global_step += W), and the fresh
+        parameters are all-gathered."""
+        dist, L = self.dist, self.layout
+        W = self.world
+        if self.shard is None:
+            # all-reduce arm / gloo: every rank holds every gradient after an all-gather and applies them in rank order
+            allg = torch.empty(W * L.total, dtype=torch.float32, device=L.grads.device)
+            dist.all_gather_into_tensor(allg, L.grads, group=self.group)
+            for q in range(W):
+                self.opts[0].apply(allg[q * L.total:(q + 1) * L.total], lr, grad_scale, num_updates=self._gs + q)
+        else:
+            s = self.shard.numel()
+            if getattr(self, "_inbox", None) is None:
+                self._inbox = torch.empty(W * s, dtype=torch.float32, device=L.grads.device)
+            dist.all_to_all_single(self._inbox, L.grads[: W * s], group=self.group)
+            o = self.opts[0]
+            for q in range(W):
+                o.apply(self._inbox[q * s:(q + 1) * s], lr, grad_scale, num_updates=self._gs + q)
+            dist.all_gather_into_tensor(L.params, L.params[o.lo:o.hi].clone(), group=self.group)
+        self._gs += W
+        return self._gs
+
     def ssp_wait(self, step, bound, timeout=600.0):
-        return 0.0
+        return 0.0            # the emulation above is lock-step: nobody is ever ahead
 
     def barrier(self):
         self.dist.barrier(group=self.group)

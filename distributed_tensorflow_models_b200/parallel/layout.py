@@ -77,11 +77,16 @@ def plan_buckets(entries: Sequence["Entry"], total: int, world: int, target_floa
     head = max(int(head_floats), 4 * world) if head_floats else target
     cuts: List[Tuple[int, List[str]]] = []          # (start offset, names)
     cur_lo, cur_names = 0, []
+    prev_big = False
     for e in ents:
-        if cur_names and e.offset - cur_lo >= (head if not cuts else target):
+        # a tensor that fills a bucket by itself (VGG's 411 MB fc6) starts one and ends it: its push then begins the
+        # moment its own gradient is complete instead of waiting for the smaller neighbours laid out before it
+        big = e.numel >= target
+        if cur_names and (e.offset - cur_lo >= (head if not cuts else target) or big or prev_big):
             cuts.append((cur_lo, cur_names))
             cur_lo, cur_names = e.offset, []
         cur_names.append(e.name)
+        prev_big = big
     cuts.append((cur_lo, cur_names))
     if len(cuts) > 1 and total - cuts[-1][0] < target // 4:       # a small tail joins its predecessor
         lo, names = cuts.pop()

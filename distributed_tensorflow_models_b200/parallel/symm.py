@@ -101,6 +101,8 @@ class SymmComm(Comm):
         # with that many CTAs fewer); None = 16 for models of >= 16 MB, 0 (and a single bucket) for smaller ones,
         # whose push is pure latency and simply follows the last weight-gradient kernel
         self.push_sms = int(env["DTF_PUSH_SMS"]) if "DTF_PUSH_SMS" in env else None
+        if env.get("DTF_ASYNC_BULK", "1") == "0":
+            nat.lib().dtf_debug_set_async_bulk(0)              # A/B: SGD ASP push on the register kernel
         self.push_enabled = True           # the engine switches the pushes off for its warm-up passes
         self._in_step = False
         self._engine_driven = False        # True once an engine runs the step hooks (the pushes are then its)
@@ -120,9 +122,8 @@ class SymmComm(Comm):
         self.bucketed = self.mode == "bsp"          # ownership: 1/W of every bucket (BSP) or flat shards (ASP / SSP)
         small = total * 4 < (16 << 20)
         if self.push_sms is None:
-            # BSP: the NVSwitch reduction saturates from 16 SMs; the one-sided ASP push keeps its in-flight data in
-            # registers (64 KB per SM) and needs about twice as many to cover the NVLink latency
-            self.push_sms = 0 if (small or W == 1) else (16 if self.bucketed else 32)
+            # the NVSwitch reduction (BSP) and the bulk-copy-engine push (ASP / SSP) both saturate from ~16 SMs
+            self.push_sms = 0 if (small or W == 1) else 16
         # small models: one bucket, pushed behind the last weight-gradient kernel on the compute stream itself
         self.inline = self.push_sms == 0
         if self.bucket_mb is None:
@@ -383,10 +384,11 @@ class SymmComm(Comm):
             if remaining[b] == 0:
                 order.append(b)
         order += [b for b in range(nb - 1, -1, -1) if b not in order]        # buckets nobody reported for: last
-        t = torch.tensor(order, dtype=torch.int64, device=self.layout.params.device)
+        agreed = order
         if self.world > 1:
+            t = torch.tensor(order, dtype=torch.int64, device=self.layout.params.device)
             self.dist.broadcast(t, src=0, group=self.group)
-        agreed = [int(v) for v in t.tolist()]
+            agreed = [int(v) for v in t.tolist()]
         if agreed != order:
             # this rank's backward pass completes the buckets in another order: it still issues in the agreed one
             order = agreed

@@ -327,6 +327,9 @@ int dtf_ps_async_step(const float* grads, float* const* peer_params, float* cons
                       float* const* peer_ema, unsigned long long* global_step, int rank, int world, long long shard,
                       long long wd_boundary, const float* hyper, int kind, long long lo, long long len, int bump_step,
                       int max_blocks, void* stream);
+/* Debug aid: 0 keeps the SGD ASP / SSP push on the register kernel; 1 (default) uses the bulk-copy-engine kernel
+ * (cp.reduce.async.bulk add into the owner's HBM, bulk loads back). */
+int dtf_debug_set_async_bulk(int enabled);
 /* SSP: publish clock[rank] = step to every peer, wait while step > min(clock) + bound (status 2 on timeout). */
 int dtf_ssp_clock(unsigned int* const* peer_clocks, int rank, int world, unsigned int step, unsigned int bound,
                   double timeout_s, unsigned int* status, unsigned int* waited_polls, void* stream);

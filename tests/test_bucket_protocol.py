@@ -1,0 +1,141 @@
+"""Host-side logic of the bucketed push (parallel/symm.py, parallel/layout.py) and the protocol checker of the fake
+backend (parallel/protocol_model.py) — everything here runs without a GPU."""
+import pytest
+import torch
+
+from distributed_tensorflow_models_b200.parallel.layout import Bucket, Entry, plan_buckets
+from distributed_tensorflow_models_b200.parallel.protocol_model import BucketProtocolModel
+from distributed_tensorflow_models_b200.parallel.symm import SymmComm
+
+
+def _entries(sizes):
+    ents, off = [], 0
+    for i, n in enumerate(sizes):
+        ents.append(Entry(f"v{i}", (n,), n, off, 0.0, i))
+        off += (n + 31) // 32 * 32
+    return ents, off
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_plan_buckets_covers_the_buffer_and_splits_evenly(world):
+    sizes = [432, 16, 16, 2304, 2304, 36864, 73728, 147456, 100000, 64, 10]
+    ents, used = _entries(sizes)
+    total = (used + world * 32 - 1) // (world * 32) * (world * 32)
+    bks = plan_buckets(ents, total, world, target_floats=60000, head_floats=2048)
+    assert bks[0].lo == 0 and bks[-1].hi == total
+    assert all(a.hi == b.lo for a, b in zip(bks, bks[1:]))                   # contiguous, no gaps
+    assert sorted(n for b in bks for n in b.names) == sorted(e.name for e in ents)    # every tensor in one bucket
+    starts = {e.offset for e in ents}
+    assert all(b.lo in starts for b in bks)                                    # cuts at tensor starts only
+    assert bks[0].length < 60000                                               # the head bucket is small
+    slot = 0
+    for b in bks:
+        assert b.chunk % 4 == 0 and b.chunk * world >= b.length and b.slot_off == slot
+        parts = [b.part(r) for r in range(world)]
+        assert parts[0][0] == b.lo and parts[-1][1] == b.hi
+        assert all(p[1] == q[0] for p, q in zip(parts, parts[1:]))            # the owners' parts tile the bucket
+        slot += b.chunk
+
+
+def _fake_comm(world, rank, buckets, total):
+    c = object.__new__(SymmComm)
+    c.world, c.rank, c.buckets, c.bucketed = world, rank, buckets, True
+    c.n_slot = sum(b.chunk for b in buckets)
+
+    class L:
+        pass
+    c.layout = L()
+    c.layout.total = total
+    return c
+
+
+def test_bucket_ownership_round_trip():
+    """gather_slot_flats / load_slot_flats: [W, S] slot arrays <-> full-length flat tensor in parameter order."""
+    world = 3
+    ents, used = _entries([1000, 5000, 64, 7000, 300])
+    total = (used + 95) // 96 * 96
+    bks = plan_buckets(ents, total, world, target_floats=4000)
+    flat = torch.arange(total, dtype=torch.float32)
+    rows = []
+    for r in range(world):
+        c = _fake_comm(world, r, bks, total)
+        dst = torch.full((c.n_slot,), -1.0)
+        c._owned_copy(flat, dst)
+        rows.append(dst)
+    back = _fake_comm(world, 0, bks, total)._unshard(torch.stack(rows))
+    assert torch.equal(back, flat)
+
+
+def test_buckets_are_issued_in_the_agreed_order_whatever_order_they_complete_in():
+    world = 2
+    ents, used = _entries([64] * 6)
+    total = 384
+    bks = plan_buckets(ents, total, world, target_floats=128)
+    assert len(bks) == 3
+    c = _fake_comm(world, 0, bks, total)
+    grads = torch.zeros(total)
+    c.layout.grads = grads
+    params = []
+    for e in ents:
+        p = torch.nn.Parameter(torch.zeros(e.numel))
+        p.grad = grads[e.offset:e.offset + e.numel]
+        params.append(p)
+    c._bucket_lo = [b.lo for b in bks]
+    c._learned, c._in_step, c.push_enabled, c.overlap, c.inline = False, True, True, True, False
+    c._need, c._need_total, c._order = [], [], None
+    c._reset_step_state()
+    launched = []
+    c._launch_bucket = lambda b, stream=None: launched.append(b)
+
+    class _Ev:
+        def record(self, s):
+            pass
+
+    class _Stream:
+        cuda_stream = 7
+
+        def wait_event(self, ev):
+            pass
+    import distributed_tensorflow_models_b200.parallel.symm as symm
+    real_event, real_cur = symm.torch.cuda.Event, symm.torch.cuda.current_stream
+    symm.torch.cuda.Event, symm.torch.cuda.current_stream = _Ev, lambda: _Stream()
+    c.comm_stream = _Stream()
+    try:
+        # learning pass: parameters report in backward order (last tensor first); bucket 2 completes first
+        for p in reversed(params):
+            c.grad_ready(p)
+        c.dist = None
+        c.world = 1                                   # (no broadcast of the order in this single-process test)
+        c._finish_learning()
+        assert c._order == [2, 1, 0]
+        # a later step in which bucket 0 happens to complete before bucket 1: nothing overtakes the agreed order
+        c._reset_step_state()
+        for i in (5, 4, 0, 1):
+            c.grad_ready(params[i])
+        assert launched == [2]
+        for i in (3, 2):
+            c.grad_ready(params[i])
+        assert launched == [2, 1, 0]
+    finally:
+        symm.torch.cuda.Event, symm.torch.cuda.current_stream = real_event, real_cur
+
+
+@pytest.mark.parametrize("world,buckets", [(2, 1), (3, 4), (8, 3)])
+def test_flag_protocol_is_clean_under_random_interleavings(world, buckets):
+    for seed in range(3):
+        errs = BucketProtocolModel(world, buckets, steps=6, seed=seed).run()
+        assert errs == [], errs
+
+
+@pytest.mark.parametrize("rule,needle", [
+    ("zero_without_gate", "zeros"),               # gradients zeroed while an owner of the previous step still reads them
+    ("forward_without_gate", "forward of step"),  # stale parameters consumed
+    ("reduce_without_ready", "reduces bucket"),   # an owner reads a gradient that is not complete yet
+])
+def test_the_checker_catches_each_race_when_its_rule_is_dropped(rule, needle):
+    found = []
+    for seed in range(8):
+        found += BucketProtocolModel(4, 3, steps=8, seed=seed, jitter=5e-4, break_rule=rule).run(timeout=20)
+        if found:
+            break
+    assert found and any(needle in m for m in found), found

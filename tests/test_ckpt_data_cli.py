@@ -528,3 +528,65 @@ def test_build_imagenet_data_without_a_synsets_file(tmp_path, capsys):
     assert sorted(got["validation"]) == [(1, b"n01000000"), (2, b"n02000000")]
     with pytest.raises(SystemExit):
         bimd.main(["--train_directory", str(out), "--labels_file", str(tmp_path / "missing.txt")])
+
+
+def test_resume_restores_optimizer_slots_and_ema_shadows(tmp_path):
+    """Save -> new process -> resume: RMSProp's ms / mom and the EMA shadows come back with the variables (the
+    reference's Supervisor / Saver restore all of them, inception/imagenet_inception_bsp.py:156-167); a resumed run
+    continues exactly like the uninterrupted one."""
+    import dataclasses
+
+    from distributed_tensorflow_models_b200 import config as cfg
+    from distributed_tensorflow_models_b200.ckpt import store as ckpt
+    from distributed_tensorflow_models_b200.parallel.comm import ThreadCluster
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    preset = dataclasses.replace(cfg.PRESETS["cnn"], optimizer="rmsprop", initial_lr=0.01, ema_decay=0.9999)
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.randn(4, 24, 24, 3, generator=g), torch.randint(0, 10, (4,), generator=g)
+
+    def mk(seed):
+        return TrainSetup(model="cnn", batch_size=4, num_workers=2, preset=preset, seed=seed)
+
+    saved = {}
+
+    def first(comm):
+        t = Trainer(mk(0), comm)
+        for _ in range(3):
+            t.train_step(x, y)
+        slots = comm.gather_slot_flats()
+        if comm.rank == 0:
+            tensors = ckpt.collect_tensors(t.store, slots, t.layout, comm.global_step(), "Variable")
+            saved["path"] = ckpt.save(str(tmp_path), tensors, comm.global_step())
+        comm.barrier()
+        out = t.train_step(x, y)                       # the uninterrupted run's 4th step
+        return float(out["loss"]), t.layout.params.clone(), {k: v.clone() for k, v in comm.gather_slot_flats().items()}
+
+    ref = ThreadCluster(2).run(first)
+    names = set(ckpt.load(saved["path"]))
+    assert {"conv1/weights/RMSProp", "conv1/weights/RMSProp_1", "conv1/weights/ExponentialMovingAverage"} <= names
+
+    def resumed(comm):
+        t = Trainer(mk(5), comm)                       # different initial values: everything must come from the file
+        done = ckpt.restore_training_state(t, ckpt.load(saved["path"]))
+        comm.set_global_step(ckpt.step_of(saved["path"]))
+        assert {"RMSProp", "RMSProp_1", "ExponentialMovingAverage"} <= set(done)
+        out = t.train_step(x, y)
+        return float(out["loss"]), t.layout.params.clone(), {k: v.clone() for k, v in comm.gather_slot_flats().items()}
+
+    got = ThreadCluster(2).run(resumed)
+    probe = Trainer(dataclasses.replace(mk(0), num_workers=1))
+    live = torch.zeros(ref[0][1].numel(), dtype=torch.bool)
+    for e in probe.layout.entries:
+        live[e.offset:e.offset + e.numel] = True
+    for (l0, p0, s0), (l1, p1, s1) in zip(ref, got):
+        assert l0 == pytest.approx(l1, rel=1e-6)
+        assert torch.allclose(p0, p1, rtol=1e-6, atol=1e-8)
+        for k in s0:                                   # (the alignment padding between tensors is not state)
+            assert torch.allclose(s0[k][live], s1[k][live], rtol=1e-6, atol=1e-8), k
+
+    # a checkpoint without shadows (e.g. written by a run without EMA): the EMA restarts from the restored weights
+    tensors = {k: v for k, v in ckpt.load(saved["path"]).items() if not k.endswith("/ExponentialMovingAverage")}
+    t = Trainer(dataclasses.replace(mk(7), num_workers=1))
+    ckpt.restore_training_state(t, tensors)
+    o = t.comm.owned_optimizers()[0]
+    assert torch.equal(o.ema, o.w)
