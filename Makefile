@@ -1,7 +1,7 @@
 # Convenience targets; everything here is a one-liner you can also type yourself (README.md "Use").
 PY ?= python
 
-.PHONY: build test gpu-test bench bench8 bench-input sass clean
+.PHONY: build test gpu-test bench bench8 bench-input sass sass-check clean
 
 build:            ## nvcc -gencode arch=compute_100a,code=sm_100a for every csrc/*.cu, in-tree .so
 	$(PY) -c "import __graft_entry__ as g; g.build()"
@@ -22,8 +22,11 @@ bench8: build     ## weak scaling on 8 GPUs
 bench-input: build  ## host input pipelines (no GPU): CIFAR-10 and ImageNet, native passes vs torch / NumPy
 	$(PY) scripts/bench_input_pipeline.py
 
-sass: build       ## SASS of the built library (compare with profiles/sass/)
-	cuobjdump -sass distributed_tensorflow_models_b200/_native/libdtfb200.so | less
+sass: build       ## regenerate profiles/sass/*.sass + MNEMONICS.txt from the current sources
+	python scripts/regen_sass.py
+
+sass-check:       ## fail when a committed SASS listing is older than its source
+	python scripts/regen_sass.py --check
 
 clean:
 	rm -rf distributed_tensorflow_models_b200/_native/build distributed_tensorflow_models_b200/_native/libdtfb200.so

@@ -51,9 +51,46 @@ def dataset_available(data_dir: str) -> bool:
         return False
 
 
-def maybe_download_and_extract(data_dir: str) -> bool:
-    """The reference downloads cifar-10-binary.tar.gz here (cnn/cifar10.py:394-411).  This box has no
-    network: report whether the dataset is present so the caller can fall back to synthetic data."""
+DATA_URL = "http://www.cs.toronto.edu/~kriz/cifar-10-binary.tar.gz"      # the reference's source (cnn/cifar10.py:101)
+
+
+def maybe_download_and_extract(data_dir: str, url: str = DATA_URL, timeout: float = 20.0) -> bool:
+    """Make ``<data_dir>/cifar-10-batches-bin`` exist the way the reference does (cnn/cifar10.py:394-411): if the
+    binary files are missing, unpack ``<data_dir>/cifar-10-binary.tar.gz``, downloading it first when it is not there
+    either.  Returns whether the dataset is present afterwards — on a machine without network access (this build
+    box) the download fails quietly and the caller falls back to synthetic data.  ``DTF_NO_DOWNLOAD=1`` skips the
+    attempt."""
+    if dataset_available(data_dir):
+        return True
+    import tarfile
+    import urllib.request
+    tarball = os.path.join(data_dir, url.split("/")[-1])
+    if not os.path.exists(tarball):
+        if os.environ.get("DTF_NO_DOWNLOAD") == "1":
+            return False
+        tmp = tarball + ".part"
+        try:
+            os.makedirs(data_dir, exist_ok=True)
+            with urllib.request.urlopen(url, timeout=timeout) as r, open(tmp, "wb") as f:
+                while True:
+                    block = r.read(1 << 20)
+                    if not block:
+                        break
+                    f.write(block)
+            os.replace(tmp, tarball)
+        except Exception:                    # no network, refused, disk full ...: not fatal, synthetic data it is
+            try:
+                os.remove(tmp)
+            except OSError:
+                pass
+            return False
+    try:
+        with tarfile.open(tarball, "r:gz") as tf:
+            members = [m for m in tf.getmembers()
+                       if m.isfile() and not os.path.isabs(m.name) and ".." not in m.name.split("/")]
+            tf.extractall(data_dir, members=members, filter="data")
+    except (tarfile.TarError, OSError):
+        return False
     return dataset_available(data_dir)
 
 

@@ -238,15 +238,26 @@ class Trainer:
             conv_native.set_wt_batch(self._wt_batch)      # dgrad operands of all layers: one launch per step
             if hasattr(self.comm, "grad_ready"):
                 native_ops.set_grad_listener(self.comm.grad_ready)
+        # --trace: device-timed phase rows (only outside graph capture: a captured step is one replay)
+        tr = getattr(self, "trace", None)
+        if tr is not None and torch.cuda.is_current_stream_capturing():
+            tr = None
         try:
+            m0 = tr.mark() if tr else None
             self.comm.begin_step()                 # zero the gradients (bucketed push: behind the previous step's flags)
             loss, logits = self._run_forward(x, y, True)
             total = loss
             if not self.setup.fused_l2:
                 total = loss + self.l2_term()
+            m1 = tr.mark() if tr else None
             self.comm.before_backward()
             total.backward()
+            m2 = tr.mark() if tr else None
             self.comm.end_step()                   # bucketed push: join the push stream
+            if tr:
+                tr.add_device("forward", m0, m1, step=self.local_step)
+                tr.add_device("backward (+ overlapped push)", m1, m2, step=self.local_step)
+                tr.add_device("push tail / join", m2, tr.mark(), step=self.local_step)
         finally:
             if native:
                 conv_native.set_wt_batch(None)

@@ -240,14 +240,17 @@ def run_worker(args) -> int:
     events = EventFileWriter(args.train_dir) if (is_chief and p.save_secs is not None and args.save_summaries_secs) \
         else None
     last_summary, last_summary_step = time.time(), 0
-    trace = ChromeTrace(args.trace, pid=rank)
+    trace = ChromeTrace(args.trace, pid=rank, device=device)
+    trainer.trace = trace if trace.on_device else None     # eager steps also get forward / backward / push rows
     last_save = time.time()
     t_run0 = time.time()
     for step in range(0, args.max_steps):          # init_global_step := 0
         t0 = time.time()
         images, labels = next(batches)
         t1 = time.time()
+        ev0 = trace.mark()
         out = trainer.train_step(images, labels, batch_size=args.batch_size)      # already on the device (prefetcher)
+        trace.add_device("train_step", ev0, trace.mark(), t_run0, step=step)
         want_log = (step % max(1, args.log_every) == 0) or step == args.max_steps - 1
         if want_log or p.nan_guard:
             # the loss is read back one step late (after the next step has been queued) so that the device never

@@ -139,3 +139,15 @@ def test_the_checker_catches_each_race_when_its_rule_is_dropped(rule, needle):
         if found:
             break
     assert found and any(needle in m for m in found), found
+
+
+def test_committed_sass_listings_match_the_sources():
+    """profiles/sass/*.sass are evidence: each carries the hash of the source it was generated from, and this test
+    fails when a kernel was edited without `python scripts/regen_sass.py` (round 1 shipped a listing of the push
+    kernel that predated its NVLS rewrite)."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "scripts" / "regen_sass.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr

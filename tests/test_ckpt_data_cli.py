@@ -590,3 +590,23 @@ def test_resume_restores_optimizer_slots_and_ema_shadows(tmp_path):
     ckpt.restore_training_state(t, tensors)
     o = t.comm.owned_optimizers()[0]
     assert torch.equal(o.ema, o.w)
+
+
+def test_cifar10_download_helper_fetches_and_unpacks(tmp_path, monkeypatch):
+    """maybe_download_and_extract (cnn/cifar10.py:394-411): missing files -> fetch the tarball -> unpack it; an
+    unreachable source is not an error (the trainers then use synthetic data)."""
+    import tarfile
+
+    from distributed_tensorflow_models_b200.data import cifar10, synthetic
+    src = tmp_path / "src"
+    synthetic.write_cifar10_binary(str(src), train_per_file=6, test=4)
+    tarball = tmp_path / "cifar-10-binary.tar.gz"
+    with tarfile.open(tarball, "w:gz") as tf:
+        tf.add(str(src / "cifar-10-batches-bin"), arcname="cifar-10-batches-bin")
+    monkeypatch.delenv("DTF_NO_DOWNLOAD", raising=False)
+    dst = tmp_path / "data"
+    assert cifar10.maybe_download_and_extract(str(dst), url="file://" + str(tarball))
+    assert len(cifar10.data_files(str(dst), False)) == 5 and os.path.exists(dst / "cifar-10-binary.tar.gz")
+    assert cifar10.maybe_download_and_extract(str(dst), url="file:///nonexistent")        # present: nothing to do
+    assert not cifar10.maybe_download_and_extract(str(tmp_path / "other"), url="file:///nonexistent/x.tar.gz")
+    assert not os.path.exists(tmp_path / "other" / "x.tar.gz.part")
