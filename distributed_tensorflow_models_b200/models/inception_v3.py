@@ -5,8 +5,10 @@ wrapper (`inference` / `loss`) follows ``inception/inception_model.py:49-136``. 
 here as data — a table of blocks, each a set of named branches made of layer specs — and a small
 interpreter walks it.  That keeps the census the reference's tests pin down (388 variables: 98 weights, 2
 biases, 96 beta, 96+96 moving statistics) in one auditable place and lets the native backend
-recognise whole blocks (branch outputs are written straight into channel slices of the block's output
-buffer, so no concat kernel runs).
+recognise whole blocks: ``_run_block`` allocates the block's output once and every branch's last kernel (the
+batch-norm apply behind its final convolution, or its pooling kernel) writes its channel slice of it with the
+block's pixel pitch, so no concat kernel runs; the backward pass reads the slices of the incoming
+gradient through the same pitch.
 
 Layer spec grammar (tuples):
     ("conv", C_out, (kh, kw))                      stride 1, block-default padding
@@ -83,24 +85,90 @@ BLOCKS: List[Tuple[str, list]] = [
 AUX_AFTER = "mixed_17x17x768e"
 
 
-def _run_specs(x: torch.Tensor, specs: Sequence[tuple]) -> torch.Tensor:
+def _spec_channels(specs: Sequence[tuple], cin: int) -> int:
+    """Output channels of a spec chain."""
+    c = cin
     for sp in specs:
+        if sp[0] == "conv":
+            c = sp[1]
+        elif sp[0] == "fork":
+            c = _spec_channels(sp[1], c) + _spec_channels(sp[2], c)
+    return c
+
+
+def _run_specs(x: torch.Tensor, specs: Sequence[tuple], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out``: the channel slice of the enclosing block's output buffer that this chain's result belongs in (native
+    backend).  The chain's last op writes straight into it — its batch-norm apply / pooling kernel takes the slice
+    through ``native_ops.set_output_slot`` — so the block never runs a concat kernel."""
+    from ..ops import native_ops
+    for i, sp in enumerate(specs):
         kind = sp[0]
-        if kind == "conv":
-            if len(sp) == 3:
-                x = ops.conv2d(x, sp[1], list(sp[2]))
+        last = out is not None and i == len(specs) - 1
+        if kind == "fork":
+            if last:
+                ca = _spec_channels(sp[1], x.shape[-1])
+                oa, ob = out[..., :ca], out[..., ca:]
+                outs = streams.run_branches([lambda a=sp[1], v=x, o=oa: _run_specs(v, a, o),
+                                             lambda b=sp[2], v=x, o=ob: _run_specs(v, b, o)], x)
+                if all(o_.data_ptr() == t_.data_ptr() for o_, t_ in zip(outs, (oa, ob))):
+                    x = native_ops.concat_views(out, outs)
+                else:
+                    x = Fn.concat_channels(outs)
             else:
-                x = ops.conv2d(x, sp[1], list(sp[2]), stride=sp[3], padding=sp[4])
-        elif kind == "avg":
-            x = ops.avg_pool(x, list(sp[1]))
-        elif kind == "max":
-            x = ops.max_pool(x, list(sp[1]), stride=sp[2], padding=sp[3])
-        elif kind == "fork":
-            x = Fn.concat_channels(streams.run_branches([lambda a=sp[1], v=x: _run_specs(v, a),
-                                                         lambda b=sp[2], v=x: _run_specs(v, b)], x))
-        else:
-            raise ValueError(kind)
+                x = Fn.concat_channels(streams.run_branches([lambda a=sp[1], v=x: _run_specs(v, a),
+                                                             lambda b=sp[2], v=x: _run_specs(v, b)], x))
+            continue
+        if last:
+            native_ops.set_output_slot(out)
+        try:
+            if kind == "conv":
+                if len(sp) == 3:
+                    x = ops.conv2d(x, sp[1], list(sp[2]))
+                else:
+                    x = ops.conv2d(x, sp[1], list(sp[2]), stride=sp[3], padding=sp[4])
+            elif kind == "avg":
+                x = ops.avg_pool(x, list(sp[1]))
+            elif kind == "max":
+                x = ops.max_pool(x, list(sp[1]), stride=sp[2], padding=sp[3])
+            else:
+                raise ValueError(kind)
+        finally:
+            if last:
+                native_ops.set_output_slot(None)     # (an op that does not write into slices leaves it untouched)
     return x
+
+
+def _block_geometry(x: torch.Tensor, branches) -> Optional[Tuple[int, int, List[int]]]:
+    """(OH, OW, channels per branch) of a block whose branches keep or (3x3 / 2 VALID) reduce the map."""
+    n, h, w, c = x.shape
+    reduce = any(len(sp) > 3 and sp[0] in ("conv", "max") and (sp[3] if sp[0] == "conv" else sp[2]) == 2
+                 for _, specs in branches for sp in specs if sp[0] != "fork")
+    oh, ow = ((h - 3) // 2 + 1, (w - 3) // 2 + 1) if reduce else (h, w)
+    return oh, ow, [_spec_channels(specs, c) for _, specs in branches]
+
+
+def _run_block(store, net: torch.Tensor, branches) -> torch.Tensor:
+    """All branches of one Inception block on ``net``; the outputs end up side by side along the channels."""
+    sliced = net.is_cuda and Fn.use_native(net)
+    if sliced:
+        oh, ow, widths = _block_geometry(net, branches)
+        buf = torch.empty((net.shape[0], oh, ow, sum(widths)), dtype=net.dtype, device=net.device)
+        offs = [sum(widths[:i]) for i in range(len(widths))]
+        slots = [buf[..., o:o + w_] for o, w_ in zip(offs, widths)]
+    else:
+        slots = [None] * len(branches)
+
+    def _branch(bname, specs, x, slot):
+        def run():
+            with store.scope(bname):
+                return _run_specs(x, specs, slot)
+        return run
+    # independent branches: side streams on CUDA (ops/streams.py), plain sequence otherwise
+    outs = streams.run_branches([_branch(b, sp, net, sl) for (b, sp), sl in zip(branches, slots)], net)
+    if sliced and all(o.shape == sl.shape and o.data_ptr() == sl.data_ptr() for o, sl in zip(outs, slots)):
+        from ..ops import native_ops
+        return native_ops.concat_views(buf, outs)
+    return Fn.concat_channels(outs)
 
 
 def inception_v3(inputs: torch.Tensor, dropout_keep_prob: float = 0.8, num_classes: int = 1000,
@@ -123,14 +191,7 @@ def inception_v3(inputs: torch.Tensor, dropout_keep_prob: float = 0.8, num_class
         with scopes.arg_scope([ops.conv2d, ops.max_pool, ops.avg_pool], stride=1, padding="SAME"):
             for name, branches in BLOCKS:
                 with store.scope(name):
-                    def _branch(bname, specs, x):
-                        def run():
-                            with store.scope(bname):
-                                return _run_specs(x, specs)
-                        return run
-                    # independent branches: side streams on CUDA (ops/streams.py), plain sequence otherwise
-                    outs = streams.run_branches([_branch(b, sp, net) for b, sp in branches], net)
-                    net = end_points[name] = Fn.concat_channels(outs)
+                    net = end_points[name] = _run_block(store, net, branches)
                 if name == AUX_AFTER:
                     # auxiliary classifier (inception_model.py:251-263); its handful of small kernels run beside the
                     # remaining blocks of the trunk (joined before the function returns)

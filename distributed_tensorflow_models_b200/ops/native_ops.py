@@ -297,6 +297,51 @@ def _grad_written(*params) -> None:
                 fn(p)
 
 
+# K11 — concat elimination.  A block that concatenates branch outputs along the channels allocates the block's
+# output once and hands every branch the channel slice it owns; the branch's LAST op (the batch-norm apply behind its
+# final convolution, or a pooling kernel) takes the slice here and writes into it with the block's pixel pitch, so no
+# concat kernel runs (the reference concatenates with tf.concat(axis=3, ...), inception/slim/inception_model.py:127).
+_out_slot = [None]
+
+
+def set_output_slot(view: Optional[torch.Tensor]) -> None:
+    _out_slot[0] = view
+
+
+def take_output_slot(shape) -> Optional[torch.Tensor]:
+    s = _out_slot[0]
+    if s is not None and tuple(s.shape) == tuple(shape):
+        _out_slot[0] = None
+        return s
+    return None
+
+
+def output_slot_pending() -> bool:
+    return _out_slot[0] is not None
+
+
+class _ConcatViewFn(torch.autograd.Function):
+    """The block buffer whose channel slices the branches have already written: forward is free, backward hands each
+    branch its slice of the incoming gradient as a strided view (the consumers read it with the buffer's pitch)."""
+
+    @staticmethod
+    def forward(ctx, buf, *outs):
+        ctx.widths = [o.shape[-1] for o in outs]
+        return buf.as_strided(buf.shape, buf.stride())
+
+    @staticmethod
+    def backward(ctx, dy):
+        grads, c0 = [], 0
+        for w in ctx.widths:
+            grads.append(dy[..., c0:c0 + w])
+            c0 += w
+        return (None, *grads)
+
+
+def concat_views(buf: torch.Tensor, outs) -> torch.Tensor:
+    return _ConcatViewFn.apply(buf, *outs)
+
+
 def _grad_slot(p):
     """The parameter's pre-allocated .grad (a view of the flat PS gradient buffer) when it can be accumulated
     into directly — saves one elementwise add kernel per parameter per step."""
@@ -315,9 +360,10 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
     c = x.shape[-1]
     m = x.numel() // c
     dx = torch.empty_like(x)
+    ld_dy = cn._pitch(dy) if dy.dim() == 4 else c      # dy may be a channel slice of a wider gradient (K11)
     if not coef.training:
         nat.check(nat.lib().dtf_affine_act_bwd(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu),
-                                               C.c_longlong(m), c, c, c, c, _p(dx), nat.stream_ptr()),
+                                               C.c_longlong(m), c, c, ld_dy, c, _p(dx), nat.stream_ptr()),
                   "dtf_affine_act_bwd")
         if add is not None:
             dx = dx + add
@@ -325,7 +371,7 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
     if sums is None:          # (the dgrad epilogue may already have produced the reductions)
         sums = _zeros(2 * c, x.device)
         nat.check(nat.lib().dtf_bn_bwd_reduce(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), int(relu),
-                                              C.c_longlong(m), c, c, c, _p(sums), nat.stream_ptr()),
+                                              C.c_longlong(m), c, c, ld_dy, _p(sums), nat.stream_ptr()),
                   "dtf_bn_bwd_reduce")
     gslot, bslot = _grad_slot(gamma), _grad_slot(beta)
     direct = coef.training and (not has_gamma or gslot is not None) and (not has_beta or bslot is not None)
@@ -336,7 +382,7 @@ def _bn_backward(dy, x, coef: BnCoef, relu: bool, has_gamma: bool, has_beta: boo
         db = torch.zeros(c, dtype=torch.float32, device=x.device) if has_beta else None
     if coef.training:
         nat.check(nat.lib().dtf_bn_bwd_apply(_p(dy), _p(x), _p(coef.scale), _p(coef.shift), _p(coef.mean),
-                                             _p(coef.invstd), _p(sums), int(relu), C.c_longlong(m), c, c, c, c,
+                                             _p(coef.invstd), _p(sums), int(relu), C.c_longlong(m), c, c, ld_dy, c,
                                              _p(add), c if add is not None else 0, _p(dx), _p(dg), _p(db),
                                              nat.stream_ptr()), "dtf_bn_bwd_apply")
     else:
@@ -357,7 +403,10 @@ class _BnApplyFn(torch.autograd.Function):
         x = x.contiguous()
         c = x.shape[-1]
         m = x.numel() // c
-        y = torch.empty_like(x)
+        y = take_output_slot(x.shape)            # a channel slice of the enclosing block's output, or None
+        if y is None:
+            y = torch.empty_like(x)
+        ld_y = cn._pitch(y)
         if isinstance(coef, _BnTrainSpec):
             # statistics, moving-average update and apply in one native call
             sp = coef
@@ -366,11 +415,11 @@ class _BnApplyFn(torch.autograd.Function):
             nat.check(nat.lib().dtf_bn_forward_train(_p(x), C.c_longlong(m), c, c, _p(gamma), _p(beta),
                                                      C.c_float(sp.eps), C.c_float(sp.decay), int(sp.update_moving),
                                                      int(sp.unbiased), _p(sp.mm), _p(sp.mv), int(relu), _p(scratch),
-                                                     _p(buf), _p(y), c, nat.stream_ptr()), "dtf_bn_forward_train")
+                                                     _p(buf), _p(y), ld_y, nat.stream_ptr()), "dtf_bn_forward_train")
             coef = BnCoef(buf[:c], buf[c:2 * c], buf[2 * c:3 * c], buf[3 * c:], True)
         else:
             nat.check(nat.lib().dtf_affine_act(_p(x), _p(coef.scale), _p(coef.shift), int(relu), C.c_longlong(m), c, c,
-                                               c, _p(y), nat.stream_ptr()), "dtf_affine_act")
+                                               ld_y, _p(y), nat.stream_ptr()), "dtf_affine_act")
         ctx.save_for_backward(x)
         ctx.coef, ctx.relu = coef, relu
         ctx.has = (gamma is not None, beta is not None)
@@ -380,7 +429,7 @@ class _BnApplyFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
-        dx, dg, db = _bn_backward(dy.contiguous(), x, ctx.coef, ctx.relu, ctx.has[0], ctx.has[1],
+        dx, dg, db = _bn_backward(cn.as_pixel_dense(dy), x, ctx.coef, ctx.relu, ctx.has[0], ctx.has[1],
                                   gamma=ctx.params[0], beta=ctx.params[1])
         return dx, dg, db, None, None
 
@@ -538,9 +587,11 @@ class _MaxPoolFn(torch.autograd.Function):
     def forward(ctx, x, k, stride, pad, out_hw):
         x = x.contiguous()
         n, h, w, c = x.shape
-        y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
+        y = take_output_slot((n, out_hw[0], out_hw[1], c))
+        if y is None:
+            y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
         arg = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.uint8, device=x.device)
-        p = _pool_params(x, k, stride, pad, out_hw, c)
+        p = _pool_params(x, k, stride, pad, out_hw, cn._pitch(y))
         nat.check(nat.lib().dtf_max_pool_fwd(C.byref(p), _p(x), _p(y), _p(arg), nat.stream_ptr()), "dtf_max_pool_fwd")
         ctx.save_for_backward(arg)
         ctx.p = p
@@ -550,10 +601,10 @@ class _MaxPoolFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         (arg,) = ctx.saved_tensors
-        dy = dy.contiguous()
+        dy = cn.as_pixel_dense(dy)
         c = ctx.in_shape[-1]
         dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dy.device)
-        nat.check(nat.lib().dtf_max_pool_bwd(C.byref(ctx.p), _p(dy), c, _p(arg), _p(dx), c, nat.stream_ptr()),
+        nat.check(nat.lib().dtf_max_pool_bwd(C.byref(ctx.p), _p(dy), cn._pitch(dy), _p(arg), _p(dx), c, nat.stream_ptr()),
                   "dtf_max_pool_bwd")
         return dx, None, None, None, None
 
@@ -563,8 +614,10 @@ class _AvgPoolFn(torch.autograd.Function):
     def forward(ctx, x, k, stride, pad, out_hw):
         x = x.contiguous()
         n, h, w, c = x.shape
-        y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
-        p = _pool_params(x, k, stride, pad, out_hw, c)
+        y = take_output_slot((n, out_hw[0], out_hw[1], c))
+        if y is None:
+            y = torch.empty((n, out_hw[0], out_hw[1], c), dtype=torch.float32, device=x.device)
+        p = _pool_params(x, k, stride, pad, out_hw, cn._pitch(y))
         nat.check(nat.lib().dtf_avg_pool_fwd(C.byref(p), _p(x), _p(y), nat.stream_ptr()), "dtf_avg_pool_fwd")
         ctx.p = p
         ctx.in_shape = x.shape
@@ -572,10 +625,10 @@ class _AvgPoolFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        dy = dy.contiguous()
+        dy = cn.as_pixel_dense(dy)
         c = ctx.in_shape[-1]
         dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dy.device)
-        nat.check(nat.lib().dtf_avg_pool_bwd(C.byref(ctx.p), _p(dy), c, _p(dx), c, nat.stream_ptr()),
+        nat.check(nat.lib().dtf_avg_pool_bwd(C.byref(ctx.p), _p(dy), cn._pitch(dy), _p(dx), c, nat.stream_ptr()),
                   "dtf_avg_pool_bwd")
         return dx, None, None, None, None
 
