@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--image-size", type=int, default=None, help="model-zoo networks only (default: the network's own)")
     ap.add_argument("--num-classes", type=int, default=None, help="model-zoo networks only (default 1001)")
+    ap.add_argument("--precision", default="tf32", choices=("tf32", "tf32x3"))
     ap.add_argument("--no-secondary", action="store_true",
                     help="headline only: skip the other BASELINE.json configs (Inception-v3 SSP / BSP, ResNet SSP)")
     ap.add_argument("--min-seconds", type=float, default=1.0,
@@ -145,7 +146,7 @@ def measure(args, model, mode, world, rank, local_rank, device, want_e2e=True):
     setup = TrainSetup(model=model, mode=mode, num_workers=world, staleness=args.staleness,
                        cuda_graph=not args.no_graph, fuse_bn=not args.no_fuse_bn, seed=0,
                        branch_streams=not args.no_branch_streams, image_size=args.image_size,
-                       num_classes=args.num_classes)
+                       num_classes=args.num_classes, precision=args.precision)
     setup.batch_size = args.batch if args.batch else spec.batch_size
     trainer = Trainer(setup, comm, device)
     bs = setup.batch_size
@@ -290,7 +291,7 @@ def main():
 
     line = measure(args, args.model, args.mode, world, rank, local_rank, device)
     line.update({"higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                 "dtype": "fp32 storage/accumulate, tf32 tensor-core multiply (reference is fp32; no bf16/fp8)",
+                 "dtype": "fp32 storage/accumulate, %s tensor-core multiply (reference is fp32; no bf16/fp8)" % args.precision,
                  "data": "synthetic (random images of the dataset's shape, random-init weights)", "impl": "ours"})
     secondary = []
     if not args.no_secondary and args.model == "resnet" and args.mode == "bsp":

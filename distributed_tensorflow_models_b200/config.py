@@ -116,7 +116,11 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
     ap.add_argument("--init_checkpoint", default="",
                     help="fine-tuning: initialise the variables from this checkpoint (directory or model.ckpt-N prefix), "
                          "ignoring missing ones, and start at global step 0 (vgg/nets/mobilenet_v1_train.py:165-181)")
-    ap.add_argument("--trace", default="", help="write a Chrome-trace JSON of step phases to this path")
+    ap.add_argument("--trace", default="", help="write a Chrome-trace JSON of step phases to this path (device-timed "
+                                                 "with CUDA events on a GPU)")
+    ap.add_argument("--precision", default="tf32", choices=("tf32", "tf32x3"),
+                    help="tensor-core multiplies: tf32 (default) or tf32x3 = split operands, three accumulating passes, "
+                         "fp32-like products for parity runs (the reference is fp32 throughout)")
     ap.add_argument("--backend", default="auto", choices=("auto", "local", "thread", "gloo", "nccl", "symm"),
                     help="transport: symm = in-kernel NVLink push/pull (product path); nccl = baseline")
     ap.add_argument("--placement", default="flat", choices=("flat", "round_robin", "axis0"))

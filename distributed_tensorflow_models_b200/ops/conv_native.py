@@ -54,7 +54,7 @@ def out_size(i: int, k: int, stride: int, pad: int) -> int:
     return (i + 2 * pad - k) // stride + 1
 
 
-def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: Tuple[int, int], *,
+def _conv_fprop_once(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: Tuple[int, int], *,
                bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
                relu: bool = False, in_scale: Optional[torch.Tensor] = None,
                in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
@@ -120,8 +120,9 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: T
     return (out, act) if want_act else out
 
 
-def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
-               pad: Tuple[int, int], out: Optional[torch.Tensor] = None, bn_bwd=None) -> torch.Tensor:
+def _conv_dgrad_once(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
+                     pad: Tuple[int, int], out: Optional[torch.Tensor] = None, bn_bwd=None,
+                     residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dx = conv_transpose(dy, w).  ``w_t`` is the dgrad operand ``[C_in, R, S, C_out]``
     (``weight_transpose`` of the OHWI weights).
 
@@ -136,7 +137,7 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
         # and zero-fill the 1 - 1/(sh*sw) of them that do not divide, element by element.
         dyu = torch.zeros((n, p_ * stride[0], q_ * stride[1], co), device=dy.device, dtype=torch.float32)
         dyu[:, ::stride[0], ::stride[1], :] = dy
-        return conv_dgrad(dyu, w_t, in_hw, (1, 1), pad, out=out, bn_bwd=bn_bwd)
+        return _conv_dgrad_once(dyu, w_t, in_hw, (1, 1), pad, out=out, bn_bwd=bn_bwd, residual=residual)
     if co % 4 != 0:
         # the gather reads 16-byte channel chunks and TMA needs a 16-byte row pitch: zero-pad the
         # (tiny: logits layers only) gradient and weight operand to a multiple of 4 channels
@@ -157,8 +158,9 @@ def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stri
     p.out, p.out_ld = out.data_ptr(), _pitch(out)
     p.in_scale = p.in_shift = None
     p.in_relu = 0
-    p.bias = p.residual = None
-    p.res_ld = 0
+    p.bias = None
+    p.residual = nat.ptr(residual)
+    p.res_ld = _pitch(residual) if residual is not None else 0
     p.out_relu = 0
     p.stats = None
     p.bnb_x = p.bnb_scale = p.bnb_shift = None
@@ -282,8 +284,8 @@ def weight_transpose(w: torch.Tensor) -> torch.Tensor:
     return wt
 
 
-def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, w_shape: Sequence[int], stride: Tuple[int, int],
-               pad: Tuple[int, int], *, in_scale: Optional[torch.Tensor] = None,
+def _conv_wgrad_once(x: torch.Tensor, dy: torch.Tensor, w_shape: Sequence[int], stride: Tuple[int, int],
+                     pad: Tuple[int, int], *, in_scale: Optional[torch.Tensor] = None,
                in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
                out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dW (OHWI).  Accumulates into ``out`` when given (it must already hold zeros / a running sum)."""
@@ -304,3 +306,80 @@ def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, w_shape: Sequence[int], stride
     p.in_scale, p.in_shift, p.in_relu = nat.ptr(in_scale), nat.ptr(in_shift), int(in_relu)
     nat.check(nat.lib().dtf_conv_wgrad(C.byref(p), nat.stream_ptr()), "dtf_conv_wgrad")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# precision: TF32 (default) or 3xTF32
+# ---------------------------------------------------------------------------------------------------
+# The tensor core multiplies fp32 operands as TF32 (10 mantissa bits) and accumulates in fp32; the reference is fp32
+# end to end (inception/slim/variables.py:249).  For parity runs and fp32-sensitive users every operand can be split
+# into a part the tensor core represents exactly and the remainder,
+#     a = a_hi + a_lo,   a_hi = a with the 13 low mantissa bits cleared,   a_lo = a - a_hi  (exact in fp32)
+# and a product is then formed as a_hi*b_hi + a_hi*b_lo + a_lo*b_hi — three passes of the same kernel accumulating into
+# one fp32 output (the dropped a_lo*b_lo term is ~2^-22 relative).  That is the error of an fp32 multiply to within a
+# bit or two, at three times the tensor-core work.  Fused input transforms (batch-norm apply + ReLU on load) are not
+# linear in the operand, so layers that use them keep the single pass; the engine switches that fusion off when
+# ``precision='tf32x3'`` is asked for.
+_precision = ["tf32"]
+
+
+def set_precision(name: str) -> None:
+    if name not in ("tf32", "tf32x3"):
+        raise ValueError("precision must be 'tf32' or 'tf32x3', not %r" % (name,))
+    _precision[0] = name
+
+
+def get_precision() -> str:
+    return _precision[0]
+
+
+def _split_tf32(t: torch.Tensor):
+    hi = (t.view(torch.int32) & -8192).view(torch.float32)
+    return hi, t - hi
+
+
+def conv_fprop(x: torch.Tensor, w: torch.Tensor, stride: Tuple[int, int], pad: Tuple[int, int], *,
+               bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+               relu: bool = False, in_scale: Optional[torch.Tensor] = None,
+               in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
+               stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+               out_hw: Optional[Tuple[int, int]] = None, want_act: bool = False, bn_pending=None):
+    """y = epilogue(conv(act(x), w)) — see :func:`_conv_fprop_once`; under ``tf32x3`` three accumulating passes."""
+    if _precision[0] == "tf32" or in_scale is not None or bn_pending is not None:
+        return _conv_fprop_once(x, w, stride, pad, bias=bias, residual=residual, relu=relu, in_scale=in_scale,
+                                in_shift=in_shift, in_relu=in_relu, stats=stats, out=out, out_hw=out_hw,
+                                want_act=want_act, bn_pending=bn_pending)
+    xh, xl = _split_tf32(x)
+    wh, wl = _split_tf32(w)
+    y = _conv_fprop_once(xh, wh, stride, pad, bias=bias, residual=residual, out=out, out_hw=out_hw)
+    y = _conv_fprop_once(xh, wl, stride, pad, residual=y, out=y, out_hw=out_hw)
+    y = _conv_fprop_once(xl, wh, stride, pad, residual=y, out=y, out_hw=out_hw, relu=relu, stats=stats)
+    return (y, None) if want_act else y
+
+
+def conv_dgrad(dy: torch.Tensor, w_t: torch.Tensor, in_hw: Tuple[int, int], stride: Tuple[int, int],
+               pad: Tuple[int, int], out: Optional[torch.Tensor] = None, bn_bwd=None) -> torch.Tensor:
+    """dx = conv_transpose(dy, w) — see :func:`_conv_dgrad_once`; under ``tf32x3`` three accumulating passes."""
+    if _precision[0] == "tf32" or bn_bwd is not None:
+        return _conv_dgrad_once(dy, w_t, in_hw, stride, pad, out=out, bn_bwd=bn_bwd)
+    gh, gl = _split_tf32(dy)
+    wh, wl = _split_tf32(w_t)
+    dx = _conv_dgrad_once(gh, wh, in_hw, stride, pad, out=out)
+    dx = _conv_dgrad_once(gh, wl, in_hw, stride, pad, out=dx, residual=dx)
+    return _conv_dgrad_once(gl, wh, in_hw, stride, pad, out=dx, residual=dx)
+
+
+def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, w_shape: Sequence[int], stride: Tuple[int, int],
+               pad: Tuple[int, int], *, in_scale: Optional[torch.Tensor] = None,
+               in_shift: Optional[torch.Tensor] = None, in_relu: bool = False,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dW (OHWI), accumulated into ``out`` when given — see :func:`_conv_wgrad_once`; under ``tf32x3`` three passes
+    (the kernel accumulates into dW anyway)."""
+    if _precision[0] == "tf32" or in_scale is not None:
+        return _conv_wgrad_once(x, dy, w_shape, stride, pad, in_scale=in_scale, in_shift=in_shift, in_relu=in_relu,
+                                out=out)
+    xh, xl = _split_tf32(x)
+    gh, gl = _split_tf32(dy)
+    out = _conv_wgrad_once(xh, gh, w_shape, stride, pad, out=out)
+    out = _conv_wgrad_once(xh, gl, w_shape, stride, pad, out=out)
+    return _conv_wgrad_once(xl, gh, w_shape, stride, pad, out=out)

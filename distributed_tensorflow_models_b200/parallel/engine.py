@@ -57,6 +57,7 @@ class TrainSetup:
     weight_decay: Optional[float] = None
     quantize: bool = False            # fake-quantised weights / activations with folded batch norm (slim/quantize.py)
     quant_delay: int = 0              # global step at which the fake-quant ops switch on
+    precision: str = "tf32"           # tensor-core multiplies: 'tf32' | 'tf32x3' (split operands, ~fp32; 3x the work)
 
     def resolved(self) -> "TrainSetup":
         p = self.preset or preset_for(self.model, self.mode)
@@ -140,7 +141,10 @@ class Trainer:
         spec = registry.spec_for(self.setup.model, self.setup.image_size, self.setup.num_classes)
         self.spec = spec
         self.store = VariableStore(seed=self.setup.seed)
-        self.store.fuse_bn = bool(self.setup.fuse_bn)
+        if self.setup.precision not in ("tf32", "tf32x3"):
+            raise ValueError("precision must be 'tf32' or 'tf32x3'")
+        # the fused batch-norm apply on load is not linear in the operand: 3xTF32 runs the unfused layers
+        self.store.fuse_bn = bool(self.setup.fuse_bn) and self.setup.precision == "tf32"
         self.forward = build_forward(self.setup)
         self.prefix = _SCOPE_PREFIX.get(self.setup.model, "")
         if self.setup.quantize:
@@ -190,6 +194,9 @@ class Trainer:
     def _run_forward(self, x, y, training, build=False):
         from ..ops import streams
         streams.set_branch_streams(self.setup.branch_streams and self.device.type == "cuda" and not build)
+        if self.device.type == "cuda":
+            from ..ops import conv_native
+            conv_native.set_precision(self.setup.precision)
         if self.setup.quantize:
             self.store.quant.is_training = bool(training)
         with self.store.as_default():

@@ -122,8 +122,9 @@ class SymmComm(Comm):
         self.bucketed = self.mode == "bsp"          # ownership: 1/W of every bucket (BSP) or flat shards (ASP / SSP)
         small = total * 4 < (16 << 20)
         if self.push_sms is None:
-            # the NVSwitch reduction (BSP) and the bulk-copy-engine push (ASP / SSP) both saturate from ~16 SMs
-            self.push_sms = 0 if (small or W == 1) else 16
+            # the NVSwitch reduction (BSP) saturates from ~16 SMs; the bulk-copy-engine push (ASP / SSP) moves
+            # ~0.3 ms x 8 / SMs per 100 MB on 8 GPUs, and 24 SMs balance it against the slower backward pass
+            self.push_sms = 0 if (small or W == 1) else (16 if self.bucketed else 24)
         # small models: one bucket, pushed behind the last weight-gradient kernel on the compute stream itself
         self.inline = self.push_sms == 0
         if self.bucket_mb is None:

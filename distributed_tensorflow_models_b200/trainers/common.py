@@ -66,7 +66,8 @@ def make_setup(args, num_workers: int) -> TrainSetup:
                       epochs_per_decay=args.num_epochs_per_decay, decay_factor=args.learning_rate_decay_factor,
                       cuda_graph=bool(args.cuda_graph), preset=args.preset, image_size=args.image_size,
                       num_classes=args.num_classes, weight_decay=args.weight_decay,
-                      quantize=bool(args.quantize), quant_delay=int(args.quant_delay))
+                      quantize=bool(args.quantize), quant_delay=int(args.quant_delay),
+                      precision=getattr(args, "precision", "tf32"))
 
 
 def make_batches(args, spec, rank: int, world: int, device=None):

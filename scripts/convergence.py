@@ -60,7 +60,8 @@ def main():
     ys = [y.to(dev) for y in ys]
 
     if world == 1:
-        arms = [("native_tf32", "auto", lambda: LocalComm()), ("torch_fp32", "torch", lambda: LocalComm())]
+        arms = [("native_tf32", "auto", lambda: LocalComm()), ("torch_fp32", "torch", lambda: LocalComm()),
+                ("native_tf32x3", "auto", lambda: LocalComm())]
     else:
         from distributed_tensorflow_models_b200.parallel.symm import SymmComm
         arms = [("symm_bucketed_push", "auto", lambda: SymmComm()), ("nccl_rs_ag", "auto", lambda: TorchDistComm("rs_ag"))]
@@ -71,7 +72,8 @@ def main():
         torch.backends.cuda.matmul.allow_tf32 = False
         comm = mk_comm()
         t = Trainer(TrainSetup(model=model, mode="bsp", num_workers=world, batch_size=bs, seed=0,
-                               cuda_graph=(backend == "auto")), comm, dev)
+                               cuda_graph=(backend == "auto"),
+                               precision="tf32x3" if name.endswith("x3") else "tf32"), comm, dev)
         losses = []
         pending = []
         for i in range(steps):
@@ -91,17 +93,18 @@ def main():
         del t, comm
         torch.cuda.empty_cache()
     Fn.set_backend("auto")
-    (na, a), (nb, b) = list(curves.items())
+    names = list(curves)
+    ref = "torch_fp32" if "torch_fp32" in curves else names[1]
     k = max(10, steps // 40)
-    sa, sb = smooth(a, k), smooth(b, k)
+    sm = {n: smooth(c, k) for n, c in curves.items()}
     marks = sorted({min(steps - 1, int(steps * f)) for f in (0.05, 0.1, 0.25, 0.5, 0.75, 1.0)})
     report = {"model": model, "steps": steps, "world": world, "batch_per_gpu": bs, "distinct_batches": n_batches,
-              "smoothing_window": k, "arms": [na, nb],
-              "smoothed_loss_at": {str(m): {na: sa[m], nb: sb[m], "rel_gap": abs(sa[m] - sb[m]) / max(abs(sb[m]), 1e-6)}
-                                   for m in marks},
-              "first_loss": {na: a[0], nb: b[0]},
-              "max_rel_gap_of_smoothed_losses": max(abs(p - q) / max(abs(q), 1e-2) for p, q in zip(sa[k:], sb[k:])),
-              "curves_every_10": {na: a[::10], nb: b[::10]}}
+              "smoothing_window": k, "arms": names, "reference_arm": ref,
+              "smoothed_loss_at": {str(m): {n: sm[n][m] for n in names} for m in marks},
+              "first_loss": {n: curves[n][0] for n in names},
+              "max_rel_gap_of_smoothed_losses_vs_reference": {
+                  n: max(abs(p - q) / max(abs(q), 1e-2) for p, q in zip(sm[n][k:], sm[ref][k:])) for n in names if n != ref},
+              "curves_every_10": {n: c[::10] for n, c in curves.items()}}
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
         path = f"gpurun_out/convergence_{model}{'_n%d' % world if world > 1 else ''}.json"

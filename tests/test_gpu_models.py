@@ -151,3 +151,39 @@ def test_branch_streams_single_block_is_race_free():
             assert w[0] < max(1e-3, 3 * floor[0]), (w, floor)
     finally:
         streams.set_branch_streams(False)
+
+
+def test_convergence_parity_with_fp32_at_equal_steps():
+    """BASELINE.json: "convergence parity at equal steps".  ResNet-32 from the same initial values on a fixed synthetic
+    set with learnable labels: the native TF32 path against plain PyTorch in full fp32 (TF32 off).  The two trajectories
+    are not bit-comparable (TF32 rounding, float atomics), so the comparison is on what a user sees: the loss falls
+    equally fast (mean loss over the run) and to the same level.  Long curves incl. 3xTF32 and Inception-v3:
+    scripts/convergence.py -> profiles/convergence_*.json (2000 steps: means 0.2579 vs 0.2594, plateau 0.00551 vs 0.00547)."""
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    dev = torch.device("cuda", 0)
+    g = torch.Generator().manual_seed(4321)
+    bs, nb, steps = 128, 8, 400
+    xs = [torch.randn(bs, 32, 32, 3, generator=g) for _ in range(nb)]
+    proj = torch.randn(3, 10, generator=torch.Generator().manual_seed(7))
+    ys = [(x.mean(dim=(1, 2)) @ proj).argmax(1).to(dev) for x in xs]
+    xs = [x.to(dev) for x in xs]
+    curves = {}
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        for name, backend in (("native", "auto"), ("fp32", "torch")):
+            Fn.set_backend(backend)
+            t = Trainer(TrainSetup(model="resnet", batch_size=bs, seed=0, cuda_graph=(backend == "auto")), device=dev)
+            ls = []
+            for i in range(steps):
+                ls.append(t.train_step(xs[i % nb], ys[i % nb])["loss"].clone())
+            curves[name] = torch.stack(ls).cpu()
+    finally:
+        Fn.set_backend("auto")
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+    a, b = curves["native"], curves["fp32"]
+    assert abs(float(a[0]) - float(b[0])) < 2e-3 * float(b[0])                  # same starting point
+    assert float(b[-50:].mean()) < 0.5 * float(b[:10].mean())                   # the reference arm does learn
+    assert abs(float(a.mean()) - float(b.mean())) < 0.1 * float(b.mean())       # equally fast ...
+    assert abs(float(a[-50:].mean()) - float(b[-50:].mean())) < 0.25 * float(b[-50:].mean()) + 0.02   # ... to the same level
