@@ -2,6 +2,8 @@
 
 #include <cudaTypedefs.h>
 
+#include <vector>
+
 #include "../include/dtf_b200.h"
 
 namespace dtf {
@@ -82,15 +84,32 @@ struct TmapKeyHash {
   }
 };
 
+// The caches are keyed by address and shape.  Under a captured graph the addresses repeat and the caches stay small;
+// an eager run with a churning allocator would grow them without bound, so a cache that passes TMAP_CACHE_CAP entries
+// is emptied.  Descriptors are handed to kernels by value (__grid_constant__), but a launcher may still hold the
+// pointer it was just given, so the memory of an emptied cache is released one overflow later, not at once.
+constexpr size_t TMAP_CACHE_CAP = 8192;
+template <typename Map>
+static void bound_cache(Map& cache, std::vector<CUtensorMap*>& retired) {
+  if (cache.size() < TMAP_CACHE_CAP) return;
+  for (CUtensorMap* p : retired) free(p);
+  retired.clear();
+  for (auto& kv : cache)
+    if (kv.second != nullptr) retired.push_back(kv.second);
+  cache.clear();
+}
+
 const CUtensorMap* get_tmap_2d_f32_sw128(const float* ptr, int rows, int cols, int box_rows) {
   static std::unordered_map<TmapKey, CUtensorMap*, TmapKeyHash> cache;
   static std::mutex mu;
   int dev = 0;
   cudaGetDevice(&dev);
   TmapKey key{ptr, rows, cols, box_rows, dev};
+  static std::vector<CUtensorMap*> retired;
   std::lock_guard<std::mutex> lk(mu);
   auto it = cache.find(key);
   if (it != cache.end()) return it->second;
+  bound_cache(cache, retired);
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_last_error("cuTensorMapEncodeTiled entry point not available");
@@ -165,9 +184,11 @@ const CUtensorMap* get_tmap_im2col_f32(const Im2colSpec& spec) {
   key.s.lower_w = spec.lower_w; key.s.lower_h = spec.lower_h; key.s.upper_w = spec.upper_w; key.s.upper_h = spec.upper_h;
   key.s.tw = spec.tw; key.s.th = spec.th; key.s.channels = spec.channels; key.s.nan_fill = spec.nan_fill;
   cudaGetDevice(&key.dev);
+  static std::vector<CUtensorMap*> retired;
   std::lock_guard<std::mutex> lk(mu);
   auto it = cache.find(key);
   if (it != cache.end()) return it->second;
+  bound_cache(cache, retired);
   EncodeIm2colFn enc = get_encode_im2col_fn();
   if (!enc) return nullptr;
   const Im2colSpec& s = key.s;

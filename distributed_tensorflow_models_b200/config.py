@@ -118,6 +118,12 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
                          "ignoring missing ones, and start at global step 0 (vgg/nets/mobilenet_v1_train.py:165-181)")
     ap.add_argument("--trace", default="", help="write a Chrome-trace JSON of step phases to this path (device-timed "
                                                  "with CUDA events on a GPU)")
+    ap.add_argument("--ps_timeout_secs", type=float, default=None,
+                    help="--backend symm: give up a parameter-server flag wait (a peer died) after this many seconds "
+                         "and abort the run (default 300, or $DTF_PS_TIMEOUT_S)")
+    ap.add_argument("--ssp_timeout_secs", type=float, default=None,
+                    help="--backend symm: give up an SSP staleness wait after this many seconds (default 30, or "
+                         "$DTF_SSP_TIMEOUT_S)")
     ap.add_argument("--precision", default="tf32", choices=("tf32", "tf32x3"),
                     help="tensor-core multiplies: tf32 (default) or tf32x3 = split operands, three accumulating passes, "
                          "fp32-like products for parity runs (the reference is fp32 throughout)")

@@ -377,10 +377,10 @@ class TorchDistComm(Comm):
         W = self.world
         if self.shard is None:
             # all-reduce arm / gloo: every rank holds every gradient after an all-gather and applies them in rank order
-            allg = torch.empty(W * L.total, dtype=torch.float32, device=L.grads.device)
-            dist.all_gather_into_tensor(allg, L.grads, group=self.group)
+            parts = [torch.empty_like(L.grads) for _ in range(W)]
+            dist.all_gather(parts, L.grads, group=self.group)
             for q in range(W):
-                self.opts[0].apply(allg[q * L.total:(q + 1) * L.total], lr, grad_scale, num_updates=self._gs + q)
+                self.opts[0].apply(parts[q], lr, grad_scale, num_updates=self._gs + q)
         else:
             s = self.shard.numel()
             if getattr(self, "_inbox", None) is None:

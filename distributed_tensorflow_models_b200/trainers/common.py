@@ -177,7 +177,8 @@ def make_comm(args, backend: str, num_workers: int):
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     if backend == "symm":
         from ..parallel.symm import SymmComm
-        return SymmComm(), dev, rank, world
+        return SymmComm(timeout_s=getattr(args, "ps_timeout_secs", None),
+                        ssp_timeout_s=getattr(args, "ssp_timeout_secs", None)), dev, rank, world
     from ..parallel.comm import TorchDistComm
     return TorchDistComm("rs_ag"), dev, rank, world
 

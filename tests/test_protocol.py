@@ -271,3 +271,52 @@ def test_branch_streams_fall_back_to_call_order_on_cpu():
         assert [float(o) for o in outs] == [0.0, 1.0, 2.0] and order == [0, 1, 2, 7] and float(aux.join()) == 7.0
     finally:
         streams.set_branch_streams(False)
+
+
+def test_collective_baseline_arm_emulates_asp_over_gloo(tmp_path):
+    """TorchDistComm.async_step (the NCCL / gloo baseline arm of the one-sided push): every worker's own gradient is
+    applied as a separate optimiser step, global_step advances by W per round, replicas stay identical — checked
+    against the two gradients applied one after the other by hand."""
+    script = tmp_path / "asp_gloo.py"
+    script.write_text(
+        "import os, sys, json, torch, torch.distributed as dist\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "from distributed_tensorflow_models_b200.parallel.comm import TorchDistComm\n"
+        "from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "g = torch.Generator().manual_seed(100 + r)\n"
+        "x, y = torch.randn(4, 24, 24, 3, generator=g), torch.randint(0, 10, (4,), generator=g)\n"
+        "t = Trainer(TrainSetup(model='cnn', mode='asp', batch_size=4, num_workers=w, seed=0), TorchDistComm('rs_ag'))\n"
+        "gs = [t.train_step(x, y)['global_step']]\n"
+        "sum1 = float(t.layout.params[:t.layout.used].double().sum())\n"
+        "gs += [t.train_step(x, y)['global_step'] for _ in range(2)]\n"
+        "p = t.layout.params[:t.layout.used]\n"
+        "chk = torch.stack([p.double().sum(), p.double().abs().sum()])\n"
+        "allc = [torch.zeros_like(chk) for _ in range(w)]\n"
+        "dist.all_gather(allc, chk)\n"
+        "if r == 0: print(json.dumps({'gs': gs, 'same': all(torch.equal(c, allc[0]) for c in allc), 'sum1': sum1}))\n"
+        "dist.destroy_process_group()\n")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29577", str(script)],
+                       capture_output=True, text=True, timeout=300, env=env)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert lines, (r.stdout[-1500:], r.stderr[-1500:])
+    import json
+    res = json.loads(lines[-1])
+    assert res["gs"] == [2, 4, 6] and res["same"]
+
+    # oracle for the first round: both workers' gradients taken at the initial parameters, applied one after the other
+    t = Trainer(TrainSetup(model="cnn", mode="asp", batch_size=4, num_workers=2, seed=0))
+    grads = []
+    for r_ in range(2):
+        g = torch.Generator().manual_seed(100 + r_)
+        x, y = torch.randn(4, 24, 24, 3, generator=g), torch.randint(0, 10, (4,), generator=g)
+        t._fwd_bwd(x, y)
+        grads.append(t.layout.grads.clone())
+    o = t.comm.owned_optimizers()[0]
+    for q, gq in enumerate(grads):
+        o.apply(gq[o.lo:o.hi], t.learning_rate(0), 1.0, num_updates=q)
+    p = t.layout.params[:t.layout.used]
+    assert float(p.double().sum()) == pytest.approx(res["sum1"], rel=1e-6)
