@@ -259,6 +259,8 @@ class Trainer:
             m1 = tr.mark() if tr else None
             self.comm.before_backward()
             total.backward()
+            if native:
+                native_ops.join_wgrad_stream(self.device)       # weight gradients issued on their side stream
             m2 = tr.mark() if tr else None
             self.comm.end_step()                   # bucketed push: join the push stream
             if tr:
