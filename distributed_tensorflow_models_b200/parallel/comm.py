@@ -317,6 +317,193 @@ class ThreadComm(Comm):
 
 
 # =================================================================================================
+class BucketedThreadComm(ThreadComm):
+    """CPU twin of the bucketed BSP push / gated pull of ``parallel/symm.py`` on the thread cluster: the same step
+    hooks (``begin_step`` / ``on_fetch`` / ``grad_ready`` / ``end_step``), the same bucket plan and per-bucket
+    ownership, the same two flag rows per bucket (``ready``, ``updated``) with epochs that count completed steps —
+    with Python threads and a condition variable in place of NVLink stores and acquire loads.  It moves real numbers,
+    so a protocol mistake (a gradient read before it is complete, a parameter read before its owner's update, a
+    gradient buffer zeroed under a reader) shows up as a result that differs from whole-buffer BSP.
+
+    ``jitter``: upper bound (seconds) of random sleeps in front of every protocol action, to vary the interleavings;
+    ``owner_delay``: the last rank updates its parts this much late (a slow parameter server).
+
+    Usage: ``cluster = ThreadCluster(n); cluster.run(lambda c: work(BucketedThreadComm(cluster, c.rank, ...)))``."""
+
+    def __init__(self, cluster: ThreadCluster, rank: int, bucket_floats: int = 1 << 16, head_floats: int = 0,
+                 jitter: float = 0.0, seed: int = 0, owner_delay: float = 0.0):
+        super().__init__(cluster, rank)
+        self.bucket_floats, self.head_floats = bucket_floats, head_floats
+        self.jitter = jitter
+        self.owner_delay = owner_delay      # the last rank is a slow owner: sleeps this long before updating its part
+        import random
+        self._rng = random.Random(seed * 7919 + rank)
+        self._gs = 0
+        self._in_step = False
+
+    def _nap(self):
+        if self.jitter:
+            time.sleep(self._rng.random() * self.jitter)
+
+    def setup(self, layout, opt_cfg):
+        from .layout import plan_buckets
+        c = self.c
+        self.layout = layout
+        self.buckets = plan_buckets(layout.entries, layout.total, self.world, self.bucket_floats,
+                                    head_floats=self.head_floats)
+        self._bucket_of_name = {n: b.index for b in self.buckets for n in b.names}
+        self._lo = [b.lo for b in self.buckets]
+        c.layouts[self.rank] = layout
+        # one optimiser per bucket part this rank owns
+        opts = []
+        for b in self.buckets:
+            lo, hi = b.part(self.rank)
+            if hi > lo:
+                opts.append(ShardOptimizer(opt_cfg, layout.params, lo, hi, layout.wd_boundary))
+        c.opts[self.rank] = opts
+        self._opt_of_bucket = {self.bucket_of(o.lo): o for o in opts}
+        with c.gs_lock:
+            if not hasattr(c, "flags"):
+                B, W = len(self.buckets), self.world
+                c.flags = {"ready": [[[0] * W for _ in range(B)] for _ in range(W)],       # [rank][bucket][from]
+                           "updated": [[[0] * W for _ in range(B)] for _ in range(W)]}
+                c.flag_cv = threading.Condition()
+        c.barrier.wait()
+        if self.rank != 0:
+            self.layout.params.copy_(c.layouts[0].params)
+        c.barrier.wait()
+        for o in opts:                      # (EMA shadows were cloned before the chief's values arrived)
+            if o.ema is not None:
+                o.ema.copy_(o.w)
+
+    def bucket_of(self, offset: int) -> int:
+        import bisect
+        return bisect.bisect_right(self._lo, offset) - 1
+
+    # -- flags ----------------------------------------------------------------------------------------
+    def _wait(self, row: str, b: int, epoch: int, timeout: float = 60.0):
+        c = self.c
+        t0 = time.time()
+        with c.flag_cv:
+            while not all(v >= epoch for v in c.flags[row][self.rank][b]):
+                if c.aborted or time.time() - t0 > timeout:
+                    raise StalenessTimeout(f"rank {self.rank}: {row}[{b}] never reached epoch {epoch}")
+                c.flag_cv.wait(0.02)
+
+    def _raise_flag(self, row: str, b: int, epoch: int):
+        c = self.c
+        with c.flag_cv:
+            for q in range(self.world):
+                c.flags[row][q][b][self.rank] = epoch
+            c.flag_cv.notify_all()
+
+    # -- step hooks -------------------------------------------------------------------------------------
+    def prepare_step(self, lr, grad_scale=1.0):
+        self._lr, self._scale = lr, grad_scale
+
+    def begin_step(self):
+        # like the side stream of the GPU transport: gate on every bucket of the previous step (then nobody reads my
+        # old gradients) and zero the gradients, while the forward pass is already running behind its own gates
+        self._aux_error = None
+
+        def aux():
+            try:
+                for b in range(len(self.buckets)):
+                    self._wait("updated", b, self._gs)
+                self._nap()
+                self.layout.zero_grads()
+            except BaseException as e:  # noqa: BLE001
+                self._aux_error = e
+        self._aux = threading.Thread(target=aux, daemon=True)
+        self._aux.start()
+        self._got = [0] * len(self.buckets)
+        self._need = [len(b.names) for b in self.buckets]
+        self._gated = set()
+        self._pushed = [False] * len(self.buckets)
+        self._in_step = True
+
+    def before_backward(self):
+        if self._in_step:
+            self._aux.join()
+            if self._aux_error is not None:
+                raise self._aux_error
+
+    def on_fetch(self, var):
+        if not (self._in_step and var.trainable):
+            return
+        b = self._bucket_of_name.get(var.name)
+        if b is None or b in self._gated:
+            return
+        self._gated.add(b)
+        self._nap()
+        self._wait("updated", b, self._gs)            # the pull: every owner's part of this bucket has landed
+
+    def grad_ready(self, param):
+        if not self._in_step or param.grad is None:
+            return
+        off = (param.grad.data_ptr() - self.layout.grads.data_ptr()) // 4
+        if off < 0 or off >= self.layout.total:
+            return
+        b = self.bucket_of(off)
+        self._got[b] += 1
+        if self._got[b] == self._need[b]:
+            self._push(b)
+
+    def _push(self, b: int):
+        c = self.c
+        e = self._gs + 1
+        bk = self.buckets[b]
+        self._nap()
+        self._raise_flag("ready", b, e)
+        self._wait("ready", b, e)
+        lo, hi = bk.part(self.rank)
+        if hi > lo:
+            self._nap()
+            if self.owner_delay and self.rank == self.world - 1:
+                time.sleep(self.owner_delay)
+            g = c.layouts[0].grads[lo:hi].clone()
+            for q in range(1, self.world):
+                g.add_(c.layouts[q].grads[lo:hi])
+            g.div_(self.world)
+            o = self._opt_of_bucket[self.bucket_of(lo)]
+            o.apply(g, self._lr, self._scale, num_updates=self._gs)
+            self._nap()
+            for q in range(self.world):                # store into every replica
+                if q != self.rank:
+                    c.layouts[q].params[lo:hi].copy_(self.layout.params[lo:hi])
+        self._raise_flag("updated", b, e)
+        self._pushed[b] = True
+
+    def end_step(self):
+        if not self._in_step:
+            return
+        self._in_step = False
+        for b in range(len(self.buckets) - 1, -1, -1):     # tensors that reported nothing: pushed at the end
+            if not self._pushed[b]:
+                self._push(b)
+
+    def sync_replica(self):
+        for b in range(len(self.buckets)):
+            self._wait("updated", b, self._gs)
+
+    def bsp_step(self, lr, grad_scale=1.0):
+        self._gs += 1
+        return self._gs
+
+    def global_step(self):
+        return self._gs
+
+    def set_global_step(self, v):
+        self._gs = int(v)
+
+    def gather_slot_flats(self):
+        self.c.barrier.wait()
+        out = ThreadComm.gather_slot_flats(self)
+        self.c.barrier.wait()
+        return out
+
+
+# =================================================================================================
 class TorchDistComm(Comm):
     """BSP (and emulated ASP / SSP) over torch.distributed collectives — the NCCL / gloo baseline arm.
 

@@ -151,3 +151,87 @@ def test_committed_sass_listings_match_the_sources():
     root = Path(__file__).resolve().parent.parent
     r = subprocess.run([sys.executable, str(root / "scripts" / "regen_sass.py"), "--check"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("model,world,jitter", [("cnn", 2, 0.0), ("cnn", 3, 2e-3), ("resnet", 2, 1e-3)])
+def test_bucketed_push_on_the_thread_cluster_equals_whole_buffer_bsp(model, world, jitter):
+    """The engine's step hooks (pull gates at variable look-up, per-bucket push from post-accumulate hooks, gated
+    zeroing) drive the CPU twin of the bucketed protocol with real numbers: parameters, slots and EMA shadows after
+    a few steps equal whole-buffer BSP on the same data, under random interleavings."""
+    import dataclasses
+
+    from distributed_tensorflow_models_b200 import config as cfg
+    from distributed_tensorflow_models_b200.models.registry import MODEL_SPECS
+    from distributed_tensorflow_models_b200.parallel.comm import BucketedThreadComm, ThreadCluster
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+    preset = None
+    if model == "cnn":
+        preset = dataclasses.replace(cfg.PRESETS[model], optimizer="rmsprop", initial_lr=0.01, ema_decay=0.9999)
+    sp = MODEL_SPECS[model]
+    bs = 4
+
+    def data(rank):
+        g = torch.Generator().manual_seed(50 + rank)
+        return torch.randn(bs, sp.image_size, sp.image_size, 3, generator=g), torch.randint(0, 10, (bs,), generator=g)
+
+    def run(make_comm):
+        def work(c):
+            comm = make_comm(c)
+            t = Trainer(TrainSetup(model=model, batch_size=bs, num_workers=world, preset=preset, seed=0,
+                                   resnet_size=8), comm)
+            x, y = data(comm.rank)
+            losses = [float(t.train_step(x, y)["loss"]) for _ in range(4)]
+            comm.sync_replica()
+            comm.barrier()
+            slots = {k: v.clone() for k, v in comm.gather_slot_flats().items()}
+            return losses, t.layout.params[: t.layout.used].clone(), slots, t.layout
+        return ThreadCluster(world).run(work)
+
+    ref = run(lambda c: c)
+    got = run(lambda c: BucketedThreadComm(c.c, c.rank, bucket_floats=1 << 14, head_floats=512, jitter=jitter,
+                                           seed=3))
+    layout = ref[0][3]
+    live = torch.zeros(layout.total, dtype=torch.bool)
+    for e in layout.entries:
+        live[e.offset:e.offset + e.numel] = True
+    for (l0, p0, s0, _), (l1, p1, s1, _) in zip(ref, got):
+        assert l0 == pytest.approx(l1, rel=1e-5)
+        assert torch.allclose(p0, p1, rtol=1e-5, atol=1e-7)
+        assert set(s0) == set(s1)
+        for k in s0:
+            assert torch.allclose(s0[k][live], s1[k][live], rtol=1e-5, atol=1e-7), k
+    assert all(torch.equal(got[0][1], g[1]) for g in got[1:])          # replicas identical across ranks
+
+
+def test_the_thread_twin_shows_what_the_pull_gate_is_for():
+    """Same run with a slow owner: with the gates at variable look-up the result is exactly whole-buffer BSP; without
+    them a fast worker's next forward pass reads the slow owner's part of a bucket before it has landed."""
+    from distributed_tensorflow_models_b200.parallel.comm import BucketedThreadComm, ThreadCluster
+    from distributed_tensorflow_models_b200.parallel.engine import Trainer, TrainSetup
+
+    def data(rank):
+        g = torch.Generator().manual_seed(50 + rank)
+        return torch.randn(4, 32, 32, 3, generator=g), torch.randint(0, 10, (4,), generator=g)
+
+    def run(make):
+        def work(c):
+            comm = make(c)
+            t = Trainer(TrainSetup(model="resnet", resnet_size=8, batch_size=4, num_workers=2, seed=0), comm)
+            x, y = data(comm.rank)
+            for _ in range(3):
+                t.train_step(x, y)
+            comm.sync_replica()
+            comm.barrier()
+            return t.layout.params[: t.layout.used].clone()
+        return ThreadCluster(2).run(work)
+
+    class NoGate(BucketedThreadComm):
+        def on_fetch(self, var):
+            pass
+
+    ref = run(lambda c: c)
+    kw = dict(bucket_floats=1 << 12, head_floats=512, owner_delay=0.05)
+    good = run(lambda c: BucketedThreadComm(c.c, c.rank, **kw))
+    bad = run(lambda c: NoGate(c.c, c.rank, **kw))
+    assert max(float((a - b).abs().max()) for a, b in zip(ref, good)) < 1e-6
+    assert max(float((a - b).abs().max()) for a, b in zip(ref, bad)) > 1e-4
