@@ -235,3 +235,20 @@ def test_the_thread_twin_shows_what_the_pull_gate_is_for():
     bad = run(lambda c: NoGate(c.c, c.rank, **kw))
     assert max(float((a - b).abs().max()) for a, b in zip(ref, good)) < 1e-6
     assert max(float((a - b).abs().max()) for a, b in zip(ref, bad)) > 1e-4
+
+
+def test_symm_transport_refuses_reference_placements_with_a_readable_message():
+    """`--placement round_robin|axis0` belongs to the transports that keep whole tensors on parameter servers; the
+    NVLink transport says so instead of tripping an assert."""
+    from distributed_tensorflow_models_b200.parallel.layout import FlatLayout
+    from distributed_tensorflow_models_b200.slim import VariableStore
+    from distributed_tensorflow_models_b200.slim import variables as V
+    st = VariableStore()
+    with st.as_default():
+        st.variable("a/weights", (6, 3, 3, 4), V.truncated_normal_initializer(0.1))
+        st.variable("b/weights", (5, 6), V.truncated_normal_initializer(0.1))
+    layout = FlatLayout(st, world_size=2, placement="round_robin")
+    comm = object.__new__(SymmComm)
+    comm.world, comm.rank = 2, 0
+    with pytest.raises(ValueError, match="--placement round_robin"):
+        comm.setup(layout, None)
