@@ -252,3 +252,49 @@ def test_symm_transport_refuses_reference_placements_with_a_readable_message():
     comm.world, comm.rank = 2, 0
     with pytest.raises(ValueError, match="--placement round_robin"):
         comm.setup(layout, None)
+
+
+def test_concat_view_function_hands_each_branch_its_gradient_slice():
+    """K11 host side: branches that wrote channel slices of one buffer are 'concatenated' for free, and the backward
+    pass gives every branch the matching slice of the incoming gradient as a view (no copy)."""
+    from distributed_tensorflow_models_b200.ops import native_ops
+    buf = torch.zeros(2, 3, 3, 10)
+    a = torch.randn(2, 3, 3, 4, requires_grad=True)
+    b = torch.randn(2, 3, 3, 6, requires_grad=True)
+
+    class WriteInto(torch.autograd.Function):          # stands in for a kernel that takes the pending output slot
+        @staticmethod
+        def forward(ctx, x):
+            slot = native_ops.take_output_slot(x.shape)
+            slot.data.copy_(x)            # like a native kernel: writes through the pointer, no version bump
+            return slot
+
+        @staticmethod
+        def backward(ctx, g):
+            assert g.stride(-1) == 1 and g.stride(2) == 10      # a strided view of the block's gradient
+            return g.clone()
+    native_ops.set_output_slot(buf[..., :4])
+    oa = WriteInto.apply(a)
+    native_ops.set_output_slot(buf[..., 4:])
+    ob = WriteInto.apply(b)
+    y = native_ops.concat_views(buf, [oa, ob])
+    assert y.shape == buf.shape and torch.equal(y[..., :4], a.detach()) and torch.equal(y[..., 4:], b.detach())
+    w = torch.randn_like(buf)
+    (y * w).sum().backward()
+    assert torch.equal(a.grad, w[..., :4]) and torch.equal(b.grad, w[..., 4:])
+    # output-slot hand-over: taken only by an op whose output has exactly the slot's shape, and only once
+    native_ops.set_output_slot(buf[..., :4])
+    assert native_ops.take_output_slot((2, 3, 3, 6)) is None and native_ops.output_slot_pending()
+    assert native_ops.take_output_slot((2, 3, 3, 4)) is not None and not native_ops.output_slot_pending()
+
+
+def test_tf32_operand_split_is_exact():
+    """--precision tf32x3: a = hi + lo exactly, hi has no bits below TF32's 10-bit mantissa, lo is at most 2^-11 |a|."""
+    from distributed_tensorflow_models_b200.ops import conv_native as cn
+    x = torch.randn(4096) * torch.logspace(-6, 6, 4096)
+    hi, lo = cn._split_tf32(x)
+    assert torch.equal(hi + lo, x)
+    assert int((hi.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    assert bool((lo.abs() <= x.abs() * 2.0 ** -10).all())
+    with pytest.raises(ValueError):
+        cn.set_precision("fp16")
