@@ -126,12 +126,15 @@ class _ConvFn(torch.autograd.Function):
         if has_bias and ctx.needs_input_grad[2]:
             co = dy.shape[-1]
             slot = _grad_slot(bparam)
-            db = slot if slot is not None else _zeros(co, dy.device)
-            nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db), nat.stream_ptr()),
-                      "dtf_colsum")
             if slot is not None:
-                db = None
-                wrote.append(bparam)
+                with _wgrad_stream(dy):        # a leaf of the backward pass like the weight gradient: off the chain
+                    nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(slot),
+                                                   nat.stream_ptr()), "dtf_colsum")
+                    _grad_written(bparam)
+            else:
+                db = _zeros(co, dy.device)
+                nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db),
+                                               nat.stream_ptr()), "dtf_colsum")
         if ctx.needs_input_grad[1]:
             slot = _grad_slot(wparam)
             if slot is not None:
@@ -179,12 +182,15 @@ class _OneTapFn(torch.autograd.Function):
         if has_bias and ctx.needs_input_grad[2]:
             co = dy.shape[-1]
             slot = _grad_slot(bparam)
-            db = slot if slot is not None else _zeros(co, dy.device)
-            nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db), nat.stream_ptr()),
-                      "dtf_colsum")
             if slot is not None:
-                db = None
-                wrote.append(bparam)
+                with _wgrad_stream(dy):        # a leaf of the backward pass like the weight gradient: off the chain
+                    nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(slot),
+                                                   nat.stream_ptr()), "dtf_colsum")
+                    _grad_written(bparam)
+            else:
+                db = _zeros(co, dy.device)
+                nat.check(nat.lib().dtf_colsum(_p(dy), C.c_longlong(dy.numel() // co), co, co, _p(db),
+                                               nat.stream_ptr()), "dtf_colsum")
         if ctx.needs_input_grad[0]:
             dx = cn.conv_dgrad(dy, cn.weight_transpose(wc), (1, 1), (1, 1), (0, 0))
         if ctx.needs_input_grad[1]:
