@@ -251,14 +251,21 @@ class Trainer:
             tr = None
         try:
             m0 = tr.mark() if tr else None
+            if tr:
+                torch.cuda.nvtx.range_push("forward")      # NVTX ranges for external profilers, same phases
             self.comm.begin_step()                 # zero the gradients (bucketed push: behind the previous step's flags)
             loss, logits = self._run_forward(x, y, True)
             total = loss
             if not self.setup.fused_l2:
                 total = loss + self.l2_term()
             m1 = tr.mark() if tr else None
+            if tr:
+                torch.cuda.nvtx.range_pop()
+                torch.cuda.nvtx.range_push("backward")
             self.comm.before_backward()
             total.backward()
+            if tr:
+                torch.cuda.nvtx.range_pop()
             if native:
                 native_ops.join_wgrad_stream(self.device)       # weight gradients issued on their side stream
             m2 = tr.mark() if tr else None
