@@ -610,3 +610,68 @@ def test_cifar10_download_helper_fetches_and_unpacks(tmp_path, monkeypatch):
     assert cifar10.maybe_download_and_extract(str(dst), url="file:///nonexistent")        # present: nothing to do
     assert not cifar10.maybe_download_and_extract(str(tmp_path / "other"), url="file:///nonexistent/x.tar.gz")
     assert not os.path.exists(tmp_path / "other" / "x.tar.gz.part")
+
+
+def test_download_and_preprocess_shell_drivers(tmp_path):
+    """inception/data/download_and_preprocess_flowers.sh and download_imagenet.sh: fetch (here: file:// URLs and
+    archives already in place), unpack into the tree the builders expect, shard to TFRecords."""
+    import glob
+    import tarfile
+
+    from PIL import Image
+    data = os.path.join(ROOT, "distributed_tensorflow_models_b200", "data")
+    # ---- flowers: tarball behind a URL -> train / validation shards ----
+    src = tmp_path / "src" / "flower_photos"
+    for lab in ("daisy", "roses"):
+        (src / lab).mkdir(parents=True)
+        for i in range(4):
+            Image.fromarray(np.random.randint(0, 255, (20, 24, 3), np.uint8)).save(src / lab / f"{i}.jpg")
+    (src / "LICENSE.txt").write_text("not a label")
+    tgz = tmp_path / "flower_photos.tgz"
+    with tarfile.open(tgz, "w:gz") as tf:
+        tf.add(str(src), arcname="flower_photos")
+    out = tmp_path / "flowers"
+    env = dict(os.environ, FLOWERS_URL="file://" + str(tgz), PYTHONPATH=ROOT)
+    r = subprocess.run(["bash", os.path.join(data, "download_and_preprocess_flowers.sh"), str(out), "1"],
+                       capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert (out / "flower_photos.tgz").exists() and open(out / "raw-data" / "labels.txt").read().split() == ["daisy", "roses"]
+    assert glob.glob(str(out / "train-*")) and glob.glob(str(out / "validation-*"))
+    assert len(os.listdir(out / "raw-data" / "validation" / "daisy")) == 1
+    # ---- ImageNet: the three official archives already in <out_dir> (no credentials needed, none stored) ----
+    raw = tmp_path / "inet"
+    raw.mkdir()
+    work = tmp_path / "work"
+    for syn in ("n01440764", "n01443537"):
+        (work / syn).mkdir(parents=True)
+        for i in range(2):
+            Image.fromarray(np.random.randint(0, 255, (16, 16, 3), np.uint8)).save(work / syn / f"{syn}_{i}.JPEG")
+        with tarfile.open(work / f"{syn}.tar", "w") as tf:
+            for f in sorted(os.listdir(work / syn)):
+                tf.add(str(work / syn / f), arcname=f)
+    with tarfile.open(raw / "ILSVRC2012_img_train.tar", "w") as tf:
+        for syn in ("n01440764", "n01443537"):
+            tf.add(str(work / f"{syn}.tar"), arcname=f"{syn}.tar")
+    (work / "val").mkdir()
+    Image.fromarray(np.zeros((8, 8, 3), np.uint8)).save(work / "val" / "ILSVRC2012_val_00000001.JPEG")
+    with tarfile.open(raw / "ILSVRC2012_img_val.tar", "w") as tf:
+        tf.add(str(work / "val" / "ILSVRC2012_val_00000001.JPEG"), arcname="ILSVRC2012_val_00000001.JPEG")
+    (work / "bb" / "n01440764").mkdir(parents=True)
+    (work / "bb" / "n01440764" / "n01440764_0.xml").write_text("<annotation/>")
+    with tarfile.open(raw / "ILSVRC2012_bbox_train_v2.tar.gz", "w:gz") as tf:
+        tf.add(str(work / "bb" / "n01440764"), arcname="n01440764")
+    env2 = {k: v for k, v in os.environ.items() if not k.startswith("IMAGENET_")}
+    r = subprocess.run(["bash", os.path.join(data, "download_imagenet.sh"), str(raw)], capture_output=True, text=True,
+                       env=env2, timeout=300)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert sorted(os.listdir(raw / "train")) == ["n01440764", "n01443537"]
+    assert len(os.listdir(raw / "train" / "n01443537")) == 2 and len(os.listdir(raw / "validation")) == 1
+    assert (raw / "bounding_boxes" / "n01440764" / "n01440764_0.xml").exists()
+    # a missing archive without credentials: a clear message, exit code 2, nothing fetched
+    os.remove(raw / "ILSVRC2012_img_val.tar")
+    r = subprocess.run(["bash", os.path.join(data, "download_imagenet.sh"), str(raw)], capture_output=True, text=True,
+                       env=env2, timeout=60)
+    assert r.returncode == 2 and "IMAGENET_USERNAME" in r.stdout
+    # no credentials anywhere in the shipped drivers (SURVEY Q19)
+    for f in glob.glob(os.path.join(data, "*.sh")):
+        assert "ACCESS_KEY=" not in open(f).read().replace('"$IMAGENET_ACCESS_KEY"', "")
