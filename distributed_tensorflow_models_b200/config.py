@@ -118,6 +118,9 @@ def build_parser(model: Optional[str] = None, mode: Optional[str] = None) -> arg
                          "ignoring missing ones, and start at global step 0 (vgg/nets/mobilenet_v1_train.py:165-181)")
     ap.add_argument("--trace", default="", help="write a Chrome-trace JSON of step phases to this path (device-timed "
                                                  "with CUDA events on a GPU)")
+    ap.add_argument("--summarize_activations", type=_tf_bool, nargs="?", const=True, default=False,
+                    help="chief: with every summary also write the reference's activation histograms / sparsity "
+                         "(one extra forward pass), variable and gradient histograms (cnn/cifar10.py:104-121,376-382)")
     ap.add_argument("--ps_timeout_secs", type=float, default=None,
                     help="--backend symm: give up a parameter-server flag wait (a peer died) after this many seconds "
                          "and abort the run (default 300, or $DTF_PS_TIMEOUT_S)")

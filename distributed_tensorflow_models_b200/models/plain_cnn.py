@@ -44,18 +44,22 @@ def inference(images: torch.Tensor, batch_size=None) -> torch.Tensor:
     spec = {s[0]: s for s in _LAYERS}
     w, b = _layer_vars(store, *spec["conv1"][:2], images.shape[-1], *spec["conv1"][2:])
     x = Fn.conv2d(images, w, b, 1, "SAME", relu=True)
+    end_points = {"conv1": x}          # what the reference hands to _activation_summary (cnn/cifar10.py:226-280)
     x = Fn.max_pool(x, 3, 2, "SAME")
     x = Fn.lrn(x, 4, 1.0, 0.001 / 9.0, 0.75)
     w, b = _layer_vars(store, *spec["conv2"][:2], 64, *spec["conv2"][2:])
     x = Fn.conv2d(x, w, b, 1, "SAME", relu=True)
+    end_points["conv2"] = x
     x = Fn.lrn(x, 4, 1.0, 0.001 / 9.0, 0.75)
     x = Fn.max_pool(x, 3, 2, "SAME")
     x = Fn.flatten(x)
     for name in ("local3", "local4"):
         w, b = _layer_vars(store, *spec[name][:2], x.shape[-1], *spec[name][2:])
-        x = Fn.linear(x, w, b, relu=True)
+        x = end_points[name] = Fn.linear(x, w, b, relu=True)
     w, b = _layer_vars(store, *spec["softmax_linear"][:2], x.shape[-1], *spec["softmax_linear"][2:])
-    return Fn.linear(x, w, b)
+    logits = end_points["softmax_linear"] = Fn.linear(x, w, b)
+    store.end_points = end_points
+    return logits
 
 
 def loss(logits: torch.Tensor, labels: torch.Tensor, batch_size=None) -> torch.Tensor:

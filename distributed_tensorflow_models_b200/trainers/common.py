@@ -242,6 +242,9 @@ def run_worker(args) -> int:
     events = EventFileWriter(args.train_dir) if (is_chief and p.save_secs is not None and args.save_summaries_secs) \
         else None
     last_summary, last_summary_step = time.time(), 0
+    from ..utils.summaries import LossAverages, activation_summaries, variable_summaries
+    loss_averages = LossAverages(0.9)              # the chief's moving average of the loss (…_bsp.py:116-120)
+    last_batch = None
     trace = ChromeTrace(args.trace, pid=rank, device=device)
     trainer.trace = trace if trace.on_device else None     # eager steps also get forward / backward / push rows
     last_save = time.time()
@@ -251,6 +254,8 @@ def run_worker(args) -> int:
         images, labels = next(batches)
         t1 = time.time()
         ev0 = trace.mark()
+        if events is not None and args.summarize_activations:
+            last_batch = (images, labels)
         out = trainer.train_step(images, labels, batch_size=args.batch_size)      # already on the device (prefetcher)
         trace.add_device("train_step", ev0, trace.mark(), t_run0, step=step)
         want_log = (step % max(1, args.log_every) == 0) or step == args.max_steps - 1
@@ -265,10 +270,22 @@ def run_worker(args) -> int:
             loss_value, (lstep, lgs, llr, lwait, lt0, llog) = losses_rb.pop()
             if p.nan_guard:
                 assert not math.isnan(loss_value), "Model diverged with loss = NaN"
+            averaged = loss_averages.update(total_loss=loss_value) if is_chief else {}
             if events is not None and time.time() - last_summary >= args.save_summaries_secs:
                 now = time.time()
-                events.add_scalars(int(lgs), {"global_step/sec": (lstep - last_summary_step) / max(now - last_summary, 1e-9),
-                                              "total_loss": loss_value, "learning_rate": llr})
+                scalars = {"global_step/sec": (lstep - last_summary_step) / max(now - last_summary, 1e-9),
+                           "learning_rate": llr}
+                scalars.update(averaged)           # 'total_loss (raw)' and its moving average 'total_loss'
+                histos = None
+                if args.summarize_activations and last_batch is not None:
+                    # one extra forward pass outside the captured step: its intermediate tensors are readable
+                    snap = trainer._snapshot_side_state()          # (moving statistics, dropout seed: put back after)
+                    trainer.evaluate_batch(last_batch[0], last_batch[1], training_bn=True)
+                    trainer._undo_warmup_side_effects(snap)
+                    act_scalars, histos = activation_summaries(trainer.store.end_points)
+                    scalars.update(act_scalars)
+                    histos.update(variable_summaries(trainer.store))
+                events.add_summaries(int(lgs), scalars, histos)
                 events.flush()
                 last_summary, last_summary_step = now, lstep
             if llog:

@@ -675,3 +675,41 @@ def test_download_and_preprocess_shell_drivers(tmp_path):
     # no credentials anywhere in the shipped drivers
     for f in glob.glob(os.path.join(data, "*.sh")):
         assert "ACCESS_KEY=" not in open(f).read().replace('"$IMAGENET_ACCESS_KEY"', "")
+
+
+def test_activation_loss_and_variable_summaries(tmp_path):
+    """The summaries the reference's model files define (cnn/cifar10.py:104-121,309-335,376-382): per end point a
+    histogram `<name>/activations` and a scalar `<name>/sparsity`, `<loss> (raw)` next to its moving average,
+    histograms of every trainable variable and of its gradient — written by the chief on request."""
+    import glob
+    import struct
+
+    from distributed_tensorflow_models_b200.trainers import cifar10_cnn_bsp
+    from distributed_tensorflow_models_b200.utils import tfevents
+    from distributed_tensorflow_models_b200.utils.summaries import LossAverages, activation_summaries
+    # histogram encoding: TensorFlow's buckets, counts add up, moments exact
+    x = torch.cat([torch.zeros(6), torch.tensor([1.0, -2.0, 3.5])])
+    h = tfevents._decode_histogram(tfevents.encode_histogram(x))
+    assert (h["min"], h["max"], h["num"], h["sum"], h["sum_squares"]) == (-2.0, 3.5, 9.0, 2.5, 17.25)
+    assert sum(h["bucket"]) == 9 and len(h["bucket"]) == len(h["bucket_limit"])
+    lim = tfevents.default_bucket_limits()
+    assert lim[len(lim) // 2 - 1] == 0.0 or 0.0 in lim
+    assert all(b > a for a, b in zip(lim, lim[1:]))
+    zero_bucket = [c for l, c in zip(h["bucket_limit"], h["bucket"]) if l == 0.0]
+    assert zero_bucket == [6.0]
+    sc, hs = activation_summaries({"tower_0/conv1": torch.tensor([0.0, 0.0, 1.0, 2.0])})
+    assert sc == {"conv1/sparsity": 0.5} and list(hs) == ["conv1/activations"]
+    la = LossAverages(0.9)
+    assert la.update(total_loss=2.0) == {"total_loss (raw)": 2.0, "total_loss": 2.0}
+    assert la.update(total_loss=1.0)["total_loss"] == pytest.approx(1.9)
+    # through the trainer
+    d = str(tmp_path / "train")
+    assert cifar10_cnn_bsp.main(["--synthetic", "--batch_size=4", "--train_dir=" + d, "--max_steps=3",
+                                 "--backend=local", "--save_summaries_secs=0.000001", "--summarize_activations"]) == 0
+    evs = tfevents.read_events(glob.glob(os.path.join(d, "events.out.tfevents.*"))[0])
+    last = evs[-1]
+    assert {"total_loss (raw)", "total_loss", "learning_rate", "conv1/sparsity", "local4/sparsity",
+            "softmax_linear/sparsity"} <= set(last["scalars"])
+    assert {"conv1/activations", "conv2/activations", "local3/activations", "conv1/weights", "conv1/weights/gradients",
+            "softmax_linear/biases"} <= set(last["histograms"])
+    assert last["histograms"]["conv1/weights"]["num"] == 64 * 5 * 5 * 3
