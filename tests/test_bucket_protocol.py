@@ -134,7 +134,7 @@ def test_flag_protocol_is_clean_under_random_interleavings(world, buckets):
 ])
 def test_the_checker_catches_each_race_when_its_rule_is_dropped(rule, needle):
     found = []
-    for seed in range(8):
+    for seed in range(24):
         found += BucketProtocolModel(4, 3, steps=8, seed=seed, jitter=5e-4, break_rule=rule).run(timeout=20)
         if found:
             break
