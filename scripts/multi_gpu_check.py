@@ -77,11 +77,12 @@ def main():
             r["slot_rel_diff_" + k] = rel(sa[k][:used], sb[k][:used])
         # the plain CNN is reproducible to rounding, so the transports must agree almost exactly; ResNet's tf32 +
         # float-atomic noise is amplified by 31 BN/ReLU layers (two runs of the SAME transport differ as much)
-        tol = 1e-5 if strict else 0.1
+        # (1e-4: the switch and NCCL's ring add the N gradients in different orders; observed 1e-12 .. 1e-6 at N = 2)
+        tol = 1e-4 if strict else 0.1
         good = r["replicas_identical"] and r["param_rel_diff"] < tol and abs(la[0] - lb[0]) / abs(lb[0]) < 1e-3 \
-            and abs(la[-1] - lb[-1]) / abs(lb[-1]) < (1e-4 if strict else 0.15)
+            and abs(la[-1] - lb[-1]) / abs(lb[-1]) < (1e-3 if strict else 0.15)
         if strict:
-            good = good and all(v < 1e-5 for k, v in r.items() if k.startswith("slot_rel_diff_"))
+            good = good and all(v < 1e-4 for k, v in r.items() if k.startswith("slot_rel_diff_"))
         r["ok"] = bool(good)
         res["bsp_" + name] = r
         ok &= good

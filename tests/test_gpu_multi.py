@@ -25,7 +25,7 @@ def test_symm_transport_matches_nccl_baseline_and_async_modes():
     res = json.loads(lines[-1])
     assert res["ok"], res
     for case in ("bsp_cnn_sgd_ema_graph", "bsp_cnn_rmsprop_eager", "bsp_cnn_rmsprop_no_overlap"):
-        assert res[case]["param_rel_diff"] < 1e-5 and res[case]["replicas_identical"], res[case]
+        assert res[case]["param_rel_diff"] < 1e-4 and res[case]["replicas_identical"], res[case]
         assert res[case]["buckets"] >= 1
     assert res["bsp_cnn_sgd_ema_graph"]["buckets"] > 1          # the overlapped path really ran bucket by bucket
     assert res["asp"]["global_step_on_rank0"] == res["asp"]["expected"]
